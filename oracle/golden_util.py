@@ -1,0 +1,63 @@
+"""Shared helpers for golden fixtures (TEST INFRASTRUCTURE): seeded inputs, subsampling, error metrics."""
+from __future__ import annotations
+
+from typing import Dict
+
+import numpy as np
+import torch
+
+GOLDEN_CASES = {
+    # name: (config name or builder args, batch, out_gain, seed)
+    "tiny_base": dict(cfg="tiny_base", batch=2, out_gain=8.0),
+    "tiny_refine": dict(cfg="tiny_refine", batch=2, out_gain=8.0),
+    "tiny_alt_qknorm": dict(cfg="tiny_alt_qknorm", batch=2, out_gain=8.0),
+    "ufm_base_assumed": dict(cfg="ufm_base_assumed", batch=1, out_gain=8.0),
+    "ufm_refine_assumed": dict(cfg="ufm_refine_assumed", batch=1, out_gain=8.0),
+}
+
+
+def case_config(name: str):
+    from ufm_b200.configs import get_config, tiny
+
+    c = GOLDEN_CASES[name]["cfg"]
+    if c == "tiny_alt_qknorm":
+        return tiny(True, info_sharing_str="alternating_attention", qk_norm=True)
+    return get_config(c)
+
+
+def make_inputs(batch: int, H: int, W: int, seed: int = 1):
+    """Synthetic uint8 pair batch, BHWC: iid uniform bytes."""
+    g = torch.Generator(device="cpu").manual_seed(seed)
+    src = torch.randint(0, 256, (batch, H, W, 3), dtype=torch.uint8, generator=g)
+    tgt = torch.randint(0, 256, (batch, H, W, 3), dtype=torch.uint8, generator=g)
+    return src, tgt
+
+
+def subsample(t: torch.Tensor, max_elems: int = 40000) -> torch.Tensor:
+    """Deterministic strided subsample of the two trailing spatial dims so a fixture stays small."""
+    t = t.detach().float()
+    s = 1
+    while t[..., ::s, ::s].numel() > max_elems and t.dim() >= 2:
+        s += 1
+    return t[..., ::s, ::s].contiguous()
+
+
+def stats(t: torch.Tensor) -> np.ndarray:
+    t = t.detach().double()
+    return np.array([t.mean().item(), t.abs().mean().item(), t.norm().item(), t.abs().max().item()])
+
+
+def rel_l2(a: torch.Tensor, b: torch.Tensor) -> float:
+    return ((a.double() - b.double()).norm() / b.double().norm().clamp_min(1e-30)).item()
+
+
+def max_abs(a: torch.Tensor, b: torch.Tensor) -> float:
+    return (a.double() - b.double()).abs().max().item()
+
+
+def pack_stages(stages: Dict[str, torch.Tensor]) -> Dict[str, np.ndarray]:
+    out = {}
+    for k, v in stages.items():
+        out["sub:" + k] = subsample(v).numpy()
+        out["stat:" + k] = stats(v)
+    return out

@@ -1,0 +1,54 @@
+"""The CPU oracle reproduces the reference's own outputs (fixtures made by oracle/make_golden.py from the
+unmodified reference).  fp32 vs fp32 on CPU: the bar is rounding-level agreement, rel-L2 < 1e-5 (the
+reference's own parity convention for fp32 is abs<1e-2 & rel<1e-3, UC/examples/models/dust3r/dust3r.py:223-230)."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import ufm_oracle as O
+from oracle.golden_util import GOLDEN_CASES, case_config, make_inputs, rel_l2, stats, subsample
+from ufm_b200.weights import make_state_dict
+
+GOLDEN = os.path.join(os.path.dirname(__file__), "golden")
+
+
+def _run_oracle(name):
+    case = GOLDEN_CASES[name]
+    cfg = case_config(name)
+    sd = make_state_dict(cfg, seed=0, out_gain=case["out_gain"])
+    W, H = cfg["inference_resolution"]
+    src, tgt = make_inputs(case["batch"], H, W)
+    with torch.no_grad():
+        s0, s1 = O.canonicalize_inputs(src, tgt, "dinov2", None)
+        st = O.forward_stages(s0, s1, sd, cfg)
+        api = O.predict_correspondences_batched(src, tgt, sd, cfg) if name.startswith("tiny") else None
+    if "log_softmax" in st:
+        st["log_softmax"] = st["log_softmax"].permute(0, 3, 4, 1, 2)
+    return st, api
+
+
+@pytest.mark.parametrize("name", list(GOLDEN_CASES))
+def test_oracle_matches_reference_golden(name):
+    torch.set_num_threads(len(os.sched_getaffinity(0)))
+    g = np.load(os.path.join(GOLDEN, name + ".npz"))
+    st, api = _run_oracle(name)
+    checked = 0
+    for key in g.files:
+        if not key.startswith("sub:"):
+            continue
+        stage = key[4:]
+        if stage == "api_flow":
+            mine = api["flow"] if api is not None else st["flow"]  # native size: un-map is the identity map
+        elif stage == "api_covis":
+            mine = api["covisibility"] if api is not None else st["covis"].squeeze(1)
+        else:
+            mine = st[stage]
+        ref_sub = torch.from_numpy(g[key])
+        r = rel_l2(subsample(mine), ref_sub)
+        tol = 1e-5 if name.startswith("tiny") or not stage.startswith("api_") else 1e-4
+        assert r < tol, f"{name}:{stage} rel-L2 {r:.3e}"
+        np.testing.assert_allclose(stats(mine), g["stat:" + stage], rtol=2e-4, atol=1e-6, err_msg=f"{name}:{stage}")
+        checked += 1
+    assert checked >= 10

@@ -1,0 +1,118 @@
+"""Model configurations for the UFM dense-correspondence forward pass.
+
+The production ``config.json`` of UFM-Base / UFM-Refine lives on the HuggingFace hub
+(reference ``uniflowmatch/models/ufm.py:1254-1256``) and is not reachable offline, so the
+"assumed" configs below pin the architecture that SURVEY.md Appendix A derives from the
+constraints in the reference code.  Every dict here is a valid ``**kwargs`` for the
+reference constructors ``UniFlowMatchConfidence`` (``ufm.py:483-509``) and
+``UniFlowMatchClassificationRefinement`` (``ufm.py:720-754``) and for the engine classes of
+the same name in :mod:`ufm_b200.models`.
+"""
+from __future__ import annotations
+
+import copy
+from typing import Any, Dict
+
+# DINOv2 hub architectures (third-party ``facebookresearch/dinov2`` ``hub/backbones.py``; see
+# SURVEY.md Appendix B).  (embed_dim, depth, heads)
+DINOV2_ARCH = {
+    "small": (384, 12, 6),
+    "base": (768, 12, 12),
+    "large": (1024, 24, 16),
+}
+
+
+def _dpt(input_dims, out_dim, layer_dims=(96, 192, 384, 768), feature_dim=256):
+    return {
+        "dpt_feature": {
+            "patch_size": 14,
+            "hooks": [0, 1, 2, 3],
+            "input_feature_dims": list(input_dims),
+            "layer_dims": list(layer_dims),
+            "feature_dim": feature_dim,
+            "use_bn": False,
+        },
+        "dpt_processor": {"input_feature_dim": feature_dim, "output_dim": out_dim},
+    }
+
+
+def ufm_base_assumed(inference_resolution=(560, 420)) -> Dict[str, Any]:
+    """SURVEY.md Appendix A "UFM-Base-arch": DINOv2 ViT-L/14 + 12x768 global attention + 2 DPT heads."""
+    W, H = inference_resolution
+    return {
+        "encoder_str": "dinov2",
+        "encoder_kwargs": {
+            "name": "dinov2_large", "size": "large", "data_norm_type": "dinov2", "patch_size": 14,
+            "with_registers": False, "indices": [11, 23], "norm_intermediate": True,
+            "keep_first_n_layers": None,
+        },
+        "info_sharing_str": "global_attention",
+        "info_sharing_kwargs": {
+            "name": "gat", "input_embed_dim": 1024, "max_num_views": 2,
+            "use_rand_idx_pe_for_non_reference_views": False, "depth": 12, "dim": 768, "num_heads": 12,
+            "mlp_ratio": 4.0, "qkv_bias": True, "qk_norm": False, "init_values": None,
+            "custom_positional_encoding": None, "indices": [5, 8], "norm_intermediate": True,
+        },
+        "head_type": "dpt",
+        "feature_head_kwargs": _dpt([1024, 768, 768, 768], 2),
+        "adaptors_kwargs": {
+            "flow": {"class": "FlowAdaptor", "kwargs": {
+                "name": "flow", "flow_mean": [0.0, 0.0], "flow_std": [1.0, 1.0],
+                "base_shape": [H, W], "scale_strategy": "none"}},
+        },
+        "uncertainty_head_type": "dpt",
+        "uncertainty_head_kwargs": _dpt([1024, 768, 768, 768], 1),
+        "uncertainty_adaptors_kwargs": {
+            "non_occluded_mask": {"class": "MaskAdaptor", "kwargs": {"name": "non_occluded_mask"}},
+        },
+        "inference_resolution": [W, H],
+    }
+
+
+def ufm_refine_assumed(inference_resolution=(560, 420)) -> Dict[str, Any]:
+    """SURVEY.md Appendix A Refine additions (``ufm.py:736-746`` defaults)."""
+    cfg = ufm_base_assumed(inference_resolution)
+    cfg.update({
+        "classification_head_type": "patch_mlp",
+        "classification_head_kwargs": {"input_feature_dim": 1792, "patch_size": 14, "output_dim": 16,
+                                       "mlp_ratio": 4},
+        "temperature": 4,
+        "refinement_range": 5,
+        "use_unet_feature": False,
+    })
+    return cfg
+
+
+def tiny(refine: bool = False, inference_resolution=(224, 168), info_sharing_str="global_attention",
+         qk_norm: bool = False) -> Dict[str, Any]:
+    """A small architecture with the same topology, for fast CPU goldens and GPU parity at every
+    stage boundary: ViT-S/14 truncated to 4 layers, 4x128 info sharing, slim DPT heads."""
+    W, H = inference_resolution
+    cfg = ufm_refine_assumed(inference_resolution) if refine else ufm_base_assumed(inference_resolution)
+    cfg = copy.deepcopy(cfg)
+    cfg["encoder_kwargs"].update({"name": "dinov2_small", "size": "small", "indices": [1, 3],
+                                  "keep_first_n_layers": 4})
+    cfg["info_sharing_str"] = info_sharing_str
+    cfg["info_sharing_kwargs"].update({"input_embed_dim": 384, "depth": 4, "dim": 128, "num_heads": 2,
+                                       "indices": [1, 2], "qk_norm": qk_norm})
+    if info_sharing_str == "alternating_attention":
+        cfg["info_sharing_kwargs"].pop("max_num_views")
+        cfg["info_sharing_kwargs"].update({"use_pe_for_non_reference_views": False, "max_num_views_for_pe": 1000})
+    cfg["feature_head_kwargs"] = _dpt([384, 128, 128, 128], 2, layer_dims=(64, 64, 128, 128), feature_dim=64)
+    cfg["uncertainty_head_kwargs"] = _dpt([384, 128, 128, 128], 1, layer_dims=(64, 64, 128, 128), feature_dim=64)
+    if refine:
+        cfg["classification_head_kwargs"].update({"input_feature_dim": 384 + 128})
+    return cfg
+
+
+CONFIGS = {
+    "ufm_base_assumed": ufm_base_assumed,
+    "ufm_refine_assumed": ufm_refine_assumed,
+    "ufm_base_hires": lambda: ufm_base_assumed((1120, 840)),
+    "tiny_base": lambda: tiny(False),
+    "tiny_refine": lambda: tiny(True),
+}
+
+
+def get_config(name: str) -> Dict[str, Any]:
+    return CONFIGS[name]()
