@@ -1,0 +1,116 @@
+/*
+ * libufm_b200 — C ABI of the B200-native UFM dense-correspondence engine.
+ *
+ * The reference (labrat97/UFM) is pure PyTorch and has no FFI of its own; its boundary for this path is the Python
+ * method  UniFlowMatchModelsBase.predict_correspondences_batched()  (uniflowmatch/models/base.py:137-234) which runs
+ * UniFlowMatchConfidence.forward (uniflowmatch/models/ufm.py:562-662) or
+ * UniFlowMatchClassificationRefinement.forward (ufm.py:843-1009).  The entry points below are what a ctypes binding of
+ * that method binds: plain pointers and sizes, int status returns (0 = ok), no exceptions across
+ * the ABI, caller owns I/O buffers, the engine owns weights and workspace, one engine per GPU, calls on one engine are
+ * stream-ordered and must not overlap.
+ */
+#ifndef UFM_B200_H
+#define UFM_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct ufm_engine ufm_engine;
+
+enum { UFM_F32 = 0, UFM_BF16 = 1, UFM_U8 = 2 };
+enum { UFM_NCHW = 0, UFM_NHWC = 1 };
+
+/* Architecture of one model instance (the reference's constructor kwargs, ufm.py:483-509 / 720-754, reduced to the
+ * numbers the engine needs).  All spatial sizes are those of the inference resolution (base.py:86-100). */
+typedef struct ufm_config {
+  int img_h, img_w, patch;                 /* H, W (multiples of patch), patch size 14 */
+  /* encoder: DINOv2 ViT (UC/models/encoders/dinov2.py) */
+  int enc_dim, enc_depth, enc_heads;       /* depth after keep_first_n_layers */
+  int enc_take_first, enc_take_last;       /* block indices whose normed output is returned (first only used by Refine) */
+  /* info sharing (UC/models/info_sharing/{global,alternating}_attention_transformer.py) */
+  int info_dim, info_depth, info_heads, info_hidden;
+  int info_take0, info_take1;              /* indices[0], indices[1] */
+  int info_alternating;                    /* 1: odd layers attend within a view */
+  int info_qk_norm, info_layerscale, info_has_proj;
+  /* DPT heads (UC/models/prediction_heads/dpt.py) */
+  int dpt_layer_dims[4];
+  int dpt_feature_dim, dpt_hidden;
+  int flow_out_ch;                         /* 2 */
+  int unc_out_ch;                          /* 0 = no uncertainty head, 1 = non_occluded_mask */
+  float flow_scale[2], flow_shift[2];      /* FlowAdaptor: flow = raw*scale + shift (adaptors.py:77-120) */
+  /* Refine (ufm.py:710-1178) */
+  int refine;                              /* 0/1 */
+  int cls_in, cls_hidden, cls_out, cls_patch, refine_P;
+  float temperature;
+} ufm_config;
+
+/* Create an engine on CUDA device `device`.  Fails (non-zero) if no sm_100 GPU is present: there is no CPU fallback. */
+int ufm_create(const ufm_config* cfg, int device, ufm_engine** out);
+void ufm_destroy(ufm_engine* e);
+const char* ufm_last_error(ufm_engine* e);
+
+/* Hand one packed weight tensor to the engine (copied; the caller may free its buffer).  `name` is the engine's
+ * packed-weight name (ufm_b200/packing.py maps the reference state_dict keys, SURVEY.md 8b, onto these names).
+ * `ptr` may be a host or a device pointer. */
+int ufm_set_weight(ufm_engine* e, const char* name, const void* ptr, int dtype, const int64_t* shape, int ndim);
+
+/* Allocate workspace for up to `max_pairs` pairs per call and validate that every weight is present. */
+int ufm_prepare(ufm_engine* e, int max_pairs);
+
+/* One forward pass over `pairs` image pairs already resident in device memory.
+ *   src, tgt : [pairs, H, W, 3] (UFM_NHWC) or [pairs, 3, H, W] (UFM_NCHW); UFM_U8 raw pixels (normalised inside as
+ *              base.py:215-229) or UFM_F32 already normalised with the encoder's data_norm_type
+ *   flow_out : [pairs, 2, H, W] fp32, x component first (Refine: after local refinement)
+ *   covis_out: [pairs, H, W] fp32 in [0,1], or NULL (ignored when the model has no uncertainty head)
+ * `stream` is a cudaStream_t; the call is asynchronous on it. */
+int ufm_forward(ufm_engine* e, const void* src, const void* tgt, int pairs, int in_dtype, int in_layout,
+                float* flow_out, float* covis_out, void* stream);
+
+/* Same, with HOST buffers: pinned-or-pageable host inputs are copied H2D, results copied D2H, and the call returns
+ * after the stream has drained.  This is the end-to-end entry measured as `e2e` by bench.py. */
+int ufm_forward_host(ufm_engine* e, const void* src, const void* tgt, int pairs, int in_dtype, int in_layout,
+                     float* flow_out, float* covis_out);
+
+/* Ask the next forward calls to also keep optional Refine outputs (residual [B,2,H,W], log_softmax [B,H,W,P*P]). */
+int ufm_set_keep_aux(ufm_engine* e, int keep);
+
+/* Parity hooks: describe / copy an internal stage buffer of the LAST forward (device-to-device or device-to-host).
+ * Names: enc_first, enc_last, info_inter0, info_inter1, info_final, dpt1, dptu, head1_raw, headu_raw, flow_reg,
+ * desc, residual, log_softmax.  Layouts are the engine's own (documented in DESIGN.md). */
+int ufm_stage_desc(ufm_engine* e, const char* name, int* dtype, int64_t* shape, int* ndim);
+int ufm_stage_copy(ufm_engine* e, const char* name, void* dst, int64_t bytes);
+
+/* Number of kernels launched by the last ufm_forward call. */
+int ufm_last_launch_count(ufm_engine* e);
+
+/* ---- kernel-level entry points (unit parity tests; device pointers, asynchronous on `stream`) ---- */
+
+/* out = epilogue(A (*) Wt): see ufm_b200/csrc/kernels.h GemmParams.  A is bf16 with logical extents (C, X, Y, Nimg) and
+ * element strides (1, a_sx, a_sy, a_sn); Wt is bf16 [n_out, taps*cin_pad]. */
+int ufm_op_gemm(const void* a, int C, int X, int Y, int Nimg, int64_t a_sx, int64_t a_sy, int64_t a_sn, int tw, int th,
+                const void* wt, int n_out, int taps, int cin_pad, const float* bias, const float* scale,
+                const float* res1, const float* res2, int64_t r2n, int64_t r2y, int64_t r2x, float* out_f32,
+                void* out_bf16, int64_t sn, int64_t sy, int64_t sx, int64_t out_off, uint32_t flags,
+                const float* tail_w2, const float* tail_b2, const float* tail_scale, const float* tail_shift,
+                int tail_out, float* out2, void* stream, char* err, int errlen);
+int ufm_op_attention(const void* qkv, int n_seq, int seq_len, int heads, float scale, void* out, void* stream,
+                     char* err, int errlen);
+int ufm_op_layernorm(const float* x, int n_seq, int src_seq_len, int src_skip, int tokens, int D, const float* w,
+                     const float* b, float eps, int remap_B, void* out_bf16, int64_t ob_pitch, int64_t ob_col,
+                     float* out_f32, int64_t of_pitch, int64_t of_col, void* stream);
+int ufm_op_qk_norm(void* qkv, int64_t rows, int heads, const float* qw, const float* qb, const float* kw,
+                   const float* kb, float eps, void* stream);
+int ufm_op_resize_ac(const float* in_f32, const void* in_bf16, int n, int h, int w, int C, int rh, int rw, int oh,
+                     int ow, float* out_f32, void* out_bf16, void* stream);
+int ufm_op_shuffle(const void* in, void* out, int is_f32, int n, int h, int w, int k, int C, void* stream);
+int ufm_op_im2col_s2(const void* in, void* out, int n, int h, int w, int C, int oh, int ow, void* stream);
+int ufm_op_refine(const float* desc, int B, int H, int W, const float* flow_in, const float* bias25,
+                  float inv_temperature, float* flow_out, float* residual, float* log_softmax, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* UFM_B200_H */

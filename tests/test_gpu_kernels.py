@@ -1,0 +1,281 @@
+"""Kernel-level parity on a B200: each hand-written kernel, called through the C ABI, against a plain PyTorch fp32
+computation of the same op on the same (bf16-rounded) operands.  Tolerances: fp32-accumulated bf16 products differ from
+torch only by summation order (<= 2e-3 relative to the output scale); bf16 outputs add one rounding (2^-9)."""
+import math
+
+import pytest
+import torch
+import torch.nn.functional as F
+
+pytestmark = pytest.mark.gpu
+
+from ufm_b200 import _lib  # noqa: E402
+
+
+@pytest.fixture(scope="module", autouse=True)
+def _built():
+    import __graft_entry__ as g
+
+    g.build()
+    assert torch.cuda.is_available(), "GPU tests need a B200"
+    torch.backends.cuda.matmul.allow_tf32 = False
+    torch.backends.cudnn.allow_tf32 = False
+
+
+def rel(a, b):
+    return ((a.double() - b.double()).norm() / b.double().norm().clamp_min(1e-30)).item()
+
+
+def _rand(*shape, scale=1.0, seed=0):
+    g = torch.Generator(device="cpu").manual_seed(seed)
+    return (torch.randn(*shape, generator=g) * scale).cuda()
+
+
+@pytest.mark.parametrize("M,K,N", [(300, 128, 128), (1000, 384, 384), (2402, 1024, 256), (257, 640, 1536), (4096, 768, 3072)])
+def test_gemm_bias_bf16_out(M, K, N):
+    import gpu_ops as ops
+
+    a = _rand(M, K, seed=1).bfloat16()
+    w = _rand(N, K, scale=K ** -0.5, seed=2).bfloat16()
+    bias = _rand(N, seed=3)
+    out = torch.zeros(M, N, dtype=torch.bfloat16, device="cuda")
+    outf = torch.zeros(M, N, dtype=torch.float32, device="cuda")
+    ops.linear(a, w, bias=bias, out_bf16=out, out_f32=outf)
+    torch.cuda.synchronize()
+    ref = a.float() @ w.float().t() + bias
+    assert rel(outf, ref) < 1e-5, rel(outf, ref)
+    assert rel(out.float(), ref) < 4e-3
+
+
+def test_gemm_gelu_scale_residual_inplace():
+    import gpu_ops as ops
+
+    M, K, N = 1201 * 2, 384, 1536
+    a = _rand(M, K, seed=1).bfloat16()
+    w = _rand(N, K, scale=K ** -0.5, seed=2).bfloat16()
+    bias = _rand(N, seed=3)
+    h = torch.zeros(M, N, dtype=torch.bfloat16, device="cuda")
+    ops.linear(a, w, bias=bias, out_bf16=h, flags=_lib.GEMM_GELU)
+    ref_h = F.gelu(a.float() @ w.float().t() + bias)
+    torch.cuda.synchronize()
+    assert rel(h.float(), ref_h) < 4e-3
+    # fc2-style: x = x + gamma * (h W2^T + b2), in place on the fp32 residual stream
+    w2 = _rand(K, N, scale=N ** -0.5, seed=4).bfloat16()
+    b2 = _rand(K, seed=5)
+    gamma = _rand(K, seed=6)
+    x = _rand(M, K, seed=7)
+    ref = x + gamma * (h.float() @ w2.float().t() + b2)
+    ops.linear(h, w2, bias=b2, scale=gamma, res1=x, out_f32=x)
+    torch.cuda.synchronize()
+    assert rel(x, ref) < 1e-5
+
+
+def test_gemm_patch_embed_addressing():
+    """3-D A view (K, tokens, images), output shifted one row (cls slot) and a row-broadcast positional add."""
+    import gpu_ops as ops
+
+    imgs, n, K, D = 3, 192, 640, 384
+    a = _rand(imgs * n, K, seed=1).bfloat16()
+    w = _rand(D, K, scale=K ** -0.5, seed=2).bfloat16()
+    bias = _rand(D, seed=3)
+    pos = _rand(n + 1, D, seed=4)
+    x = torch.full((imgs, n + 1, D), 7.0, device="cuda")
+    ops.gemm(a, w, X=n, Y=1, Nimg=imgs, C_=K, a_strides=(K, n * K, n * K), bias=bias, res2=pos[1:].contiguous(),
+             r2=(0, 0, D), out_f32=x, out_strides=(D, 0, (n + 1) * D), out_off=D)
+    torch.cuda.synchronize()
+    ref = (a.float() @ w.float().t() + bias).view(imgs, n, D) + pos[1:]
+    assert rel(x[:, 1:], ref) < 1e-5
+    assert torch.all(x[:, 0] == 7.0)
+
+
+def _pack3(w):
+    from ufm_b200.packing import _conv3_pack
+
+    return _conv3_pack(w.cpu()).cuda()
+
+
+@pytest.mark.parametrize("n,H,W,Ci,Co", [(2, 30, 40, 96, 64), (1, 15, 20, 64, 64), (2, 24, 32, 256, 256), (1, 42, 56, 32, 128)])
+def test_conv3x3_implicit_gemm(n, H, W, Ci, Co):
+    import gpu_ops as ops
+
+    x = _rand(n, H, W, Ci, seed=1).bfloat16()
+    w = _rand(Co, Ci, 3, 3, scale=(9 * Ci) ** -0.5, seed=2).bfloat16().float()
+    bias = _rand(Co, seed=3)
+    r1 = _rand(n, H, W, Co, seed=4)
+    r2 = _rand(n, H, W, Co, seed=5)
+    of = torch.zeros(n, H, W, Co, device="cuda")
+    ob = torch.zeros(n, H, W, Co, dtype=torch.bfloat16, device="cuda")
+    ops.conv3x3(x, _pack3(w), bias=bias, res1=r1, res2=r2, r2=(H * W * Co, W * Co, Co), out_f32=of, out_bf16=ob,
+                flags=_lib.GEMM_RELU_BF16)
+    torch.cuda.synchronize()
+    ref = F.conv2d(x.float().permute(0, 3, 1, 2), w, bias, padding=1).permute(0, 2, 3, 1) + r1 + r2
+    assert rel(of, ref) < 1e-5, rel(of, ref)
+    assert rel(ob.float(), F.relu(ref)) < 4e-3
+
+
+def test_conv3x3_tail_epilogue():
+    import gpu_ops as ops
+
+    n, H, W, Ci, hid, out = 2, 42, 56, 128, 128, 2
+    x = _rand(n, H, W, Ci, seed=1).bfloat16()
+    w = _rand(hid, Ci, 3, 3, scale=(9 * Ci) ** -0.5, seed=2).bfloat16().float()
+    bias = _rand(hid, seed=3)
+    w2 = _rand(out, hid, scale=hid ** -0.5, seed=4)
+    b2, sc, sh = [0.3, -0.2], [2.0, 3.0], [0.5, -1.0]
+    y = torch.zeros(n, out, H, W, device="cuda")
+    raw = torch.zeros(n, out, H, W, device="cuda")
+    ops.conv3x3(x, _pack3(w), bias=bias, out_f32=y, out2=raw, flags=_lib.GEMM_TAIL, tail=(w2, b2, sc, sh))
+    torch.cuda.synchronize()
+    hdn = F.relu(F.conv2d(x.float().permute(0, 3, 1, 2), w, bias, padding=1))
+    ref_raw = F.conv2d(hdn, w2.view(out, hid, 1, 1), torch.tensor(b2).cuda())
+    ref = ref_raw * torch.tensor(sc).cuda().view(1, 2, 1, 1) + torch.tensor(sh).cuda().view(1, 2, 1, 1)
+    assert rel(raw, ref_raw) < 1e-5
+    assert rel(y, ref) < 1e-5
+    # sigmoid variant, one output, narrow hidden (tiny config)
+    w2 = _rand(1, hid, scale=hid ** -0.5, seed=5)
+    y1 = torch.zeros(n, 1, H, W, device="cuda")
+    ops.conv3x3(x, _pack3(w), bias=bias, out_f32=y1, flags=_lib.GEMM_TAIL | _lib.GEMM_TAIL_SIGMOID,
+                tail=(w2, [0.1], [1.0], [0.0]))
+    torch.cuda.synchronize()
+    ref1 = torch.sigmoid(F.conv2d(hdn, w2.view(1, hid, 1, 1), torch.tensor([0.1]).cuda()))
+    assert (y1 - ref1).abs().max().item() < 1e-5
+
+
+@pytest.mark.parametrize("n_seq,seq_len,heads", [(2, 193, 6), (3, 1201, 2), (1, 2400, 3), (2, 130, 2), (1, 256, 1), (2, 384, 2)])
+def test_attention(n_seq, seq_len, heads):
+    import gpu_ops as ops
+
+    D = heads * 64
+    qkv = _rand(n_seq * seq_len, 3 * D, seed=1).bfloat16()
+    qkv[:, :D] *= 2.0  # sharper softmax: exercises the lazy-rescale path
+    out = ops.attention(qkv, n_seq, seq_len, heads, 0.125)
+    torch.cuda.synchronize()
+    t = qkv.float().view(n_seq, seq_len, 3, heads, 64).permute(2, 0, 3, 1, 4)
+    ref = F.scaled_dot_product_attention(t[0], t[1], t[2], scale=0.125).transpose(1, 2).reshape(n_seq * seq_len, D)
+    r = rel(out.float(), ref)
+    assert r < 1e-2, r  # P is rounded to bf16 before the PV product (as in every flash kernel)
+
+
+def test_layernorm_remap():
+    lib = _lib.load()
+    B, S, D = 2, 13, 384
+    x = _rand(2 * B * S, D, seed=1)
+    w, b = _rand(D, seed=2), _rand(D, seed=3)
+    ob = torch.zeros(B * 2 * (S - 1), D + 128, dtype=torch.bfloat16, device="cuda")
+    of = torch.zeros(B * 2 * (S - 1), D, device="cuda")
+    st = torch.cuda.current_stream().cuda_stream
+    assert lib.ufm_op_layernorm(x.data_ptr(), 2 * B, S, 1, S - 1, D, w.data_ptr(), b.data_ptr(), 1e-6, B, ob.data_ptr(),
+                                D + 128, 128, of.data_ptr(), D, 0, st) == 0
+    torch.cuda.synchronize()
+    ref = F.layer_norm(x.view(2, B, S, D)[:, :, 1:], (D,), w, b, 1e-6).permute(1, 0, 2, 3).reshape(-1, D)
+    assert rel(of, ref) < 1e-6
+    assert rel(ob[:, 128:].float(), ref) < 3e-3
+    assert torch.all(ob[:, :128] == 0)
+
+
+def test_qk_norm():
+    lib = _lib.load()
+    rows, heads = 77, 3
+    qkv = _rand(rows, 3 * heads * 64, seed=1).bfloat16()
+    orig = qkv.clone()
+    ws = [_rand(64, seed=s) for s in (2, 3, 4, 5)]
+    st = torch.cuda.current_stream().cuda_stream
+    assert lib.ufm_op_qk_norm(qkv.data_ptr(), rows, heads, *[t.data_ptr() for t in ws], 1e-6, st) == 0
+    torch.cuda.synchronize()
+    o = orig.float().view(rows, 3, heads, 64)
+    q = F.layer_norm(o[:, 0], (64,), ws[0], ws[1], 1e-6)
+    k = F.layer_norm(o[:, 1], (64,), ws[2], ws[3], 1e-6)
+    got = qkv.float().view(rows, 3, heads, 64)
+    assert rel(got[:, 0], q) < 4e-3 and rel(got[:, 1], k) < 4e-3
+    assert torch.equal(got[:, 2], o[:, 2])
+
+
+@pytest.mark.parametrize("h,w,rh,rw,oh,ow", [(15, 20, 30, 40, 30, 40), (8, 10, 16, 20, 15, 19), (96, 128, 168, 224, 168, 224)])
+def test_resize_align_corners(h, w, rh, rw, oh, ow):
+    lib = _lib.load()
+    n, Cc = 2, 64
+    x = _rand(n, h, w, Cc, seed=1)
+    of = torch.zeros(n, oh, ow, Cc, device="cuda")
+    ob = torch.zeros(n, oh, ow, Cc, dtype=torch.bfloat16, device="cuda")
+    st = torch.cuda.current_stream().cuda_stream
+    assert lib.ufm_op_resize_ac(x.data_ptr(), None, n, h, w, Cc, rh, rw, oh, ow, of.data_ptr(), ob.data_ptr(), st) == 0
+    xb = x.bfloat16()
+    of2 = torch.zeros_like(of)
+    assert lib.ufm_op_resize_ac(None, xb.data_ptr(), n, h, w, Cc, rh, rw, oh, ow, of2.data_ptr(), None, st) == 0
+    torch.cuda.synchronize()
+    ref = F.interpolate(x.permute(0, 3, 1, 2), size=(rh, rw), mode="bilinear", align_corners=True)[:, :, :oh, :ow]
+    ref = ref.permute(0, 2, 3, 1)
+    assert (of - ref).abs().max().item() < 2e-5
+    assert rel(ob.float(), ref) < 3e-3
+    ref2 = F.interpolate(xb.float().permute(0, 3, 1, 2), size=(rh, rw), mode="bilinear", align_corners=True)
+    assert (of2 - ref2[:, :, :oh, :ow].permute(0, 2, 3, 1)).abs().max().item() < 2e-5
+
+
+def test_shuffle_and_convt_fold():
+    """1x1 conv -> ConvTranspose2d(k==s) folded into one GEMM + pixel shuffle (dpt.py:107-125)."""
+    import gpu_ops as ops
+    from ufm_b200.packing import _fold_convt
+
+    lib = _lib.load()
+    n, h, w, Ci, m, k = 2, 12, 16, 384, 64, 4
+    x = _rand(n, h, w, Ci, seed=1).bfloat16()
+    w1, b1 = _rand(m, Ci, 1, 1, scale=Ci ** -0.5, seed=2), _rand(m, seed=3)
+    wt, bt = _rand(m, m, k, k, scale=m ** -0.5, seed=4), _rand(m, seed=5)
+    wf, bf_ = _fold_convt(w1.cpu(), b1.cpu(), wt.cpu(), bt.cpu())
+    wf, bf_ = wf.cuda(), bf_.cuda()
+    G = torch.zeros(n * h * w, k * k * m, dtype=torch.bfloat16, device="cuda")
+    ops.linear(x.view(-1, Ci), wf, bias=bf_, out_bf16=G)
+    T = torch.zeros(n, h * k, w * k, m, dtype=torch.bfloat16, device="cuda")
+    st = torch.cuda.current_stream().cuda_stream
+    assert lib.ufm_op_shuffle(G.data_ptr(), T.data_ptr(), 0, n, h, w, k, m, st) == 0
+    torch.cuda.synchronize()
+    ref = F.conv_transpose2d(F.conv2d(x.float().permute(0, 3, 1, 2), w1, b1), wt, bt, stride=k).permute(0, 2, 3, 1)
+    assert rel(T.float(), ref) < 6e-3
+
+
+def test_im2col_s2_conv():
+    import gpu_ops as ops
+
+    lib = _lib.load()
+    n, h, w, Cc, Co = 2, 12, 15, 128, 128
+    oh, ow = (h - 1) // 2 + 1, (w - 1) // 2 + 1
+    x = _rand(n, h, w, Cc, seed=1).bfloat16()
+    wgt = _rand(Co, Cc, 3, 3, scale=(9 * Cc) ** -0.5, seed=2).bfloat16()
+    bias = _rand(Co, seed=3)
+    col = torch.zeros(n * oh * ow, 9 * Cc, dtype=torch.bfloat16, device="cuda")
+    st = torch.cuda.current_stream().cuda_stream
+    assert lib.ufm_op_im2col_s2(x.data_ptr(), col.data_ptr(), n, h, w, Cc, oh, ow, st) == 0
+    out = torch.zeros(n * oh * ow, Co, device="cuda")
+    ops.linear(col, wgt.permute(0, 2, 3, 1).reshape(Co, -1).contiguous(), bias=bias, out_f32=out)
+    torch.cuda.synchronize()
+    ref = F.conv2d(x.float().permute(0, 3, 1, 2), wgt.float(), bias, stride=2, padding=1).permute(0, 2, 3, 1)
+    assert tuple(ref.shape[1:3]) == (oh, ow)
+    assert rel(out.view(n, oh, ow, Co), ref) < 1e-5
+
+
+def test_local_refinement_vs_oracle():
+    from oracle import ufm_oracle as O
+
+    lib = _lib.load()
+    B, H, W, Cc = 2, 56, 70, 16
+    g = torch.Generator().manual_seed(0)
+    desc = torch.randn(B, 2, H, W, Cc, generator=g)
+    # smooth field U(-40,40) + N(0,1), with some targets far outside the image
+    base = F.interpolate(torch.rand(B, 2, 4, 5, generator=g) * 80 - 40, size=(H, W), mode="bilinear", align_corners=True)
+    flow = base + torch.randn(B, 2, H, W, generator=g)
+    flow[0, :, :2, :2] = 1e4
+    bias = torch.randn(25, generator=g) * 0.3
+    d_desc, d_flow, d_bias = desc.cuda(), flow.cuda(), bias.cuda()
+    out = torch.zeros(B, 2, H, W, device="cuda")
+    res = torch.zeros(B, 2, H, W, device="cuda")
+    lsm = torch.zeros(B, H, W, 25, device="cuda")
+    st = torch.cuda.current_stream().cuda_stream
+    assert lib.ufm_op_refine(d_desc.data_ptr(), B, H, W, d_flow.data_ptr(), d_bias.data_ptr(), 0.25, out.data_ptr(),
+                             res.data_ptr(), lsm.data_ptr(), st) == 0
+    torch.cuda.synchronize()
+    f1 = desc[:, 0].permute(0, 3, 1, 2).contiguous()
+    f2 = desc[:, 1].permute(0, 3, 1, 2).contiguous()
+    r_ref, l_ref = O.local_refinement(flow, f1, f2, bias, 4.0, 5)
+    assert (res.cpu() - r_ref).abs().max().item() < 2e-4
+    assert (lsm.cpu().view(B, H, W, 5, 5) - l_ref).abs().max().item() < 2e-3
+    assert (out.cpu() - (flow + r_ref)).abs()[..., 2:, 2:].max().item() < 1e-3

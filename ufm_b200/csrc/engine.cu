@@ -1,0 +1,915 @@
+// UFM engine: owns packed weights and workspace on one B200 and sequences the hand-written kernels for
+// UniFlowMatchConfidence.forward (uniflowmatch/models/ufm.py:562-662) and
+// UniFlowMatchClassificationRefinement.forward (ufm.py:843-1009) behind the C ABI of include/ufm_b200.h.
+// There is no CPU path: creation fails without an sm_100 device.
+#include <cuda.h>
+#include <cuda_bf16.h>
+#include <cuda_runtime.h>
+#include <math.h>
+#include <stdarg.h>
+#include <stdio.h>
+#include <string.h>
+
+#include <map>
+#include <string>
+#include <vector>
+
+#include "../../include/ufm_b200.h"
+#include "kernels.h"
+
+using namespace ufm;
+typedef __nv_bfloat16 bf16;
+
+namespace {
+
+struct Tensor {
+  void* ptr = nullptr;
+  int dtype = UFM_F32;
+  std::vector<int64_t> shape;
+  std::vector<float> host;  // host copy of small fp32 tensors (epilogue constants)
+  int64_t numel() const {
+    int64_t n = 1;
+    for (auto s : shape) n *= s;
+    return n;
+  }
+  int64_t bytes() const { return numel() * (dtype == UFM_F32 ? 4 : dtype == UFM_BF16 ? 2 : 1); }
+};
+
+struct AView {
+  const void* p;
+  int C, X, Y, N;
+  long long sx, sy, sn;  // element strides
+  int tw, th;
+};
+
+void pick_tile(int W, int H, int* tw, int* th) {
+  static const int cand[7][2] = {{16, 8}, {8, 16}, {32, 4}, {4, 32}, {64, 2}, {128, 1}, {2, 64}};
+  long long best = -1;
+  for (auto& c : cand) {
+    const long long tiles = (long long)((W + c[0] - 1) / c[0]) * ((H + c[1] - 1) / c[1]);
+    if (best < 0 || tiles < best) {
+      best = tiles;
+      *tw = c[0];
+      *th = c[1];
+    }
+  }
+}
+
+AView rows_view(const void* p, long long M, int C) { return AView{p, C, (int)M, 1, 1, C, M * C, M * C, 128, 1}; }
+AView image_view(const void* p, int N, int H, int W, int C) {
+  AView a{p, C, W, H, N, C, (long long)W * C, (long long)H * W * C, 16, 8};
+  pick_tile(W, H, &a.tw, &a.th);
+  return a;
+}
+
+struct Epi {
+  const float* bias = nullptr;
+  const float* scale = nullptr;
+  const float* res1 = nullptr;
+  const float* res2 = nullptr;
+  long long r2n = 0, r2y = 0, r2x = 0;
+  float* out_f32 = nullptr;
+  bf16* out_bf16 = nullptr;
+  long long sn = 0, sy = 0, sx = 0, out_off = 0;
+  uint32_t flags = 0;
+  const float* w2 = nullptr;
+  float b2[4] = {0, 0, 0, 0}, tscale[4] = {1, 1, 1, 1}, tshift[4] = {0, 0, 0, 0};
+  int tail_out = 0;
+  float* out2 = nullptr;
+};
+
+bool build_gemm(GemmParams* gp, int* BN, const AView& a, const void* wt, int n_out, int taps, int cin_pad, const Epi& e,
+                char* err, int errlen) {
+  memset(gp, 0, sizeof(*gp));
+  if (a.tw * a.th != 128) {
+    snprintf(err, errlen, "tile %dx%d != 128", a.tw, a.th);
+    return false;
+  }
+  const uint64_t adims[4] = {(uint64_t)a.C, (uint64_t)a.X, (uint64_t)a.Y, (uint64_t)a.N};
+  const uint64_t astr[4] = {2, (uint64_t)a.sx * 2, (uint64_t)a.sy * 2, (uint64_t)a.sn * 2};
+  const uint32_t abox[4] = {64, (uint32_t)a.tw, (uint32_t)a.th, 1};
+  if (!make_tmap_bf16(&gp->tmA, a.p, 4, adims, astr, abox, err, errlen)) return false;
+  const bool tail = (e.flags & GEMM_TAIL) != 0;
+  *BN = (!tail && n_out % 256 == 0) ? 256 : 128;
+  const uint64_t bdims[2] = {(uint64_t)taps * cin_pad, (uint64_t)n_out};
+  const uint64_t bstr[2] = {2, (uint64_t)taps * cin_pad * 2};
+  const uint32_t bbox[2] = {64, (uint32_t)*BN};
+  if (!make_tmap_bf16(&gp->tmB, wt, 2, bdims, bstr, bbox, err, errlen)) return false;
+  if (tail) {
+    if (n_out > 128 || e.tail_out < 1 || e.tail_out > 4 || n_out % 32) {
+      snprintf(err, errlen, "tail epilogue needs N<=128, N%%32==0, 1..4 outputs (N=%d out=%d)", n_out, e.tail_out);
+      return false;
+    }
+  } else if (n_out % 32) {
+    snprintf(err, errlen, "GEMM N=%d must be a multiple of 32", n_out);
+    return false;
+  }
+  gp->tw = a.tw; gp->th = a.th;
+  gp->X = a.X; gp->Y = a.Y; gp->Nimg = a.N;
+  gp->tiles_x = (a.X + a.tw - 1) / a.tw;
+  gp->tiles_y = (a.Y + a.th - 1) / a.th;
+  gp->N = n_out;
+  gp->tiles_n = (n_out + *BN - 1) / *BN;
+  gp->taps = taps;
+  gp->cchunks = (a.C + 63) / 64;
+  gp->cin_pad = cin_pad;
+  if (gp->cchunks * 64 > cin_pad && taps > 1) {
+    snprintf(err, errlen, "conv weight pitch %d too small for C=%d", cin_pad, a.C);
+    return false;
+  }
+  gp->flags = e.flags;
+  gp->bias = e.bias; gp->scale = e.scale; gp->res1 = e.res1; gp->res2 = e.res2;
+  gp->out_f32 = e.out_f32; gp->out_bf16 = e.out_bf16;
+  gp->sN = e.sn; gp->sY = e.sy; gp->sX = e.sx; gp->out_off = e.out_off;
+  gp->r2N = e.r2n; gp->r2Y = e.r2y; gp->r2X = e.r2x;
+  gp->w2 = e.w2; gp->tail_out = e.tail_out; gp->out2 = e.out2;
+  for (int i = 0; i < 4; ++i) {
+    gp->tail_b2[i] = e.b2[i];
+    gp->tail_scale[i] = e.tscale[i];
+    gp->tail_shift[i] = e.tshift[i];
+  }
+  return true;
+}
+
+bool build_attn(AttnParams* ap, const void* qkv, int n_seq, int seq_len, int heads, float scale, void* out, char* err,
+                int errlen) {
+  memset(ap, 0, sizeof(*ap));
+  const uint64_t pitch = (uint64_t)3 * heads * 64;
+  const uint64_t dims[4] = {64, (uint64_t)3 * heads, (uint64_t)seq_len, (uint64_t)n_seq};
+  const uint64_t str[4] = {2, 128, pitch * 2, pitch * 2 * (uint64_t)seq_len};
+  const uint32_t box[4] = {64, 1, 128, 1};
+  if (!make_tmap_bf16(&ap->tmQKV, qkv, 4, dims, str, box, err, errlen)) return false;
+  ap->n_seq = n_seq; ap->seq_len = seq_len; ap->heads = heads;
+  ap->scale_log2 = scale * 1.4426950408889634f;
+  ap->out = reinterpret_cast<bf16*>(out);
+  ap->out_pitch = (long long)heads * 64;
+  return true;
+}
+
+}  // namespace
+
+struct ufm_engine {
+  ufm_config cfg;
+  int device = 0;
+  int num_sms = 148;
+  int max_pairs = 0;
+  bool prepared = false;
+  bool keep_aux = false;
+  int launches = 0;
+  int last_pairs = 0;
+  std::string err;
+  std::map<std::string, Tensor> w;
+  std::map<std::string, Tensor> buf;    // workspace
+  std::map<std::string, Tensor> stage;  // views of the last forward (not owned)
+  cudaStream_t st = nullptr;
+
+  int fail(const char* fmt, ...) {
+    char tmp[1024];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(tmp, sizeof(tmp), fmt, ap);
+    va_end(ap);
+    err = tmp;
+    return 1;
+  }
+  bool ck(cudaError_t e, const char* what) {
+    if (e != cudaSuccess) {
+      fail("%s: %s", what, cudaGetErrorString(e));
+      return false;
+    }
+    return true;
+  }
+  const Tensor* W(const std::string& n) {
+    auto it = w.find(n);
+    if (it == w.end()) {
+      fail("missing weight '%s'", n.c_str());
+      return nullptr;
+    }
+    return &it->second;
+  }
+  const float* Wf(const std::string& n) {
+    const Tensor* t = W(n);
+    return t ? reinterpret_cast<const float*>(t->ptr) : nullptr;
+  }
+  bool has(const std::string& n) { return w.count(n) != 0; }
+  bool alloc(const std::string& n, int dtype, int64_t numel) {
+    Tensor t;
+    t.dtype = dtype;
+    t.shape = {numel};
+    if (numel <= 0) numel = 1;
+    if (!ck(cudaMalloc(&t.ptr, (size_t)numel * (dtype == UFM_F32 ? 4 : 2)), ("cudaMalloc " + n).c_str())) return false;
+    buf[n] = t;
+    return true;
+  }
+  template <typename T>
+  T* B(const char* n) {
+    return reinterpret_cast<T*>(buf[n].ptr);
+  }
+  void set_stage(const char* name, void* p, int dtype, std::vector<int64_t> shape) {
+    Tensor t;
+    t.ptr = p;
+    t.dtype = dtype;
+    t.shape = shape;
+    stage[name] = t;
+  }
+
+  // ---- launch helpers -------------------------------------------------------------------------------------------
+  bool gemm(const AView& a, const std::string& wname, int taps, const Epi& e) {
+    const Tensor* wt = W(wname);
+    if (!wt) return false;
+    const int n_out = (int)wt->shape[0];
+    const int ktot = (int)wt->shape[1];
+    GemmParams gp;
+    int BN;
+    char eb[512];
+    if (!build_gemm(&gp, &BN, a, wt->ptr, n_out, taps, ktot / taps, e, eb, sizeof(eb))) {
+      fail("gemm %s: %s", wname.c_str(), eb);
+      return false;
+    }
+    ++launches;
+    return ck(launch_gemm(gp, BN, num_sms, st), ("launch gemm " + wname).c_str());
+  }
+  bool attention(const void* qkv, int n_seq, int seq_len, int heads, void* out) {
+    AttnParams ap;
+    char eb[512];
+    if (!build_attn(&ap, qkv, n_seq, seq_len, heads, 0.125f, out, eb, sizeof(eb))) {
+      fail("attention: %s", eb);
+      return false;
+    }
+    ++launches;
+    return ck(launch_attention(ap, st), "launch attention");
+  }
+  bool layernorm(const float* x, int n_seq, int src_seq_len, int skip, int tokens, int D, const std::string& pre,
+                 int remap_B, bf16* ob, long long ob_pitch, long long ob_col, float* of = nullptr, long long of_pitch = 0,
+                 long long of_col = 0) {
+    LNParams p;
+    p.x = x; p.D = D; p.eps = 1e-6f;
+    p.w = Wf(pre + ".w"); p.b = Wf(pre + ".b");
+    if (!p.w || !p.b) return false;
+    p.n_seq = n_seq; p.src_seq_len = src_seq_len; p.src_skip = skip; p.tokens = tokens; p.remap_B = remap_B;
+    p.out_bf16 = ob; p.ob_pitch = ob_pitch; p.ob_col = ob_col;
+    p.out_f32 = of; p.of_pitch = of_pitch; p.of_col = of_col;
+    ++launches;
+    return ck(launch_layernorm(p, st), ("layernorm " + pre).c_str());
+  }
+
+  // One pre-LN transformer block over x [n_rows, D] (fp32 residual stream), attention over n_seq sequences of seq_len.
+  bool block(const std::string& pre, float* x, int n_seq, int seq_len, int D, int heads, int hidden, bool qk_norm) {
+    const long long M = (long long)n_seq * seq_len;
+    bf16* xn = B<bf16>("xn");
+    bf16* qkv = B<bf16>("qkv");
+    bf16* att = B<bf16>("att");
+    bf16* h = B<bf16>("h");
+    if (!layernorm(x, 1, (int)M, 0, (int)M, D, pre + ".ln1", 0, xn, D, 0)) return false;
+    {
+      Epi e;
+      e.bias = has(pre + ".qkv.b") ? Wf(pre + ".qkv.b") : nullptr;
+      e.out_bf16 = qkv; e.sx = 3LL * D; e.sy = e.sn = 0;
+      if (!gemm(rows_view(xn, M, D), pre + ".qkv.w", 1, e)) return false;
+    }
+    if (qk_norm) {
+      ++launches;
+      if (!ck(launch_qk_norm(qkv, M, heads, Wf(pre + ".qn.w"), Wf(pre + ".qn.b"), Wf(pre + ".kn.w"), Wf(pre + ".kn.b"),
+                             1e-6f, st), "qk_norm"))
+        return false;
+    }
+    if (!attention(qkv, n_seq, seq_len, heads, att)) return false;
+    {
+      Epi e;
+      e.bias = Wf(pre + ".proj.b");
+      e.scale = has(pre + ".ls1") ? Wf(pre + ".ls1") : nullptr;
+      e.res1 = x; e.out_f32 = x; e.sx = D;
+      if (!gemm(rows_view(att, M, D), pre + ".proj.w", 1, e)) return false;
+    }
+    if (!layernorm(x, 1, (int)M, 0, (int)M, D, pre + ".ln2", 0, xn, D, 0)) return false;
+    {
+      Epi e;
+      e.bias = Wf(pre + ".fc1.b");
+      e.flags = GEMM_GELU;
+      e.out_bf16 = h; e.sx = hidden;
+      if (!gemm(rows_view(xn, M, D), pre + ".fc1.w", 1, e)) return false;
+    }
+    {
+      Epi e;
+      e.bias = Wf(pre + ".fc2.b");
+      e.scale = has(pre + ".ls2") ? Wf(pre + ".ls2") : nullptr;
+      e.res1 = x; e.out_f32 = x; e.sx = D;
+      if (!gemm(rows_view(h, M, hidden), pre + ".fc2.w", 1, e)) return false;
+    }
+    return true;
+  }
+
+  // 3x3 conv (pad 1, stride 1) on an NHWC bf16 image through the implicit-GEMM kernel
+  bool conv3(const bf16* in, int N, int H, int Wd, int C, const std::string& wname, const float* bias, const float* res1,
+             const float* res2, float* of, bf16* ob, bool relu_bf16) {
+    const Tensor* wt = W(wname);
+    if (!wt) return false;
+    const int n_out = (int)wt->shape[0];
+    Epi e;
+    e.bias = bias; e.res1 = res1; e.res2 = res2;
+    e.out_f32 = of; e.out_bf16 = ob;
+    e.sx = n_out; e.sy = (long long)Wd * n_out; e.sn = (long long)H * Wd * n_out;
+    e.r2x = e.sx; e.r2y = e.sy; e.r2n = e.sn;
+    e.flags = relu_bf16 ? GEMM_RELU_BF16 : 0;
+    return gemm(image_view(in, N, H, Wd, C), wname, 9, e);
+  }
+
+  bool dpt_head(const std::string& hp, int Bp, int out_ch, bool sigmoid, const float* tscale, const float* tshift,
+                bf16* dpt_out, float* out_final, float* out_raw);
+  int forward(const void* src, const void* tgt, int pairs, int in_dtype, int in_layout, float* flow_out, float* covis_out,
+              cudaStream_t stream);
+};
+
+// UC/models/prediction_heads/dpt.py:180-232 (DPTFeature.forward) + :285-311 (DPTRegressionProcessor.forward) + adaptor.
+bool ufm_engine::dpt_head(const std::string& hp, int Bp, int out_ch, bool sigmoid, const float* tscale,
+                          const float* tshift, bf16* dpt_out, float* out_final, float* out_raw) {
+  const ufm_config& c = cfg;
+  const int hpn = c.img_h / c.patch, wpn = c.img_w / c.patch, n = hpn * wpn;
+  const int D = c.enc_dim, d = c.info_dim, fd = c.dpt_feature_dim, hid = c.dpt_hidden;
+  const int* ld = c.dpt_layer_dims;
+  const int h3 = (hpn - 1) / 2 + 1, w3 = (wpn - 1) / 2 + 1;
+  const bf16* F0 = B<bf16>("enc_last");
+  const bf16* F1 = B<bf16>("inter0");
+  const bf16* F2 = B<bf16>("inter1");
+  const bf16* F3 = B<bf16>("final");
+  auto tok_view = [&](const bf16* p, int C) { return AView{p, C, n, 1, Bp, C, (long long)n * C, 2LL * n * C, 128, 1}; };
+  bf16* G = B<bf16>("G");
+  bf16 *T0 = B<bf16>("T0"), *T1 = B<bf16>("T1"), *T2 = B<bf16>("T2"), *T3 = B<bf16>("T3"), *T3c = B<bf16>("T3col"),
+       *T3b = B<bf16>("T3b");
+  float* Lf[4] = {B<float>("L0f"), B<float>("L1f"), B<float>("L2f"), B<float>("L3f")};
+  bf16* Lr[4] = {B<bf16>("L0r"), B<bf16>("L1r"), B<bf16>("L2r"), B<bf16>("L3r")};
+  const int LH[4] = {4 * hpn, 2 * hpn, hpn, h3}, LW[4] = {4 * wpn, 2 * wpn, wpn, w3};
+
+  // input_process.0: 1x1 (D -> ld0) folded with ConvT 4x4/s4 into one GEMM, pixel shuffle, 3x3 -> fd (dpt.py:107-125)
+  {
+    Epi e;
+    e.bias = Wf(hp + ".in0.b"); e.out_bf16 = G; e.sx = 16LL * ld[0]; e.sn = (long long)n * e.sx;
+    if (!gemm(tok_view(F0, D), hp + ".in0.w", 1, e)) return false;
+    ++launches;
+    if (!ck(launch_shuffle_bf16(G, T0, Bp, hpn, wpn, 4, ld[0], st), "shuffle0")) return false;
+    if (!conv3(T0, Bp, LH[0], LW[0], ld[0], hp + ".rn0.w", nullptr, nullptr, nullptr, Lf[0], Lr[0], true)) return false;
+  }
+  // input_process.1: 1x1 + ConvT 2x2/s2 (dpt.py:127-145)
+  {
+    Epi e;
+    e.bias = Wf(hp + ".in1.b"); e.out_bf16 = G; e.sx = 4LL * ld[1]; e.sn = (long long)n * e.sx;
+    if (!gemm(tok_view(F1, d), hp + ".in1.w", 1, e)) return false;
+    ++launches;
+    if (!ck(launch_shuffle_bf16(G, T1, Bp, hpn, wpn, 2, ld[1], st), "shuffle1")) return false;
+    if (!conv3(T1, Bp, LH[1], LW[1], ld[1], hp + ".rn1.w", nullptr, nullptr, nullptr, Lf[1], Lr[1], true)) return false;
+  }
+  // input_process.2: 1x1 (dpt.py:147-155)
+  {
+    Epi e;
+    e.bias = Wf(hp + ".in2.b"); e.out_bf16 = T2; e.sx = ld[2]; e.sn = (long long)n * e.sx;
+    if (!gemm(tok_view(F2, d), hp + ".in2.w", 1, e)) return false;
+    if (!conv3(T2, Bp, LH[2], LW[2], ld[2], hp + ".rn2.w", nullptr, nullptr, nullptr, Lf[2], Lr[2], true)) return false;
+  }
+  // input_process.3: 1x1, 3x3 stride 2 (as im2col + GEMM) (dpt.py:157-172)
+  {
+    Epi e;
+    e.bias = Wf(hp + ".in3a.b"); e.out_bf16 = T3; e.sx = ld[3]; e.sn = (long long)n * e.sx;
+    if (!gemm(tok_view(F3, d), hp + ".in3a.w", 1, e)) return false;
+    ++launches;
+    if (!ck(launch_im2col_s2(T3, T3c, Bp, hpn, wpn, ld[3], h3, w3, st), "im2col_s2")) return false;
+    Epi e2;
+    e2.bias = Wf(hp + ".in3b.b"); e2.out_bf16 = T3b; e2.sx = ld[3];
+    if (!gemm(rows_view(T3c, (long long)Bp * h3 * w3, 9 * ld[3]), hp + ".in3b.w", 1, e2)) return false;
+    if (!conv3(T3b, Bp, LH[3], LW[3], ld[3], hp + ".rn3.w", nullptr, nullptr, nullptr, Lf[3], Lr[3], true)) return false;
+  }
+  // fusion blocks (dpt_block.py:225-255): refinenet4 (no resConfUnit1) ... refinenet1
+  bf16* bufA = B<bf16>("bufA");
+  bf16* bufO = B<bf16>("bufO");
+  float* sF = B<float>("sF");
+  bf16* sR = B<bf16>("sR");
+  float* low = B<float>("low");
+  float* path = B<float>("path");
+  for (int r = 4; r >= 1; --r) {
+    const int k = r - 1;  // skip level
+    const int H = LH[k], Wd = LW[k];
+    const std::string rp = hp + ".ref" + std::to_string(r);
+    const float* sumF;
+    const bf16* sumR;
+    if (r == 4) {
+      sumF = Lf[3];
+      sumR = Lr[3];
+    } else {
+      // output = path + resConfUnit1(skip):  skip + conv2(relu(conv1(relu(skip)))) + path
+      if (!conv3(Lr[k], Bp, H, Wd, fd, rp + ".rcu1.c1.w", Wf(rp + ".rcu1.c1.b"), nullptr, nullptr, nullptr, bufA, true))
+        return false;
+      if (!conv3(bufA, Bp, H, Wd, fd, rp + ".rcu1.c2.w", Wf(rp + ".rcu1.c2.b"), Lf[k], path, sF, sR, true)) return false;
+      sumF = sF;
+      sumR = sR;
+    }
+    // resConfUnit2
+    if (!conv3(sumR, Bp, H, Wd, fd, rp + ".rcu2.c1.w", Wf(rp + ".rcu2.c1.b"), nullptr, nullptr, nullptr, bufA, true))
+      return false;
+    if (!conv3(bufA, Bp, H, Wd, fd, rp + ".rcu2.c2.w", Wf(rp + ".rcu2.c2.b"), sumF, nullptr, nullptr, bufO, false))
+      return false;
+    // out_conv (1x1) commuted in front of the x2 bilinear upsample (both linear; interpolation weights sum to 1)
+    {
+      Epi e;
+      e.bias = Wf(rp + ".out.b"); e.out_f32 = low; e.sx = fd;
+      if (!gemm(rows_view(bufO, (long long)Bp * H * Wd, fd), rp + ".out.w", 1, e)) return false;
+    }
+    int oh = 2 * H, ow = 2 * Wd;
+    if (r == 4) {  // crop to the next skip's shape (dpt.py:213)
+      oh = LH[2] < oh ? LH[2] : oh;
+      ow = LW[2] < ow ? LW[2] : ow;
+    }
+    ++launches;
+    if (r > 1) {
+      if (!ck(launch_resize_ac(low, nullptr, Bp, H, Wd, fd, 2 * H, 2 * Wd, oh, ow, path, nullptr, st), "upsample"))
+        return false;
+    } else {
+      if (!ck(launch_resize_ac(low, nullptr, Bp, H, Wd, fd, 2 * H, 2 * Wd, oh, ow, nullptr, dpt_out, st), "upsample"))
+        return false;
+    }
+  }
+  // processor (dpt.py:285-311): conv3x3 fd->hid @8x, bilinear to the image, conv3x3 + ReLU + 1x1 + adaptor (tail epilogue)
+  const int H8 = 8 * hpn, W8 = 8 * wpn;
+  bf16* c1 = B<bf16>("c1");
+  bf16* rs = B<bf16>("rs");
+  if (!conv3(dpt_out, Bp, H8, W8, fd, hp + ".proc.c1.w", Wf(hp + ".proc.c1.b"), nullptr, nullptr, nullptr, c1, false))
+    return false;
+  ++launches;
+  if (!ck(launch_resize_ac(nullptr, c1, Bp, H8, W8, hid, c.img_h, c.img_w, c.img_h, c.img_w, nullptr, rs, st), "resize"))
+    return false;
+  {
+    Epi e;
+    e.bias = Wf(hp + ".proc.c2.b");
+    e.flags = GEMM_TAIL | (sigmoid ? GEMM_TAIL_SIGMOID : 0);
+    e.w2 = Wf(hp + ".proc.out.w");
+    const Tensor* b2 = W(hp + ".proc.out.b");
+    if (!e.w2 || !b2) return false;
+    if ((int)b2->host.size() < out_ch) {
+      fail("%s.proc.out.b has %d entries, need %d", hp.c_str(), (int)b2->host.size(), out_ch);
+      return false;
+    }
+    for (int i = 0; i < out_ch; ++i) {
+      e.b2[i] = b2->host[i];
+      e.tscale[i] = tscale ? tscale[i] : 1.f;
+      e.tshift[i] = tshift ? tshift[i] : 0.f;
+    }
+    e.tail_out = out_ch;
+    e.out_f32 = out_final;
+    e.out2 = out_raw;
+    if (!gemm(image_view(rs, Bp, c.img_h, c.img_w, hid), hp + ".proc.c2.w", 9, e)) return false;
+  }
+  return true;
+}
+
+int ufm_engine::forward(const void* src, const void* tgt, int pairs, int in_dtype, int in_layout, float* flow_out,
+                        float* covis_out, cudaStream_t stream) {
+  if (!prepared) return fail("ufm_prepare was not called");
+  if (pairs < 1 || pairs > max_pairs) return fail("pairs=%d outside [1, %d]", pairs, max_pairs);
+  if (in_dtype != UFM_U8 && in_dtype != UFM_F32) return fail("input dtype must be u8 or f32");
+  st = stream;
+  launches = 0;
+  last_pairs = pairs;
+  stage.clear();
+  const ufm_config& c = cfg;
+  const int Bp = pairs;
+  const int hpn = c.img_h / c.patch, wpn = c.img_w / c.patch, n = hpn * wpn, S = n + 1;
+  const int D = c.enc_dim, d = c.info_dim;
+  const int Kpad = (int)w["enc.patch.w"].shape[1];
+  const long long Me = 2LL * Bp * S, Mi = 2LL * Bp * n;
+
+  // ---- encoder (hub DINOv2 forward) ----
+  {
+    PatchParams pp;
+    pp.src = src; pp.tgt = tgt; pp.B = Bp; pp.H = c.img_h; pp.W = c.img_w; pp.P = c.patch; pp.Kpad = Kpad;
+    pp.is_u8 = in_dtype == UFM_U8; pp.is_nhwc = in_layout == UFM_NHWC;
+    const float mean[3] = {0.485f, 0.456f, 0.406f}, stdv[3] = {0.229f, 0.224f, 0.225f};
+    for (int i = 0; i < 3; ++i) {
+      pp.mean[i] = mean[i];
+      pp.inv_std[i] = 1.0f / stdv[i];
+    }
+    pp.out = B<bf16>("Apatch");
+    ++launches;
+    if (!ck(launch_patch_im2col(pp, st), "patch_im2col")) return 1;
+  }
+  float* x = B<float>("x");
+  {
+    Epi e;
+    e.bias = Wf("enc.patch.b");
+    const float* pos = Wf("enc.pos");
+    if (!e.bias || !pos) return 1;
+    e.res2 = pos + D; e.r2x = D; e.r2n = 0; e.r2y = 0;
+    e.out_f32 = x; e.sx = D; e.sn = (long long)S * D; e.out_off = D;
+    AView a{B<bf16>("Apatch"), Kpad, n, 1, 2 * Bp, Kpad, (long long)n * Kpad, (long long)n * Kpad, 128, 1};
+    if (!gemm(a, "enc.patch.w", 1, e)) return 1;
+    ++launches;
+    if (!ck(launch_cls_rows(x, Wf("enc.cls"), pos, 2 * Bp, S, D, st), "cls_rows")) return 1;
+  }
+  bf16* enc_last = B<bf16>("enc_last");
+  for (int i = 0; i < c.enc_depth; ++i) {
+    if (!block("enc." + std::to_string(i), x, 2 * Bp, S, D, c.enc_heads, 4 * D, false)) return 1;
+    if (c.refine && i == c.enc_take_first) {
+      // final norm, drop cls, (view,b) -> (b,view) order, into the left D columns of the classification-head input
+      if (!layernorm(x, 2 * Bp, S, 1, n, D, "enc.norm", Bp, B<bf16>("Xcls"), c.cls_in, 0)) return 1;
+      set_stage("enc_first", B<bf16>("Xcls"), UFM_BF16, {Bp, 2, n, c.cls_in});
+    }
+    if (i == c.enc_take_last) {
+      if (!layernorm(x, 2 * Bp, S, 1, n, D, "enc.norm", Bp, enc_last, D, 0)) return 1;
+      set_stage("enc_last", enc_last, UFM_BF16, {Bp, 2, n, D});
+    }
+  }
+  // ---- info sharing ----
+  float* y = B<float>("y");
+  {
+    Epi e;
+    e.bias = Wf("info.proj.b");
+    e.res2 = Wf("info.viewpos");
+    if (!e.bias || !e.res2) return 1;
+    e.r2y = d; e.r2x = 0; e.r2n = 0;
+    e.out_f32 = y; e.sx = d; e.sy = (long long)n * d; e.sn = 2LL * n * d;
+    AView a{enc_last, D, n, 2, Bp, D, (long long)n * D, 2LL * n * D, 128, 1};
+    if (!gemm(a, "info.proj.w", 1, e)) return 1;
+  }
+  for (int i = 0; i < c.info_depth; ++i) {
+    const bool per_view = c.info_alternating && (i & 1);
+    if (!block("info." + std::to_string(i), y, per_view ? 2 * Bp : Bp, per_view ? n : 2 * n, d, c.info_heads,
+               c.info_hidden, c.info_qk_norm != 0))
+      return 1;
+    if (i == c.info_take0) {
+      if (!layernorm(y, 1, (int)Mi, 0, (int)Mi, d, "info.norm", 0, B<bf16>("inter0"), d, 0)) return 1;
+      set_stage("info_inter0", B<bf16>("inter0"), UFM_BF16, {Bp, 2, n, d});
+    }
+    if (i == c.info_take1) {
+      if (!layernorm(y, 1, (int)Mi, 0, (int)Mi, d, "info.norm", 0, B<bf16>("inter1"), d, 0)) return 1;
+      set_stage("info_inter1", B<bf16>("inter1"), UFM_BF16, {Bp, 2, n, d});
+    }
+  }
+  if (!layernorm(y, 1, (int)Mi, 0, (int)Mi, d, "info.norm", 0, B<bf16>("final"), d, 0)) return 1;
+  set_stage("info_final", B<bf16>("final"), UFM_BF16, {Bp, 2, n, d});
+  if (c.refine) {
+    if (!layernorm(y, 1, (int)Mi, 0, (int)Mi, d, "info.norm", 0, B<bf16>("Xcls"), c.cls_in, D)) return 1;
+  }
+  // ---- heads (view 1 only: "dual+single", ufm.py:180,700) ----
+  float* flow_reg = c.refine ? B<float>("flow_reg") : flow_out;
+  if (!dpt_head("h1", Bp, c.flow_out_ch, false, c.flow_scale, c.flow_shift, B<bf16>("dpt1"), flow_reg,
+                B<float>("head1_raw")))
+    return 1;
+  const int H8 = 8 * hpn, W8 = 8 * wpn;
+  set_stage("dpt1", B<bf16>("dpt1"), UFM_BF16, {Bp, H8, W8, c.dpt_feature_dim});
+  set_stage("head1_raw", B<float>("head1_raw"), UFM_F32, {Bp, c.flow_out_ch, c.img_h, c.img_w});
+  set_stage("flow_reg", flow_reg, UFM_F32, {Bp, 2, c.img_h, c.img_w});
+  if (c.unc_out_ch > 0) {
+    float* cov = covis_out ? covis_out : B<float>("covis");
+    if (!dpt_head("hu", Bp, c.unc_out_ch, true, nullptr, nullptr, B<bf16>("dptu"), cov, B<float>("headu_raw"))) return 1;
+    set_stage("dptu", B<bf16>("dptu"), UFM_BF16, {Bp, H8, W8, c.dpt_feature_dim});
+    set_stage("headu_raw", B<float>("headu_raw"), UFM_F32, {Bp, c.unc_out_ch, c.img_h, c.img_w});
+  }
+  // ---- Refine: classification head + local refinement (ufm.py:954-991) ----
+  if (c.refine) {
+    const long long Mc = Mi;
+    {
+      Epi e;
+      e.bias = Wf("cls.fc1.b"); e.flags = GEMM_GELU; e.out_bf16 = B<bf16>("Hcls"); e.sx = c.cls_hidden;
+      if (!gemm(rows_view(B<bf16>("Xcls"), Mc, c.cls_in), "cls.fc1.w", 1, e)) return 1;
+    }
+    {
+      Epi e;
+      e.bias = Wf("cls.fc2.b"); e.out_bf16 = B<bf16>("Ycls"); e.sx = c.cls_in;
+      if (!gemm(rows_view(B<bf16>("Hcls"), Mc, c.cls_hidden), "cls.fc2.w", 1, e)) return 1;
+    }
+    const int zc = c.cls_patch * c.cls_patch * c.cls_out;
+    {
+      Epi e;
+      e.bias = Wf("cls.lin.b"); e.out_f32 = B<float>("Z"); e.sx = zc;
+      if (!gemm(rows_view(B<bf16>("Ycls"), Mc, c.cls_in), "cls.lin.w", 1, e)) return 1;
+    }
+    ++launches;
+    if (!ck(launch_shuffle_f32(B<float>("Z"), B<float>("desc"), 2 * Bp, hpn, wpn, c.cls_patch, c.cls_out, st), "shuffle desc"))
+      return 1;
+    set_stage("desc", B<float>("desc"), UFM_F32, {Bp, 2, c.img_h, c.img_w, c.cls_out});
+    RefineParams rp;
+    rp.desc = B<float>("desc"); rp.B = Bp; rp.H = c.img_h; rp.W = c.img_w;
+    rp.flow_in = flow_reg;
+    rp.bias25 = Wf("cls.bias");
+    if (!rp.bias25) return 1;
+    rp.inv_temperature = 1.0f / c.temperature;
+    rp.flow_out = flow_out;
+    rp.residual = keep_aux ? B<float>("residual") : nullptr;
+    rp.log_softmax = keep_aux ? B<float>("log_softmax") : nullptr;
+    ++launches;
+    if (!ck(launch_refine(rp, st), "refine")) return 1;
+    if (keep_aux) {
+      set_stage("residual", B<float>("residual"), UFM_F32, {Bp, 2, c.img_h, c.img_w});
+      set_stage("log_softmax", B<float>("log_softmax"), UFM_F32, {Bp, c.img_h, c.img_w, 25});
+    }
+  }
+  return 0;
+}
+
+// ================================================================================================ C ABI
+extern "C" {
+
+int ufm_create(const ufm_config* cfg, int device, ufm_engine** out) {
+  if (!cfg || !out) return 1;
+  *out = nullptr;
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || device >= ndev) {
+    fprintf(stderr, "ufm_create: no CUDA device %d (this engine has no CPU fallback)\n", device);
+    return 2;
+  }
+  cudaDeviceProp prop;
+  if (cudaGetDeviceProperties(&prop, device) != cudaSuccess || prop.major != 10) {
+    fprintf(stderr, "ufm_create: device %d is not sm_100 (compute capability %d.%d)\n", device, prop.major, prop.minor);
+    return 3;
+  }
+  ufm_engine* e = new ufm_engine();
+  e->cfg = *cfg;
+  e->device = device;
+  e->num_sms = prop.multiProcessorCount;
+  cudaSetDevice(device);
+  const ufm_config& c = e->cfg;
+  if (c.img_h % c.patch || c.img_w % c.patch) {
+    delete e;
+    fprintf(stderr, "ufm_create: Input shape must be divisible by patch size\n");
+    return 4;
+  }
+  if (c.enc_dim % 128 || c.info_dim % 128 || c.enc_dim / c.enc_heads != 64 || c.info_dim / c.info_heads != 64) {
+    delete e;
+    fprintf(stderr, "ufm_create: dims must be multiples of 128 with head_dim 64\n");
+    return 5;
+  }
+  if (c.refine && (c.cls_out != 16 || c.refine_P != 5)) {
+    delete e;
+    fprintf(stderr, "ufm_create: refinement kernel is specialised for 16-channel descriptors and a 5x5 window\n");
+    return 6;
+  }
+  *out = e;
+  return 0;
+}
+
+void ufm_destroy(ufm_engine* e) {
+  if (!e) return;
+  cudaSetDevice(e->device);
+  for (auto& kv : e->w) cudaFree(kv.second.ptr);
+  for (auto& kv : e->buf) cudaFree(kv.second.ptr);
+  delete e;
+}
+
+const char* ufm_last_error(ufm_engine* e) { return e ? e->err.c_str() : "null engine"; }
+
+int ufm_set_weight(ufm_engine* e, const char* name, const void* ptr, int dtype, const int64_t* shape, int ndim) {
+  if (!e) return 1;
+  cudaSetDevice(e->device);
+  Tensor t;
+  t.dtype = dtype;
+  t.shape.assign(shape, shape + ndim);
+  auto it = e->w.find(name);
+  if (it != e->w.end()) {
+    cudaFree(it->second.ptr);
+    e->w.erase(it);
+  }
+  if (!e->ck(cudaMalloc(&t.ptr, (size_t)t.bytes()), "cudaMalloc weight")) return 1;
+  if (!e->ck(cudaMemcpy(t.ptr, ptr, (size_t)t.bytes(), cudaMemcpyDefault), "copy weight")) return 1;
+  if (dtype == UFM_F32 && t.numel() <= 64) {
+    t.host.resize((size_t)t.numel());
+    if (!e->ck(cudaMemcpy(t.host.data(), t.ptr, (size_t)t.bytes(), cudaMemcpyDeviceToHost), "copy small weight")) return 1;
+  }
+  e->w[name] = t;
+  return 0;
+}
+
+int ufm_prepare(ufm_engine* e, int max_pairs) {
+  if (!e) return 1;
+  cudaSetDevice(e->device);
+  for (auto& kv : e->buf) cudaFree(kv.second.ptr);
+  e->buf.clear();
+  e->prepared = false;
+  const ufm_config& c = e->cfg;
+  const long long Bp = max_pairs;
+  const long long hpn = c.img_h / c.patch, wpn = c.img_w / c.patch, n = hpn * wpn, S = n + 1;
+  const long long D = c.enc_dim, d = c.info_dim, fd = c.dpt_feature_dim, hid = c.dpt_hidden;
+  const long long Me = 2 * Bp * S, Mi = 2 * Bp * n;
+  if (!e->W("enc.patch.w")) return 1;
+  const long long Kpad = e->w["enc.patch.w"].shape[1];
+  auto mx = [](long long a, long long b) { return a > b ? a : b; };
+  bool ok = true;
+  ok = ok && e->alloc("Apatch", UFM_BF16, 2 * Bp * n * Kpad);
+  ok = ok && e->alloc("x", UFM_F32, Me * D);
+  ok = ok && e->alloc("y", UFM_F32, Mi * d);
+  ok = ok && e->alloc("xn", UFM_BF16, mx(Me * D, Mi * d));
+  ok = ok && e->alloc("qkv", UFM_BF16, mx(Me * 3 * D, Mi * 3 * d));
+  ok = ok && e->alloc("att", UFM_BF16, mx(Me * D, Mi * d));
+  ok = ok && e->alloc("h", UFM_BF16, mx(Me * 4 * D, Mi * c.info_hidden));
+  ok = ok && e->alloc("enc_last", UFM_BF16, Mi * D);
+  ok = ok && e->alloc("inter0", UFM_BF16, Mi * d);
+  ok = ok && e->alloc("inter1", UFM_BF16, Mi * d);
+  ok = ok && e->alloc("final", UFM_BF16, Mi * d);
+  const int* ld = c.dpt_layer_dims;
+  const long long h3 = (hpn - 1) / 2 + 1, w3 = (wpn - 1) / 2 + 1;
+  ok = ok && e->alloc("G", UFM_BF16, Bp * n * mx(16 * ld[0], 4 * ld[1]));
+  ok = ok && e->alloc("T0", UFM_BF16, Bp * 16 * n * ld[0]);
+  ok = ok && e->alloc("T1", UFM_BF16, Bp * 4 * n * ld[1]);
+  ok = ok && e->alloc("T2", UFM_BF16, Bp * n * ld[2]);
+  ok = ok && e->alloc("T3", UFM_BF16, Bp * n * ld[3]);
+  ok = ok && e->alloc("T3col", UFM_BF16, Bp * h3 * w3 * 9 * ld[3]);
+  ok = ok && e->alloc("T3b", UFM_BF16, Bp * h3 * w3 * ld[3]);
+  const long long lv[4] = {16 * n, 4 * n, n, h3 * w3};
+  const char* lfn[4] = {"L0f", "L1f", "L2f", "L3f"};
+  const char* lrn[4] = {"L0r", "L1r", "L2r", "L3r"};
+  for (int k = 0; k < 4; ++k) {
+    ok = ok && e->alloc(lfn[k], UFM_F32, Bp * lv[k] * fd);
+    ok = ok && e->alloc(lrn[k], UFM_BF16, Bp * lv[k] * fd);
+  }
+  ok = ok && e->alloc("bufA", UFM_BF16, Bp * 16 * n * fd);
+  ok = ok && e->alloc("bufO", UFM_BF16, Bp * 16 * n * fd);
+  ok = ok && e->alloc("sF", UFM_F32, Bp * 16 * n * fd);
+  ok = ok && e->alloc("sR", UFM_BF16, Bp * 16 * n * fd);
+  ok = ok && e->alloc("low", UFM_F32, Bp * 16 * n * fd);
+  ok = ok && e->alloc("path", UFM_F32, Bp * 16 * n * fd);
+  ok = ok && e->alloc("dpt1", UFM_BF16, Bp * 64 * n * fd);
+  ok = ok && e->alloc("c1", UFM_BF16, Bp * 64 * n * hid);
+  ok = ok && e->alloc("rs", UFM_BF16, Bp * c.img_h * c.img_w * hid);
+  ok = ok && e->alloc("head1_raw", UFM_F32, Bp * c.flow_out_ch * c.img_h * c.img_w);
+  if (c.unc_out_ch > 0) {
+    ok = ok && e->alloc("dptu", UFM_BF16, Bp * 64 * n * fd);
+    ok = ok && e->alloc("headu_raw", UFM_F32, Bp * c.unc_out_ch * c.img_h * c.img_w);
+    ok = ok && e->alloc("covis", UFM_F32, Bp * c.unc_out_ch * c.img_h * c.img_w);
+  }
+  if (c.refine) {
+    ok = ok && e->alloc("flow_reg", UFM_F32, Bp * 2 * c.img_h * c.img_w);
+    ok = ok && e->alloc("Xcls", UFM_BF16, Mi * c.cls_in);
+    ok = ok && e->alloc("Hcls", UFM_BF16, Mi * c.cls_hidden);
+    ok = ok && e->alloc("Ycls", UFM_BF16, Mi * c.cls_in);
+    ok = ok && e->alloc("Z", UFM_F32, Mi * c.cls_patch * c.cls_patch * c.cls_out);
+    ok = ok && e->alloc("desc", UFM_F32, 2 * Bp * c.img_h * c.img_w * c.cls_out);
+    ok = ok && e->alloc("residual", UFM_F32, Bp * 2 * c.img_h * c.img_w);
+    ok = ok && e->alloc("log_softmax", UFM_F32, Bp * c.img_h * c.img_w * 25);
+  }
+  // staging buffers for ufm_forward_host
+  ok = ok && e->alloc("in_src", UFM_F32, Bp * 3 * c.img_h * c.img_w);
+  ok = ok && e->alloc("in_tgt", UFM_F32, Bp * 3 * c.img_h * c.img_w);
+  ok = ok && e->alloc("out_flow", UFM_F32, Bp * 2 * c.img_h * c.img_w);
+  if (!ok) return 1;
+  e->max_pairs = max_pairs;
+  e->prepared = true;
+  return 0;
+}
+
+int ufm_forward(ufm_engine* e, const void* src, const void* tgt, int pairs, int in_dtype, int in_layout,
+                float* flow_out, float* covis_out, void* stream) {
+  if (!e) return 1;
+  cudaSetDevice(e->device);
+  if (!flow_out) return e->fail("flow_out is NULL");
+  return e->forward(src, tgt, pairs, in_dtype, in_layout, flow_out, covis_out, reinterpret_cast<cudaStream_t>(stream));
+}
+
+int ufm_forward_host(ufm_engine* e, const void* src, const void* tgt, int pairs, int in_dtype, int in_layout,
+                     float* flow_out, float* covis_out) {
+  if (!e) return 1;
+  cudaSetDevice(e->device);
+  if (!e->prepared) return e->fail("ufm_prepare was not called");
+  if (pairs < 1 || pairs > e->max_pairs) return e->fail("pairs=%d outside [1, %d]", pairs, e->max_pairs);
+  const ufm_config& c = e->cfg;
+  const size_t px = (size_t)pairs * 3 * c.img_h * c.img_w;
+  const size_t in_bytes = px * (in_dtype == UFM_U8 ? 1 : 4);
+  cudaStream_t st = nullptr;
+  void* dsrc = e->buf["in_src"].ptr;
+  void* dtgt = e->buf["in_tgt"].ptr;
+  float* dflow = reinterpret_cast<float*>(e->buf["out_flow"].ptr);
+  float* dcov = c.unc_out_ch > 0 ? reinterpret_cast<float*>(e->buf["covis"].ptr) : nullptr;
+  if (!e->ck(cudaMemcpyAsync(dsrc, src, in_bytes, cudaMemcpyHostToDevice, st), "H2D src")) return 1;
+  if (!e->ck(cudaMemcpyAsync(dtgt, tgt, in_bytes, cudaMemcpyHostToDevice, st), "H2D tgt")) return 1;
+  if (e->forward(dsrc, dtgt, pairs, in_dtype, in_layout, dflow, dcov, st)) return 1;
+  const size_t plane = (size_t)c.img_h * c.img_w;
+  if (!e->ck(cudaMemcpyAsync(flow_out, dflow, pairs * 2 * plane * 4, cudaMemcpyDeviceToHost, st), "D2H flow")) return 1;
+  if (covis_out && dcov)
+    if (!e->ck(cudaMemcpyAsync(covis_out, dcov, pairs * plane * 4, cudaMemcpyDeviceToHost, st), "D2H covis")) return 1;
+  if (!e->ck(cudaStreamSynchronize(st), "sync")) return 1;
+  return 0;
+}
+
+int ufm_set_keep_aux(ufm_engine* e, int keep) {
+  if (!e) return 1;
+  e->keep_aux = keep != 0;
+  return 0;
+}
+
+int ufm_stage_desc(ufm_engine* e, const char* name, int* dtype, int64_t* shape, int* ndim) {
+  if (!e) return 1;
+  auto it = e->stage.find(name);
+  if (it == e->stage.end()) return e->fail("no stage '%s' in the last forward", name);
+  *dtype = it->second.dtype;
+  *ndim = (int)it->second.shape.size();
+  for (int i = 0; i < *ndim; ++i) shape[i] = it->second.shape[i];
+  return 0;
+}
+
+int ufm_stage_copy(ufm_engine* e, const char* name, void* dst, int64_t bytes) {
+  if (!e) return 1;
+  cudaSetDevice(e->device);
+  auto it = e->stage.find(name);
+  if (it == e->stage.end()) return e->fail("no stage '%s' in the last forward", name);
+  if (bytes != it->second.bytes()) return e->fail("stage '%s' is %lld bytes, caller gave %lld", name,
+                                                  (long long)it->second.bytes(), (long long)bytes);
+  if (!e->ck(cudaStreamSynchronize(e->st), "sync")) return 1;
+  if (!e->ck(cudaMemcpy(dst, it->second.ptr, (size_t)bytes, cudaMemcpyDefault), "stage copy")) return 1;
+  return 0;
+}
+
+int ufm_last_launch_count(ufm_engine* e) { return e ? e->launches : -1; }
+
+// ---- kernel-level entry points ---------------------------------------------------------------------------------------
+static int g_num_sms() {
+  static int n = 0;
+  if (!n) {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
+  }
+  return n;
+}
+
+int ufm_op_gemm(const void* a, int C, int X, int Y, int Nimg, int64_t a_sx, int64_t a_sy, int64_t a_sn, int tw, int th,
+                const void* wt, int n_out, int taps, int cin_pad, const float* bias, const float* scale,
+                const float* res1, const float* res2, int64_t r2n, int64_t r2y, int64_t r2x, float* out_f32,
+                void* out_bf16, int64_t sn, int64_t sy, int64_t sx, int64_t out_off, uint32_t flags,
+                const float* tail_w2, const float* tail_b2, const float* tail_scale, const float* tail_shift,
+                int tail_out, float* out2, void* stream, char* err, int errlen) {
+  AView av{a, C, X, Y, Nimg, a_sx, a_sy, a_sn, tw, th};
+  if (tw <= 0) pick_tile(X, Y, &av.tw, &av.th);
+  Epi e;
+  e.bias = bias; e.scale = scale; e.res1 = res1; e.res2 = res2;
+  e.r2n = r2n; e.r2y = r2y; e.r2x = r2x;
+  e.out_f32 = out_f32; e.out_bf16 = reinterpret_cast<bf16*>(out_bf16);
+  e.sn = sn; e.sy = sy; e.sx = sx; e.out_off = out_off;
+  e.flags = flags;
+  e.w2 = tail_w2; e.tail_out = tail_out; e.out2 = out2;
+  for (int i = 0; i < tail_out && i < 4; ++i) {
+    e.b2[i] = tail_b2 ? tail_b2[i] : 0.f;
+    e.tscale[i] = tail_scale ? tail_scale[i] : 1.f;
+    e.tshift[i] = tail_shift ? tail_shift[i] : 0.f;
+  }
+  GemmParams gp;
+  int BN;
+  if (!build_gemm(&gp, &BN, av, wt, n_out, taps, cin_pad, e, err, errlen)) return 1;
+  cudaError_t ce = launch_gemm(gp, BN, g_num_sms(), reinterpret_cast<cudaStream_t>(stream));
+  if (ce != cudaSuccess) {
+    snprintf(err, errlen, "launch_gemm: %s", cudaGetErrorString(ce));
+    return 1;
+  }
+  return 0;
+}
+
+int ufm_op_attention(const void* qkv, int n_seq, int seq_len, int heads, float scale, void* out, void* stream, char* err,
+                     int errlen) {
+  AttnParams ap;
+  if (!build_attn(&ap, qkv, n_seq, seq_len, heads, scale, out, err, errlen)) return 1;
+  cudaError_t ce = launch_attention(ap, reinterpret_cast<cudaStream_t>(stream));
+  if (ce != cudaSuccess) {
+    snprintf(err, errlen, "launch_attention: %s", cudaGetErrorString(ce));
+    return 1;
+  }
+  return 0;
+}
+
+int ufm_op_layernorm(const float* x, int n_seq, int src_seq_len, int src_skip, int tokens, int D, const float* w,
+                     const float* b, float eps, int remap_B, void* out_bf16, int64_t ob_pitch, int64_t ob_col,
+                     float* out_f32, int64_t of_pitch, int64_t of_col, void* stream) {
+  LNParams p;
+  p.x = x; p.D = D; p.eps = eps; p.w = w; p.b = b;
+  p.n_seq = n_seq; p.src_seq_len = src_seq_len; p.src_skip = src_skip; p.tokens = tokens; p.remap_B = remap_B;
+  p.out_bf16 = reinterpret_cast<bf16*>(out_bf16); p.ob_pitch = ob_pitch; p.ob_col = ob_col;
+  p.out_f32 = out_f32; p.of_pitch = of_pitch; p.of_col = of_col;
+  return launch_layernorm(p, reinterpret_cast<cudaStream_t>(stream)) != cudaSuccess;
+}
+
+int ufm_op_qk_norm(void* qkv, int64_t rows, int heads, const float* qw, const float* qb, const float* kw,
+                   const float* kb, float eps, void* stream) {
+  return launch_qk_norm(reinterpret_cast<bf16*>(qkv), rows, heads, qw, qb, kw, kb, eps,
+                        reinterpret_cast<cudaStream_t>(stream)) != cudaSuccess;
+}
+
+int ufm_op_resize_ac(const float* in_f32, const void* in_bf16, int n, int h, int w, int C, int rh, int rw, int oh, int ow,
+                     float* out_f32, void* out_bf16, void* stream) {
+  return launch_resize_ac(in_f32, reinterpret_cast<const bf16*>(in_bf16), n, h, w, C, rh, rw, oh, ow, out_f32,
+                          reinterpret_cast<bf16*>(out_bf16), reinterpret_cast<cudaStream_t>(stream)) != cudaSuccess;
+}
+
+int ufm_op_shuffle(const void* in, void* out, int is_f32, int n, int h, int w, int k, int C, void* stream) {
+  cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+  if (is_f32)
+    return launch_shuffle_f32(reinterpret_cast<const float*>(in), reinterpret_cast<float*>(out), n, h, w, k, C, s) != cudaSuccess;
+  return launch_shuffle_bf16(reinterpret_cast<const bf16*>(in), reinterpret_cast<bf16*>(out), n, h, w, k, C, s) != cudaSuccess;
+}
+
+int ufm_op_im2col_s2(const void* in, void* out, int n, int h, int w, int C, int oh, int ow, void* stream) {
+  return launch_im2col_s2(reinterpret_cast<const bf16*>(in), reinterpret_cast<bf16*>(out), n, h, w, C, oh, ow,
+                          reinterpret_cast<cudaStream_t>(stream)) != cudaSuccess;
+}
+
+int ufm_op_refine(const float* desc, int B, int H, int W, const float* flow_in, const float* bias25, float inv_temperature,
+                  float* flow_out, float* residual, float* log_softmax, void* stream) {
+  RefineParams p;
+  p.desc = desc; p.B = B; p.H = H; p.W = W; p.flow_in = flow_in; p.bias25 = bias25; p.inv_temperature = inv_temperature;
+  p.flow_out = flow_out; p.residual = residual; p.log_softmax = log_softmax;
+  return launch_refine(p, reinterpret_cast<cudaStream_t>(stream)) != cudaSuccess;
+}
+
+}  // extern "C"

@@ -1,0 +1,318 @@
+// Persistent warp-specialised tcgen05 GEMM / implicit-GEMM 3x3 convolution for sm_100a.
+//
+// Replaces every nn.Linear of the reference's transformers (UC/models/utils/transformer_blocks.py:75-78,137-145;
+// hub DINOv2 qkv/proj/fc1/fc2), the patch-embed conv (as im2col GEMM), the DPT 1x1 / 3x3 convs
+// (UC/models/prediction_heads/dpt.py:107-172,271-277; UC/models/libs/croco/dpt_block.py:34-69,128-146,210-218)
+// and the classification-head MLP (UC/models/prediction_heads/mlp_feature.py:55-70).
+//
+// Roles (384 threads, 1 CTA / SM, grid = #SMs, static round-robin tile schedule, n fastest so the CTAs
+// running concurrently share A tiles through L2 and the whole weight panel stays L2 resident):
+//   warp 0     TMA producer: A box (64ch x tw x th x 1) and B box (64 x BN), 128B-swizzled, mbarrier ring
+//   warp 1     MMA issuer: one thread, tcgen05.mma cta_group::1 kind::f16, M=128 N=BN K=16, fp32 accum in TMEM
+//   warp 2     TMEM allocator (2 accumulator stages x BN columns)
+//   warps 4-11 epilogue: tcgen05.ld 32x32b.x32 -> registers -> fused bias/GELU/LayerScale/residual/ReLU -> global
+// Pipelines: smem full/empty (TMA <-> MMA), TMEM full/empty (MMA <-> epilogue), so the epilogue of tile i
+// overlaps the mainloop of tile i+1.
+#include <stdio.h>
+
+#include "kernels.h"
+#include "ptx.cuh"
+
+namespace ufm {
+
+namespace {
+
+constexpr int BM = 128;
+constexpr int BK = 64;
+constexpr int kEpiWarps = 8;
+constexpr int kThreads = 128 + kEpiWarps * 32;
+
+template <int BN>
+struct Cfg {
+  static constexpr int A_BYTES = BM * BK * 2;
+  static constexpr int B_BYTES = BN * BK * 2;
+  static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
+  static constexpr int STAGES = (BN == 256) ? 4 : 6;
+  static constexpr int BAR_BYTES = 256;
+  static constexpr int SCRATCH_BYTES = 2 * 2 * 128 * 4 * 4;  // [acc][half][row][4] floats (TAIL mode)
+  static constexpr int SMEM_BYTES = 1024 + STAGES * STAGE_BYTES + BAR_BYTES + SCRATCH_BYTES;
+  static constexpr int TMEM_COLS = 2 * BN;
+};
+
+__device__ __forceinline__ float gelu_erf(float x) { return 0.5f * x * (1.0f + erff(x * 0.70710678118654752f)); }
+
+template <int BN>
+__global__ void __launch_bounds__(kThreads, 1) gemm_kernel(const __grid_constant__ GemmParams p) {
+  using C = Cfg<BN>;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* sA = smem;
+  uint8_t* sB = smem + C::STAGES * C::A_BYTES;
+  uint64_t* full = reinterpret_cast<uint64_t*>(smem + C::STAGES * C::STAGE_BYTES);
+  uint64_t* empty = full + C::STAGES;
+  uint64_t* tfull = empty + C::STAGES;
+  uint64_t* tempty = tfull + 2;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty + 2);
+  float* scratch = reinterpret_cast<float*>(smem + C::STAGES * C::STAGE_BYTES + C::BAR_BYTES);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&p.tmA);
+    tma_prefetch_desc(&p.tmB);
+  }
+  if (warp == 1 && lane == 0) {
+    for (int i = 0; i < C::STAGES; ++i) {
+      mbar_init(&full[i], 1);
+      mbar_init(&empty[i], 1);
+    }
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(&tfull[i], 1);
+      mbar_init(&tempty[i], kEpiWarps);
+    }
+    fence_barrier_init();
+  }
+  if (warp == 2) tmem_alloc<C::TMEM_COLS>(tmem_slot);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  const int tiles_m = p.Nimg * p.tiles_y * p.tiles_x;
+  const int total_tiles = tiles_m * p.tiles_n;
+  const int k_iters = p.taps * p.cchunks;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+        const int tn = tile % p.tiles_n;
+        const int tm = tile / p.tiles_n;
+        const int tx = tm % p.tiles_x;
+        const int ty = (tm / p.tiles_x) % p.tiles_y;
+        const int img = tm / (p.tiles_x * p.tiles_y);
+        const int x0 = tx * p.tw, y0 = ty * p.th, n0 = tn * BN;
+        for (int k = 0; k < k_iters; ++k) {
+          const int tap = k / p.cchunks;
+          const int cc = k - tap * p.cchunks;
+          int dy = 0, dx = 0;
+          if (p.taps == 9) {
+            dy = tap / 3 - 1;
+            dx = tap % 3 - 1;
+          }
+          mbar_wait(&empty[stage], phase ^ 1);
+          mbar_expect_tx(&full[stage], C::STAGE_BYTES);
+          tma_load_4d(sA + stage * C::A_BYTES, &p.tmA, &full[stage], cc * BK, x0 + dx, y0 + dy, img);
+          tma_load_2d(sB + stage * C::B_BYTES, &p.tmB, &full[stage], tap * p.cin_pad + cc * BK, n0);
+          if (++stage == C::STAGES) {
+            stage = 0;
+            phase ^= 1;
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      constexpr uint32_t idesc = umma_idesc_bf16(BM, BN, 0, 0);
+      int stage = 0;
+      uint32_t phase = 0;
+      int acc = 0;
+      uint32_t accphase = 0;
+      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+        mbar_wait(&tempty[acc], accphase ^ 1);
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + acc * BN;
+        for (int k = 0; k < k_iters; ++k) {
+          mbar_wait(&full[stage], phase);
+          tc_fence_after();
+          const uint32_t a_addr = smem_u32(sA + stage * C::A_BYTES);
+          const uint32_t b_addr = smem_u32(sB + stage * C::B_BYTES);
+#pragma unroll
+          for (int kk = 0; kk < BK / 16; ++kk) {
+            umma_ss(d_tmem, umma_desc_sw128(a_addr + kk * 32), umma_desc_sw128(b_addr + kk * 32), idesc,
+                    (k | kk) != 0 ? 1u : 0u);
+          }
+          umma_commit(&empty[stage]);
+          if (k == k_iters - 1) umma_commit(&tfull[acc]);
+          if (++stage == C::STAGES) {
+            stage = 0;
+            phase ^= 1;
+          }
+        }
+        acc ^= 1;
+        if (acc == 0) accphase ^= 1;
+      }
+    }
+  } else if (warp >= 4) {
+    const int e = warp - 4;
+    const int q = warp & 3;  // TMEM lane quadrant this warp may access
+    const int half = e >> 2;
+    constexpr int HALF_COLS = BN / 2;
+    const bool tail = (p.flags & GEMM_TAIL) != 0;
+    int acc = 0;
+    uint32_t accphase = 0;
+    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+      const int tn = tile % p.tiles_n;
+      const int tm = tile / p.tiles_n;
+      const int tx = tm % p.tiles_x;
+      const int ty = (tm / p.tiles_x) % p.tiles_y;
+      const int img = tm / (p.tiles_x * p.tiles_y);
+      const int n0 = tn * BN;
+      const int r = q * 32 + lane;
+      const int ly = r / p.tw;
+      const int lx = r - ly * p.tw;
+      const int x = tx * p.tw + lx, y = ty * p.th + ly;
+      const bool valid = (x < p.X) && (y < p.Y);
+      const long long off = (long long)img * p.sN + (long long)y * p.sY + (long long)x * p.sX + p.out_off;
+      const long long off2 = (long long)img * p.r2N + (long long)y * p.r2Y + (long long)x * p.r2X;
+
+      mbar_wait(&tfull[acc], accphase);
+      tc_fence_after();
+      float part[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll 1
+      for (int c = 0; c < HALF_COLS / 32; ++c) {
+        const int col0 = half * HALF_COLS + c * 32;
+        const int gcol = n0 + col0;
+        if (gcol >= p.N) break;
+        uint32_t vr[32];
+        __syncwarp();  // tcgen05.ld is .sync.aligned: reconverge after the per-row predicated body
+        tmem_ld32(tmem_base + (uint32_t(q * 32) << 16) + uint32_t(acc * BN + col0), vr);
+        tmem_ld_wait();
+        if (!valid) continue;
+        float v[32];
+#pragma unroll
+        for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(vr[j]);
+        if (p.bias) {
+#pragma unroll
+          for (int j = 0; j < 32; j += 4) {
+            const float4 b4 = __ldg(reinterpret_cast<const float4*>(p.bias + gcol + j));
+            v[j] += b4.x; v[j + 1] += b4.y; v[j + 2] += b4.z; v[j + 3] += b4.w;
+          }
+        }
+        if (tail) {
+#pragma unroll
+          for (int j = 0; j < 32; ++j) v[j] = fmaxf(v[j], 0.f);
+          for (int o = 0; o < p.tail_out; ++o) {
+            const float* w = p.w2 + (long long)o * p.N + gcol;
+            float s = 0.f;
+#pragma unroll
+            for (int j = 0; j < 32; j += 4) {
+              const float4 w4 = __ldg(reinterpret_cast<const float4*>(w + j));
+              s += v[j] * w4.x + v[j + 1] * w4.y + v[j + 2] * w4.z + v[j + 3] * w4.w;
+            }
+            part[o] += s;
+          }
+          continue;
+        }
+        if (p.flags & GEMM_GELU) {
+#pragma unroll
+          for (int j = 0; j < 32; ++j) v[j] = gelu_erf(v[j]);
+        }
+        if (p.scale) {
+#pragma unroll
+          for (int j = 0; j < 32; j += 4) {
+            const float4 s4 = __ldg(reinterpret_cast<const float4*>(p.scale + gcol + j));
+            v[j] *= s4.x; v[j + 1] *= s4.y; v[j + 2] *= s4.z; v[j + 3] *= s4.w;
+          }
+        }
+        if (p.res1) {
+          const float4* rp = reinterpret_cast<const float4*>(p.res1 + off + gcol);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            const float4 r4 = rp[j];
+            v[4 * j] += r4.x; v[4 * j + 1] += r4.y; v[4 * j + 2] += r4.z; v[4 * j + 3] += r4.w;
+          }
+        }
+        if (p.res2) {
+          const float4* rp = reinterpret_cast<const float4*>(p.res2 + off2 + gcol);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            const float4 r4 = rp[j];
+            v[4 * j] += r4.x; v[4 * j + 1] += r4.y; v[4 * j + 2] += r4.z; v[4 * j + 3] += r4.w;
+          }
+        }
+        if (p.out_f32) {
+          float4* op = reinterpret_cast<float4*>(p.out_f32 + off + gcol);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) op[j] = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+        }
+        if (p.out_bf16) {
+          if (p.flags & GEMM_RELU_BF16) {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) v[j] = fmaxf(v[j], 0.f);
+          }
+          uint4* op = reinterpret_cast<uint4*>(p.out_bf16 + off + gcol);
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            op[j] = make_uint4(pack_bf16(v[8 * j], v[8 * j + 1]), pack_bf16(v[8 * j + 2], v[8 * j + 3]),
+                               pack_bf16(v[8 * j + 4], v[8 * j + 5]), pack_bf16(v[8 * j + 6], v[8 * j + 7]));
+          }
+        }
+      }
+      // accumulator stage drained -> hand it back to the MMA warp
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&tempty[acc]);
+
+      if (tail) {
+        // combine the two column halves of each row through smem (double-buffered by accumulator stage)
+        float* sc = scratch + acc * (2 * 128 * 4);
+        float4* mine = reinterpret_cast<float4*>(sc + (half * 128 + r) * 4);
+        *mine = make_float4(part[0], part[1], part[2], part[3]);
+        asm volatile("bar.sync %0, 64;" ::"r"(1 + q) : "memory");
+        if (half == 0 && valid) {
+          const float4 o4 = *reinterpret_cast<const float4*>(sc + (128 + r) * 4);
+          float yv[4] = {part[0] + o4.x, part[1] + o4.y, part[2] + o4.z, part[3] + o4.w};
+          const long long plane = (long long)p.Y * p.X;
+          for (int o = 0; o < p.tail_out; ++o) {
+            float t = yv[o] + p.tail_b2[o];
+            const long long idx = ((long long)img * p.tail_out + o) * plane + (long long)y * p.X + x;
+            if (p.out2) p.out2[idx] = t;
+            if (p.flags & GEMM_TAIL_SIGMOID) t = 1.0f / (1.0f + __expf(-t));
+            else t = t * p.tail_scale[o] + p.tail_shift[o];
+            p.out_f32[idx] = t;
+          }
+        }
+      }
+      acc ^= 1;
+      if (acc == 0) accphase ^= 1;
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 2) tmem_dealloc<C::TMEM_COLS>(tmem_base);
+}
+
+}  // namespace
+
+cudaError_t launch_gemm(const GemmParams& p, int BN, int num_sms, cudaStream_t stream) {
+  const int total = p.Nimg * p.tiles_y * p.tiles_x * p.tiles_n;
+  if (total <= 0) return cudaSuccess;
+  const int grid = total < num_sms ? total : num_sms;
+  cudaError_t err;
+  if (BN == 256) {
+    static bool attr = false;
+    if (!attr) {
+      err = cudaFuncSetAttribute(gemm_kernel<256>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg<256>::SMEM_BYTES);
+      if (err != cudaSuccess) return err;
+      attr = true;
+    }
+    gemm_kernel<256><<<grid, kThreads, Cfg<256>::SMEM_BYTES, stream>>>(p);
+  } else if (BN == 128) {
+    static bool attr = false;
+    if (!attr) {
+      err = cudaFuncSetAttribute(gemm_kernel<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg<128>::SMEM_BYTES);
+      if (err != cudaSuccess) return err;
+      attr = true;
+    }
+    gemm_kernel<128><<<grid, kThreads, Cfg<128>::SMEM_BYTES, stream>>>(p);
+  } else {
+    return cudaErrorInvalidValue;
+  }
+  return cudaGetLastError();
+}
+
+}  // namespace ufm

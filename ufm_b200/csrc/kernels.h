@@ -1,0 +1,148 @@
+// Host-side launch interface of the UFM engine kernels (all sm_100a, hand-written).
+#pragma once
+#include <cuda.h>
+#include <cuda_bf16.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace ufm {
+
+// ------------------------------------------------------------------------------------------------
+// Tensor maps (cuTensorMapEncodeTiled through cudaGetDriverEntryPoint; no link-time libcuda).
+// dims/strides innermost first; strides in BYTES for dims 1..rank-1. bf16 elements, SWIZZLE_128B.
+// ------------------------------------------------------------------------------------------------
+bool make_tmap_bf16(CUtensorMap* out, const void* base, int rank, const uint64_t* dims, const uint64_t* strides_bytes,
+                    const uint32_t* box, char* err, int errlen);
+
+// ------------------------------------------------------------------------------------------------
+// tcgen05 GEMM / implicit-GEMM convolution.
+//   out[n, y, x, :N] = epilogue( sum_{tap, c} A[n, y+dy(tap), x+dx(tap), c] * Wt[:, tap*cin_pad + c] )
+// A is addressed through a 4-D tensor map (C, X, Y, Nimg) with box (64, tw, th, 1), tw*th == 128 (a plain
+// row-major GEMM is X = M, Y = Nimg = 1, tw = 128).  Wt is a 2-D map (Ktotal, N) with box (64, BN).
+// Epilogue per output element v (fp32 accumulator):
+//   v += bias[col]; if GELU v = gelu_erf(v); v *= scale[col]; v += res1[...]; v += res2[...];
+//   out_f32[...] = v;  out_bf16[...] = RELU_BF16 ? max(v,0) : v
+// TAIL mode (DPT processor tail, dpt.py:273-277 + adaptors): v = relu(v + bias); y_o = sum_col v * w2[o][col] + b2[o];
+//   y_o = affine / sigmoid adaptor; planar store out_f32[n][o][y][x] (and raw logits to out2 if given).
+// ------------------------------------------------------------------------------------------------
+enum : uint32_t {
+  GEMM_GELU = 1u << 0,
+  GEMM_RELU_BF16 = 1u << 1,
+  GEMM_TAIL = 1u << 2,
+  GEMM_TAIL_SIGMOID = 1u << 3,
+};
+
+struct alignas(64) GemmParams {
+  CUtensorMap tmA;
+  CUtensorMap tmB;
+  // tile geometry
+  int tw, th;            // A box extents, tw*th == 128
+  int X, Y, Nimg;        // logical output extents per image
+  int tiles_x, tiles_y;  // ceil(X/tw), ceil(Y/th)
+  int N;                 // output channels (multiple of 32, or anything in TAIL mode with N <= 128)
+  int tiles_n;           // ceil(N/BN)
+  int taps;              // 1 or 9 (3x3, pad 1, stride 1)
+  int cchunks;           // ceil(Cin/64)
+  int cin_pad;           // K pitch of one tap in Wt (multiple of 64)
+  uint32_t flags;
+  // epilogue operands
+  const float* bias;     // [N] or null
+  const float* scale;    // [N] or null (LayerScale)
+  const float* res1;     // same addressing as out (sN,sY,sX)
+  const float* res2;     // own strides (r2N,r2Y,r2X); used for row-broadcast adds as well
+  float* out_f32;
+  __nv_bfloat16* out_bf16;
+  long long sN, sY, sX;        // element strides of out / res1
+  long long r2N, r2Y, r2X;     // element strides of res2
+  long long out_off;           // element offset added to out / res1 addresses
+  // TAIL
+  const float* w2;       // [tail_out][N]
+  float tail_b2[4];
+  float tail_scale[4];
+  float tail_shift[4];
+  int tail_out;          // <= 4
+  float* out2;           // optional planar raw (logits) output
+};
+
+// BN in {128, 256}.  Returns cudaError from the launch.
+cudaError_t launch_gemm(const GemmParams& p, int BN, int num_sms, cudaStream_t stream);
+
+// ------------------------------------------------------------------------------------------------
+// Flash-style attention forward, head_dim 64, non-causal: O = softmax(Q K^T * scale) V per (sequence, head).
+// qkv is the fused projection output [n_seq * seq_len, 3, heads, 64] bf16 (row pitch 3*heads*64);
+// out is [n_seq * seq_len, heads * 64] bf16.  Optional per-head LayerNorm of q and k over head_dim
+// (qk_norm, transformer_blocks.py:164) is applied by a separate kernel before the call.
+// ------------------------------------------------------------------------------------------------
+struct alignas(64) AttnParams {
+  CUtensorMap tmQKV;     // 4-D (64, 3*heads, seq_len, n_seq), box (64, 1, 128, 1)
+  int n_seq, seq_len, heads;
+  float scale_log2;      // scale * log2(e)
+  __nv_bfloat16* out;
+  long long out_pitch;   // heads*64
+};
+cudaError_t launch_attention(const AttnParams& p, cudaStream_t stream);
+
+// ------------------------------------------------------------------------------------------------
+// SIMT kernels (bandwidth-bound stages)
+// ------------------------------------------------------------------------------------------------
+// LayerNorm over the last dim D (fp32 stats, eps) of x[rows, D] fp32 -> bf16 and/or fp32, with an optional row remap:
+// source row r = seq*src_seq_len + src_skip + t (t < tokens), destination row = dst_row(seq, t) * dst_pitch + dst_col.
+// dst sequence index = (seq % views_inner) * 0 ... see simt.cu for the exact mapping modes.
+struct LNParams {
+  const float* x; int D; float eps;
+  const float* w; const float* b;
+  int n_seq, src_seq_len, src_skip, tokens;   // rows processed: n_seq * tokens
+  // destination sequence remap: dseq = (seq / swap_inner) + (seq % swap_inner) * swap_outer_stride ... (see kernel)
+  int remap_B;            // 0: dseq = seq.  B>0: seq = v*B + b  ->  dseq = b*2 + v   (encoder (view,b) -> info (b,view))
+  __nv_bfloat16* out_bf16; long long ob_pitch; long long ob_col;   // element pitch/offset
+  float* out_f32; long long of_pitch; long long of_col;
+};
+cudaError_t launch_layernorm(const LNParams& p, cudaStream_t stream);
+
+// per-head LayerNorm of q and k inside the fused qkv buffer (in place, bf16), head_dim 64
+cudaError_t launch_qk_norm(__nv_bfloat16* qkv, long long rows, int heads, const float* qw, const float* qb,
+                           const float* kw, const float* kb, float eps, cudaStream_t stream);
+
+// Patch im2col: image (uint8 or fp32, NHWC or NCHW) -> A[(img, py, px), Kpad] bf16 with
+// k = c*P*P + ky*P + kx (conv weight flatten order), zero padded to Kpad.  uint8 pixels are normalised
+// (x/255 - mean)/std (base.py:215-229) before the bf16 rounding, as under the reference's autocast.
+struct PatchParams {
+  const void* src; const void* tgt;   // each [B, ...]; image index = view*B + b
+  int B, H, W, P, Kpad;
+  int is_u8, is_nhwc;
+  float mean[3], inv_std[3];
+  __nv_bfloat16* out;
+};
+cudaError_t launch_patch_im2col(const PatchParams& p, cudaStream_t stream);
+
+// x[img, 0, :] = cls + pos[0]   (fp32 residual stream, seq_len = 1 + tokens)
+cudaError_t launch_cls_rows(float* x, const float* cls, const float* pos, int n_img, int seq_len, int D, cudaStream_t s);
+
+// Pixel shuffle of a GEMM result: in[(n, y, x), (i, j, c)] -> out[n, y*k+i, x*k+j, c]   (ConvTranspose k==s and
+// F.pixel_shuffle; the (i,j,c) column order is produced by host-side weight row permutation)
+cudaError_t launch_shuffle_bf16(const __nv_bfloat16* in, __nv_bfloat16* out, int n, int h, int w, int k, int C, cudaStream_t s);
+cudaError_t launch_shuffle_f32(const float* in, float* out, int n, int h, int w, int k, int C, cudaStream_t s);
+
+// im2col for the 3x3 stride-2 pad-1 conv (dpt.py:163-169): in NHWC bf16 [n,h,w,C] -> out [(n,oy,ox), 9*C]
+cudaError_t launch_im2col_s2(const __nv_bfloat16* in, __nv_bfloat16* out, int n, int h, int w, int C, int oh, int ow, cudaStream_t s);
+
+// Bilinear resize, align_corners=True, NHWC: in (fp32 or bf16) [n,h,w,C] -> out [n,oh,ow,C] (crop to oh x ow of the
+// resized (rh x rw) grid: scale = (h-1)/(rh-1)).
+cudaError_t launch_resize_ac(const float* in_f32, const __nv_bfloat16* in_bf16, int n, int h, int w, int C, int rh, int rw,
+                             int oh, int ow, float* out_f32, __nv_bfloat16* out_bf16, cudaStream_t s);
+
+// Local classification refinement (ufm.py:1012-1178): desc NHWC fp32 [(b, view), H, W, C=16]; flow planar [B,2,H,W].
+struct RefineParams {
+  const float* desc; int B, H, W;
+  const float* flow_in;       // [B,2,H,W]
+  const float* bias25; float inv_temperature;
+  float* flow_out;            // [B,2,H,W] = flow_in + residual
+  float* residual;            // optional [B,2,H,W]
+  float* log_softmax;         // optional [B,H,W,25]
+};
+cudaError_t launch_refine(const RefineParams& p, cudaStream_t s);
+
+// NHWC fp32 [n,H,W,C] -> NCHW fp32 (stage dumps / descriptor export)
+cudaError_t launch_nhwc_to_nchw(const float* in, float* out, int n, int H, int W, int C, cudaStream_t s);
+
+}  // namespace ufm

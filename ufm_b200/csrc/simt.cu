@@ -1,0 +1,414 @@
+// Bandwidth-bound SIMT kernels of the UFM engine (sm_100a): LayerNorm, patch im2col, pixel shuffles, strided
+// im2col, align_corners bilinear resampling, the fused local classification refinement, layout export.
+// All are coalesced along the channel / pixel axis with 128-bit accesses; none has data reuse worth a TMA stage
+// except the refinement gather, which relies on L1 for the overlapping 8x8 windows of neighbouring pixels.
+#include <math.h>
+#include <type_traits>
+
+#include "kernels.h"
+#include "ptx.cuh"
+
+namespace ufm {
+
+namespace {
+
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+
+// ------------------------------------------------------------------------------------------------ LayerNorm
+// One warp per row, the row held in registers (D <= 1024, D % 128 == 0): fp32 two-pass statistics as nn.LayerNorm
+// (transformer_blocks.py norm1/norm2, final `norm` on returned layers: global_attention_transformer.py:546-550,586).
+constexpr int LN_MAXV = 8;
+__global__ void __launch_bounds__(256) layernorm_kernel(const LNParams p) {
+  const int warps_per_block = blockDim.x >> 5;
+  const long long row = (long long)blockIdx.x * warps_per_block + (threadIdx.x >> 5);
+  const long long rows = (long long)p.n_seq * p.tokens;
+  if (row >= rows) return;
+  const int lane = threadIdx.x & 31;
+  const int seq = (int)(row / p.tokens);
+  const int t = (int)(row - (long long)seq * p.tokens);
+  const float* xr = p.x + ((long long)seq * p.src_seq_len + p.src_skip + t) * p.D;
+  const int nv = p.D >> 7;
+  float4 v[LN_MAXV];
+  float s = 0.f;
+#pragma unroll
+  for (int i = 0; i < LN_MAXV; ++i)
+    if (i < nv) {
+      v[i] = __ldg(reinterpret_cast<const float4*>(xr) + i * 32 + lane);
+      s += v[i].x + v[i].y + v[i].z + v[i].w;
+    }
+  const float mean = warp_sum(s) / p.D;
+  float q = 0.f;
+#pragma unroll
+  for (int i = 0; i < LN_MAXV; ++i)
+    if (i < nv) {
+      const float a = v[i].x - mean, b = v[i].y - mean, c = v[i].z - mean, d = v[i].w - mean;
+      q += a * a + b * b + c * c + d * d;
+    }
+  const float rstd = rsqrtf(warp_sum(q) / p.D + p.eps);
+  int dseq = seq;
+  if (p.remap_B > 0) {
+    const int vv = seq / p.remap_B, bb = seq - vv * p.remap_B;
+    dseq = bb * 2 + vv;
+  }
+  const long long drow = (long long)dseq * p.tokens + t;
+#pragma unroll
+  for (int i = 0; i < LN_MAXV; ++i)
+    if (i < nv) {
+      const int col = (i * 32 + lane) * 4;
+      const float4 w = __ldg(reinterpret_cast<const float4*>(p.w + col));
+      const float4 b = __ldg(reinterpret_cast<const float4*>(p.b + col));
+      float4 y;
+      y.x = (v[i].x - mean) * rstd * w.x + b.x;
+      y.y = (v[i].y - mean) * rstd * w.y + b.y;
+      y.z = (v[i].z - mean) * rstd * w.z + b.z;
+      y.w = (v[i].w - mean) * rstd * w.w + b.w;
+      if (p.out_bf16) {
+        uint2 o = make_uint2(pack_bf16(y.x, y.y), pack_bf16(y.z, y.w));
+        *reinterpret_cast<uint2*>(p.out_bf16 + drow * p.ob_pitch + p.ob_col + col) = o;
+      }
+      if (p.out_f32) *reinterpret_cast<float4*>(p.out_f32 + drow * p.of_pitch + p.of_col + col) = y;
+    }
+}
+
+// per-head LayerNorm of q and k (head_dim 64) in place inside the fused qkv buffer; one warp per (row, head, q|k)
+__global__ void __launch_bounds__(256) qk_norm_kernel(__nv_bfloat16* qkv, long long rows, int heads, const float* qw,
+                                                     const float* qb, const float* kw, const float* kb, float eps) {
+  const long long wid = (long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  const long long total = rows * heads * 2;
+  if (wid >= total) return;
+  const int lane = threadIdx.x & 31;
+  const int which = (int)(wid % 2);
+  const int head = (int)((wid / 2) % heads);
+  const long long row = wid / (2 * heads);
+  __nv_bfloat162* ptr =
+      reinterpret_cast<__nv_bfloat162*>(qkv + row * (3LL * heads * 64) + (long long)which * heads * 64 + head * 64) + lane;
+  const float2 x = __bfloat1622float2(*ptr);
+  const float mean = warp_sum(x.x + x.y) * (1.f / 64.f);
+  const float a = x.x - mean, b = x.y - mean;
+  const float rstd = rsqrtf(warp_sum(a * a + b * b) * (1.f / 64.f) + eps);
+  const float* w = which ? kw : qw;
+  const float* bb = which ? kb : qb;
+  *ptr = __floats2bfloat162_rn(a * rstd * w[2 * lane] + bb[2 * lane], b * rstd * w[2 * lane + 1] + bb[2 * lane + 1]);
+}
+
+// ------------------------------------------------------------------------------------------------ patch im2col
+__global__ void __launch_bounds__(256) patch_im2col_kernel(const PatchParams p) {
+  const int hp = p.H / p.P, wp = p.W / p.P;
+  const int kgroups = p.Kpad >> 3;
+  const long long total = 2LL * p.B * hp * wp * kgroups;
+  const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= total) return;
+  const int kg = (int)(idx % kgroups);
+  const long long row = idx / kgroups;
+  const int px = (int)(row % wp);
+  const int py = (int)((row / wp) % hp);
+  const int img = (int)(row / ((long long)wp * hp));
+  const int view = img / p.B, b = img - view * p.B;
+  const void* base = view ? p.tgt : p.src;
+  const int PP = p.P * p.P;
+  const int K = 3 * PP;
+  float f[8];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    const int k = kg * 8 + i;
+    float val = 0.f;
+    if (k < K) {
+      const int c = k / PP;
+      const int rem = k - c * PP;
+      const int ky = rem / p.P, kx = rem - ky * p.P;
+      const int y = py * p.P + ky, x = px * p.P + kx;
+      const long long off = p.is_nhwc ? (((long long)b * p.H + y) * p.W + x) * 3 + c
+                                      : (((long long)b * 3 + c) * p.H + y) * p.W + x;
+      if (p.is_u8) {
+        const float u = (float)reinterpret_cast<const uint8_t*>(base)[off];
+        val = (u / 255.0f - p.mean[c]) * p.inv_std[c];
+      } else {
+        val = reinterpret_cast<const float*>(base)[off];
+      }
+    }
+    f[i] = val;
+  }
+  *reinterpret_cast<uint4*>(p.out + row * p.Kpad + kg * 8) =
+      make_uint4(pack_bf16(f[0], f[1]), pack_bf16(f[2], f[3]), pack_bf16(f[4], f[5]), pack_bf16(f[6], f[7]));
+}
+
+__global__ void cls_rows_kernel(float* x, const float* cls, const float* pos, int n_img, int seq_len, int D) {
+  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= n_img * D) return;
+  const int img = idx / D, d = idx - img * D;
+  x[(long long)img * seq_len * D + d] = cls[d] + pos[d];
+}
+
+// ------------------------------------------------------------------------------------------------ pixel shuffle
+template <typename T, int VEC>
+__global__ void __launch_bounds__(256) shuffle_kernel(const T* in, T* out, int n, int h, int w, int k, int C) {
+  const int cg = C / VEC;
+  const long long total = (long long)n * h * w * k * k * cg;
+  const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= total) return;
+  // idx enumerates the INPUT contiguously: (row=(n,y,x), i, j, cgroup)
+  const int g = (int)(idx % cg);
+  const int j = (int)((idx / cg) % k);
+  const int i = (int)((idx / ((long long)cg * k)) % k);
+  const long long row = idx / ((long long)cg * k * k);
+  const int x = (int)(row % w);
+  const int y = (int)((row / w) % h);
+  const int nn = (int)(row / ((long long)w * h));
+  typedef typename std::conditional<sizeof(T) * VEC == 16, uint4, uint2>::type V;
+  const V val = *reinterpret_cast<const V*>(in + idx * VEC);
+  const long long o = ((((long long)nn * h * k + (y * k + i)) * (w * k)) + (x * k + j)) * C + g * VEC;
+  *reinterpret_cast<V*>(out + o) = val;
+}
+
+// ------------------------------------------------------------------------------------------------ 3x3 s2 im2col
+__global__ void __launch_bounds__(256) im2col_s2_kernel(const __nv_bfloat16* in, __nv_bfloat16* out, int n, int h, int w,
+                                                       int C, int oh, int ow) {
+  const int cg = C >> 3;
+  const long long total = (long long)n * oh * ow * 9 * cg;
+  const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= total) return;
+  const int g = (int)(idx % cg);
+  const int tap = (int)((idx / cg) % 9);
+  const long long row = idx / ((long long)cg * 9);
+  const int ox = (int)(row % ow);
+  const int oy = (int)((row / ow) % oh);
+  const int nn = (int)(row / ((long long)ow * oh));
+  const int y = 2 * oy + tap / 3 - 1, x = 2 * ox + tap % 3 - 1;
+  uint4 v = make_uint4(0, 0, 0, 0);
+  if (y >= 0 && y < h && x >= 0 && x < w)
+    v = *reinterpret_cast<const uint4*>(in + (((long long)nn * h + y) * w + x) * C + g * 8);
+  *reinterpret_cast<uint4*>(out + idx * 8) = v;
+}
+
+// ------------------------------------------------------------------------------------------------ bilinear (ac=True)
+__device__ __forceinline__ float4 ld4(const float* p) { return __ldg(reinterpret_cast<const float4*>(p)); }
+__device__ __forceinline__ float4 ld4(const __nv_bfloat16* p) {
+  const uint2 u = __ldg(reinterpret_cast<const uint2*>(p));
+  const float2 a = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&u.x));
+  const float2 b = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&u.y));
+  return make_float4(a.x, a.y, b.x, b.y);
+}
+// PyTorch upsample_bilinear2d, align_corners=True (dpt_block.py:251-253, dpt.py:304): src = dst*(in-1)/(out-1).
+template <typename T>
+__global__ void __launch_bounds__(256) resize_ac_kernel(const T* in, int n, int h, int w, int C, float sy, float sx,
+                                                       int oh, int ow, float* out_f32, __nv_bfloat16* out_bf16) {
+  const int cg = C >> 2;
+  const long long total = (long long)n * oh * ow * cg;
+  const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= total) return;
+  const int g = (int)(idx % cg);
+  const long long pix = idx / cg;
+  const int ox = (int)(pix % ow);
+  const int oy = (int)((pix / ow) % oh);
+  const int nn = (int)(pix / ((long long)ow * oh));
+  const float fy = sy * oy, fx = sx * ox;
+  const int y0 = (int)fy, x0 = (int)fx;
+  const int y1 = y0 + (y0 < h - 1 ? 1 : 0), x1 = x0 + (x0 < w - 1 ? 1 : 0);
+  const float ly = fy - y0, lx = fx - x0;
+  const float hy = 1.f - ly, hx = 1.f - lx;
+  const T* b = in + (long long)nn * h * w * C + g * 4;
+  const float4 a00 = ld4(b + ((long long)y0 * w + x0) * C), a01 = ld4(b + ((long long)y0 * w + x1) * C);
+  const float4 a10 = ld4(b + ((long long)y1 * w + x0) * C), a11 = ld4(b + ((long long)y1 * w + x1) * C);
+  float4 r;
+  r.x = hy * (hx * a00.x + lx * a01.x) + ly * (hx * a10.x + lx * a11.x);
+  r.y = hy * (hx * a00.y + lx * a01.y) + ly * (hx * a10.y + lx * a11.y);
+  r.z = hy * (hx * a00.z + lx * a01.z) + ly * (hx * a10.z + lx * a11.z);
+  r.w = hy * (hx * a00.w + lx * a01.w) + ly * (hx * a10.w + lx * a11.w);
+  const long long o = pix * C + g * 4;
+  if (out_f32) *reinterpret_cast<float4*>(out_f32 + o) = r;
+  if (out_bf16) *reinterpret_cast<uint2*>(out_bf16 + o) = make_uint2(pack_bf16(r.x, r.y), pack_bf16(r.z, r.w));
+}
+
+// ------------------------------------------------------------------------------------------------ local refinement
+// ufm.py:1012-1178 fused: one thread per source pixel.  Because the 25 bicubic samples of a pixel share one fractional
+// offset and the score is linear in the sampled key, score[a][b] = sum_ty sum_tx wy[ty] wx[tx] D[a+ty][b+tx] with
+// D[r][s] = <q, F2[y0-3+r][x0-3+s]> (zero outside the image = grid_sample padding_mode="zeros" per tap):
+// 64 dot products of 16 channels, then a separable 8x8 -> 5x5 cubic filter, softmax over 25 and the expectation of
+// the (dj, di) offsets.  Nothing is materialised (the reference writes 376 MB/pair here).
+__device__ __forceinline__ void cubic_w(float t, float (&w)[4]) {
+  const float A = -0.75f;
+  const float x0 = t + 1.f, x1 = t, x2 = 1.f - t, x3 = 2.f - t;
+  w[0] = ((A * x0 - 5.f * A) * x0 + 8.f * A) * x0 - 4.f * A;
+  w[1] = ((A + 2.f) * x1 - (A + 3.f)) * x1 * x1 + 1.f;
+  w[2] = ((A + 2.f) * x2 - (A + 3.f)) * x2 * x2 + 1.f;
+  w[3] = ((A * x3 - 5.f * A) * x3 + 8.f * A) * x3 - 4.f * A;
+}
+
+__global__ void __launch_bounds__(128) refine_kernel(const RefineParams p) {
+  const int x = blockIdx.x * 32 + (threadIdx.x & 31);
+  const int y = blockIdx.y * 4 + (threadIdx.x >> 5);
+  const int b = blockIdx.z;
+  if (x >= p.W || y >= p.H) return;
+  const long long plane = (long long)p.H * p.W;
+  const float* f1 = p.desc + ((long long)(2 * b) * plane + (long long)y * p.W + x) * 16;
+  const float* f2 = p.desc + (long long)(2 * b + 1) * plane * 16;
+  float q[16];
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const float4 t = __ldg(reinterpret_cast<const float4*>(f1) + i);
+    q[4 * i] = t.x; q[4 * i + 1] = t.y; q[4 * i + 2] = t.z; q[4 * i + 3] = t.w;
+  }
+  const float fx = p.flow_in[(2LL * b) * plane + (long long)y * p.W + x];
+  const float fy = p.flow_in[(2LL * b + 1) * plane + (long long)y * p.W + x];
+  // same float sequence as the reference: normalise with align_corners=False then grid_sample's unnormalise
+  const float gx = (((float)x + fx) + 0.5f) / (float)p.W * 2.f - 1.f;
+  const float gy = (((float)y + fy) + 0.5f) / (float)p.H * 2.f - 1.f;
+  const float ix = ((gx + 1.f) * (float)p.W - 1.f) * 0.5f;
+  const float iy = ((gy + 1.f) * (float)p.H - 1.f) * 0.5f;
+  const float flx = floorf(ix), fly = floorf(iy);
+  float wx[4], wy[4];
+  cubic_w(ix - flx, wx);
+  cubic_w(iy - fly, wy);
+  // clamp far-away targets so the integer window arithmetic cannot overflow; such windows are all-zero anyway
+  const int x0 = (int)fminf(fmaxf(flx, -16.f), (float)p.W + 16.f) - 3;
+  const int y0 = (int)fminf(fmaxf(fly, -16.f), (float)p.H + 16.f) - 3;
+  float E[8][5];  // E[r][bb] = sum_tx wx[tx] * D[r][bb+tx]
+#pragma unroll
+  for (int r = 0; r < 8; ++r) {
+    const int yy = y0 + r;
+    float D[8];
+#pragma unroll
+    for (int s = 0; s < 8; ++s) {
+      const int xx = x0 + s;
+      float d = 0.f;
+      if (yy >= 0 && yy < p.H && xx >= 0 && xx < p.W) {
+        const float4* k = reinterpret_cast<const float4*>(f2 + ((long long)yy * p.W + xx) * 16);
+        const float4 k0 = __ldg(k), k1 = __ldg(k + 1), k2 = __ldg(k + 2), k3 = __ldg(k + 3);
+        d = q[0] * k0.x + q[1] * k0.y + q[2] * k0.z + q[3] * k0.w + q[4] * k1.x + q[5] * k1.y + q[6] * k1.z +
+            q[7] * k1.w + q[8] * k2.x + q[9] * k2.y + q[10] * k2.z + q[11] * k2.w + q[12] * k3.x + q[13] * k3.y +
+            q[14] * k3.z + q[15] * k3.w;
+      }
+      D[s] = d;
+    }
+#pragma unroll
+    for (int bb = 0; bb < 5; ++bb) E[r][bb] = wx[0] * D[bb] + wx[1] * D[bb + 1] + wx[2] * D[bb + 2] + wx[3] * D[bb + 3];
+  }
+  float sc[25];
+  float mx = -INFINITY;
+#pragma unroll
+  for (int a = 0; a < 5; ++a)
+#pragma unroll
+    for (int bb = 0; bb < 5; ++bb) {
+      const float s = wy[0] * E[a][bb] + wy[1] * E[a + 1][bb] + wy[2] * E[a + 2][bb] + wy[3] * E[a + 3][bb];
+      sc[a * 5 + bb] = s * p.inv_temperature + __ldg(p.bias25 + a * 5 + bb);
+      mx = fmaxf(mx, sc[a * 5 + bb]);
+    }
+  float sum = 0.f, rx = 0.f, ry = 0.f;
+#pragma unroll
+  for (int k = 0; k < 25; ++k) {
+    const float e = __expf(sc[k] - mx);
+    sum += e;
+    rx += e * (float)(k % 5 - 2);
+    ry += e * (float)(k / 5 - 2);
+  }
+  const float inv = 1.f / sum;
+  rx *= inv;
+  ry *= inv;
+  const long long o0 = (2LL * b) * plane + (long long)y * p.W + x, o1 = o0 + plane;
+  p.flow_out[o0] = fx + rx;
+  p.flow_out[o1] = fy + ry;
+  if (p.residual) {
+    p.residual[o0] = rx;
+    p.residual[o1] = ry;
+  }
+  if (p.log_softmax) {
+    const float lse = mx + __logf(sum);
+    float* ls = p.log_softmax + ((long long)b * plane + (long long)y * p.W + x) * 25;
+#pragma unroll
+    for (int k = 0; k < 25; ++k) ls[k] = sc[k] - lse;
+  }
+}
+
+__global__ void __launch_bounds__(256) nhwc_to_nchw_kernel(const float* in, float* out, int n, int H, int W, int C) {
+  const long long total = (long long)n * H * W * C;
+  const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;  // output index (n,c,y,x)
+  if (idx >= total) return;
+  const int x = (int)(idx % W);
+  const int y = (int)((idx / W) % H);
+  const int c = (int)((idx / ((long long)W * H)) % C);
+  const int nn = (int)(idx / ((long long)W * H * C));
+  out[idx] = in[(((long long)nn * H + y) * W + x) * C + c];
+}
+
+inline unsigned blocks_for(long long total, int per) { return (unsigned)((total + per - 1) / per); }
+
+}  // namespace
+
+cudaError_t launch_layernorm(const LNParams& p, cudaStream_t stream) {
+  if ((p.D & 127) || p.D > 128 * LN_MAXV) return cudaErrorInvalidValue;
+  const long long rows = (long long)p.n_seq * p.tokens;
+  if (rows == 0) return cudaSuccess;
+  layernorm_kernel<<<blocks_for(rows, 8), 256, 0, stream>>>(p);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_qk_norm(__nv_bfloat16* qkv, long long rows, int heads, const float* qw, const float* qb,
+                           const float* kw, const float* kb, float eps, cudaStream_t stream) {
+  const long long warps = rows * heads * 2;
+  qk_norm_kernel<<<blocks_for(warps, 8), 256, 0, stream>>>(qkv, rows, heads, qw, qb, kw, kb, eps);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_patch_im2col(const PatchParams& p, cudaStream_t stream) {
+  const long long total = 2LL * p.B * (p.H / p.P) * (p.W / p.P) * (p.Kpad / 8);
+  patch_im2col_kernel<<<blocks_for(total, 256), 256, 0, stream>>>(p);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_cls_rows(float* x, const float* cls, const float* pos, int n_img, int seq_len, int D, cudaStream_t s) {
+  cls_rows_kernel<<<blocks_for((long long)n_img * D, 256), 256, 0, s>>>(x, cls, pos, n_img, seq_len, D);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_shuffle_bf16(const __nv_bfloat16* in, __nv_bfloat16* out, int n, int h, int w, int k, int C,
+                                cudaStream_t s) {
+  if (C % 8) return cudaErrorInvalidValue;
+  const long long total = (long long)n * h * w * k * k * (C / 8);
+  shuffle_kernel<__nv_bfloat16, 8><<<blocks_for(total, 256), 256, 0, s>>>(in, out, n, h, w, k, C);
+  return cudaGetLastError();
+}
+cudaError_t launch_shuffle_f32(const float* in, float* out, int n, int h, int w, int k, int C, cudaStream_t s) {
+  if (C % 4) return cudaErrorInvalidValue;
+  const long long total = (long long)n * h * w * k * k * (C / 4);
+  shuffle_kernel<float, 4><<<blocks_for(total, 256), 256, 0, s>>>(in, out, n, h, w, k, C);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_im2col_s2(const __nv_bfloat16* in, __nv_bfloat16* out, int n, int h, int w, int C, int oh, int ow,
+                             cudaStream_t s) {
+  if (C % 8) return cudaErrorInvalidValue;
+  const long long total = (long long)n * oh * ow * 9 * (C / 8);
+  im2col_s2_kernel<<<blocks_for(total, 256), 256, 0, s>>>(in, out, n, h, w, C, oh, ow);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_resize_ac(const float* in_f32, const __nv_bfloat16* in_bf16, int n, int h, int w, int C, int rh, int rw,
+                             int oh, int ow, float* out_f32, __nv_bfloat16* out_bf16, cudaStream_t s) {
+  if (C % 4) return cudaErrorInvalidValue;
+  const float sy = rh > 1 ? (float)(h - 1) / (float)(rh - 1) : 0.f;
+  const float sx = rw > 1 ? (float)(w - 1) / (float)(rw - 1) : 0.f;
+  const long long total = (long long)n * oh * ow * (C / 4);
+  if (in_f32)
+    resize_ac_kernel<float><<<blocks_for(total, 256), 256, 0, s>>>(in_f32, n, h, w, C, sy, sx, oh, ow, out_f32, out_bf16);
+  else
+    resize_ac_kernel<__nv_bfloat16><<<blocks_for(total, 256), 256, 0, s>>>(in_bf16, n, h, w, C, sy, sx, oh, ow, out_f32, out_bf16);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_refine(const RefineParams& p, cudaStream_t s) {
+  dim3 grid((p.W + 31) / 32, (p.H + 3) / 4, p.B);
+  refine_kernel<<<grid, 128, 0, s>>>(p);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_nhwc_to_nchw(const float* in, float* out, int n, int H, int W, int C, cudaStream_t s) {
+  const long long total = (long long)n * H * W * C;
+  nhwc_to_nchw_kernel<<<blocks_for(total, 256), 256, 0, s>>>(in, out, n, H, W, C);
+  return cudaGetLastError();
+}
+
+}  // namespace ufm

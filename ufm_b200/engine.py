@@ -1,0 +1,92 @@
+"""Python handle on one ``ufm_engine`` (one per GPU): weights in, device pointers in/out.  PyTorch is used only
+for device memory and streams; every kernel on the path is in ``libufm_b200.so``."""
+from __future__ import annotations
+
+import ctypes as C
+from typing import Any, Dict, Optional, Tuple
+
+import torch
+
+from . import _lib
+from .packing import engine_config, pack_weights
+
+_DT = {torch.float32: _lib.UFM_F32, torch.bfloat16: _lib.UFM_BF16, torch.uint8: _lib.UFM_U8}
+_TD = {_lib.UFM_F32: torch.float32, _lib.UFM_BF16: torch.bfloat16}
+
+
+class UfmEngineError(RuntimeError):
+    pass
+
+
+class Engine:
+    def __init__(self, cfg: Dict[str, Any], state_dict: Dict[str, torch.Tensor], device: torch.device, max_pairs: int = 16):
+        self.lib = _lib.load()
+        if not torch.cuda.is_available():
+            raise UfmEngineError("ufm_b200 needs a B200 (sm_100) GPU: there is no CPU fallback")
+        self.device = torch.device(device)
+        if self.device.type != "cuda":
+            raise UfmEngineError(f"engine device must be CUDA, got {self.device}")
+        self.index = self.device.index if self.device.index is not None else torch.cuda.current_device()
+        self.cfg = cfg
+        self.ec = engine_config(cfg)
+        self.H, self.W = self.ec.img_h, self.ec.img_w
+        self.max_pairs = max_pairs
+        h = C.c_void_p()
+        rc = self.lib.ufm_create(C.byref(self.ec), self.index, C.byref(h))
+        if rc != 0:
+            raise UfmEngineError(f"ufm_create failed with status {rc} (no sm_100 device?)")
+        self.h = h
+        for name, t in pack_weights(cfg, state_dict).items():
+            shape = (C.c_int64 * t.dim())(*t.shape)
+            self._ck(self.lib.ufm_set_weight(self.h, name.encode(), t.data_ptr(), _DT[t.dtype], shape, t.dim()))
+        self._ck(self.lib.ufm_prepare(self.h, max_pairs))
+
+    def _ck(self, rc):
+        if rc != 0:
+            raise UfmEngineError(self.lib.ufm_last_error(self.h).decode())
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.lib.ufm_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def set_keep_aux(self, keep: bool):
+        self._ck(self.lib.ufm_set_keep_aux(self.h, int(keep)))
+
+    def forward(self, src: torch.Tensor, tgt: torch.Tensor, layout: int) -> Tuple[torch.Tensor, Optional[torch.Tensor]]:
+        """src/tgt: CUDA tensors [B,H,W,3] (NHWC) or [B,3,H,W] (NCHW), uint8 or normalised float32, B <= max_pairs.
+        Returns (flow [B,2,H,W] fp32, covisibility [B,H,W] fp32 or None), asynchronous on the current stream."""
+        assert src.is_cuda and tgt.is_cuda and src.is_contiguous() and tgt.is_contiguous()
+        assert src.dtype == tgt.dtype and src.shape == tgt.shape
+        B = src.shape[0]
+        flow = torch.empty(B, 2, self.H, self.W, dtype=torch.float32, device=src.device)
+        cov = torch.empty(B, self.H, self.W, dtype=torch.float32, device=src.device) if self.ec.unc_out_ch else None
+        stream = torch.cuda.current_stream(src.device).cuda_stream
+        self._ck(self.lib.ufm_forward(self.h, src.data_ptr(), tgt.data_ptr(), B, _DT[src.dtype], layout,
+                                      flow.data_ptr(), cov.data_ptr() if cov is not None else None, stream))
+        return flow, cov
+
+    def forward_host(self, src: torch.Tensor, tgt: torch.Tensor, layout: int, flow: torch.Tensor,
+                     cov: Optional[torch.Tensor]):
+        """Host tensors in (ideally pinned), host tensors out; H2D + forward + D2H + sync inside the C call."""
+        assert not src.is_cuda and not flow.is_cuda
+        self._ck(self.lib.ufm_forward_host(self.h, src.data_ptr(), tgt.data_ptr(), src.shape[0], _DT[src.dtype], layout,
+                                           flow.data_ptr(), cov.data_ptr() if cov is not None else None))
+
+    def launch_count(self) -> int:
+        return self.lib.ufm_last_launch_count(self.h)
+
+    def stage(self, name: str) -> torch.Tensor:
+        """Copy of an internal stage buffer of the last forward, in the engine's own layout."""
+        dt, nd = C.c_int(), C.c_int()
+        shape = (C.c_int64 * 8)()
+        self._ck(self.lib.ufm_stage_desc(self.h, name.encode(), C.byref(dt), shape, C.byref(nd)))
+        t = torch.empty(tuple(shape[i] for i in range(nd.value)), dtype=_TD[dt.value], device=self.device)
+        self._ck(self.lib.ufm_stage_copy(self.h, name.encode(), t.data_ptr(), t.numel() * t.element_size()))
+        return t

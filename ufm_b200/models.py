@@ -1,0 +1,225 @@
+"""Drop-in model classes: same names, constructor kwargs, ``state_dict`` keys and
+``predict_correspondences_batched`` contract as the reference (uniflowmatch/models/base.py:85-334,
+uniflowmatch/models/ufm.py:120-1009), with the forward pass executed by the sm_100a engine.
+"""
+from __future__ import annotations
+
+from dataclasses import dataclass
+from typing import Any, Dict, Optional
+
+import torch
+import torch.nn as nn
+
+from . import _lib, prepost
+from .engine import Engine
+from .packing import inference_hw
+from .weights import make_state_dict, model_spec
+
+
+# ---- output dataclasses (base.py:11-73) ------------------------------------------------------------------------------
+@dataclass
+class UFMFlowFieldOutput:
+    flow_output: torch.Tensor
+    flow_covariance: Optional[torch.Tensor] = None
+    flow_covariance_inv: Optional[torch.Tensor] = None
+    flow_covariance_log_det: Optional[torch.Tensor] = None
+
+
+@dataclass
+class UFMMaskFieldOutput:
+    mask: torch.Tensor
+    logits: Optional[torch.Tensor]
+
+
+@dataclass
+class UFMClassificationRefinementOutput:
+    regression_flow_output: torch.Tensor
+    residual: torch.Tensor
+    log_softmax: torch.Tensor
+    feature_map_0: torch.Tensor
+    feature_map_1: torch.Tensor
+
+
+@dataclass
+class UFMOutputInterface:
+    flow: Optional[UFMFlowFieldOutput] = None
+    classification_refinement: Optional[UFMClassificationRefinementOutput] = None
+    covisibility: Optional[UFMMaskFieldOutput] = None
+
+
+class _EncoderShim:
+    def __init__(self, data_norm_type):
+        self.data_norm_type = data_norm_type
+
+
+class UniFlowMatchModelsBase(nn.Module):
+    """Holds the reference-named tensors as buffers (inference only) and owns one engine per CUDA device."""
+
+    _refine = False
+
+    def __init__(self, max_pairs_per_call: int = 16, seed: int = 0, **cfg):
+        super().__init__()
+        cfg.pop("pretrained_checkpoint_path", None)
+        cfg.pop("pretrained_backbone_checkpoint_path", None)
+        if cfg.get("info_sharing_and_head_structure", "dual+single") != "dual+single":
+            raise AssertionError("Only dual+single is supported now")  # ufm.py:180
+        if self._refine and "classification_head_kwargs" not in cfg:
+            raise ValueError("UniFlowMatchClassificationRefinement needs classification_head_kwargs")
+        if not self._refine:
+            for k in ("classification_head_kwargs", "temperature", "refinement_range", "use_unet_feature",
+                      "classification_head_type", "feature_combine_method"):
+                cfg.pop(k, None)
+        self.config = cfg
+        self.max_pairs_per_call = max_pairs_per_call
+        self.inference_resolution = cfg.get("inference_resolution") or [560, 420]
+        self.encoder = _EncoderShim(cfg["encoder_kwargs"].get("data_norm_type", "dinov2"))
+        self._names = {}
+        for key, t in make_state_dict(cfg, seed=seed).items():
+            safe = key.replace(".", "__")
+            self._names[safe] = key
+            self.register_buffer(safe, t)
+        self._engines: Dict[Any, Engine] = {}
+
+    # reference key names in/out -------------------------------------------------------------------------------------
+    def state_dict(self, *a, **k):
+        return {self._names[n]: t for n, t in self.named_buffers(remove_duplicate=False) if n in self._names}
+
+    def load_state_dict(self, sd, strict: bool = True):
+        want = set(self._names.values())
+        missing = sorted(want - set(sd))
+        unexpected = sorted(set(sd) - want)
+        if strict and (missing or unexpected):
+            raise RuntimeError(f"load_state_dict: missing {missing[:5]}, unexpected {unexpected[:5]}")
+        for safe, key in self._names.items():
+            if key in sd:
+                getattr(self, safe).copy_(sd[key])
+        for e in self._engines.values():
+            e.close()
+        self._engines = {}
+        return torch.nn.modules.module._IncompatibleKeys(missing, unexpected)
+
+    def _engine(self, device) -> Engine:
+        device = torch.device(device)
+        key = (device.type, device.index if device.index is not None else torch.cuda.current_device())
+        if key not in self._engines:
+            self._engines[key] = Engine(self.config, self.state_dict(), device, self.max_pairs_per_call)
+        return self._engines[key]
+
+    def _device(self):
+        return next(self.buffers()).device
+
+    # forward (ufm.py:562 / 843) ---------------------------------------------------------------------------------------
+    def _run(self, img0: torch.Tensor, img1: torch.Tensor, layout: int, keep_aux: bool = False):
+        """img0/img1 at the inference resolution, uint8 or normalised fp32, on CUDA."""
+        if img0.shape != img1.shape:
+            raise NotImplementedError("Unequal Image sizes are not supported now")  # ufm.py:316-317
+        eng = self._engine(img0.device)
+        H, W = eng.H, eng.W
+        hw = img0.shape[1:3] if layout == _lib.UFM_NHWC else img0.shape[2:4]
+        assert tuple(hw) == (H, W), f"engine prepared for {(H, W)}, got {tuple(hw)}"
+        eng.set_keep_aux(keep_aux)
+        flows, covs, aux = [], [], []
+        B = img0.shape[0]
+        for s in range(0, B, self.max_pairs_per_call):
+            a = img0[s:s + self.max_pairs_per_call].contiguous()
+            b = img1[s:s + self.max_pairs_per_call].contiguous()
+            f, c = eng.forward(a, b, layout)
+            flows.append(f)
+            covs.append(c)
+            if keep_aux and self._refine:
+                aux.append({k: eng.stage(k) for k in ("flow_reg", "residual", "log_softmax", "desc")})
+        flow = flows[0] if len(flows) == 1 else torch.cat(flows)
+        cov = None if covs[0] is None else (covs[0] if len(covs) == 1 else torch.cat(covs))
+        return flow, cov, aux
+
+    def forward(self, view1, view2) -> UFMOutputInterface:
+        img1, img2 = view1["img"], view2["img"]
+        assert view1.get("data_norm_type", self.encoder.data_norm_type) == self.encoder.data_norm_type
+        assert img1.dim() == 4 and img1.shape[1] == 3, "Input must be of shape (B, C, H, W)"
+        flow, cov, aux = self._run(img1.float().contiguous(), img2.float().contiguous(), _lib.UFM_NCHW,
+                                   keep_aux=self._refine)
+        res = UFMOutputInterface(flow=UFMFlowFieldOutput(flow_output=flow))
+        if cov is not None:
+            res.covisibility = UFMMaskFieldOutput(mask=cov.unsqueeze(1), logits=None)
+        if self._refine and aux:
+            cat = lambda k: torch.cat([a[k] for a in aux])
+            desc = cat("desc")  # (B, 2, H, W, C)
+            P = int(self.config.get("refinement_range", 5))
+            res.classification_refinement = UFMClassificationRefinementOutput(
+                regression_flow_output=flow, residual=cat("residual"),
+                log_softmax=cat("log_softmax").reshape(flow.shape[0], flow.shape[2], flow.shape[3], P, P),
+                feature_map_0=desc[:, 0].permute(0, 3, 1, 2), feature_map_1=desc[:, 1].permute(0, 3, 1, 2))
+        return res
+
+    # API shell (base.py:137-334) --------------------------------------------------------------------------------------
+    def predict_correspondences_batched(self, source_image: torch.Tensor, target_image: torch.Tensor,
+                                        data_norm_type: Optional[str] = None) -> UFMOutputInterface:
+        assert isinstance(source_image, torch.Tensor) and isinstance(target_image, torch.Tensor), \
+            "source_image and target_image must be torch.Tensors"
+        assert source_image.dim() in [3, 4], "source_image must have dimensions 3 or 4"
+        assert target_image.dim() in [3, 4], "target_image must have dimensions 3 or 4"
+        if source_image.dim() == 3:
+            source_image, target_image = source_image.unsqueeze(0), target_image.unsqueeze(0)
+        if source_image.shape[1] == 3 and target_image.shape[1] == 3:
+            layout = _lib.UFM_NCHW
+        elif source_image.shape[-1] == 3 and target_image.shape[-1] == 3:
+            layout = _lib.UFM_NHWC
+        else:
+            raise ValueError("source_image and target_image must have 3 channels in either BCHW or BHWC format")
+        required = self.encoder.data_norm_type
+        if source_image.dtype == torch.float32:
+            assert data_norm_type is not None, "data_norm_type must be provided for float32 images"
+            assert data_norm_type in prepost.IMAGE_NORMALIZATION, \
+                f"data_norm_type must be one of {list(prepost.IMAGE_NORMALIZATION.keys())}"
+        elif source_image.dtype != torch.uint8:
+            raise ValueError("source_image and target_image must be of type torch.float32 or torch.uint8")
+        in_device = source_image.device
+        dev = self._device()
+        if dev.type != "cuda":
+            raise RuntimeError("ufm_b200 models run on CUDA only: call .to('cuda') (there is no CPU fallback)")
+        src = source_image.to(dev, non_blocking=True)
+        tgt = target_image.to(dev, non_blocking=True)
+        H, W = inference_hw(self.config) if isinstance(self.inference_resolution[0], int) else (None, None)
+        hw0 = tuple(src.shape[1:3] if layout == _lib.UFM_NHWC else src.shape[2:4])
+        hw1 = tuple(tgt.shape[1:3] if layout == _lib.UFM_NHWC else tgt.shape[2:4])
+        native = hw0 == (H, W) and hw1 == (H, W)
+        renorm = src.dtype == torch.float32 and data_norm_type != required
+        if native and not renorm:
+            # the engine reads the images as they are (u8 normalisation is fused into the patch gather);
+            # the reference's un-map at native size is the identity up to (flow + c) - c rounding
+            flow, cov, _ = self._run(src.contiguous(), tgt.contiguous(), layout)
+        else:
+            if layout == _lib.UFM_NHWC:
+                src, tgt = src.permute(0, 3, 1, 2), tgt.permute(0, 3, 1, 2)
+            mean, std = prepost.norm_tensors(required, dev)
+            if src.dtype == torch.uint8:
+                src = (src.float() / 255.0 - mean) / std
+                tgt = (tgt.float() / 255.0 - mean) / std
+            elif renorm:
+                pm, ps = prepost.norm_tensors(data_norm_type, dev)
+                src = src * (ps / std) + (pm - mean) / std
+                tgt = tgt * (ps / std) + (pm - mean) / std
+            res = self.inference_resolution
+            res = [res] if isinstance(res[0], int) else res
+            th, tw = prepost.closest_aspect(res, hw0[0], hw0[1], hw1[0], hw1[1])
+            s0 = prepost.resize_to_fixed(src, th, tw).contiguous()
+            s1 = prepost.resize_to_fixed(tgt, th, tw).contiguous()
+            f, c, _ = self._run(s0, s1, _lib.UFM_NCHW)
+            rep0 = prepost.scaled_region(th, tw, hw0[0], hw0[1])
+            src0, src1 = [0, hw0[0], 0, hw0[1]], [0, hw1[0], 0, hw1[1]]
+            flow = prepost.unmap_flow(f, rep0, src0, src1, hw0)
+            cov = prepost.unmap_channels(c.unsqueeze(1), rep0, src0, hw0).squeeze(1) if c is not None else None
+        out = UFMOutputInterface(flow=UFMFlowFieldOutput(flow_output=flow.to(in_device)))
+        if cov is not None:
+            out.covisibility = UFMMaskFieldOutput(mask=cov.to(in_device), logits=None)
+        return out
+
+
+class UniFlowMatchConfidence(UniFlowMatchModelsBase):
+    """Engine-backed ``UniFlowMatchConfidence`` (ufm.py:474-708): flow head + uncertainty (covisibility) head."""
+    _refine = False
+
+
+class UniFlowMatchClassificationRefinement(UniFlowMatchModelsBase):
+    """Engine-backed ``UniFlowMatchClassificationRefinement`` (ufm.py:710-1178)."""
+    _refine = True

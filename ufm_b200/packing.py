@@ -1,0 +1,253 @@
+"""Host-side weight packing: reference ``state_dict`` (SURVEY.md 8b key names) -> engine packed tensors.
+
+One-time layout work at model load, not on the hot path: bf16 casts, conv weights to tap-major K layout with the
+input channels padded to 64, the 1x1 -> ConvTranspose(k == stride) pairs of the DPT input stages folded into one
+GEMM (``dpt.py:107-145``), the classification 1x1 conv rows permuted so the GEMM output is pixel-shuffle ordered
+(``mlp_feature.py:62-70,99``), and the DINOv2 positional embedding interpolated for the inference resolution
+(hub ``interpolate_pos_encoding``).
+"""
+from __future__ import annotations
+
+import math
+from typing import Any, Dict, Tuple
+
+import torch
+import torch.nn.functional as F
+
+from . import _lib
+from .configs import DINOV2_ARCH
+
+PATCH_KPAD = 64
+
+
+def _norm_indices(indices, depth):
+    if isinstance(indices, int):
+        return list(range(depth - indices, depth))
+    return [depth + i if i < 0 else i for i in indices]
+
+
+def inference_hw(cfg) -> Tuple[int, int]:
+    res = cfg.get("inference_resolution") or [560, 420]
+    if not isinstance(res[0], int):
+        if len(res) != 1:
+            raise NotImplementedError("the engine is prepared for one inference resolution per model instance")
+        res = res[0]
+    return int(res[1]), int(res[0])  # (H, W)
+
+
+def flow_affine(cfg, H, W):
+    a = cfg["adaptors_kwargs"]
+    if list(a.keys()) != ["flow"] or a["flow"]["class"] != "FlowAdaptor":
+        raise NotImplementedError("engine flow head supports a single FlowAdaptor named 'flow' (ufm.py:645)")
+    kw = a["flow"]["kwargs"]
+    if kw.get("output_normalized_coordinate", False):
+        raise NotImplementedError("FlowAdaptor.output_normalized_coordinate is not built into the tail epilogue")
+    bh, bw = kw["base_shape"]
+    sx, sy = {"none": (1.0, 1.0), "scale_width": (W / bw, W / bw), "scale_height": (H / bh, H / bh),
+              "scale_both": (W / bw, H / bh)}[kw.get("scale_strategy", "none")]
+    std, mean = kw["flow_std"], kw["flow_mean"]
+    return (std[0] * sx, std[1] * sy), (mean[0] * sx, mean[1] * sy)
+
+
+def engine_config(cfg: Dict[str, Any]) -> "_lib.UfmConfig":
+    H, W = inference_hw(cfg)
+    ek, ik = cfg["encoder_kwargs"], cfg["info_sharing_kwargs"]
+    if cfg.get("encoder_str", "dinov2") != "dinov2" or ek.get("with_registers"):
+        raise NotImplementedError("engine encoder is DINOv2 ViT-S/B/L without registers")
+    if cfg["info_sharing_str"] not in ("global_attention", "alternating_attention"):
+        raise NotImplementedError(f"info_sharing_str={cfg['info_sharing_str']} (SURVEY.md 8f N2)")
+    if ik.get("custom_positional_encoding") is not None:
+        raise NotImplementedError("custom_positional_encoding='rope' is not built yet")
+    if ik.get("use_rand_idx_pe_for_non_reference_views") and cfg["info_sharing_str"] == "global_attention":
+        raise NotImplementedError("use_rand_idx_pe_for_non_reference_views draws from the global RNG (SURVEY.md H7)")
+    if cfg.get("head_type", "dpt") != "dpt":
+        raise NotImplementedError("head_type must be 'dpt'")
+    if cfg.get("use_unet_feature"):
+        raise NotImplementedError("use_unet_feature (SURVEY.md 8f N3)")
+    dim, depth, heads = DINOV2_ARCH[ek["size"]]
+    if ek.get("keep_first_n_layers") is not None:
+        depth = min(depth, ek["keep_first_n_layers"])
+    take = _norm_indices(ek["indices"], depth)
+    c = _lib.UfmConfig()
+    c.img_h, c.img_w, c.patch = H, W, ek.get("patch_size", 14)
+    c.enc_dim, c.enc_heads = dim, heads
+    c.enc_take_first, c.enc_take_last = take[0], take[-1]
+    c.enc_depth = take[-1] + 1  # blocks after the last returned index do not influence any output
+    c.info_dim, c.info_depth, c.info_heads = ik["dim"], ik["depth"], ik["num_heads"]
+    c.info_hidden = int(ik["dim"] * ik.get("mlp_ratio", 4.0))
+    it = _norm_indices(ik["indices"], ik["depth"])
+    if len(it) < 2:
+        raise ValueError("info_sharing indices must name at least two layers (ufm.py:605-606)")
+    c.info_take0, c.info_take1 = it[0], it[1]
+    c.info_alternating = int(cfg["info_sharing_str"] == "alternating_attention")
+    c.info_qk_norm = int(bool(ik.get("qk_norm")))
+    c.info_layerscale = int(bool(ik.get("init_values")))
+    c.info_has_proj = 1
+    f = cfg["feature_head_kwargs"]["dpt_feature"]
+    pr = cfg["feature_head_kwargs"]["dpt_processor"]
+    if f.get("use_bn") or list(f.get("hooks", [0, 1, 2, 3])) != [0, 1, 2, 3]:
+        raise NotImplementedError("DPT use_bn / hooks != [0,1,2,3]")
+    for i in range(4):
+        c.dpt_layer_dims[i] = f["layer_dims"][i]
+    c.dpt_feature_dim = f["feature_dim"]
+    hd = pr.get("hidden_dims") or [pr["input_feature_dim"] // 2] * 2
+    if hd[0] != hd[1]:
+        raise NotImplementedError("DPT processor hidden dims must match")
+    c.dpt_hidden = hd[0]
+    c.flow_out_ch = pr["output_dim"]
+    (s0, s1), (b0, b1) = flow_affine(cfg, H, W)
+    c.flow_scale[0], c.flow_scale[1], c.flow_shift[0], c.flow_shift[1] = s0, s1, b0, b1
+    c.unc_out_ch = 0
+    if cfg.get("uncertainty_head_kwargs"):
+        ua = cfg.get("uncertainty_adaptors_kwargs", {})
+        if list(ua.keys()) != ["non_occluded_mask"] or ua["non_occluded_mask"]["class"] != "MaskAdaptor":
+            raise NotImplementedError("uncertainty head supports the 'non_occluded_mask' MaskAdaptor (SURVEY.md 8f N3)")
+        c.unc_out_ch = 1
+    c.refine = int("classification_head_kwargs" in cfg)
+    if c.refine:
+        ck = cfg["classification_head_kwargs"]
+        c.cls_in = ck["input_feature_dim"]
+        c.cls_hidden = int(ck.get("mlp_ratio", 4) * ck["input_feature_dim"])
+        c.cls_out, c.cls_patch = ck["output_dim"], ck["patch_size"]
+        c.refine_P = cfg.get("refinement_range", 5)
+        c.temperature = float(cfg.get("temperature", 4))
+    return c
+
+
+def interpolate_pos_embed(pos_embed: torch.Tensor, h0: int, w0: int, offset: float = 0.1) -> torch.Tensor:
+    """Hub DINOv2 ``interpolate_pos_encoding``: bicubic, scale_factor=(n+0.1)/M, no antialias -> (1+h0*w0, D)."""
+    N = pos_embed.shape[1] - 1
+    M = int(math.sqrt(N))
+    D = pos_embed.shape[-1]
+    pe = pos_embed.float()
+    if h0 * w0 == N and h0 == w0:
+        return pe[0]
+    patch = pe[:, 1:].reshape(1, M, M, D).permute(0, 3, 1, 2)
+    patch = F.interpolate(patch, mode="bicubic", antialias=False,
+                          scale_factor=(float(h0 + offset) / M, float(w0 + offset) / M))
+    assert patch.shape[-2:] == (h0, w0)
+    return torch.cat([pe[0, :1], patch.permute(0, 2, 3, 1).reshape(-1, D)], dim=0)
+
+
+def _pad64(c):
+    return (c + 63) // 64 * 64
+
+
+def _conv3_pack(w: torch.Tensor) -> torch.Tensor:
+    """(Cout, Cin, 3, 3) -> bf16 (Cout, 9 * pad64(Cin)), K index = (ky*3+kx) * Cpad + ci."""
+    co, ci = w.shape[:2]
+    t = torch.zeros(co, 9, _pad64(ci), dtype=torch.float32)
+    t[:, :, :ci] = w.permute(0, 2, 3, 1).reshape(co, 9, ci)
+    return t.reshape(co, -1).to(torch.bfloat16)
+
+
+def _fold_convt(w1, b1, wt, bt):
+    """1x1 conv (m<-c) followed by ConvTranspose2d(k == stride) (o<-m): one GEMM with rows ordered (kh, kw, o)."""
+    w1 = w1.reshape(w1.shape[0], -1).double()
+    wt = wt.double()
+    k = wt.shape[-1]
+    wf = torch.einsum("mokl,mc->kloc", wt, w1).reshape(k * k * wt.shape[1], w1.shape[1])
+    bf = (torch.einsum("mokl,m->klo", wt, b1.double()) + bt.double()).reshape(-1)
+    return wf.float().to(torch.bfloat16), bf.float()
+
+
+def pack_weights(cfg: Dict[str, Any], sd: Dict[str, torch.Tensor]) -> Dict[str, torch.Tensor]:
+    """Returns {engine name: CPU tensor (fp32 or bf16, contiguous)}."""
+    sd = {k: v.detach().float().cpu() for k, v in sd.items()}
+    ec = engine_config(cfg)
+    out: Dict[str, torch.Tensor] = {}
+    bf = lambda t: t.to(torch.bfloat16)
+    hp, wp = ec.img_h // ec.patch, ec.img_w // ec.patch
+
+    p = "encoder.model."
+    D = ec.enc_dim
+    wpe = sd[p + "patch_embed.proj.weight"].reshape(D, -1)
+    kpad = (wpe.shape[1] + PATCH_KPAD - 1) // PATCH_KPAD * PATCH_KPAD
+    wpad = torch.zeros(D, kpad)
+    wpad[:, : wpe.shape[1]] = wpe
+    out["enc.patch.w"] = bf(wpad)
+    out["enc.patch.b"] = sd[p + "patch_embed.proj.bias"]
+    out["enc.pos"] = interpolate_pos_embed(sd[p + "pos_embed"], hp, wp)
+    out["enc.cls"] = sd[p + "cls_token"].reshape(-1)
+
+    def block(dst, src, layerscale, qk_norm):
+        out[dst + ".ln1.w"], out[dst + ".ln1.b"] = sd[src + "norm1.weight"], sd[src + "norm1.bias"]
+        out[dst + ".qkv.w"] = bf(sd[src + "attn.qkv.weight"])
+        if src + "attn.qkv.bias" in sd:
+            out[dst + ".qkv.b"] = sd[src + "attn.qkv.bias"]
+        if qk_norm:
+            out[dst + ".qn.w"], out[dst + ".qn.b"] = sd[src + "attn.q_norm.weight"], sd[src + "attn.q_norm.bias"]
+            out[dst + ".kn.w"], out[dst + ".kn.b"] = sd[src + "attn.k_norm.weight"], sd[src + "attn.k_norm.bias"]
+        out[dst + ".proj.w"], out[dst + ".proj.b"] = bf(sd[src + "attn.proj.weight"]), sd[src + "attn.proj.bias"]
+        out[dst + ".ln2.w"], out[dst + ".ln2.b"] = sd[src + "norm2.weight"], sd[src + "norm2.bias"]
+        out[dst + ".fc1.w"], out[dst + ".fc1.b"] = bf(sd[src + "mlp.fc1.weight"]), sd[src + "mlp.fc1.bias"]
+        out[dst + ".fc2.w"], out[dst + ".fc2.b"] = bf(sd[src + "mlp.fc2.weight"]), sd[src + "mlp.fc2.bias"]
+        if layerscale:
+            out[dst + ".ls1"], out[dst + ".ls2"] = sd[src + "ls1.gamma"], sd[src + "ls2.gamma"]
+
+    for i in range(ec.enc_depth):
+        block(f"enc.{i}", f"{p}blocks.{i}.", True, False)
+    out["enc.norm.w"], out["enc.norm.b"] = sd[p + "norm.weight"], sd[p + "norm.bias"]
+
+    p = "info_sharing."
+    d = ec.info_dim
+    if p + "proj_embed.weight" in sd:
+        out["info.proj.w"], out["info.proj.b"] = bf(sd[p + "proj_embed.weight"]), sd[p + "proj_embed.bias"]
+    else:  # nn.Identity (global_attention_transformer.py:104-107) as an exact identity GEMM
+        out["info.proj.w"], out["info.proj.b"] = bf(torch.eye(d)), torch.zeros(d)
+    tab = sd[p + "view_pos_table"]
+    vp = torch.zeros(2, d)
+    vp[0] = tab[0]
+    ik = cfg["info_sharing_kwargs"]
+    if not ec.info_alternating or ik.get("use_pe_for_non_reference_views", False):
+        if ec.info_alternating and ik.get("use_rand_idx_pe_for_non_reference_views", True):
+            raise NotImplementedError("random view indices (SURVEY.md H7)")
+        vp[1] = tab[1]
+    out["info.viewpos"] = vp
+    for i in range(ec.info_depth):
+        block(f"info.{i}", f"{p}self_attention_blocks.{i}.", bool(ec.info_layerscale), bool(ec.info_qk_norm))
+    out["info.norm.w"], out["info.norm.b"] = sd[p + "norm.weight"], sd[p + "norm.bias"]
+
+    def head(dst, src):
+        ip = src + "0.0.input_process."
+        out[dst + ".in0.w"], out[dst + ".in0.b"] = _fold_convt(sd[ip + "0.0.0.weight"], sd[ip + "0.0.0.bias"],
+                                                               sd[ip + "0.0.1.weight"], sd[ip + "0.0.1.bias"])
+        out[dst + ".in1.w"], out[dst + ".in1.b"] = _fold_convt(sd[ip + "1.0.0.weight"], sd[ip + "1.0.0.bias"],
+                                                               sd[ip + "1.0.1.weight"], sd[ip + "1.0.1.bias"])
+        out[dst + ".in2.w"] = bf(sd[ip + "2.0.0.weight"].reshape(sd[ip + "2.0.0.weight"].shape[0], -1))
+        out[dst + ".in2.b"] = sd[ip + "2.0.0.bias"]
+        out[dst + ".in3a.w"] = bf(sd[ip + "3.0.0.weight"].reshape(sd[ip + "3.0.0.weight"].shape[0], -1))
+        out[dst + ".in3a.b"] = sd[ip + "3.0.0.bias"]
+        w3 = sd[ip + "3.0.1.weight"]
+        out[dst + ".in3b.w"] = bf(w3.permute(0, 2, 3, 1).reshape(w3.shape[0], -1))
+        out[dst + ".in3b.b"] = sd[ip + "3.0.1.bias"]
+        sc = src + "0.0.scratch."
+        for k in range(4):
+            out[f"{dst}.rn{k}.w"] = _conv3_pack(sd[f"{sc}layer{k + 1}_rn.weight"])
+        for r in (1, 2, 3, 4):
+            q = f"{sc}refinenet{r}."
+            w = sd[q + "out_conv.weight"]
+            out[f"{dst}.ref{r}.out.w"], out[f"{dst}.ref{r}.out.b"] = bf(w.reshape(w.shape[0], -1)), sd[q + "out_conv.bias"]
+            for u in ((1, 2) if r != 4 else (2,)):
+                for cc in (1, 2):
+                    out[f"{dst}.ref{r}.rcu{u}.c{cc}.w"] = _conv3_pack(sd[f"{q}resConfUnit{u}.conv{cc}.weight"])
+                    out[f"{dst}.ref{r}.rcu{u}.c{cc}.b"] = sd[f"{q}resConfUnit{u}.conv{cc}.bias"]
+        q = src + "0.1."
+        out[dst + ".proc.c1.w"], out[dst + ".proc.c1.b"] = _conv3_pack(sd[q + "conv1.weight"]), sd[q + "conv1.bias"]
+        out[dst + ".proc.c2.w"], out[dst + ".proc.c2.b"] = _conv3_pack(sd[q + "conv2.0.weight"]), sd[q + "conv2.0.bias"]
+        w = sd[q + "conv2.2.weight"]
+        out[dst + ".proc.out.w"], out[dst + ".proc.out.b"] = w.reshape(w.shape[0], -1).contiguous(), sd[q + "conv2.2.bias"]
+
+    head("h1", "head1.")
+    if ec.unc_out_ch:
+        head("hu", "uncertainty_head.")
+    if ec.refine:
+        p = "classification_head."
+        out["cls.fc1.w"], out["cls.fc1.b"] = bf(sd[p + "mlp.fc1.weight"]), sd[p + "mlp.fc1.bias"]
+        out["cls.fc2.w"], out["cls.fc2.b"] = bf(sd[p + "mlp.fc2.weight"]), sd[p + "mlp.fc2.bias"]
+        P, od = ec.cls_patch, ec.cls_out
+        w = sd[p + "linear.weight"].reshape(od, P, P, -1).permute(1, 2, 0, 3).reshape(P * P * od, -1)
+        out["cls.lin.w"] = bf(w)
+        out["cls.lin.b"] = sd[p + "linear.bias"].reshape(od, P, P).permute(1, 2, 0).reshape(-1)
+        out["cls.bias"] = sd["classification_bias"]
+    return {k: v.contiguous() for k, v in out.items()}
