@@ -1,0 +1,362 @@
+#!/usr/bin/env python
+"""bench.py -- image pairs / second of the UFM dense-correspondence forward pass (BASELINE.json metric).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl engine|reference] [--workload base16|refine16|hires4]
+
+A "step" is one pass of the hot path over one batch of synthetic image pairs (random-init weights of the assumed
+UFM-Base architecture; iid uint8 images of the named shape):
+  * value  : device-timed (CUDA events), inputs already resident in HBM, max over ranks, whole-job pairs/s
+  * e2e    : the same metric through the public API `predict_correspondences_batched` with pinned HOST tensors in and
+             HOST tensors out (one `ufm_forward_host` C-ABI call per step: H2D + forward + D2H inside the timed region)
+  * roofline: the dominant kernel family (the tcgen05 GEMM / implicit-GEMM conv kernel), algorithmic FLOPs / summed
+             launch durations measured with CUDA events on the launching stream during the timed steps
+  * cpu_baseline: the CPU fp32 oracle (port of the reference path) timed on this box's host cores on a bounded sample
+`--impl reference` times that CPU path alone (the reference is pure Python + an un-vendored torch.hub model and cannot
+travel to the GPU box; the oracle restates it and is pinned against it by tests/golden).
+Multi-GPU: one process per GPU (torchrun), each rank runs its own batch (weak scaling, no data-path collective).
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import tempfile
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+METRIC = "image pairs/sec at 560x420 (UFM-Base)"
+UNIT = "pairs/s"
+
+WORKLOADS = {
+    # name: (config name, inference resolution (W, H), pairs per step, description)
+    "base16": ("ufm_base_assumed", (560, 420), 16, "UFM-Base batch 16 pairs 560x420 bf16 on 1xB200 (BASELINE.json configs[1])"),
+    "refine16": ("ufm_refine_assumed", (560, 420), 16, "UFM-Refine batch 16 pairs 560x420 (configs[2])"),
+    "hires4": ("ufm_base_assumed", (1120, 840), 4, "UFM-Base 1120x840 batch 4 (configs[3])"),
+}
+
+
+def algorithmic_tflop_per_pair(cfg, refine: bool) -> dict:
+    """SURVEY.md section 8(d) formulas: GEMM/layer = 2*M*D^2*(3+1+2r), attention/layer = 4*M*S*D, conv = 2*Cin*Cout*k^2*HW."""
+    from ufm_b200.packing import engine_config
+
+    ec = engine_config(cfg)
+    hp, wp = ec.img_h // ec.patch, ec.img_w // ec.patch
+    n = hp * wp
+    S = n + 1
+    D, d = ec.enc_dim, ec.info_dim
+    enc_gemm = ec.enc_depth * 2 * (2 * S) * D * D * 12 + 2 * (2 * n) * D * 3 * ec.patch ** 2
+    enc_attn = ec.enc_depth * 4 * (2 * S) * S * D
+    info_gemm = ec.info_depth * 2 * (2 * n) * d * (4 * d + 2 * ec.info_hidden) + 2 * (2 * n) * D * d
+    info_attn = 0
+    for i in range(ec.info_depth):
+        span = n if (ec.info_alternating and i % 2 == 1) else 2 * n
+        info_attn += 4 * (2 * n) * span * d
+    ld = list(ec.dpt_layer_dims)
+    fd, hid = ec.dpt_feature_dim, ec.dpt_hidden
+    h3, w3 = (hp - 1) // 2 + 1, (wp - 1) // 2 + 1
+
+    def head(out_ch):
+        f = 2 * n * (D * ld[0] + 16 * ld[0] * ld[0]) + 2 * 16 * n * 9 * ld[0] * fd
+        f += 2 * n * (d * ld[1] + 4 * ld[1] * ld[1]) + 2 * 4 * n * 9 * ld[1] * fd
+        f += 2 * n * d * ld[2] + 2 * n * 9 * ld[2] * fd
+        f += 2 * n * d * ld[3] + 2 * h3 * w3 * 9 * ld[3] * ld[3] + 2 * h3 * w3 * 9 * ld[3] * fd
+        rcu = lambda px: 2 * 2 * px * 9 * fd * fd
+        f += rcu(h3 * w3) + 2 * n * fd * fd                      # refinenet4: RCU2, 1x1 after x2 upsample (cropped)
+        f += 2 * rcu(n) + 2 * 4 * n * fd * fd                    # refinenet3
+        f += 2 * rcu(4 * n) + 2 * 16 * n * fd * fd               # refinenet2
+        f += 2 * rcu(16 * n) + 2 * 64 * n * fd * fd              # refinenet1
+        f += 2 * 64 * n * 9 * fd * hid                           # processor conv1 @ 8x
+        f += 2 * ec.img_h * ec.img_w * (9 * hid * hid + hid * out_ch)
+        return f
+
+    heads = head(ec.flow_out_ch) + (head(ec.unc_out_ch) if ec.unc_out_ch else 0)
+    cls = 0
+    if refine:
+        cls = 2 * (2 * n) * (2 * ec.cls_in * ec.cls_hidden + ec.cls_in * ec.cls_out * ec.cls_patch ** 2)
+    t = {"enc_gemm": enc_gemm, "enc_attn": enc_attn, "info_gemm": info_gemm, "info_attn": info_attn, "heads": heads,
+         "cls_head": cls}
+    t = {k: v / 1e12 for k, v in t.items()}
+    t["total"] = sum(t.values())
+    t["gemm_conv"] = t["enc_gemm"] + t["info_gemm"] + t["heads"] + t["cls_head"]
+    return t
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region (B200_PROFILING.md clocks line)."""
+
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index: int):
+        self.idx = gpu_index
+        self.f = tempfile.NamedTemporaryFile("w+", suffix=".csv", delete=False)
+        self.p = None
+
+    def start(self):
+        try:
+            self.p = subprocess.Popen(["nvidia-smi", "-i", str(self.idx), f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                       "-lms", "100"], stdout=self.f, stderr=subprocess.DEVNULL)
+        except Exception:
+            self.p = None
+
+    def stop(self) -> dict:
+        if self.p is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.p.terminate()
+        try:
+            self.p.wait(timeout=5)
+        except Exception:
+            self.p.kill()
+        self.f.flush()
+        self.f.seek(0)
+        sm, mx, pw, reasons = [], [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for line in self.f.read().splitlines():
+            c = [x.strip() for x in line.split(",")]
+            if len(c) < 9:
+                continue
+            try:
+                sm.append(float(c[1])); mx.append(float(c[2])); pw.append(float(c[3]))
+            except ValueError:
+                continue
+            for nm, v in zip(names, c[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(nm)
+        try:
+            os.unlink(self.f.name)
+        except OSError:
+            pass
+        if not sm:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["no samples"]}
+        return {"sm_mhz": statistics.median(sm), "sm_max_mhz": max(mx), "power_w_max": max(pw), "samples": len(sm),
+                "reasons": sorted(reasons)}
+
+
+def _peaks() -> dict:
+    """MEASURED_PEAKS.json (driver-written) else the fallback B200_PROFILING.md states."""
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        with open(p) as f:
+            d = json.load(f)
+        return {"bf16_burst": d.get("bf16_tflops", 1590.0), "bf16_sustained": d.get("bf16_tflops_sustained", 1400.0),
+                "hbm": d.get("hbm_gbs", 6650.0), "source": "measured"}
+    return {"bf16_burst": 1590.0, "bf16_sustained": 1400.0, "hbm": 6650.0, "source": "fallback"}
+
+
+def _make_cfg(workload: str):
+    from ufm_b200 import configs
+
+    name, res, pairs, desc = WORKLOADS[workload]
+    cfg = getattr(configs, name)(res)
+    return cfg, pairs, desc, name
+
+
+def cpu_reference_pairs_per_s(cfg, refine: bool, n_calls: int = 1, warmup: int = 0):
+    """The CPU fp32 path (oracle port of the reference forward) on this box's host cores: one pair per call.
+    Returns (pairs/s, threads, seconds per pair list)."""
+    import torch
+
+    from oracle import ufm_oracle as O
+    from oracle.golden_util import make_inputs
+    from ufm_b200.weights import make_state_dict
+
+    threads = len(os.sched_getaffinity(0))
+    torch.set_num_threads(threads)
+    sd = make_state_dict(cfg, seed=0)
+    W, H = cfg["inference_resolution"]
+    src, tgt = make_inputs(1, H, W, seed=1)
+    ts = []
+    with torch.no_grad():
+        for i in range(warmup + n_calls):
+            t0 = time.perf_counter()
+            O.predict_correspondences_batched(src, tgt, sd, cfg)
+            dt = time.perf_counter() - t0
+            if i >= warmup:
+                ts.append(dt)
+    return 1.0 / statistics.median(ts), threads, ts
+
+
+def run_reference(args):
+    """--impl reference: the reference's CPU fp32 path for the same metric/config.  The reference itself (pure Python +
+    un-vendored torch.hub DINOv2) cannot travel to the GPU box, so its oracle port is what is timed (kind = "port")."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return 0
+    cfg, pairs, desc, name = _make_cfg(args.workload)
+    refine = "classification_head_kwargs" in cfg
+    t0 = time.perf_counter()
+    v, threads, ts = cpu_reference_pairs_per_s(cfg, refine, n_calls=max(1, args.steps), warmup=min(args.warmup, 1))
+    sample = f"{len(ts)} timed call(s) of one 560x420 pair each (batch 1) of workload {args.workload}, fp32, {threads} threads"
+    line = {
+        "impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": len(ts),
+        "warmup": min(args.warmup, 1), "ms_per_step": 1e3 * statistics.median(ts), "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": desc, "pairs_per_step": 1, "resolution": cfg["inference_resolution"], "weights": "random-init seed 0"},
+        "cpu_baseline": {"value": v, "unit": UNIT, "cores": threads, "kind": "port", "sample": sample},
+        "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0, "wall_s": time.perf_counter() - t0,
+    }
+    print(json.dumps(line))
+    return 0
+
+
+def run_engine(args):
+    import torch
+    import torch.distributed as dist
+
+    import __graft_entry__ as g
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device (ufm_b200 has no CPU path; use --impl reference for the CPU baseline)")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    g.build()
+    from oracle.golden_util import make_inputs
+    from ufm_b200 import UniFlowMatchClassificationRefinement, UniFlowMatchConfidence, _lib
+    from ufm_b200.weights import make_state_dict
+
+    cfg, pairs, desc, name = _make_cfg(args.workload)
+    if args.pairs:
+        pairs = args.pairs
+    refine = "classification_head_kwargs" in cfg
+    W, H = cfg["inference_resolution"]
+    cls = UniFlowMatchClassificationRefinement if refine else UniFlowMatchConfidence
+    model = cls(max_pairs_per_call=pairs, **cfg)
+    model.load_state_dict(make_state_dict(cfg, seed=0))
+    model = model.to(dev)
+    src, tgt = make_inputs(pairs, H, W, seed=1 + rank)
+    dsrc, dtgt = src.to(dev), tgt.to(dev)
+    eng = model._engine(dev)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def maxreduce(x: float) -> float:
+        if world == 1:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return t.item()
+
+    # ---- value: device-timed, inputs resident in HBM -----------------------------------------------------------------
+    for _ in range(args.warmup):
+        eng.forward(dsrc, dtgt, _lib.UFM_NHWC)
+    sampler = ClockSampler(local)
+    barrier()
+    sampler.start()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(args.steps):
+        flow, cov = eng.forward(dsrc, dtgt, _lib.UFM_NHWC)
+    e1.record()
+    barrier()
+    clocks = sampler.stop()
+    launches = eng.launch_count() * args.steps
+    ms = maxreduce(e0.elapsed_time(e1))
+    ms_per_step = ms / args.steps
+    value = world * pairs * args.steps / (ms / 1e3)
+
+    # ---- e2e: public API, pinned host tensors in, host tensors out ---------------------------------------------------
+    hsrc, htgt = src.pin_memory(), tgt.pin_memory()
+    for _ in range(max(1, min(args.warmup, 2))):
+        model.predict_correspondences_batched(hsrc, htgt)
+    barrier()
+    t0 = time.perf_counter()
+    e0.record()
+    for _ in range(args.steps):
+        out = model.predict_correspondences_batched(hsrc, htgt)
+    e1.record()
+    barrier()
+    e2e_ms = maxreduce(max(e0.elapsed_time(e1), (time.perf_counter() - t0) * 1e3))
+    assert out.flow.flow_output.device.type == "cpu"
+    h2d = 2 * pairs * H * W * 3
+    d2h = pairs * H * W * 4 * (2 + (1 if out.covisibility is not None else 0))
+    e2e = {"value": world * pairs * args.steps / (e2e_ms / 1e3), "unit": UNIT, "h2d_bytes_per_step": h2d,
+           "d2h_bytes_per_step": d2h, "api": "predict_correspondences_batched(pinned host uint8 BHWC) -> host tensors"}
+
+    # ---- roofline: per-kernel-family durations (CUDA events around every launch, on the launching stream) ------------
+    eng.set_profile(True)
+    psteps = max(1, min(args.steps, 3))
+    for _ in range(psteps):
+        eng.forward(dsrc, dtgt, _lib.UFM_NHWC)
+    prof = eng.profile_read()
+    eng.set_profile(False)
+    peaks = _peaks()
+    fl = algorithmic_tflop_per_pair(cfg, refine)
+    fam = {}
+    tot_ms = sum(v["ms"] for v in prof.values())
+    for k, v in prof.items():
+        if not v["launches"]:
+            continue
+        d = {"ms_per_step": v["ms"] / psteps, "launches_per_step": v["launches"] // psteps, "share": v["ms"] / tot_ms}
+        if v["flops"] > 0:
+            d.update(bound="tensor", achieved=v["flops"] / (v["ms"] * 1e-3) / 1e12, peak=peaks["bf16_sustained"], unit="TFLOP/s")
+        else:
+            d.update(bound="hbm", achieved=v["bytes"] / (v["ms"] * 1e-3) / 1e9, peak=peaks["hbm"], unit="GB/s")
+        d["frac"] = d["achieved"] / d["peak"]
+        fam[k] = d
+    gm = {k: prof[k] for k in ("gemm", "conv3x3")}
+    g_ms = sum(v["ms"] for v in gm.values())
+    g_fl = sum(v["flops"] for v in gm.values())
+    g_n = sum(v["launches"] for v in gm.values())
+    roofline = {"kernel": "gemm_kernel<BN> (tcgen05 GEMM + implicit-GEMM 3x3 conv)", "bound": "tensor",
+                "achieved": g_fl / (g_ms * 1e-3) / 1e12, "peak": peaks["bf16_sustained"], "unit": "TFLOP/s",
+                "peak_source": f"{peaks['source']} bf16 sustained", "traffic": None,
+                "avg_launch_ms": g_ms / g_n, "flops_per_launch": g_fl / g_n, "share_of_step": g_ms / tot_ms}
+    roofline["frac"] = roofline["achieved"] / roofline["peak"]
+    whole = {"tflop_per_pair": fl["total"], "achieved_tflops_per_gpu": value / world * fl["total"],
+             "frac_of_bf16_sustained": value / world * fl["total"] / peaks["bf16_sustained"]}
+
+    line = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "bf16",
+        "data": "synthetic",
+        "config": {"workload": desc, "pairs_per_step_per_gpu": pairs, "resolution": [W, H], "weights": "random-init seed 0",
+                   "l2": "no flush needed: per-step working set (0.9 GB weights + >10 GB activations) exceeds the 126 MB L2",
+                   "parallelism": f"dp{world} (independent pairs, no data-path collective)"},
+        "e2e": e2e, "gpu_launches": launches, "clocks": clocks, "roofline": roofline, "kernel_families": fam,
+        "whole_pass": whole,
+    }
+    if rank == 0 and world == 1 and not args.no_cpu:
+        v, threads, ts = cpu_reference_pairs_per_s(cfg, refine, n_calls=args.cpu_calls, warmup=0)
+        line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": threads, "kind": "port",
+                                "sample": f"{len(ts)} call(s) of one 560x420 pair (batch 1) of the same model, CPU fp32 oracle"}
+    if rank == 0:
+        print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="engine", choices=["engine", "reference"])
+    ap.add_argument("--workload", default="base16", choices=list(WORKLOADS))
+    ap.add_argument("--pairs", type=int, default=0, help="override pairs per step per GPU")
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--cpu-calls", type=int, default=3)
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "engine" else args.warmup
+    return run_reference(args) if args.impl == "reference" else run_engine(args)
+
+
+if __name__ == "__main__":
+    sys.exit(main())

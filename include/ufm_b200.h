@@ -86,6 +86,22 @@ int ufm_stage_copy(ufm_engine* e, const char* name, void* dst, int64_t bytes);
 /* Number of kernels launched by the last ufm_forward call. */
 int ufm_last_launch_count(ufm_engine* e);
 
+/* Per-kernel-family device timing for bench.py's roofline (no reference counterpart; the reference's profiling aid is
+ * UC/models/encoders/utils.py:11-86).  While profiling is on, every launch is bracketed by CUDA events on the forward's
+ * stream; ufm_profile_read drains the stream and returns, per family, the summed kernel durations [ms], the algorithmic
+ * FLOPs (tensor-bound families) or algorithmic HBM bytes (bandwidth-bound families) and the launch count accumulated
+ * since the last read.  Arrays have UFM_NUM_CATS entries. */
+enum { UFM_CAT_GEMM = 0,   /* gemm_kernel, taps == 1: Linear / 1x1 conv / folded ConvT */
+       UFM_CAT_CONV = 1,   /* gemm_kernel, taps == 9: implicit-GEMM 3x3 conv */
+       UFM_CAT_ATTN = 2,   /* attn_kernel */
+       UFM_CAT_LN = 3,     /* layernorm_kernel, qk_norm_kernel */
+       UFM_CAT_RESIZE = 4, /* resize_ac_kernel */
+       UFM_CAT_MOVE = 5,   /* patch im2col, cls rows, pixel shuffles, stride-2 im2col */
+       UFM_CAT_REFINE = 6, /* refine_kernel */
+       UFM_NUM_CATS = 7 };
+int ufm_set_profile(ufm_engine* e, int on);
+int ufm_profile_read(ufm_engine* e, double* ms, double* flops, double* bytes, int64_t* launches);
+
 /* ---- kernel-level entry points (unit parity tests; device pointers, asynchronous on `stream`) ---- */
 
 /* out = epilogue(A (*) Wt): see ufm_b200/csrc/kernels.h GemmParams.  A is bf16 with logical extents (C, X, Y, Nimg) and

@@ -14,6 +14,7 @@ LIB_PATH = os.path.join(_HERE, "libufm_b200.so")
 UFM_F32, UFM_BF16, UFM_U8 = 0, 1, 2
 UFM_NCHW, UFM_NHWC = 0, 1
 GEMM_GELU, GEMM_RELU_BF16, GEMM_TAIL, GEMM_TAIL_SIGMOID = 1, 2, 4, 8
+PROFILE_CATS = ("gemm", "conv3x3", "attention", "layernorm", "resize", "move", "refine")
 
 
 class UfmConfig(C.Structure):
@@ -50,6 +51,8 @@ SYMBOLS = {
     "ufm_stage_desc": (_I, [_P, C.c_char_p, C.POINTER(_I), C.POINTER(_L), C.POINTER(_I)]),
     "ufm_stage_copy": (_I, [_P, C.c_char_p, _P, _L]),
     "ufm_last_launch_count": (_I, [_P]),
+    "ufm_set_profile": (_I, [_P, _I]),
+    "ufm_profile_read": (_I, [_P, C.POINTER(C.c_double), C.POINTER(C.c_double), C.POINTER(C.c_double), C.POINTER(_L)]),
     "ufm_op_gemm": (_I, [_P, _I, _I, _I, _I, _L, _L, _L, _I, _I, _P, _I, _I, _I, _P, _P, _P, _P, _L, _L, _L, _P, _P,
                          _L, _L, _L, _L, _U, _P, _P, _P, _P, _I, _P, _P, C.c_char_p, _I]),
     "ufm_op_attention": (_I, [_P, _I, _I, _I, _F, _P, _P, C.c_char_p, _I]),

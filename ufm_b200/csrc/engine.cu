@@ -163,6 +163,38 @@ struct ufm_engine {
   std::map<std::string, Tensor> stage;  // views of the last forward (not owned)
   cudaStream_t st = nullptr;
 
+  // ---- per-kernel-family timing (CUDA events on the launching stream; read by bench.py for the roofline) ----
+  bool profile = false;
+  struct ProfRec { int cat; double flops, bytes; cudaEvent_t a, b; };
+  std::vector<ProfRec> prof;
+  std::vector<cudaEvent_t> ev_pool;
+  size_t ev_used = 0;
+  double flops_override = -1.0;  // algorithmic FLOPs of the next GEMM launch when they differ from the executed ones
+  cudaEvent_t next_event() {
+    if (ev_used == ev_pool.size()) {
+      cudaEvent_t e;
+      cudaEventCreate(&e);
+      ev_pool.push_back(e);
+    }
+    return ev_pool[ev_used++];
+  }
+  template <class F>
+  bool run(int cat, double flops, double bytes, const char* what, F&& f) {
+    ++launches;
+    ProfRec r{cat, flops, bytes, nullptr, nullptr};
+    if (profile) {
+      r.a = next_event();
+      cudaEventRecord(r.a, st);
+    }
+    const cudaError_t e = f();
+    if (profile) {
+      r.b = next_event();
+      cudaEventRecord(r.b, st);
+      prof.push_back(r);
+    }
+    return ck(e, what);
+  }
+
   int fail(const char* fmt, ...) {
     char tmp[1024];
     va_list ap;
@@ -226,8 +258,11 @@ struct ufm_engine {
       fail("gemm %s: %s", wname.c_str(), eb);
       return false;
     }
-    ++launches;
-    return ck(launch_gemm(gp, BN, num_sms, st), ("launch gemm " + wname).c_str());
+    double fl = 2.0 * a.N * a.X * a.Y * (double)n_out * taps * a.C;
+    if (flops_override >= 0) fl = flops_override;
+    flops_override = -1.0;
+    return run(taps == 9 ? UFM_CAT_CONV : UFM_CAT_GEMM, fl, 0.0, ("launch gemm " + wname).c_str(),
+               [&] { return launch_gemm(gp, BN, num_sms, st); });
   }
   bool attention(const void* qkv, int n_seq, int seq_len, int heads, void* out) {
     AttnParams ap;
@@ -236,8 +271,8 @@ struct ufm_engine {
       fail("attention: %s", eb);
       return false;
     }
-    ++launches;
-    return ck(launch_attention(ap, st), "launch attention");
+    return run(UFM_CAT_ATTN, 4.0 * n_seq * heads * (double)seq_len * seq_len * 64, 0.0, "launch attention",
+               [&] { return launch_attention(ap, st); });
   }
   bool layernorm(const float* x, int n_seq, int src_seq_len, int skip, int tokens, int D, const std::string& pre,
                  int remap_B, bf16* ob, long long ob_pitch, long long ob_col, float* of = nullptr, long long of_pitch = 0,
@@ -249,8 +284,9 @@ struct ufm_engine {
     p.n_seq = n_seq; p.src_seq_len = src_seq_len; p.src_skip = skip; p.tokens = tokens; p.remap_B = remap_B;
     p.out_bf16 = ob; p.ob_pitch = ob_pitch; p.ob_col = ob_col;
     p.out_f32 = of; p.of_pitch = of_pitch; p.of_col = of_col;
-    ++launches;
-    return ck(launch_layernorm(p, st), ("layernorm " + pre).c_str());
+    const double rows = (double)n_seq * tokens;
+    return run(UFM_CAT_LN, 0.0, rows * D * (4 + (ob ? 2 : 0) + (of ? 4 : 0)), ("layernorm " + pre).c_str(),
+               [&] { return launch_layernorm(p, st); });
   }
 
   // One pre-LN transformer block over x [n_rows, D] (fp32 residual stream), attention over n_seq sequences of seq_len.
@@ -268,9 +304,10 @@ struct ufm_engine {
       if (!gemm(rows_view(xn, M, D), pre + ".qkv.w", 1, e)) return false;
     }
     if (qk_norm) {
-      ++launches;
-      if (!ck(launch_qk_norm(qkv, M, heads, Wf(pre + ".qn.w"), Wf(pre + ".qn.b"), Wf(pre + ".kn.w"), Wf(pre + ".kn.b"),
-                             1e-6f, st), "qk_norm"))
+      if (!run(UFM_CAT_LN, 0.0, (double)M * heads * 64 * 2 * 4, "qk_norm", [&] {
+            return launch_qk_norm(qkv, M, heads, Wf(pre + ".qn.w"), Wf(pre + ".qn.b"), Wf(pre + ".kn.w"),
+                                  Wf(pre + ".kn.b"), 1e-6f, st);
+          }))
         return false;
     }
     if (!attention(qkv, n_seq, seq_len, heads, att)) return false;
@@ -344,18 +381,22 @@ bool ufm_engine::dpt_head(const std::string& hp, int Bp, int out_ch, bool sigmoi
   {
     Epi e;
     e.bias = Wf(hp + ".in0.b"); e.out_bf16 = G; e.sx = 16LL * ld[0]; e.sn = (long long)n * e.sx;
+    flops_override = 2.0 * Bp * n * ((double)D * ld[0] + 16.0 * ld[0] * ld[0]);  // reference: 1x1 then ConvT 4x4/s4
     if (!gemm(tok_view(F0, D), hp + ".in0.w", 1, e)) return false;
-    ++launches;
-    if (!ck(launch_shuffle_bf16(G, T0, Bp, hpn, wpn, 4, ld[0], st), "shuffle0")) return false;
+    if (!run(UFM_CAT_MOVE, 0.0, 4.0 * Bp * n * 16 * ld[0], "shuffle0",
+             [&] { return launch_shuffle_bf16(G, T0, Bp, hpn, wpn, 4, ld[0], st); }))
+      return false;
     if (!conv3(T0, Bp, LH[0], LW[0], ld[0], hp + ".rn0.w", nullptr, nullptr, nullptr, Lf[0], Lr[0], true)) return false;
   }
   // input_process.1: 1x1 + ConvT 2x2/s2 (dpt.py:127-145)
   {
     Epi e;
     e.bias = Wf(hp + ".in1.b"); e.out_bf16 = G; e.sx = 4LL * ld[1]; e.sn = (long long)n * e.sx;
+    flops_override = 2.0 * Bp * n * ((double)d * ld[1] + 4.0 * ld[1] * ld[1]);  // reference: 1x1 then ConvT 2x2/s2
     if (!gemm(tok_view(F1, d), hp + ".in1.w", 1, e)) return false;
-    ++launches;
-    if (!ck(launch_shuffle_bf16(G, T1, Bp, hpn, wpn, 2, ld[1], st), "shuffle1")) return false;
+    if (!run(UFM_CAT_MOVE, 0.0, 4.0 * Bp * n * 4 * ld[1], "shuffle1",
+             [&] { return launch_shuffle_bf16(G, T1, Bp, hpn, wpn, 2, ld[1], st); }))
+      return false;
     if (!conv3(T1, Bp, LH[1], LW[1], ld[1], hp + ".rn1.w", nullptr, nullptr, nullptr, Lf[1], Lr[1], true)) return false;
   }
   // input_process.2: 1x1 (dpt.py:147-155)
@@ -370,8 +411,9 @@ bool ufm_engine::dpt_head(const std::string& hp, int Bp, int out_ch, bool sigmoi
     Epi e;
     e.bias = Wf(hp + ".in3a.b"); e.out_bf16 = T3; e.sx = ld[3]; e.sn = (long long)n * e.sx;
     if (!gemm(tok_view(F3, d), hp + ".in3a.w", 1, e)) return false;
-    ++launches;
-    if (!ck(launch_im2col_s2(T3, T3c, Bp, hpn, wpn, ld[3], h3, w3, st), "im2col_s2")) return false;
+    if (!run(UFM_CAT_MOVE, 0.0, 2.0 * Bp * ld[3] * (n + 9.0 * h3 * w3), "im2col_s2",
+             [&] { return launch_im2col_s2(T3, T3c, Bp, hpn, wpn, ld[3], h3, w3, st); }))
+      return false;
     Epi e2;
     e2.bias = Wf(hp + ".in3b.b"); e2.out_bf16 = T3b; e2.sx = ld[3];
     if (!gemm(rows_view(T3c, (long long)Bp * h3 * w3, 9 * ld[3]), hp + ".in3b.w", 1, e2)) return false;
@@ -417,14 +459,12 @@ bool ufm_engine::dpt_head(const std::string& hp, int Bp, int out_ch, bool sigmoi
       oh = LH[2] < oh ? LH[2] : oh;
       ow = LW[2] < ow ? LW[2] : ow;
     }
-    ++launches;
-    if (r > 1) {
-      if (!ck(launch_resize_ac(low, nullptr, Bp, H, Wd, fd, 2 * H, 2 * Wd, oh, ow, path, nullptr, st), "upsample"))
-        return false;
-    } else {
-      if (!ck(launch_resize_ac(low, nullptr, Bp, H, Wd, fd, 2 * H, 2 * Wd, oh, ow, nullptr, dpt_out, st), "upsample"))
-        return false;
-    }
+    const double up_bytes = (double)Bp * fd * (4.0 * H * Wd + (r > 1 ? 4.0 : 2.0) * oh * ow);
+    if (!run(UFM_CAT_RESIZE, 0.0, up_bytes, "upsample", [&] {
+          return launch_resize_ac(low, nullptr, Bp, H, Wd, fd, 2 * H, 2 * Wd, oh, ow, r > 1 ? path : nullptr,
+                                  r > 1 ? nullptr : dpt_out, st);
+        }))
+      return false;
   }
   // processor (dpt.py:285-311): conv3x3 fd->hid @8x, bilinear to the image, conv3x3 + ReLU + 1x1 + adaptor (tail epilogue)
   const int H8 = 8 * hpn, W8 = 8 * wpn;
@@ -432,8 +472,9 @@ bool ufm_engine::dpt_head(const std::string& hp, int Bp, int out_ch, bool sigmoi
   bf16* rs = B<bf16>("rs");
   if (!conv3(dpt_out, Bp, H8, W8, fd, hp + ".proc.c1.w", Wf(hp + ".proc.c1.b"), nullptr, nullptr, nullptr, c1, false))
     return false;
-  ++launches;
-  if (!ck(launch_resize_ac(nullptr, c1, Bp, H8, W8, hid, c.img_h, c.img_w, c.img_h, c.img_w, nullptr, rs, st), "resize"))
+  if (!run(UFM_CAT_RESIZE, 0.0, 2.0 * Bp * hid * ((double)H8 * W8 + (double)c.img_h * c.img_w), "resize", [&] {
+        return launch_resize_ac(nullptr, c1, Bp, H8, W8, hid, c.img_h, c.img_w, c.img_h, c.img_w, nullptr, rs, st);
+      }))
     return false;
   {
     Epi e;
@@ -466,6 +507,7 @@ int ufm_engine::forward(const void* src, const void* tgt, int pairs, int in_dtyp
   if (in_dtype != UFM_U8 && in_dtype != UFM_F32) return fail("input dtype must be u8 or f32");
   st = stream;
   launches = 0;
+  if (profile && prof.size() > (1u << 20)) return fail("profile records not drained: call ufm_profile_read");
   last_pairs = pairs;
   stage.clear();
   const ufm_config& c = cfg;
@@ -486,8 +528,10 @@ int ufm_engine::forward(const void* src, const void* tgt, int pairs, int in_dtyp
       pp.inv_std[i] = 1.0f / stdv[i];
     }
     pp.out = B<bf16>("Apatch");
-    ++launches;
-    if (!ck(launch_patch_im2col(pp, st), "patch_im2col")) return 1;
+    const double px = 2.0 * Bp * c.img_h * c.img_w * 3;
+    if (!run(UFM_CAT_MOVE, 0.0, px * (in_dtype == UFM_U8 ? 1 : 4) + 2.0 * 2 * Bp * n * Kpad, "patch_im2col",
+             [&] { return launch_patch_im2col(pp, st); }))
+      return 1;
   }
   float* x = B<float>("x");
   {
@@ -498,9 +542,11 @@ int ufm_engine::forward(const void* src, const void* tgt, int pairs, int in_dtyp
     e.res2 = pos + D; e.r2x = D; e.r2n = 0; e.r2y = 0;
     e.out_f32 = x; e.sx = D; e.sn = (long long)S * D; e.out_off = D;
     AView a{B<bf16>("Apatch"), Kpad, n, 1, 2 * Bp, Kpad, (long long)n * Kpad, (long long)n * Kpad, 128, 1};
+    flops_override = 2.0 * 2 * Bp * n * (double)D * 3 * c.patch * c.patch;  // K = 588, not the padded 640
     if (!gemm(a, "enc.patch.w", 1, e)) return 1;
-    ++launches;
-    if (!ck(launch_cls_rows(x, Wf("enc.cls"), pos, 2 * Bp, S, D, st), "cls_rows")) return 1;
+    if (!run(UFM_CAT_MOVE, 0.0, 2.0 * Bp * D * 4, "cls_rows",
+             [&] { return launch_cls_rows(x, Wf("enc.cls"), pos, 2 * Bp, S, D, st); }))
+      return 1;
   }
   bf16* enc_last = B<bf16>("enc_last");
   for (int i = 0; i < c.enc_depth; ++i) {
@@ -580,8 +626,9 @@ int ufm_engine::forward(const void* src, const void* tgt, int pairs, int in_dtyp
       e.bias = Wf("cls.lin.b"); e.out_f32 = B<float>("Z"); e.sx = zc;
       if (!gemm(rows_view(B<bf16>("Ycls"), Mc, c.cls_in), "cls.lin.w", 1, e)) return 1;
     }
-    ++launches;
-    if (!ck(launch_shuffle_f32(B<float>("Z"), B<float>("desc"), 2 * Bp, hpn, wpn, c.cls_patch, c.cls_out, st), "shuffle desc"))
+    if (!run(UFM_CAT_MOVE, 0.0, 8.0 * Mi * zc, "shuffle desc", [&] {
+          return launch_shuffle_f32(B<float>("Z"), B<float>("desc"), 2 * Bp, hpn, wpn, c.cls_patch, c.cls_out, st);
+        }))
       return 1;
     set_stage("desc", B<float>("desc"), UFM_F32, {Bp, 2, c.img_h, c.img_w, c.cls_out});
     RefineParams rp;
@@ -593,8 +640,12 @@ int ufm_engine::forward(const void* src, const void* tgt, int pairs, int in_dtyp
     rp.flow_out = flow_out;
     rp.residual = keep_aux ? B<float>("residual") : nullptr;
     rp.log_softmax = keep_aux ? B<float>("log_softmax") : nullptr;
-    ++launches;
-    if (!ck(launch_refine(rp, st), "refine")) return 1;
+    {
+      // algorithmic bytes: F1, F2 (16 ch fp32) + flow in + flow out (+ residual, log-softmax when kept)
+      const double plane = (double)c.img_h * c.img_w;
+      const double rb = Bp * plane * (2 * 16 * 4 + 2 * 4 + 2 * 4 + (keep_aux ? 2 * 4 + 25 * 4 : 0));
+      if (!run(UFM_CAT_REFINE, 0.0, rb, "refine", [&] { return launch_refine(rp, st); })) return 1;
+    }
     if (keep_aux) {
       set_stage("residual", B<float>("residual"), UFM_F32, {Bp, 2, c.img_h, c.img_w});
       set_stage("log_softmax", B<float>("log_softmax"), UFM_F32, {Bp, c.img_h, c.img_w, 25});
@@ -647,6 +698,7 @@ int ufm_create(const ufm_config* cfg, int device, ufm_engine** out) {
 void ufm_destroy(ufm_engine* e) {
   if (!e) return;
   cudaSetDevice(e->device);
+  for (auto ev : e->ev_pool) cudaEventDestroy(ev);
   for (auto& kv : e->w) cudaFree(kv.second.ptr);
   for (auto& kv : e->buf) cudaFree(kv.second.ptr);
   delete e;
@@ -814,6 +866,35 @@ int ufm_stage_copy(ufm_engine* e, const char* name, void* dst, int64_t bytes) {
 }
 
 int ufm_last_launch_count(ufm_engine* e) { return e ? e->launches : -1; }
+
+int ufm_set_profile(ufm_engine* e, int on) {
+  if (!e) return 1;
+  e->profile = on != 0;
+  e->prof.clear();
+  e->ev_used = 0;
+  return 0;
+}
+
+int ufm_profile_read(ufm_engine* e, double* ms, double* flops, double* bytes, int64_t* launches) {
+  if (!e) return 1;
+  cudaSetDevice(e->device);
+  if (!e->ck(cudaStreamSynchronize(e->st), "sync")) return 1;
+  for (int i = 0; i < UFM_NUM_CATS; ++i) {
+    ms[i] = flops[i] = bytes[i] = 0.0;
+    launches[i] = 0;
+  }
+  for (auto& r : e->prof) {
+    float t = 0.f;
+    if (!e->ck(cudaEventElapsedTime(&t, r.a, r.b), "event elapsed")) return 1;
+    ms[r.cat] += t;
+    flops[r.cat] += r.flops;
+    bytes[r.cat] += r.bytes;
+    launches[r.cat] += 1;
+  }
+  e->prof.clear();
+  e->ev_used = 0;
+  return 0;
+}
 
 // ---- kernel-level entry points ---------------------------------------------------------------------------------------
 static int g_num_sms() {

@@ -79,6 +79,17 @@ class Engine:
         self._ck(self.lib.ufm_forward_host(self.h, src.data_ptr(), tgt.data_ptr(), src.shape[0], _DT[src.dtype], layout,
                                            flow.data_ptr(), cov.data_ptr() if cov is not None else None))
 
+    def set_profile(self, on: bool):
+        self._ck(self.lib.ufm_set_profile(self.h, int(on)))
+
+    def profile_read(self) -> Dict[str, Dict[str, float]]:
+        """Per kernel family since the last read: summed device ms, algorithmic FLOPs / HBM bytes, launches."""
+        n = len(_lib.PROFILE_CATS)
+        ms, fl, by, la = (C.c_double * n)(), (C.c_double * n)(), (C.c_double * n)(), (C.c_int64 * n)()
+        self._ck(self.lib.ufm_profile_read(self.h, ms, fl, by, la))
+        return {name: {"ms": ms[i], "flops": fl[i], "bytes": by[i], "launches": int(la[i])}
+                for i, name in enumerate(_lib.PROFILE_CATS)}
+
     def launch_count(self) -> int:
         return self.lib.ufm_last_launch_count(self.h)
 
