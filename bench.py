@@ -260,12 +260,15 @@ def run_engine(args):
     barrier()
     sampler.start()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    marks = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps)]
     e0.record()
-    for _ in range(args.steps):
+    for i in range(args.steps):
         flow, cov = eng.forward(dsrc, dtgt, _lib.UFM_NHWC)
+        marks[i].record()
     e1.record()
     barrier()
     clocks = sampler.stop()
+    step_ms = [round((e0 if i == 0 else marks[i - 1]).elapsed_time(marks[i]), 3) for i in range(args.steps)]
     launches = eng.launch_count() * args.steps
     ms = maxreduce(e0.elapsed_time(e1))
     ms_per_step = ms / args.steps
@@ -329,7 +332,7 @@ def run_engine(args):
         "config": {"workload": desc, "pairs_per_step_per_gpu": pairs, "resolution": [W, H], "weights": "random-init seed 0",
                    "l2": "no flush needed: per-step working set (0.9 GB weights + >10 GB activations) exceeds the 126 MB L2",
                    "parallelism": f"dp{world} (independent pairs, no data-path collective)"},
-        "e2e": e2e, "gpu_launches": launches, "clocks": clocks, "roofline": roofline, "kernel_families": fam,
+        "step_ms": step_ms, "e2e": e2e, "gpu_launches": launches, "clocks": clocks, "roofline": roofline, "kernel_families": fam,
         "whole_pass": whole,
     }
     if rank == 0 and world == 1 and not args.no_cpu:

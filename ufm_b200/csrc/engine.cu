@@ -81,8 +81,8 @@ struct Epi {
 bool build_gemm(GemmParams* gp, int* BN, const AView& a, const void* wt, int n_out, int taps, int cin_pad, const Epi& e,
                 char* err, int errlen) {
   memset(gp, 0, sizeof(*gp));
-  if (a.tw * a.th != 128) {
-    snprintf(err, errlen, "tile %dx%d != 128", a.tw, a.th);
+  if (a.tw * a.th != 128 || (a.tw & (a.tw - 1))) {
+    snprintf(err, errlen, "tile %dx%d must cover 128 rows with a power-of-two width", a.tw, a.th);
     return false;
   }
   const uint64_t adims[4] = {(uint64_t)a.C, (uint64_t)a.X, (uint64_t)a.Y, (uint64_t)a.N};
@@ -105,6 +105,8 @@ bool build_gemm(GemmParams* gp, int* BN, const AView& a, const void* wt, int n_o
     return false;
   }
   gp->tw = a.tw; gp->th = a.th;
+  gp->tw_log2 = 0;
+  while ((1 << gp->tw_log2) < a.tw) ++gp->tw_log2;
   gp->X = a.X; gp->Y = a.Y; gp->Nimg = a.N;
   gp->tiles_x = (a.X + a.tw - 1) / a.tw;
   gp->tiles_y = (a.Y + a.th - 1) / a.th;

@@ -36,7 +36,8 @@ struct alignas(64) GemmParams {
   CUtensorMap tmA;
   CUtensorMap tmB;
   // tile geometry
-  int tw, th;            // A box extents, tw*th == 128
+  int tw, th;            // A box extents, tw*th == 128, tw a power of two
+  int tw_log2;
   int X, Y, Nimg;        // logical output extents per image
   int tiles_x, tiles_y;  // ceil(X/tw), ceil(Y/th)
   int N;                 // output channels (multiple of 32, or anything in TAIL mode with N <= 128)

@@ -185,42 +185,58 @@ __global__ void __launch_bounds__(256) im2col_s2_kernel(const __nv_bfloat16* in,
 }
 
 // ------------------------------------------------------------------------------------------------ bilinear (ac=True)
-__device__ __forceinline__ float4 ld4(const float* p) { return __ldg(reinterpret_cast<const float4*>(p)); }
-__device__ __forceinline__ float4 ld4(const __nv_bfloat16* p) {
-  const uint2 u = __ldg(reinterpret_cast<const uint2*>(p));
+// PyTorch upsample_bilinear2d, align_corners=True (dpt_block.py:251-253, dpt.py:304): src = dst*(in-1)/(out-1).
+// Grid (x-chunks, oy, n): no 64-bit index arithmetic in the kernel (a flat 64-bit index costs four software divisions
+// per thread and made the first version issue-bound at 20 % of HBM).  Each thread produces 16 bytes' worth of input
+// channels (4 fp32 / 8 bf16) of one output pixel; a warp covers consecutive channels, then consecutive pixels.
+template <int N>
+struct Vec { float v[N]; };
+__device__ __forceinline__ Vec<4> ldv(const float* p) {
+  const float4 t = __ldg(reinterpret_cast<const float4*>(p));
+  return Vec<4>{{t.x, t.y, t.z, t.w}};
+}
+__device__ __forceinline__ Vec<8> ldv(const __nv_bfloat16* p) {
+  const uint4 u = __ldg(reinterpret_cast<const uint4*>(p));
   const float2 a = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&u.x));
   const float2 b = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&u.y));
-  return make_float4(a.x, a.y, b.x, b.y);
+  const float2 c = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&u.z));
+  const float2 d = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&u.w));
+  return Vec<8>{{a.x, a.y, b.x, b.y, c.x, c.y, d.x, d.y}};
 }
-// PyTorch upsample_bilinear2d, align_corners=True (dpt_block.py:251-253, dpt.py:304): src = dst*(in-1)/(out-1).
 template <typename T>
-__global__ void __launch_bounds__(256) resize_ac_kernel(const T* in, int n, int h, int w, int C, float sy, float sx,
-                                                       int oh, int ow, float* out_f32, __nv_bfloat16* out_bf16) {
-  const int cg = C >> 2;
-  const long long total = (long long)n * oh * ow * cg;
-  const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-  if (idx >= total) return;
-  const int g = (int)(idx % cg);
-  const long long pix = idx / cg;
-  const int ox = (int)(pix % ow);
-  const int oy = (int)((pix / ow) % oh);
-  const int nn = (int)(pix / ((long long)ow * oh));
+__global__ void __launch_bounds__(256) resize_ac_kernel(const T* in, int h, int w, int C, float sy, float sx, int oh,
+                                                       int ow, float* out_f32, __nv_bfloat16* out_bf16) {
+  constexpr int V = 16 / sizeof(T);
+  const unsigned cg = (unsigned)C / V;
+  const unsigned t = blockIdx.x * 256u + threadIdx.x;
+  const unsigned ox = t / cg;
+  if (ox >= (unsigned)ow) return;
+  const unsigned g = t - ox * cg;
+  const int oy = blockIdx.y, nn = blockIdx.z;
   const float fy = sy * oy, fx = sx * ox;
   const int y0 = (int)fy, x0 = (int)fx;
   const int y1 = y0 + (y0 < h - 1 ? 1 : 0), x1 = x0 + (x0 < w - 1 ? 1 : 0);
   const float ly = fy - y0, lx = fx - x0;
   const float hy = 1.f - ly, hx = 1.f - lx;
-  const T* b = in + (long long)nn * h * w * C + g * 4;
-  const float4 a00 = ld4(b + ((long long)y0 * w + x0) * C), a01 = ld4(b + ((long long)y0 * w + x1) * C);
-  const float4 a10 = ld4(b + ((long long)y1 * w + x0) * C), a11 = ld4(b + ((long long)y1 * w + x1) * C);
-  float4 r;
-  r.x = hy * (hx * a00.x + lx * a01.x) + ly * (hx * a10.x + lx * a11.x);
-  r.y = hy * (hx * a00.y + lx * a01.y) + ly * (hx * a10.y + lx * a11.y);
-  r.z = hy * (hx * a00.z + lx * a01.z) + ly * (hx * a10.z + lx * a11.z);
-  r.w = hy * (hx * a00.w + lx * a01.w) + ly * (hx * a10.w + lx * a11.w);
-  const long long o = pix * C + g * 4;
-  if (out_f32) *reinterpret_cast<float4*>(out_f32 + o) = r;
-  if (out_bf16) *reinterpret_cast<uint2*>(out_bf16 + o) = make_uint2(pack_bf16(r.x, r.y), pack_bf16(r.z, r.w));
+  const T* b = in + (size_t)nn * h * w * C + g * V;
+  const Vec<V> a00 = ldv(b + ((size_t)y0 * w + x0) * C), a01 = ldv(b + ((size_t)y0 * w + x1) * C);
+  const Vec<V> a10 = ldv(b + ((size_t)y1 * w + x0) * C), a11 = ldv(b + ((size_t)y1 * w + x1) * C);
+  float r[V];
+#pragma unroll
+  for (int i = 0; i < V; ++i)
+    r[i] = hy * (hx * a00.v[i] + lx * a01.v[i]) + ly * (hx * a10.v[i] + lx * a11.v[i]);
+  const size_t o = (((size_t)nn * oh + oy) * ow + ox) * C + g * V;
+  if (out_f32) {
+#pragma unroll
+    for (int i = 0; i < V; i += 4) *reinterpret_cast<float4*>(out_f32 + o + i) = make_float4(r[i], r[i + 1], r[i + 2], r[i + 3]);
+  }
+  if (out_bf16) {
+    if constexpr (V == 8)
+      *reinterpret_cast<uint4*>(out_bf16 + o) =
+          make_uint4(pack_bf16(r[0], r[1]), pack_bf16(r[2], r[3]), pack_bf16(r[4], r[5]), pack_bf16(r[6], r[7]));
+    else
+      *reinterpret_cast<uint2*>(out_bf16 + o) = make_uint2(pack_bf16(r[0], r[1]), pack_bf16(r[2], r[3]));
+  }
 }
 
 // ------------------------------------------------------------------------------------------------ local refinement
@@ -388,14 +404,17 @@ cudaError_t launch_im2col_s2(const __nv_bfloat16* in, __nv_bfloat16* out, int n,
 
 cudaError_t launch_resize_ac(const float* in_f32, const __nv_bfloat16* in_bf16, int n, int h, int w, int C, int rh, int rw,
                              int oh, int ow, float* out_f32, __nv_bfloat16* out_bf16, cudaStream_t s) {
-  if (C % 4) return cudaErrorInvalidValue;
+  if (C % (in_f32 ? 4 : 8) || oh > 65535 || n > 65535) return cudaErrorInvalidValue;
   const float sy = rh > 1 ? (float)(h - 1) / (float)(rh - 1) : 0.f;
   const float sx = rw > 1 ? (float)(w - 1) / (float)(rw - 1) : 0.f;
-  const long long total = (long long)n * oh * ow * (C / 4);
-  if (in_f32)
-    resize_ac_kernel<float><<<blocks_for(total, 256), 256, 0, s>>>(in_f32, n, h, w, C, sy, sx, oh, ow, out_f32, out_bf16);
-  else
-    resize_ac_kernel<__nv_bfloat16><<<blocks_for(total, 256), 256, 0, s>>>(in_bf16, n, h, w, C, sy, sx, oh, ow, out_f32, out_bf16);
+  if (n == 0) return cudaSuccess;
+  if (in_f32) {
+    dim3 grid(blocks_for((long long)ow * (C / 4), 256), oh, n);
+    resize_ac_kernel<float><<<grid, 256, 0, s>>>(in_f32, h, w, C, sy, sx, oh, ow, out_f32, out_bf16);
+  } else {
+    dim3 grid(blocks_for((long long)ow * (C / 8), 256), oh, n);
+    resize_ac_kernel<__nv_bfloat16><<<grid, 256, 0, s>>>(in_bf16, h, w, C, sy, sx, oh, ow, out_f32, out_bf16);
+  }
   return cudaGetLastError();
 }
 
