@@ -102,6 +102,11 @@ enum { UFM_CAT_GEMM = 0,   /* gemm_kernel, taps == 1: Linear / 1x1 conv / folded
 int ufm_set_profile(ufm_engine* e, int on);
 int ufm_profile_read(ufm_engine* e, double* ms, double* flops, double* bytes, int64_t* launches);
 
+/* Process-wide tuning switches for kernel experiments (no reference counterpart).  which = 0: GEMM epilogue variant
+ * (0 = row-per-thread stores, 1 = shared-memory transposed, coalesced stores); which = 1: CTA-pair (cta_group::2) GEMM
+ * tiles on/off.  Returns non-zero for an unknown switch. */
+int ufm_debug_flag(int which, int value);
+
 /* ---- kernel-level entry points (unit parity tests; device pointers, asynchronous on `stream`) ---- */
 
 /* out = epilogue(A (*) Wt): see ufm_b200/csrc/kernels.h GemmParams.  A is bf16 with logical extents (C, X, Y, Nimg) and

@@ -53,6 +53,7 @@ SYMBOLS = {
     "ufm_last_launch_count": (_I, [_P]),
     "ufm_set_profile": (_I, [_P, _I]),
     "ufm_profile_read": (_I, [_P, C.POINTER(C.c_double), C.POINTER(C.c_double), C.POINTER(C.c_double), C.POINTER(_L)]),
+    "ufm_debug_flag": (_I, [_I, _I]),
     "ufm_op_gemm": (_I, [_P, _I, _I, _I, _I, _L, _L, _L, _I, _I, _P, _I, _I, _I, _P, _P, _P, _P, _L, _L, _L, _P, _P,
                          _L, _L, _L, _L, _U, _P, _P, _P, _P, _I, _P, _P, C.c_char_p, _I]),
     "ufm_op_attention": (_I, [_P, _I, _I, _I, _F, _P, _P, C.c_char_p, _I]),

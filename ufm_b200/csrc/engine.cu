@@ -8,6 +8,7 @@
 #include <math.h>
 #include <stdarg.h>
 #include <stdio.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include <map>
@@ -93,7 +94,8 @@ bool build_gemm(GemmParams* gp, int* BN, const AView& a, const void* wt, int n_o
   *BN = (!tail && n_out % 256 == 0) ? 256 : 128;
   const uint64_t bdims[2] = {(uint64_t)taps * cin_pad, (uint64_t)n_out};
   const uint64_t bstr[2] = {2, (uint64_t)taps * cin_pad * 2};
-  const uint32_t bbox[2] = {64, (uint32_t)*BN};
+  gp->ctas = (*BN == 256 && gemm_pair_mode()) ? 2 : 1;
+  const uint32_t bbox[2] = {64, (uint32_t)(*BN / gp->ctas)};
   if (!make_tmap_bf16(&gp->tmB, wt, 2, bdims, bstr, bbox, err, errlen)) return false;
   if (tail) {
     if (n_out > 128 || e.tail_out < 1 || e.tail_out > 4 || n_out % 32) {
@@ -167,7 +169,7 @@ struct ufm_engine {
 
   // ---- per-kernel-family timing (CUDA events on the launching stream; read by bench.py for the roofline) ----
   bool profile = false;
-  struct ProfRec { int cat; double flops, bytes; cudaEvent_t a, b; };
+  struct ProfRec { int cat; double flops, bytes; cudaEvent_t a, b; std::string what; };
   std::vector<ProfRec> prof;
   std::vector<cudaEvent_t> ev_pool;
   size_t ev_used = 0;
@@ -183,7 +185,7 @@ struct ufm_engine {
   template <class F>
   bool run(int cat, double flops, double bytes, const char* what, F&& f) {
     ++launches;
-    ProfRec r{cat, flops, bytes, nullptr, nullptr};
+    ProfRec r{cat, flops, bytes, nullptr, nullptr, what};
     if (profile) {
       r.a = next_event();
       cudaEventRecord(r.a, st);
@@ -885,17 +887,37 @@ int ufm_profile_read(ufm_engine* e, double* ms, double* flops, double* bytes, in
     ms[i] = flops[i] = bytes[i] = 0.0;
     launches[i] = 0;
   }
+  // UFM_PROFILE_DUMP=<path>: also append one "label,family,ms,flops,bytes" line per launch (tuning aid)
+  FILE* dump = nullptr;
+  if (const char* path = getenv("UFM_PROFILE_DUMP")) dump = fopen(path, "a");
   for (auto& r : e->prof) {
     float t = 0.f;
-    if (!e->ck(cudaEventElapsedTime(&t, r.a, r.b), "event elapsed")) return 1;
+    if (!e->ck(cudaEventElapsedTime(&t, r.a, r.b), "event elapsed")) {
+      if (dump) fclose(dump);
+      return 1;
+    }
+    if (dump) fprintf(dump, "%s,%d,%.4f,%.6g,%.6g\n", r.what.c_str(), r.cat, t, r.flops, r.bytes);
     ms[r.cat] += t;
     flops[r.cat] += r.flops;
     bytes[r.cat] += r.bytes;
     launches[r.cat] += 1;
   }
+  if (dump) fclose(dump);
   e->prof.clear();
   e->ev_used = 0;
   return 0;
+}
+
+int ufm_debug_flag(int which, int value) {
+  if (which == 0) {
+    set_gemm_epilogue_variant(value);
+    return 0;
+  }
+  if (which == 1) {
+    set_gemm_pair_mode(value);
+    return 0;
+  }
+  return 1;
 }
 
 // ---- kernel-level entry points ---------------------------------------------------------------------------------------

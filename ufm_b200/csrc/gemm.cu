@@ -27,14 +27,19 @@ constexpr int BK = 64;
 constexpr int kEpiWarps = 8;
 constexpr int kThreads = 128 + kEpiWarps * 32;
 
-template <int BN>
+// CTAS = 2: a CTA pair (cluster of 2, tcgen05 cta_group::2) computes a 256 x BN tile; each CTA stages its own 128 rows
+// of A and only HALF of the B tile, which cuts the L2 -> SM operand traffic per FLOP by a third (the single-CTA
+// 128 x 256 tile needs 96 B/clk/SM at the MMA floor; the chip-wide L2 cap is about 43 B/clk/SM).
+template <int BN, int CTAS>
 struct Cfg {
   static constexpr int A_BYTES = BM * BK * 2;
-  static constexpr int B_BYTES = BN * BK * 2;
+  static constexpr int B_ROWS = BN / CTAS;
+  static constexpr int B_BYTES = B_ROWS * BK * 2;
   static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
-  static constexpr int STAGES = (BN == 256) ? 4 : 6;
+  static constexpr int STAGES = (STAGE_BYTES == 49152) ? 4 : 6;
   static constexpr int BAR_BYTES = 256;
-  static constexpr int SCRATCH_BYTES = 2 * 2 * 128 * 4 * 4;  // [acc][half][row][4] floats (TAIL mode)
+  // epilogue staging: 8 warps x (32 x 32 fp32) transpose tiles; TAIL mode reuses it as [acc][half][row][4] floats
+  static constexpr int SCRATCH_BYTES = kEpiWarps * 32 * 32 * 4;
   static constexpr int SMEM_BYTES = 1024 + STAGES * STAGE_BYTES + BAR_BYTES + SCRATCH_BYTES;
   static constexpr int TMEM_COLS = 2 * BN;
 };
@@ -56,9 +61,12 @@ __device__ __forceinline__ float gelu_erf(float x) {
   return fmaf(-ax * 0.3989422804014327f, pl * e, fmaxf(x, 0.f));
 }
 
-template <int BN>
+template <int BN, int EPI, int CTAS>
 __global__ void __launch_bounds__(kThreads, 1) gemm_kernel(const __grid_constant__ GemmParams p) {
-  using C = Cfg<BN>;
+  using C = Cfg<BN, CTAS>;
+  const uint32_t cta_rank = (CTAS == 2) ? cluster_ctarank() : 0u;
+  const int unit = blockIdx.x / CTAS;          // scheduling unit: a CTA (CTAS 1) or a CTA pair (CTAS 2)
+  const int num_units = gridDim.x / CTAS;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* sA = smem;
@@ -68,7 +76,8 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_kernel(const __grid_constant
   uint64_t* tfull = empty + C::STAGES;
   uint64_t* tempty = tfull + 2;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty + 2);
-  float* scratch = reinterpret_cast<float*>(smem + C::STAGES * C::STAGE_BYTES + C::BAR_BYTES);
+  uint8_t* stage_smem = smem + C::STAGES * C::STAGE_BYTES + C::BAR_BYTES;
+  float* scratch = reinterpret_cast<float*>(stage_smem);
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -84,17 +93,24 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_kernel(const __grid_constant
     }
     for (int i = 0; i < 2; ++i) {
       mbar_init(&tfull[i], 1);
-      mbar_init(&tempty[i], kEpiWarps);
+      mbar_init(&tempty[i], kEpiWarps * CTAS);  // pair: the leader's barrier also collects the peer's epilogue warps
     }
     fence_barrier_init();
   }
-  if (warp == 2) tmem_alloc<C::TMEM_COLS>(tmem_slot);
+  if (warp == 2) {
+    if constexpr (CTAS == 2) tmem_alloc2<C::TMEM_COLS>(tmem_slot);
+    else tmem_alloc<C::TMEM_COLS>(tmem_slot);
+  }
   tc_fence_before();
-  __syncthreads();
+  if constexpr (CTAS == 2) cluster_sync_all();  // peer barriers initialised before any remote arrive / multicast commit
+  else __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
-  const int tiles_m = p.Nimg * p.tiles_y * p.tiles_x;
+  // a scheduling unit owns CTAS consecutive 128-row tiles (one per CTA) x one BN-wide column tile; a CTA whose row tile
+  // lies past the end loads zero-filled boxes (image index out of range) and stores nothing
+  const int tiles_m1 = p.Nimg * p.tiles_y * p.tiles_x;
+  const int tiles_m = (tiles_m1 + CTAS - 1) / CTAS;
   const int total_tiles = tiles_m * p.tiles_n;
   const int k_iters = p.taps * p.cchunks;
 
@@ -102,13 +118,13 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_kernel(const __grid_constant
     if (lane == 0) {
       int stage = 0;
       uint32_t phase = 0;
-      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+      for (int tile = unit; tile < total_tiles; tile += num_units) {
         const int tn = tile % p.tiles_n;
-        const int tm = tile / p.tiles_n;
+        const int tm = (tile / p.tiles_n) * CTAS + (int)cta_rank;
         const int tx = tm % p.tiles_x;
         const int ty = (tm / p.tiles_x) % p.tiles_y;
         const int img = tm / (p.tiles_x * p.tiles_y);
-        const int x0 = tx * p.tw, y0 = ty * p.th, n0 = tn * BN;
+        const int x0 = tx * p.tw, y0 = ty * p.th, n0 = tn * BN + (int)cta_rank * C::B_ROWS;
         for (int k = 0; k < k_iters; ++k) {
           const int tap = k / p.cchunks;
           const int cc = k - tap * p.cchunks;
@@ -118,9 +134,17 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_kernel(const __grid_constant
             dx = tap % 3 - 1;
           }
           mbar_wait(&empty[stage], phase ^ 1);
-          mbar_expect_tx(&full[stage], C::STAGE_BYTES);
-          tma_load_4d(sA + stage * C::A_BYTES, &p.tmA, &full[stage], cc * BK, x0 + dx, y0 + dy, img);
-          tma_load_2d(sB + stage * C::B_BYTES, &p.tmB, &full[stage], tap * p.cin_pad + cc * BK, n0);
+          if constexpr (CTAS == 2) {
+            // both CTAs' boxes complete on the LEADER's full barrier, which expects the bytes of the whole pair
+            if (cta_rank == 0) mbar_expect_tx(&full[stage], 2 * C::STAGE_BYTES);
+            const uint32_t lbar = smem_u32(&full[stage]) & kPeerBitMask;
+            tma2_load_4d(sA + stage * C::A_BYTES, &p.tmA, lbar, cc * BK, x0 + dx, y0 + dy, img);
+            tma2_load_2d(sB + stage * C::B_BYTES, &p.tmB, lbar, tap * p.cin_pad + cc * BK, n0);
+          } else {
+            mbar_expect_tx(&full[stage], C::STAGE_BYTES);
+            tma_load_4d(sA + stage * C::A_BYTES, &p.tmA, &full[stage], cc * BK, x0 + dx, y0 + dy, img);
+            tma_load_2d(sB + stage * C::B_BYTES, &p.tmB, &full[stage], tap * p.cin_pad + cc * BK, n0);
+          }
           if (++stage == C::STAGES) {
             stage = 0;
             phase ^= 1;
@@ -129,13 +153,13 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_kernel(const __grid_constant
       }
     }
   } else if (warp == 1) {
-    if (lane == 0) {
-      constexpr uint32_t idesc = umma_idesc_bf16(BM, BN, 0, 0);
+    if (lane == 0 && cta_rank == 0) {
+      constexpr uint32_t idesc = umma_idesc_bf16(BM * CTAS, BN, 0, 0);
       int stage = 0;
       uint32_t phase = 0;
       int acc = 0;
       uint32_t accphase = 0;
-      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+      for (int tile = unit; tile < total_tiles; tile += num_units) {
         mbar_wait(&tempty[acc], accphase ^ 1);
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + acc * BN;
@@ -146,11 +170,20 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_kernel(const __grid_constant
           const uint32_t b_addr = smem_u32(sB + stage * C::B_BYTES);
 #pragma unroll
           for (int kk = 0; kk < BK / 16; ++kk) {
-            umma_ss(d_tmem, umma_desc_sw128(a_addr + kk * 32), umma_desc_sw128(b_addr + kk * 32), idesc,
-                    (k | kk) != 0 ? 1u : 0u);
+            if constexpr (CTAS == 2)
+              umma2_ss(d_tmem, umma_desc_sw128(a_addr + kk * 32), umma_desc_sw128(b_addr + kk * 32), idesc,
+                       (k | kk) != 0 ? 1u : 0u);
+            else
+              umma_ss(d_tmem, umma_desc_sw128(a_addr + kk * 32), umma_desc_sw128(b_addr + kk * 32), idesc,
+                      (k | kk) != 0 ? 1u : 0u);
           }
-          umma_commit(&empty[stage]);
-          if (k == k_iters - 1) umma_commit(&tfull[acc]);
+          if constexpr (CTAS == 2) {
+            umma2_commit_mc(&empty[stage]);
+            if (k == k_iters - 1) umma2_commit_mc(&tfull[acc]);
+          } else {
+            umma_commit(&empty[stage]);
+            if (k == k_iters - 1) umma_commit(&tfull[acc]);
+          }
           if (++stage == C::STAGES) {
             stage = 0;
             phase ^= 1;
@@ -166,11 +199,19 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_kernel(const __grid_constant
     const int half = e >> 2;
     constexpr int HALF_COLS = BN / 2;
     const bool tail = (p.flags & GEMM_TAIL) != 0;
+    float4* stg = reinterpret_cast<float4*>(stage_smem) + e * 256;  // this warp's 32x32 fp32 transpose tile (EPI 1)
+    const int g4 = lane & 7;     // column group (4 floats) owned after the transpose
+    const int rsub = lane >> 3;  // row within each group of 4 rows
     int acc = 0;
     uint32_t accphase = 0;
-    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+    uint32_t tempty_remote[2] = {0u, 0u};
+    if constexpr (CTAS == 2) {
+      tempty_remote[0] = mapa_cluster(smem_u32(&tempty[0]), 0);
+      tempty_remote[1] = mapa_cluster(smem_u32(&tempty[1]), 0);
+    }
+    for (int tile = unit; tile < total_tiles; tile += num_units) {
       const int tn = tile % p.tiles_n;
-      const int tm = tile / p.tiles_n;
+      const int tm = (tile / p.tiles_n) * CTAS + (int)cta_rank;
       const int tx = tm % p.tiles_x;
       const int ty = (tm / p.tiles_x) % p.tiles_y;
       const int img = tm / (p.tiles_x * p.tiles_y);
@@ -179,7 +220,7 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_kernel(const __grid_constant
       const int ly = r / p.tw;
       const int lx = r - ly * p.tw;
       const int x = tx * p.tw + lx, y = ty * p.th + ly;
-      const bool valid = (x < p.X) && (y < p.Y);
+      const bool valid = (x < p.X) && (y < p.Y) && (img < p.Nimg);
       const long long off = (long long)img * p.sN + (long long)y * p.sY + (long long)x * p.sX + p.out_off;
       const long long off2 = (long long)img * p.r2N + (long long)y * p.r2Y + (long long)x * p.r2X;
 
@@ -200,8 +241,72 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_kernel(const __grid_constant
       mbar_wait(&tfull[acc], accphase);
       tc_fence_after();
       float part[4] = {0.f, 0.f, 0.f, 0.f};
+      if (EPI == 1 && !tail) {
+        // rows this thread stores after the transpose: q*32 + 4*i + rsub, i = 0..7
+        long long offs[8];
+        uint32_t vmask = 0;
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          const int rr = q * 32 + 4 * i + rsub;
+          const int ly = rr >> p.tw_log2;
+          const int lx = rr & (p.tw - 1);
+          const int x = tx * p.tw + lx, y = ty * p.th + ly;
+          if (x < p.X && y < p.Y && img < p.Nimg) vmask |= 1u << i;
+          offs[i] = (long long)img * p.sN + (long long)y * p.sY + (long long)x * p.sX + p.out_off;
+        }
 #pragma unroll 1
-      for (int c = 0; c < HALF_COLS / 32; ++c) {
+        for (int c = 0; c < HALF_COLS / 32; ++c) {
+          const int col0 = half * HALF_COLS + c * 32;
+          const int gcol = n0 + col0;
+          if (gcol >= p.N) break;
+          uint32_t vr[32];
+          tmem_ld32(tmem_base + (uint32_t(q * 32) << 16) + uint32_t(acc * BN + col0), vr);
+          tmem_ld_wait();
+          __syncwarp();  // previous chunk's reads of the staging tile are done
+#pragma unroll
+          for (int j = 0; j < 8; ++j)
+            stg[lane * 8 + (j ^ (lane & 7))] =
+                make_float4(__uint_as_float(vr[4 * j]), __uint_as_float(vr[4 * j + 1]), __uint_as_float(vr[4 * j + 2]),
+                            __uint_as_float(vr[4 * j + 3]));
+          __syncwarp();
+          const int mycol = gcol + g4 * 4;
+          float4 b4 = make_float4(0.f, 0.f, 0.f, 0.f), s4 = make_float4(1.f, 1.f, 1.f, 1.f);
+          if (p.bias) b4 = __ldg(reinterpret_cast<const float4*>(p.bias + mycol));
+          if (p.scale) s4 = __ldg(reinterpret_cast<const float4*>(p.scale + mycol));
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            const int row = 4 * i + rsub;
+            float4 v = stg[row * 8 + (g4 ^ (row & 7))];
+            if ((vmask >> i) & 1u) {
+            v.x += b4.x; v.y += b4.y; v.z += b4.z; v.w += b4.w;
+            if (p.flags & GEMM_GELU) {
+              v.x = gelu_erf(v.x); v.y = gelu_erf(v.y); v.z = gelu_erf(v.z); v.w = gelu_erf(v.w);
+            }
+            v.x *= s4.x; v.y *= s4.y; v.z *= s4.z; v.w *= s4.w;
+            if (p.res1) {
+              const float4 r4 = *reinterpret_cast<const float4*>(p.res1 + offs[i] + mycol);
+              v.x += r4.x; v.y += r4.y; v.z += r4.z; v.w += r4.w;
+            }
+            if (p.res2) {
+              const int rr = q * 32 + row;
+              const int x = tx * p.tw + (rr & (p.tw - 1)), y = ty * p.th + (rr >> p.tw_log2);
+              const long long off2 = (long long)img * p.r2N + (long long)y * p.r2Y + (long long)x * p.r2X;
+              const float4 r4 = *reinterpret_cast<const float4*>(p.res2 + off2 + mycol);
+              v.x += r4.x; v.y += r4.y; v.z += r4.z; v.w += r4.w;
+            }
+            if (p.out_f32) *reinterpret_cast<float4*>(p.out_f32 + offs[i] + mycol) = v;
+            if (p.out_bf16) {
+              if (p.flags & GEMM_RELU_BF16) {
+                v.x = fmaxf(v.x, 0.f); v.y = fmaxf(v.y, 0.f); v.z = fmaxf(v.z, 0.f); v.w = fmaxf(v.w, 0.f);
+              }
+              *reinterpret_cast<uint2*>(p.out_bf16 + offs[i] + mycol) = make_uint2(pack_bf16(v.x, v.y), pack_bf16(v.z, v.w));
+            }
+            }
+          }
+        }
+      }
+#pragma unroll 1
+      for (int c = 0; c < ((EPI == 0 || tail) ? HALF_COLS / 32 : 0); ++c) {
         const int col0 = half * HALF_COLS + c * 32;
         const int gcol = n0 + col0;
         if (gcol >= p.N) break;
@@ -289,7 +394,10 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_kernel(const __grid_constant
       // accumulator stage drained -> hand it back to the MMA warp
       tc_fence_before();
       __syncwarp();
-      if (lane == 0) mbar_arrive(&tempty[acc]);
+      if (lane == 0) {
+        if constexpr (CTAS == 2) mbar_arrive_cluster(tempty_remote[acc]);
+        else mbar_arrive(&tempty[acc]);
+      }
 
       if (tail) {
         // combine the two column halves of each row through smem (double-buffered by accumulator stage)
@@ -317,37 +425,65 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_kernel(const __grid_constant
   }
 
   tc_fence_before();
-  __syncthreads();
-  if (warp == 2) tmem_dealloc<C::TMEM_COLS>(tmem_base);
+  if constexpr (CTAS == 2) {
+    cluster_sync_all();  // neither CTA may exit (or free TMEM) while the pair's MMAs / remote arrives are in flight
+    if (warp == 2) tmem_dealloc2<C::TMEM_COLS>(tmem_base);
+  } else {
+    __syncthreads();
+    if (warp == 2) tmem_dealloc<C::TMEM_COLS>(tmem_base);
+  }
+}
+
+int g_gemm_epi = 0;   // epilogue variant (ufm_debug_flag 0): 0 = row-per-thread direct, 1 = smem-transposed coalesced
+int g_gemm_pair = 1;  // ufm_debug_flag 1: allow CTA-pair (cta_group::2) tiles for BN = 256
+
+template <int BN, int EPI, int CTAS>
+static cudaError_t launch_one(const GemmParams& p, int grid, cudaStream_t stream) {
+  using C = Cfg<BN, CTAS>;
+  static bool attr = false;
+  if (!attr) {
+    cudaError_t err = cudaFuncSetAttribute(gemm_kernel<BN, EPI, CTAS>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM_BYTES);
+    if (err != cudaSuccess) return err;
+    attr = true;
+  }
+  if (CTAS == 1) {
+    gemm_kernel<BN, EPI, CTAS><<<grid, kThreads, C::SMEM_BYTES, stream>>>(p);
+    return cudaGetLastError();
+  }
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(grid, 1, 1);
+  cfg.blockDim = dim3(kThreads, 1, 1);
+  cfg.dynamicSmemBytes = C::SMEM_BYTES;
+  cfg.stream = stream;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeClusterDimension;
+  at[0].val.clusterDim.x = CTAS;
+  at[0].val.clusterDim.y = 1;
+  at[0].val.clusterDim.z = 1;
+  cfg.attrs = at;
+  cfg.numAttrs = 1;
+  return cudaLaunchKernelEx(&cfg, gemm_kernel<BN, EPI, CTAS>, p);
 }
 
 }  // namespace
 
+void set_gemm_epilogue_variant(int v) { g_gemm_epi = v; }
+void set_gemm_pair_mode(int v) { g_gemm_pair = v; }
+int gemm_pair_mode() { return g_gemm_pair; }
+
 cudaError_t launch_gemm(const GemmParams& p, int BN, int num_sms, cudaStream_t stream) {
-  const int total = p.Nimg * p.tiles_y * p.tiles_x * p.tiles_n;
+  const int ctas = p.ctas == 2 ? 2 : 1;
+  const int tiles_m1 = p.Nimg * p.tiles_y * p.tiles_x;
+  const int total = ((tiles_m1 + ctas - 1) / ctas) * p.tiles_n;
   if (total <= 0) return cudaSuccess;
-  const int grid = total < num_sms ? total : num_sms;
-  cudaError_t err;
-  if (BN == 256) {
-    static bool attr = false;
-    if (!attr) {
-      err = cudaFuncSetAttribute(gemm_kernel<256>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg<256>::SMEM_BYTES);
-      if (err != cudaSuccess) return err;
-      attr = true;
-    }
-    gemm_kernel<256><<<grid, kThreads, Cfg<256>::SMEM_BYTES, stream>>>(p);
-  } else if (BN == 128) {
-    static bool attr = false;
-    if (!attr) {
-      err = cudaFuncSetAttribute(gemm_kernel<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg<128>::SMEM_BYTES);
-      if (err != cudaSuccess) return err;
-      attr = true;
-    }
-    gemm_kernel<128><<<grid, kThreads, Cfg<128>::SMEM_BYTES, stream>>>(p);
-  } else {
-    return cudaErrorInvalidValue;
+  int grid = total * ctas < num_sms ? total * ctas : num_sms / ctas * ctas;
+  if (ctas == 2) {
+    if (BN != 256) return cudaErrorInvalidValue;
+    return g_gemm_epi ? launch_one<256, 1, 2>(p, grid, stream) : launch_one<256, 0, 2>(p, grid, stream);
   }
-  return cudaGetLastError();
+  if (BN == 256) return g_gemm_epi ? launch_one<256, 1, 1>(p, grid, stream) : launch_one<256, 0, 1>(p, grid, stream);
+  if (BN == 128) return g_gemm_epi ? launch_one<128, 1, 1>(p, grid, stream) : launch_one<128, 0, 1>(p, grid, stream);
+  return cudaErrorInvalidValue;
 }
 
 }  // namespace ufm

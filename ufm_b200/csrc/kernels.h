@@ -38,6 +38,7 @@ struct alignas(64) GemmParams {
   // tile geometry
   int tw, th;            // A box extents, tw*th == 128, tw a power of two
   int tw_log2;
+  int ctas;              // 1, or 2 = CTA-pair tiles (tmB box is then BN/2 rows)
   int X, Y, Nimg;        // logical output extents per image
   int tiles_x, tiles_y;  // ceil(X/tw), ceil(Y/th)
   int N;                 // output channels (multiple of 32, or anything in TAIL mode with N <= 128)
@@ -67,6 +68,9 @@ struct alignas(64) GemmParams {
 
 // BN in {128, 256}.  Returns cudaError from the launch.
 cudaError_t launch_gemm(const GemmParams& p, int BN, int num_sms, cudaStream_t stream);
+void set_gemm_epilogue_variant(int v);  // tuning hook: 0 = row-per-thread stores, 1 = smem-transposed coalesced stores
+void set_gemm_pair_mode(int v);         // tuning hook: 1 = CTA-pair (cta_group::2) tiles where BN = 256 (default)
+int gemm_pair_mode();
 
 // ------------------------------------------------------------------------------------------------
 // Flash-style attention forward, head_dim 64, non-causal: O = softmax(Q K^T * scale) V per (sequence, head).
