@@ -121,6 +121,35 @@ bool build_gemm(GemmParams* gp, int* BN, const AView& a, const void* wt, int n_o
     snprintf(err, errlen, "conv weight pitch %d too small for C=%d", cin_pad, a.C);
     return false;
   }
+  // ---- epilogue path: TMA slabs when the output (and residual) is one dense-row tensor the box geometry can address ----
+  gp->epi_mode = EPI_DIRECT;
+  if (!tail && gemm_epilogue_variant() && !e.res2 && (e.out_f32 != nullptr) != (e.out_bf16 != nullptr) &&
+      !(e.out_bf16 && e.res1)) {
+    const bool f32 = e.out_f32 != nullptr;
+    const long long es = f32 ? 4 : 2;
+    const int bw = a.tw < 32 ? a.tw : 32;
+    // strides of extent-1 dimensions are never used for addressing: give them any legal value
+    const long long sx = e.sx, sy = a.Y > 1 ? e.sy : e.sx * a.X, sn = a.N > 1 ? e.sn : sy * a.Y;
+    const char* base = f32 ? reinterpret_cast<const char*>(e.out_f32) : reinterpret_cast<const char*>(e.out_bf16);
+    base += e.out_off * es;
+    const bool ok = sx > 0 && sy > 0 && sn > 0 && (sx * es) % 16 == 0 && (sy * es) % 16 == 0 && (sn * es) % 16 == 0 &&
+                    (reinterpret_cast<uintptr_t>(base) & 15) == 0 && sx >= n_out;
+    if (ok) {
+      const uint64_t od[4] = {(uint64_t)n_out, (uint64_t)a.X, (uint64_t)a.Y, (uint64_t)a.N};
+      const uint64_t os[4] = {(uint64_t)es, (uint64_t)(sx * es), (uint64_t)(sy * es), (uint64_t)(sn * es)};
+      const uint32_t ob[4] = {f32 ? 32u : 64u, (uint32_t)bw, (uint32_t)(32 / bw), 1u};
+      if (!make_tmap(&gp->tmOut, f32, base, 4, od, os, ob, err, errlen)) return false;
+      if (f32 && e.res1) {
+        const char* rb = reinterpret_cast<const char*>(e.res1) + e.out_off * es;
+        if ((reinterpret_cast<uintptr_t>(rb) & 15) != 0) {
+          snprintf(err, errlen, "residual base not 16-byte aligned");
+          return false;
+        }
+        if (!make_tmap(&gp->tmRes, true, rb, 4, od, os, ob, err, errlen)) return false;
+      }
+      gp->epi_mode = f32 ? EPI_TMA_F32 : EPI_TMA_BF16;
+    }
+  }
   gp->flags = e.flags;
   gp->bias = e.bias; gp->scale = e.scale; gp->res1 = e.res1; gp->res2 = e.res2;
   gp->out_f32 = e.out_f32; gp->out_bf16 = e.out_bf16;

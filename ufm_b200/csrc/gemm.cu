@@ -36,10 +36,10 @@ struct Cfg {
   static constexpr int B_ROWS = BN / CTAS;
   static constexpr int B_BYTES = B_ROWS * BK * 2;
   static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
-  static constexpr int STAGES = (STAGE_BYTES == 49152) ? 4 : 6;
-  static constexpr int BAR_BYTES = 256;
-  // epilogue staging: 8 warps x (32 x 32 fp32) transpose tiles; TAIL mode reuses it as [acc][half][row][4] floats
-  static constexpr int SCRATCH_BYTES = kEpiWarps * 32 * 32 * 4;
+  static constexpr int STAGES = (STAGE_BYTES == 49152) ? 3 : 5;
+  static constexpr int BAR_BYTES = 512;
+  // epilogue slabs: 8 warps x 2 x (32 rows x 128 B); TAIL mode reuses them as [acc][half][row][4] floats
+  static constexpr int SCRATCH_BYTES = kEpiWarps * 2 * 4096;
   static constexpr int SMEM_BYTES = 1024 + STAGES * STAGE_BYTES + BAR_BYTES + SCRATCH_BYTES;
   static constexpr int TMEM_COLS = 2 * BN;
 };
@@ -61,7 +61,7 @@ __device__ __forceinline__ float gelu_erf(float x) {
   return fmaf(-ax * 0.3989422804014327f, pl * e, fmaxf(x, 0.f));
 }
 
-template <int BN, int EPI, int CTAS>
+template <int BN, int CTAS>
 __global__ void __launch_bounds__(kThreads, 1) gemm_kernel(const __grid_constant__ GemmParams p) {
   using C = Cfg<BN, CTAS>;
   const uint32_t cta_rank = (CTAS == 2) ? cluster_ctarank() : 0u;
@@ -71,13 +71,14 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_kernel(const __grid_constant
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* sA = smem;
   uint8_t* sB = smem + C::STAGES * C::A_BYTES;
-  uint64_t* full = reinterpret_cast<uint64_t*>(smem + C::STAGES * C::STAGE_BYTES);
+  uint8_t* epi_smem = smem + C::STAGES * C::STAGE_BYTES;  // 8 warps x 2 x 4 KB TMA slabs (1024-byte aligned)
+  uint64_t* full = reinterpret_cast<uint64_t*>(epi_smem + C::SCRATCH_BYTES);
   uint64_t* empty = full + C::STAGES;
   uint64_t* tfull = empty + C::STAGES;
   uint64_t* tempty = tfull + 2;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty + 2);
-  uint8_t* stage_smem = smem + C::STAGES * C::STAGE_BYTES + C::BAR_BYTES;
-  float* scratch = reinterpret_cast<float*>(stage_smem);
+  uint64_t* resbar = tempty + 2;  // [8 warps][2 slabs] residual-slab "full" barriers
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(resbar + 2 * kEpiWarps);
+  float* scratch = reinterpret_cast<float*>(epi_smem);  // TAIL mode: [acc][half][row][4] floats
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -85,6 +86,8 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_kernel(const __grid_constant
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&p.tmA);
     tma_prefetch_desc(&p.tmB);
+    if (p.epi_mode != EPI_DIRECT) tma_prefetch_desc(&p.tmOut);
+    if (p.epi_mode == EPI_TMA_F32 && p.res1) tma_prefetch_desc(&p.tmRes);
   }
   if (warp == 1 && lane == 0) {
     for (int i = 0; i < C::STAGES; ++i) {
@@ -95,6 +98,7 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_kernel(const __grid_constant
       mbar_init(&tfull[i], 1);
       mbar_init(&tempty[i], kEpiWarps * CTAS);  // pair: the leader's barrier also collects the peer's epilogue warps
     }
+    for (int i = 0; i < 2 * kEpiWarps; ++i) mbar_init(&resbar[i], 1);
     fence_barrier_init();
   }
   if (warp == 2) {
@@ -199,16 +203,21 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_kernel(const __grid_constant
     const int half = e >> 2;
     constexpr int HALF_COLS = BN / 2;
     const bool tail = (p.flags & GEMM_TAIL) != 0;
-    float4* stg = reinterpret_cast<float4*>(stage_smem) + e * 256;  // this warp's 32x32 fp32 transpose tile (EPI 1)
-    const int g4 = lane & 7;     // column group (4 floats) owned after the transpose
-    const int rsub = lane >> 3;  // row within each group of 4 rows
-    int acc = 0;
-    uint32_t accphase = 0;
+    const int emode = p.epi_mode;
+    // TMA epilogues: two 4 KB slabs per warp = 32 rows x 128 bytes in the 128B-swizzle pattern (16-byte chunk j of row r
+    // lives at chunk j ^ (r & 7)), so a thread touches only its own row, conflict free, and the slab is the smem image of
+    // a (32 fp32 | 64 bf16) x 32-row TMA box.
+    uint8_t* wbuf = epi_smem + e * 8192;
+    uint64_t* rbar = resbar + e * 2;
+    uint32_t rph0 = 0, rph1 = 0;
+    const uint32_t sw = lane & 7;
     uint32_t tempty_remote[2] = {0u, 0u};
     if constexpr (CTAS == 2) {
       tempty_remote[0] = mapa_cluster(smem_u32(&tempty[0]), 0);
       tempty_remote[1] = mapa_cluster(smem_u32(&tempty[1]), 0);
     }
+    int acc = 0;
+    uint32_t accphase = 0;
     for (int tile = unit; tile < total_tiles; tile += num_units) {
       const int tn = tile % p.tiles_n;
       const int tm = (tile / p.tiles_n) * CTAS + (int)cta_rank;
@@ -216,212 +225,303 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_kernel(const __grid_constant
       const int ty = (tm / p.tiles_x) % p.tiles_y;
       const int img = tm / (p.tiles_x * p.tiles_y);
       const int n0 = tn * BN;
-      const int r = q * 32 + lane;
-      const int ly = r / p.tw;
-      const int lx = r - ly * p.tw;
-      const int x = tx * p.tw + lx, y = ty * p.th + ly;
-      const bool valid = (x < p.X) && (y < p.Y) && (img < p.Nimg);
-      const long long off = (long long)img * p.sN + (long long)y * p.sY + (long long)x * p.sX + p.out_off;
-      const long long off2 = (long long)img * p.r2N + (long long)y * p.r2Y + (long long)x * p.r2X;
+      const int c0 = n0 + half * HALF_COLS;  // first column of this warp
+      const uint32_t acc_addr = tmem_base + (uint32_t(q * 32) << 16) + uint32_t(acc * BN + half * HALF_COLS);
 
-      // the residual rows of this tile do not depend on the accumulator: pull them into L2 while the MMAs still run
-      if (valid && !tail) {
-        const int pc0 = n0 + half * HALF_COLS;
-        if (p.res1) {
-#pragma unroll
-          for (int c = 0; c < HALF_COLS / 32; ++c)
-            if (pc0 + c * 32 < p.N) prefetch_l2(p.res1 + off + pc0 + c * 32);
+      if (emode == EPI_TMA_F32) {
+        // ---- fp32 output (+ optional fp32 residual) through TMA: 32-column slabs -------------------------------------
+        const int wx = tx * p.tw + ((32 * q) & (p.tw - 1));
+        const int wy = ty * p.th + ((32 * q) >> p.tw_log2);
+        int nch = (p.N - c0 + 31) >> 5;
+        nch = nch < 0 ? 0 : (nch > HALF_COLS / 32 ? HALF_COLS / 32 : nch);
+        const bool has_res = p.res1 != nullptr;
+        if (lane == 0) {
+          bulk_wait_read<0>();  // the previous tile's stores have left both slabs
+          if (has_res) {
+            for (int c = 0; c < nch; ++c) {
+              if (c < 2) {
+                mbar_expect_tx(&rbar[c], 4096);
+                tma_load_4d(wbuf + c * 4096, &p.tmRes, &rbar[c], c0 + 32 * c, wx, wy, img);
+              } else {
+                tma_prefetch_4d(&p.tmRes, c0 + 32 * c, wx, wy, img);  // pull the rest into L2 under the mainloop
+              }
+            }
+          }
         }
-        if (p.res2) {
+        __syncwarp();
+        mbar_wait(&tfull[acc], accphase);
+        tc_fence_after();
+#pragma unroll 1
+        for (int c = 0; c < nch; ++c) {
+          uint8_t* buf = wbuf + (c & 1) * 4096;
+          uint8_t* rowp = buf + lane * 128;
+          if (has_res) {
+            if (c >= 1 && c + 1 < nch && lane == 0) {
+              bulk_wait_read<0>();  // slab (c+1)&1 was stored by chunk c-1
+              mbar_expect_tx(&rbar[(c + 1) & 1], 4096);
+              tma_load_4d(wbuf + ((c + 1) & 1) * 4096, &p.tmRes, &rbar[(c + 1) & 1], c0 + 32 * (c + 1), wx, wy, img);
+            }
+            if (c & 1) {
+              mbar_wait(&rbar[1], rph1);
+              rph1 ^= 1;
+            } else {
+              mbar_wait(&rbar[0], rph0);
+              rph0 ^= 1;
+            }
+          } else if (c >= 2) {
+            if (lane == 0) bulk_wait_read<1>();
+            __syncwarp();
+          }
+          uint32_t vr[32];
+          tmem_ld32(acc_addr + c * 32, vr);
+          tmem_ld_wait();
+          const int gcol = c0 + c * 32;
 #pragma unroll
-          for (int c = 0; c < HALF_COLS / 32; ++c)
-            if (pc0 + c * 32 < p.N) prefetch_l2(p.res2 + off2 + pc0 + c * 32);
+          for (int j = 0; j < 8; ++j) {
+            float4 v = make_float4(__uint_as_float(vr[4 * j]), __uint_as_float(vr[4 * j + 1]),
+                                   __uint_as_float(vr[4 * j + 2]), __uint_as_float(vr[4 * j + 3]));
+            if (p.bias) {
+              const float4 b4 = __ldg(reinterpret_cast<const float4*>(p.bias + gcol + 4 * j));
+              v.x += b4.x; v.y += b4.y; v.z += b4.z; v.w += b4.w;
+            }
+            if (p.flags & GEMM_GELU) {
+              v.x = gelu_erf(v.x); v.y = gelu_erf(v.y); v.z = gelu_erf(v.z); v.w = gelu_erf(v.w);
+            }
+            if (p.scale) {
+              const float4 s4 = __ldg(reinterpret_cast<const float4*>(p.scale + gcol + 4 * j));
+              v.x *= s4.x; v.y *= s4.y; v.z *= s4.z; v.w *= s4.w;
+            }
+            float4* sp = reinterpret_cast<float4*>(rowp + ((j ^ sw) << 4));
+            if (has_res) {
+              const float4 r4 = *sp;
+              v.x += r4.x; v.y += r4.y; v.z += r4.z; v.w += r4.w;
+            }
+            *sp = v;
+          }
+          fence_proxy_async_smem();
+          __syncwarp();
+          if (lane == 0) {
+            tma_store_4d(&p.tmOut, buf, gcol, wx, wy, img);
+            bulk_commit_group();
+          }
         }
-      }
-      mbar_wait(&tfull[acc], accphase);
-      tc_fence_after();
-      float part[4] = {0.f, 0.f, 0.f, 0.f};
-      if (EPI == 1 && !tail) {
-        // rows this thread stores after the transpose: q*32 + 4*i + rsub, i = 0..7
-        long long offs[8];
-        uint32_t vmask = 0;
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) {
+          if constexpr (CTAS == 2) mbar_arrive_cluster(tempty_remote[acc]);
+          else mbar_arrive(&tempty[acc]);
+        }
+      } else if (emode == EPI_TMA_BF16) {
+        // ---- bf16 output through TMA: 64-column slabs ----------------------------------------------------------------
+        const int wx = tx * p.tw + ((32 * q) & (p.tw - 1));
+        const int wy = ty * p.th + ((32 * q) >> p.tw_log2);
+        int nch = (p.N - c0 + 63) >> 6;
+        nch = nch < 0 ? 0 : (nch > HALF_COLS / 64 ? HALF_COLS / 64 : nch);
+        if (lane == 0) bulk_wait_read<0>();
+        __syncwarp();
+        mbar_wait(&tfull[acc], accphase);
+        tc_fence_after();
+#pragma unroll 1
+        for (int c = 0; c < nch; ++c) {
+          uint8_t* buf = wbuf + (c & 1) * 4096;
+          uint8_t* rowp = buf + lane * 128;
+          const int gcol = c0 + c * 64;
 #pragma unroll
-        for (int i = 0; i < 8; ++i) {
-          const int rr = q * 32 + 4 * i + rsub;
-          const int ly = rr >> p.tw_log2;
-          const int lx = rr & (p.tw - 1);
-          const int x = tx * p.tw + lx, y = ty * p.th + ly;
-          if (x < p.X && y < p.Y && img < p.Nimg) vmask |= 1u << i;
-          offs[i] = (long long)img * p.sN + (long long)y * p.sY + (long long)x * p.sX + p.out_off;
+          for (int h2 = 0; h2 < 2; ++h2) {
+            uint32_t vr[32];
+            tmem_ld32(acc_addr + c * 64 + h2 * 32, vr);
+            tmem_ld_wait();
+            if (gcol + h2 * 32 < p.N) {
+#pragma unroll
+              for (int j = 0; j < 4; ++j) {
+                float v[8];
+#pragma unroll
+                for (int i = 0; i < 8; ++i) v[i] = __uint_as_float(vr[8 * j + i]);
+                const int col = gcol + h2 * 32 + 8 * j;
+                if (p.bias) {
+                  const float4 b0 = __ldg(reinterpret_cast<const float4*>(p.bias + col));
+                  const float4 b1 = __ldg(reinterpret_cast<const float4*>(p.bias + col + 4));
+                  v[0] += b0.x; v[1] += b0.y; v[2] += b0.z; v[3] += b0.w;
+                  v[4] += b1.x; v[5] += b1.y; v[6] += b1.z; v[7] += b1.w;
+                }
+                if (p.flags & GEMM_GELU) {
+#pragma unroll
+                  for (int i = 0; i < 8; ++i) v[i] = gelu_erf(v[i]);
+                }
+                if (p.scale) {
+                  const float4 s0 = __ldg(reinterpret_cast<const float4*>(p.scale + col));
+                  const float4 s1 = __ldg(reinterpret_cast<const float4*>(p.scale + col + 4));
+                  v[0] *= s0.x; v[1] *= s0.y; v[2] *= s0.z; v[3] *= s0.w;
+                  v[4] *= s1.x; v[5] *= s1.y; v[6] *= s1.z; v[7] *= s1.w;
+                }
+                if (p.flags & GEMM_RELU_BF16) {
+#pragma unroll
+                  for (int i = 0; i < 8; ++i) v[i] = fmaxf(v[i], 0.f);
+                }
+                *reinterpret_cast<uint4*>(rowp + ((uint32_t(h2 * 4 + j) ^ sw) << 4)) =
+                    make_uint4(pack_bf16(v[0], v[1]), pack_bf16(v[2], v[3]), pack_bf16(v[4], v[5]), pack_bf16(v[6], v[7]));
+              }
+            }
+          }
+          fence_proxy_async_smem();
+          __syncwarp();
+          if (lane == 0) {
+            tma_store_4d(&p.tmOut, buf, gcol, wx, wy, img);
+            bulk_commit_group();
+          }
         }
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) {
+          if constexpr (CTAS == 2) mbar_arrive_cluster(tempty_remote[acc]);
+          else mbar_arrive(&tempty[acc]);
+        }
+      } else {
+        // ---- direct epilogue: one output row per thread (strided / broadcast residuals, dual outputs, TAIL mode) ------
+        const int r = q * 32 + lane;
+        const int ly = r / p.tw;
+        const int lx = r - ly * p.tw;
+        const int x = tx * p.tw + lx, y = ty * p.th + ly;
+        const bool valid = (x < p.X) && (y < p.Y) && (img < p.Nimg);
+        const long long off = (long long)img * p.sN + (long long)y * p.sY + (long long)x * p.sX + p.out_off;
+        const long long off2 = (long long)img * p.r2N + (long long)y * p.r2Y + (long long)x * p.r2X;
+
+        // the residual rows of this tile do not depend on the accumulator: pull them into L2 while the MMAs still run
+        if (valid && !tail) {
+          const int pc0 = n0 + half * HALF_COLS;
+          if (p.res1) {
+#pragma unroll
+            for (int c = 0; c < HALF_COLS / 32; ++c)
+              if (pc0 + c * 32 < p.N) prefetch_l2(p.res1 + off + pc0 + c * 32);
+          }
+          if (p.res2) {
+#pragma unroll
+            for (int c = 0; c < HALF_COLS / 32; ++c)
+              if (pc0 + c * 32 < p.N) prefetch_l2(p.res2 + off2 + pc0 + c * 32);
+          }
+        }
+        mbar_wait(&tfull[acc], accphase);
+        tc_fence_after();
+        float part[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll 1
         for (int c = 0; c < HALF_COLS / 32; ++c) {
           const int col0 = half * HALF_COLS + c * 32;
           const int gcol = n0 + col0;
           if (gcol >= p.N) break;
           uint32_t vr[32];
+          __syncwarp();  // tcgen05.ld is .sync.aligned: reconverge after the per-row predicated body
+          // issue the residual loads first so that their latency overlaps the TMEM read
+          float4 rr[8];
+          const bool has_r1 = valid && !tail && p.res1 != nullptr;
+          if (has_r1) {
+            const float4* rp = reinterpret_cast<const float4*>(p.res1 + off + gcol);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) rr[j] = rp[j];
+          }
           tmem_ld32(tmem_base + (uint32_t(q * 32) << 16) + uint32_t(acc * BN + col0), vr);
           tmem_ld_wait();
-          __syncwarp();  // previous chunk's reads of the staging tile are done
+          if (!valid) continue;
+          float v[32];
 #pragma unroll
-          for (int j = 0; j < 8; ++j)
-            stg[lane * 8 + (j ^ (lane & 7))] =
-                make_float4(__uint_as_float(vr[4 * j]), __uint_as_float(vr[4 * j + 1]), __uint_as_float(vr[4 * j + 2]),
-                            __uint_as_float(vr[4 * j + 3]));
-          __syncwarp();
-          const int mycol = gcol + g4 * 4;
-          float4 b4 = make_float4(0.f, 0.f, 0.f, 0.f), s4 = make_float4(1.f, 1.f, 1.f, 1.f);
-          if (p.bias) b4 = __ldg(reinterpret_cast<const float4*>(p.bias + mycol));
-          if (p.scale) s4 = __ldg(reinterpret_cast<const float4*>(p.scale + mycol));
-#pragma unroll
-          for (int i = 0; i < 8; ++i) {
-            const int row = 4 * i + rsub;
-            float4 v = stg[row * 8 + (g4 ^ (row & 7))];
-            if ((vmask >> i) & 1u) {
-            v.x += b4.x; v.y += b4.y; v.z += b4.z; v.w += b4.w;
-            if (p.flags & GEMM_GELU) {
-              v.x = gelu_erf(v.x); v.y = gelu_erf(v.y); v.z = gelu_erf(v.z); v.w = gelu_erf(v.w);
-            }
-            v.x *= s4.x; v.y *= s4.y; v.z *= s4.z; v.w *= s4.w;
-            if (p.res1) {
-              const float4 r4 = *reinterpret_cast<const float4*>(p.res1 + offs[i] + mycol);
-              v.x += r4.x; v.y += r4.y; v.z += r4.z; v.w += r4.w;
-            }
-            if (p.res2) {
-              const int rr = q * 32 + row;
-              const int x = tx * p.tw + (rr & (p.tw - 1)), y = ty * p.th + (rr >> p.tw_log2);
-              const long long off2 = (long long)img * p.r2N + (long long)y * p.r2Y + (long long)x * p.r2X;
-              const float4 r4 = *reinterpret_cast<const float4*>(p.res2 + off2 + mycol);
-              v.x += r4.x; v.y += r4.y; v.z += r4.z; v.w += r4.w;
-            }
-            if (p.out_f32) *reinterpret_cast<float4*>(p.out_f32 + offs[i] + mycol) = v;
-            if (p.out_bf16) {
-              if (p.flags & GEMM_RELU_BF16) {
-                v.x = fmaxf(v.x, 0.f); v.y = fmaxf(v.y, 0.f); v.z = fmaxf(v.z, 0.f); v.w = fmaxf(v.w, 0.f);
-              }
-              *reinterpret_cast<uint2*>(p.out_bf16 + offs[i] + mycol) = make_uint2(pack_bf16(v.x, v.y), pack_bf16(v.z, v.w));
-            }
-            }
-          }
-        }
-      }
-#pragma unroll 1
-      for (int c = 0; c < ((EPI == 0 || tail) ? HALF_COLS / 32 : 0); ++c) {
-        const int col0 = half * HALF_COLS + c * 32;
-        const int gcol = n0 + col0;
-        if (gcol >= p.N) break;
-        uint32_t vr[32];
-        __syncwarp();  // tcgen05.ld is .sync.aligned: reconverge after the per-row predicated body
-        // issue the residual loads first so that their latency overlaps the TMEM read
-        float4 rr[8];
-        const bool has_r1 = valid && !tail && p.res1 != nullptr;
-        if (has_r1) {
-          const float4* rp = reinterpret_cast<const float4*>(p.res1 + off + gcol);
-#pragma unroll
-          for (int j = 0; j < 8; ++j) rr[j] = rp[j];
-        }
-        tmem_ld32(tmem_base + (uint32_t(q * 32) << 16) + uint32_t(acc * BN + col0), vr);
-        tmem_ld_wait();
-        if (!valid) continue;
-        float v[32];
-#pragma unroll
-        for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(vr[j]);
-        if (p.bias) {
-#pragma unroll
-          for (int j = 0; j < 32; j += 4) {
-            const float4 b4 = __ldg(reinterpret_cast<const float4*>(p.bias + gcol + j));
-            v[j] += b4.x; v[j + 1] += b4.y; v[j + 2] += b4.z; v[j + 3] += b4.w;
-          }
-        }
-        if (tail) {
-#pragma unroll
-          for (int j = 0; j < 32; ++j) v[j] = fmaxf(v[j], 0.f);
-          for (int o = 0; o < p.tail_out; ++o) {
-            const float* w = p.w2 + (long long)o * p.N + gcol;
-            float s = 0.f;
+          for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(vr[j]);
+          if (p.bias) {
 #pragma unroll
             for (int j = 0; j < 32; j += 4) {
-              const float4 w4 = __ldg(reinterpret_cast<const float4*>(w + j));
-              s += v[j] * w4.x + v[j + 1] * w4.y + v[j + 2] * w4.z + v[j + 3] * w4.w;
+              const float4 b4 = __ldg(reinterpret_cast<const float4*>(p.bias + gcol + j));
+              v[j] += b4.x; v[j + 1] += b4.y; v[j + 2] += b4.z; v[j + 3] += b4.w;
             }
-            part[o] += s;
           }
-          continue;
-        }
-        if (p.flags & GEMM_GELU) {
-#pragma unroll
-          for (int j = 0; j < 32; ++j) v[j] = gelu_erf(v[j]);
-        }
-        if (p.scale) {
-#pragma unroll
-          for (int j = 0; j < 32; j += 4) {
-            const float4 s4 = __ldg(reinterpret_cast<const float4*>(p.scale + gcol + j));
-            v[j] *= s4.x; v[j + 1] *= s4.y; v[j + 2] *= s4.z; v[j + 3] *= s4.w;
-          }
-        }
-        if (has_r1) {
-#pragma unroll
-          for (int j = 0; j < 8; ++j) {
-            v[4 * j] += rr[j].x; v[4 * j + 1] += rr[j].y; v[4 * j + 2] += rr[j].z; v[4 * j + 3] += rr[j].w;
-          }
-        }
-        if (p.res2) {
-          const float4* rp = reinterpret_cast<const float4*>(p.res2 + off2 + gcol);
-#pragma unroll
-          for (int j = 0; j < 8; ++j) {
-            const float4 r4 = rp[j];
-            v[4 * j] += r4.x; v[4 * j + 1] += r4.y; v[4 * j + 2] += r4.z; v[4 * j + 3] += r4.w;
-          }
-        }
-        if (p.out_f32) {
-          float4* op = reinterpret_cast<float4*>(p.out_f32 + off + gcol);
-#pragma unroll
-          for (int j = 0; j < 8; ++j) op[j] = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
-        }
-        if (p.out_bf16) {
-          if (p.flags & GEMM_RELU_BF16) {
+          if (tail) {
 #pragma unroll
             for (int j = 0; j < 32; ++j) v[j] = fmaxf(v[j], 0.f);
-          }
-          uint4* op = reinterpret_cast<uint4*>(p.out_bf16 + off + gcol);
+            for (int o = 0; o < p.tail_out; ++o) {
+              const float* w = p.w2 + (long long)o * p.N + gcol;
+              float s = 0.f;
 #pragma unroll
-          for (int j = 0; j < 4; ++j) {
-            op[j] = make_uint4(pack_bf16(v[8 * j], v[8 * j + 1]), pack_bf16(v[8 * j + 2], v[8 * j + 3]),
-                               pack_bf16(v[8 * j + 4], v[8 * j + 5]), pack_bf16(v[8 * j + 6], v[8 * j + 7]));
+              for (int j = 0; j < 32; j += 4) {
+                const float4 w4 = __ldg(reinterpret_cast<const float4*>(w + j));
+                s += v[j] * w4.x + v[j + 1] * w4.y + v[j + 2] * w4.z + v[j + 3] * w4.w;
+              }
+              part[o] += s;
+            }
+            continue;
+          }
+          if (p.flags & GEMM_GELU) {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) v[j] = gelu_erf(v[j]);
+          }
+          if (p.scale) {
+#pragma unroll
+            for (int j = 0; j < 32; j += 4) {
+              const float4 s4 = __ldg(reinterpret_cast<const float4*>(p.scale + gcol + j));
+              v[j] *= s4.x; v[j + 1] *= s4.y; v[j + 2] *= s4.z; v[j + 3] *= s4.w;
+            }
+          }
+          if (has_r1) {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+              v[4 * j] += rr[j].x; v[4 * j + 1] += rr[j].y; v[4 * j + 2] += rr[j].z; v[4 * j + 3] += rr[j].w;
+            }
+          }
+          if (p.res2) {
+            const float4* rp = reinterpret_cast<const float4*>(p.res2 + off2 + gcol);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+              const float4 r4 = rp[j];
+              v[4 * j] += r4.x; v[4 * j + 1] += r4.y; v[4 * j + 2] += r4.z; v[4 * j + 3] += r4.w;
+            }
+          }
+          if (p.out_f32) {
+            float4* op = reinterpret_cast<float4*>(p.out_f32 + off + gcol);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) op[j] = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+          }
+          if (p.out_bf16) {
+            if (p.flags & GEMM_RELU_BF16) {
+#pragma unroll
+              for (int j = 0; j < 32; ++j) v[j] = fmaxf(v[j], 0.f);
+            }
+            uint4* op = reinterpret_cast<uint4*>(p.out_bf16 + off + gcol);
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+              op[j] = make_uint4(pack_bf16(v[8 * j], v[8 * j + 1]), pack_bf16(v[8 * j + 2], v[8 * j + 3]),
+                                 pack_bf16(v[8 * j + 4], v[8 * j + 5]), pack_bf16(v[8 * j + 6], v[8 * j + 7]));
+            }
           }
         }
-      }
-      // accumulator stage drained -> hand it back to the MMA warp
-      tc_fence_before();
-      __syncwarp();
-      if (lane == 0) {
-        if constexpr (CTAS == 2) mbar_arrive_cluster(tempty_remote[acc]);
-        else mbar_arrive(&tempty[acc]);
-      }
+        // accumulator stage drained -> hand it back to the MMA warp
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) {
+          if constexpr (CTAS == 2) mbar_arrive_cluster(tempty_remote[acc]);
+          else mbar_arrive(&tempty[acc]);
+        }
 
-      if (tail) {
-        // combine the two column halves of each row through smem (double-buffered by accumulator stage)
-        float* sc = scratch + acc * (2 * 128 * 4);
-        float4* mine = reinterpret_cast<float4*>(sc + (half * 128 + r) * 4);
-        *mine = make_float4(part[0], part[1], part[2], part[3]);
-        asm volatile("bar.sync %0, 64;" ::"r"(1 + q) : "memory");
-        if (half == 0 && valid) {
-          const float4 o4 = *reinterpret_cast<const float4*>(sc + (128 + r) * 4);
-          float yv[4] = {part[0] + o4.x, part[1] + o4.y, part[2] + o4.z, part[3] + o4.w};
-          const long long plane = (long long)p.Y * p.X;
-          for (int o = 0; o < p.tail_out; ++o) {
-            float t = yv[o] + p.tail_b2[o];
-            const long long idx = ((long long)img * p.tail_out + o) * plane + (long long)y * p.X + x;
-            if (p.out2) p.out2[idx] = t;
-            if (p.flags & GEMM_TAIL_SIGMOID) t = 1.0f / (1.0f + __expf(-t));
-            else t = t * p.tail_scale[o] + p.tail_shift[o];
-            p.out_f32[idx] = t;
+        if (tail) {
+          // combine the two column halves of each row through smem (double-buffered by accumulator stage)
+          float* sc = scratch + acc * (2 * 128 * 4);
+          float4* mine = reinterpret_cast<float4*>(sc + (half * 128 + r) * 4);
+          *mine = make_float4(part[0], part[1], part[2], part[3]);
+          asm volatile("bar.sync %0, 64;" ::"r"(1 + q) : "memory");
+          if (half == 0 && valid) {
+            const float4 o4 = *reinterpret_cast<const float4*>(sc + (128 + r) * 4);
+            float yv[4] = {part[0] + o4.x, part[1] + o4.y, part[2] + o4.z, part[3] + o4.w};
+            const long long plane = (long long)p.Y * p.X;
+            for (int o = 0; o < p.tail_out; ++o) {
+              float t = yv[o] + p.tail_b2[o];
+              const long long idx = ((long long)img * p.tail_out + o) * plane + (long long)y * p.X + x;
+              if (p.out2) p.out2[idx] = t;
+              if (p.flags & GEMM_TAIL_SIGMOID) t = 1.0f / (1.0f + __expf(-t));
+              else t = t * p.tail_scale[o] + p.tail_shift[o];
+              p.out_f32[idx] = t;
+            }
           }
         }
       }
       acc ^= 1;
       if (acc == 0) accphase ^= 1;
     }
+    if (emode != EPI_DIRECT && lane == 0) bulk_wait<0>();
   }
 
   tc_fence_before();
@@ -434,20 +534,20 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_kernel(const __grid_constant
   }
 }
 
-int g_gemm_epi = 0;   // epilogue variant (ufm_debug_flag 0): 0 = row-per-thread direct, 1 = smem-transposed coalesced
+int g_gemm_epi = 1;   // ufm_debug_flag 0: 1 = TMA-store epilogues where eligible (default), 0 = always the direct epilogue
 int g_gemm_pair = 1;  // ufm_debug_flag 1: allow CTA-pair (cta_group::2) tiles for BN = 256
 
-template <int BN, int EPI, int CTAS>
+template <int BN, int CTAS>
 static cudaError_t launch_one(const GemmParams& p, int grid, cudaStream_t stream) {
   using C = Cfg<BN, CTAS>;
   static bool attr = false;
   if (!attr) {
-    cudaError_t err = cudaFuncSetAttribute(gemm_kernel<BN, EPI, CTAS>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM_BYTES);
+    cudaError_t err = cudaFuncSetAttribute(gemm_kernel<BN, CTAS>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM_BYTES);
     if (err != cudaSuccess) return err;
     attr = true;
   }
   if (CTAS == 1) {
-    gemm_kernel<BN, EPI, CTAS><<<grid, kThreads, C::SMEM_BYTES, stream>>>(p);
+    gemm_kernel<BN, CTAS><<<grid, kThreads, C::SMEM_BYTES, stream>>>(p);
     return cudaGetLastError();
   }
   cudaLaunchConfig_t cfg = {};
@@ -462,12 +562,13 @@ static cudaError_t launch_one(const GemmParams& p, int grid, cudaStream_t stream
   at[0].val.clusterDim.z = 1;
   cfg.attrs = at;
   cfg.numAttrs = 1;
-  return cudaLaunchKernelEx(&cfg, gemm_kernel<BN, EPI, CTAS>, p);
+  return cudaLaunchKernelEx(&cfg, gemm_kernel<BN, CTAS>, p);
 }
 
 }  // namespace
 
 void set_gemm_epilogue_variant(int v) { g_gemm_epi = v; }
+int gemm_epilogue_variant() { return g_gemm_epi; }
 void set_gemm_pair_mode(int v) { g_gemm_pair = v; }
 int gemm_pair_mode() { return g_gemm_pair; }
 
@@ -479,10 +580,10 @@ cudaError_t launch_gemm(const GemmParams& p, int BN, int num_sms, cudaStream_t s
   int grid = total * ctas < num_sms ? total * ctas : num_sms / ctas * ctas;
   if (ctas == 2) {
     if (BN != 256) return cudaErrorInvalidValue;
-    return g_gemm_epi ? launch_one<256, 1, 2>(p, grid, stream) : launch_one<256, 0, 2>(p, grid, stream);
+    return launch_one<256, 2>(p, grid, stream);
   }
-  if (BN == 256) return g_gemm_epi ? launch_one<256, 1, 1>(p, grid, stream) : launch_one<256, 0, 1>(p, grid, stream);
-  if (BN == 128) return g_gemm_epi ? launch_one<128, 1, 1>(p, grid, stream) : launch_one<128, 0, 1>(p, grid, stream);
+  if (BN == 256) return launch_one<256, 1>(p, grid, stream);
+  if (BN == 128) return launch_one<128, 1>(p, grid, stream);
   return cudaErrorInvalidValue;
 }
 

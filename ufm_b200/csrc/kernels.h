@@ -13,6 +13,9 @@ namespace ufm {
 // ------------------------------------------------------------------------------------------------
 bool make_tmap_bf16(CUtensorMap* out, const void* base, int rank, const uint64_t* dims, const uint64_t* strides_bytes,
                     const uint32_t* box, char* err, int errlen);
+// same for fp32 (is_f32) or bf16 elements
+bool make_tmap(CUtensorMap* out, bool is_f32, const void* base, int rank, const uint64_t* dims,
+               const uint64_t* strides_bytes, const uint32_t* box, char* err, int errlen);
 
 // ------------------------------------------------------------------------------------------------
 // tcgen05 GEMM / implicit-GEMM convolution.
@@ -32,9 +35,20 @@ enum : uint32_t {
   GEMM_TAIL_SIGMOID = 1u << 3,
 };
 
+// Epilogue paths of the GEMM kernel (chosen per launch by the host, engine.cu build_gemm):
+//   EPI_DIRECT    one output row per thread, vector loads/stores straight to global (any combination of outputs/residuals,
+//                 TAIL mode); costs 32 L1 wavefronts per warp instruction, so it paces short-K GEMMs
+//   EPI_TMA_F32   fp32 output, optional fp32 residual with the same addressing (in-place residual stream): 32-column
+//                 slabs staged in swizzled smem, residual slab in by TMA load, result out by TMA store
+//   EPI_TMA_BF16  bf16 output only: 64-column slabs, out by TMA store
+enum : int { EPI_DIRECT = 0, EPI_TMA_F32 = 1, EPI_TMA_BF16 = 2 };
+
 struct alignas(64) GemmParams {
   CUtensorMap tmA;
   CUtensorMap tmB;
+  CUtensorMap tmOut;     // EPI_TMA_*: 4-D (N, X, Y, Nimg) over the output, box (32 fp32 | 64 bf16, bw, 32/bw, 1)
+  CUtensorMap tmRes;     // EPI_TMA_F32 with res1: same geometry over the residual
+  int epi_mode;
   // tile geometry
   int tw, th;            // A box extents, tw*th == 128, tw a power of two
   int tw_log2;
@@ -68,7 +82,8 @@ struct alignas(64) GemmParams {
 
 // BN in {128, 256}.  Returns cudaError from the launch.
 cudaError_t launch_gemm(const GemmParams& p, int BN, int num_sms, cudaStream_t stream);
-void set_gemm_epilogue_variant(int v);  // tuning hook: 0 = row-per-thread stores, 1 = smem-transposed coalesced stores
+void set_gemm_epilogue_variant(int v);  // tuning hook: 1 = TMA-store epilogues where eligible (default), 0 = direct only
+int gemm_epilogue_variant();
 void set_gemm_pair_mode(int v);         // tuning hook: 1 = CTA-pair (cta_group::2) tiles where BN = 256 (default)
 int gemm_pair_mode();
 

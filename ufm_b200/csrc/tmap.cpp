@@ -27,6 +27,11 @@ static EncodeTiledFn get_encode() {
 
 bool make_tmap_bf16(CUtensorMap* out, const void* base, int rank, const uint64_t* dims, const uint64_t* strides_bytes,
                     const uint32_t* box, char* err, int errlen) {
+  return make_tmap(out, false, base, rank, dims, strides_bytes, box, err, errlen);
+}
+
+bool make_tmap(CUtensorMap* out, bool is_f32, const void* base, int rank, const uint64_t* dims,
+               const uint64_t* strides_bytes, const uint32_t* box, char* err, int errlen) {
   EncodeTiledFn fn = get_encode();
   if (!fn) {
     snprintf(err, errlen, "cuTensorMapEncodeTiled entry point unavailable");
@@ -42,7 +47,7 @@ bool make_tmap_bf16(CUtensorMap* out, const void* base, int rank, const uint64_t
     es[i] = 1;
     if (i > 0) gstr[i - 1] = strides_bytes[i];
   }
-  CUresult r = fn(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, (cuuint32_t)rank, const_cast<void*>(base), gdim, gstr, bx, es,
+  CUresult r = fn(out, is_f32 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, (cuuint32_t)rank, const_cast<void*>(base), gdim, gstr, bx, es,
                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) {
