@@ -221,6 +221,10 @@ def run_engine(args):
         raise SystemExit("bench.py: no CUDA device (ufm_b200 has no CPU path; use --impl reference for the CPU baseline)")
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
+    # keep stdout for the one JSON line: libraries (NCCL's version banner) write to fd 1 during init
+    sys.stdout.flush()
+    saved_fd = os.dup(1)
+    os.dup2(2, 1)
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
     g.build()
@@ -339,8 +343,11 @@ def run_engine(args):
         v, threads, ts = cpu_reference_pairs_per_s(cfg, refine, n_calls=args.cpu_calls, warmup=0)
         line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": threads, "kind": "port",
                                 "sample": f"{len(ts)} call(s) of one 560x420 pair (batch 1) of the same model, CPU fp32 oracle"}
+    sys.stdout.flush()
+    os.dup2(saved_fd, 1)
     if rank == 0:
-        print(json.dumps(line))
+        print(json.dumps(line), flush=True)
+    os.dup2(2, 1)
     if world > 1:
         dist.destroy_process_group()
     return 0
