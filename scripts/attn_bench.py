@@ -24,7 +24,7 @@ def main():
     from ufm_b200 import _lib
 
     lib = _lib.load()
-    variants = [int(v) for v in (sys.argv[1] if len(sys.argv) > 1 else "0").split(",")]
+    variants = [int(v) for v in (sys.argv[1] if len(sys.argv) > 1 else "4").split(",")]
     for name, n_seq, S, heads in [("enc", 32, 1201, 16), ("info", 16, 2400, 12), ("hires.enc", 8, 4801, 16)]:
         D = heads * 64
         gen = torch.Generator(device="cuda").manual_seed(0)
@@ -32,6 +32,7 @@ def main():
         t = qkv[: 2 * S].float().view(2, S, 3, heads, 64).permute(2, 0, 3, 1, 4)
         ref = F.scaled_dot_product_attention(t[0], t[1], t[2], scale=0.125).transpose(1, 2).reshape(2 * S, D)
         for var in variants:
+            lib.ufm_debug_flag(2, var)
             for _ in range(3):
                 out = ops.attention(qkv, n_seq, S, heads, 0.125)
             torch.cuda.synchronize()

@@ -5,21 +5,24 @@
 // (UC/models/utils/transformer_blocks.py:174-176; 2*h*w tokens per pair for global attention, h*w per view on the
 // odd layers of alternating attention).
 //
-// One CTA = one 128-row query tile of one (sequence, head); TWO CTAs are resident per SM (256 TMEM columns and
-// ~112 KB of shared memory each), so the tensor pipe, the MUFU (exp2) pipe and the TMA engine of an SM are shared by
-// two independent tiles: while one tile is in its softmax the other one's MMAs run, and the prologue / epilogue of a
-// CTA overlaps the main loop of its neighbour.  With head_dim 64 the kernel is bound by the 16 exp2/clk/SM of the
-// MUFU pipe (1024 clk per 128x128 tile against 512 clk of MMA), not by the tensor pipe.
-//   warp 0      TMA: Q once; K_j,V_j through a 3-stage ring, straight out of the fused qkv buffer
-//               ([tokens, 3, heads, 64]) with a 4-D tensor map, so no head-major copy of q/k/v is ever made
+// PERSISTENT kernel, two CTAs resident per SM (256 TMEM columns and ~97 KB of shared memory each): every CTA walks
+// a strided list of work items (one item = one 128-row query tile of one (sequence, head)), so barrier setup, the
+// TMEM allocation and the first TMA round trip are paid once per CTA instead of once per tile, and the K/V/Q
+// prefetch of the next tile runs underneath the last iterations of the current one.  The tensor pipe, the MUFU
+// (exp2) pipe and the TMA engine of an SM are shared by two independent tile streams.  With head_dim 64 the kernel
+// is bound by the 16 exp2/clk/SM of the MUFU pipe (1024 clk per 128x128 tile against 512 clk of MMA), not by the
+// tensor pipe.
+//   warp 0      TMA: Q through a 2-deep ring, K_j and V_j through separate 2-deep rings, straight out of the fused
+//               qkv buffer ([tokens, 3, heads, 64]) with a 4-D tensor map: no head-major copy of q/k/v is ever made
 //   warp 1      MMA issuer (one thread).  S = Q K_j^T: A=Q, B=K_j (both K-major SW128 smem).  O += P V_j: A=P read
 //               from TENSOR MEMORY (bf16 pairs written there by the softmax threads, no smem round trip), B=V_j as
-//               MN-major SW128 (the row-major [kv,64] tile as loaded).  S_{j+1} is issued as soon as the softmax
-//               threads have pulled S_j into registers, so it runs underneath the exponentials of step j.
+//               MN-major SW128 (the row-major [kv,64] tile as loaded).  S_{g+1} is issued as soon as the softmax
+//               threads have pulled S_g into registers, so it runs underneath the exponentials of step g -- also
+//               across tile boundaries.  A ragged last K/V tile with <= 64 keys is run as N = 64 / K = 64 MMAs.
 //   warp 2      TMEM allocator: S (128 cols), P (64 cols, bf16x2), O (64 cols)
-//   warps 4-7   softmax warpgroup, one query row per thread, the whole 128-wide S row in registers (setmaxnreg):
-//               online softmax in fp32 with exp2 and lazy rescale (O is rescaled in TMEM only when the row max grows by
-//               more than 2^8), P -> bf16 -> TMEM
+//   warps 4-7   softmax warpgroup, one query row per thread, the whole S row in registers: 3-input max tree,
+//               packed f32x2 FMA / ADD around the exp2, online softmax with lazy rescale (O is rescaled in TMEM only
+//               when the row max grows by more than 2^8), P -> bf16 -> TMEM; then the tile epilogue O / l -> bf16.
 #include <stdio.h>
 
 #include "kernels.h"
@@ -31,19 +34,69 @@ namespace {
 
 constexpr int kThreads = 256;
 constexpr int TILE_BYTES = 128 * 64 * 2;  // 16 KB: one [128 x 64] bf16 SW128 tile
-constexpr int KV_STAGES = 3;
+constexpr int Q_STAGES = 2, K_STAGES = 3, V_STAGES = 2;
 constexpr int OFF_Q = 0;
-constexpr int OFF_K = OFF_Q + TILE_BYTES;
-constexpr int OFF_V = OFF_K + KV_STAGES * TILE_BYTES;
-constexpr int OFF_BAR = OFF_V + KV_STAGES * TILE_BYTES;
-constexpr int SMEM_BYTES = OFF_BAR + 128;  // 114816 B: two CTAs per SM
+constexpr int OFF_K = OFF_Q + Q_STAGES * TILE_BYTES;
+constexpr int OFF_V = OFF_K + K_STAGES * TILE_BYTES;
+constexpr int OFF_BAR = OFF_V + V_STAGES * TILE_BYTES;
+constexpr int SMEM_BYTES = OFF_BAR + 256;  // 114944 B: two CTAs per SM
 constexpr int TMEM_COLS = 256;
 constexpr uint32_t TM_S = 0, TM_P = 128, TM_O = 192;
+int g_attn_poly = 4;  // every n-th pair of exponentials of a full tile runs on the FMA pipe (0 = never); ufm_debug_flag 2
 
 __device__ __forceinline__ float ex2(float x) {
   float y;
   asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
   return y;
+}
+// packed f32x2 arithmetic (one issue slot for two lanes of work)
+__device__ __forceinline__ uint64_t pack2(float a, float b) {
+  uint64_t r;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(a), "f"(b));
+  return r;
+}
+__device__ __forceinline__ void unpack2(uint64_t v, float& a, float& b) {
+  asm("mov.b64 {%0, %1}, %2;" : "=f"(a), "=f"(b) : "l"(v));
+}
+__device__ __forceinline__ uint64_t fma2(uint64_t a, uint64_t b, uint64_t c) {
+  uint64_t d;
+  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c));
+  return d;
+}
+__device__ __forceinline__ uint64_t add2(uint64_t a, uint64_t b) {
+  uint64_t d;
+  asm("add.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+  return d;
+}
+
+__device__ __forceinline__ uint64_t add2_rm(uint64_t a, uint64_t b) {
+  uint64_t d;
+  asm("add.rm.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+  return d;
+}
+// exp2 of two values on the FMA / ALU pipes (Cody-Waite split + degree-3 minimax polynomial of 2^f on [0,1), relative
+// error 8.8e-5: far below the bf16 rounding of P), so that a fixed share of the exponentials does not occupy the
+// MUFU pipe, which bounds this kernel.  x + 1.5*2^23 rounded DOWN leaves floor(x) in the low mantissa bits; the
+// integer add of (bits << 23) puts it into the exponent of the polynomial value.
+__device__ __forceinline__ void ex2_poly2(float x0, float x1, float& p0, float& p1) {
+  constexpr float kMagic = 12582912.0f;
+  x0 = fmaxf(x0, -126.0f);
+  x1 = fmaxf(x1, -126.0f);
+  const uint64_t x = pack2(x0, x1);
+  const uint64_t t = add2_rm(x, pack2(kMagic, kMagic));
+  const uint64_t fl = add2(t, pack2(-kMagic, -kMagic));
+  float fl0, fl1;
+  unpack2(fl, fl0, fl1);
+  const uint64_t f = add2(x, pack2(-fl0, -fl1));
+  uint64_t r = fma2(f, pack2(0.077119089663028717041015625f, 0.077119089663028717041015625f),
+                    pack2(0.227564394474029541015625f, 0.227564394474029541015625f));
+  r = fma2(r, f, pack2(0.695146143436431884765625f, 0.695146143436431884765625f));
+  r = fma2(r, f, pack2(1.0f, 1.0f));
+  float t0, t1, r0, r1;
+  unpack2(t, t0, t1);
+  unpack2(r, r0, r1);
+  p0 = __uint_as_float(__float_as_uint(r0) + (__float_as_uint(t0) << 23));
+  p1 = __uint_as_float(__float_as_uint(r1) + (__float_as_uint(t1) << 23));
 }
 
 __device__ __forceinline__ void tmem_ld32_at(uint32_t taddr, uint32_t* v) {
@@ -53,23 +106,179 @@ __device__ __forceinline__ void tmem_st32_at(uint32_t taddr, const uint32_t* v) 
   tmem_st32(taddr, *reinterpret_cast<const uint32_t(*)[32]>(v));
 }
 
+// max over N values as a tree of 3-input maxima (FMNMX3): depth ~log3(N) instead of a few long dependent chains
+template <int N>
+__device__ __forceinline__ float tree_max(const float (&v)[N]) {
+  if constexpr (N == 1) {
+    return v[0];
+  } else if constexpr (N == 2) {
+    return fmaxf(v[0], v[1]);
+  } else {
+    constexpr int M = (N + 2) / 3;
+    float w[M];
+#pragma unroll
+    for (int i = 0; i < N / 3; ++i) w[i] = fmaxf(fmaxf(v[3 * i], v[3 * i + 1]), v[3 * i + 2]);
+    if constexpr (N % 3 == 1) w[M - 1] = v[N - 1];
+    if constexpr (N % 3 == 2) w[M - 1] = fmaxf(v[N - 2], v[N - 1]);
+    return tree_max<M>(w);
+  }
+}
+
+struct Bars {
+  uint64_t q_full[Q_STAGES], q_free[Q_STAGES];
+  uint64_t k_full[K_STAGES], k_empty[K_STAGES];
+  uint64_t v_full[V_STAGES], v_empty[V_STAGES];
+  uint64_t s_full;  // S_g in TMEM             (MMA -> softmax)
+  uint64_t s_free;  // S_g pulled to registers  (softmax -> MMA), 4 warp arrivals
+  uint64_t p_full;  // P_g in TMEM              (softmax -> MMA), 4 warp arrivals
+  uint64_t o_done;  // O += P_g V_g finished    (MMA -> softmax)
+  uint32_t tmem_slot;
+};
+static_assert(sizeof(Bars) <= 256, "barrier block");
+
+// One softmax step on NC (= 128, or 64 for a short ragged tail) key columns.  g = global step index of this CTA
+// (runs on across tiles: it is the phase counter of the s/p/o barriers), j = step index within the tile.
+template <int NC, int VAR>
+__device__ __forceinline__ void softmax_step(Bars* b, uint32_t s_addr, uint32_t p_addr, uint32_t o_addr, uint32_t g, int j,
+                                             int kv_left, float sl2, float& m_ref, float& l, int lane) {
+  constexpr int POLY = VAR & 15;
+  constexpr bool SCALAR = (VAR & 16) != 0, SPLIT_LD = (VAR & 32) != 0 && NC == 128, EARLY_ST = (VAR & 64) != 0 && NC == 128;
+  uint32_t s[NC];
+  mbar_wait(&b->s_full, g & 1);
+  tc_fence_after();
+  float tmax;
+  if constexpr (SPLIT_LD) {
+    // second half of the row is still in flight while the maximum of the first half is taken
+    tmem_ld32_at(s_addr, s);
+    tmem_ld32_at(s_addr + 32, s + 32);
+    tmem_ld_wait();
+    tmem_ld32_at(s_addr + 64, s + 64);
+    tmem_ld32_at(s_addr + 96, s + 96);
+    if (kv_left < 64) {
+#pragma unroll
+      for (int i = 0; i < 64; ++i)
+        if (i >= kv_left) s[i] = 0xff800000u;
+    }
+    const float ma = tree_max<64>(*reinterpret_cast<const float(*)[64]>(s));
+    tmem_ld_wait();
+    tc_fence_before();
+    __syncwarp();
+    if (lane == 0) mbar_arrive(&b->s_free);
+    if (kv_left < NC) {
+#pragma unroll
+      for (int i = 64; i < NC; ++i)
+        if (i >= kv_left) s[i] = 0xff800000u;
+    }
+    tmax = fmaxf(ma, tree_max<64>(*reinterpret_cast<const float(*)[64]>(s + 64)));
+  } else {
+#pragma unroll
+    for (int c = 0; c < NC / 32; ++c) tmem_ld32_at(s_addr + c * 32, s + c * 32);
+    tmem_ld_wait();
+    tc_fence_before();
+    __syncwarp();
+    if (lane == 0) mbar_arrive(&b->s_free);
+    if (kv_left < NC) {
+#pragma unroll
+      for (int i = 0; i < NC; ++i)
+        if (i >= kv_left) s[i] = 0xff800000u;  // -inf
+    }
+    tmax = tree_max<NC>(*reinterpret_cast<const float(*)[NC]>(s));
+  }
+  if (j == 0) {
+    m_ref = tmax;
+  } else {
+    const bool need = (tmax - m_ref) * sl2 > 8.0f;
+    if (__any_sync(0xffffffffu, need)) {
+      mbar_wait(&b->o_done, (g - 1) & 1);  // PV_{g-1} finished: O stable
+      tc_fence_after();
+      float alpha = 1.0f;
+      if (need) {
+        alpha = ex2((m_ref - tmax) * sl2);
+        m_ref = tmax;
+      }
+      l *= alpha;
+#pragma unroll 1
+      for (int c = 0; c < 2; ++c) {
+        uint32_t v[32];
+        tmem_ld32(o_addr + c * 32, v);
+        tmem_ld_wait();
+#pragma unroll
+        for (int i = 0; i < 32; ++i) v[i] = __float_as_uint(__uint_as_float(v[i]) * alpha);
+        tmem_st32(o_addr + c * 32, v);
+      }
+      tmem_st_wait();
+    }
+  }
+  // p = exp2(s * scale*log2e - m_ref * scale*log2e), row sum, bf16 pairs
+  const float mb = -m_ref * sl2;
+  const uint64_t sl2_2 = pack2(sl2, sl2), mb_2 = pack2(mb, mb);
+  uint64_t sum_a = pack2(0.f, 0.f), sum_b = sum_a;
+  float fs0 = 0.f, fs1 = 0.f;
+#pragma unroll
+  for (int i = 0; i < NC / 2; ++i) {
+    float x0, x1, p0, p1;
+    const bool poly = POLY > 0 && (i % (POLY > 0 ? POLY : 1)) == POLY - 1;
+    if (SCALAR && !poly) {
+      x0 = fmaf(__uint_as_float(s[2 * i]), sl2, mb);
+      x1 = fmaf(__uint_as_float(s[2 * i + 1]), sl2, mb);
+    } else {
+      unpack2(fma2(pack2(__uint_as_float(s[2 * i]), __uint_as_float(s[2 * i + 1])), sl2_2, mb_2), x0, x1);
+    }
+    if (poly) {
+      ex2_poly2(x0, x1, p0, p1);
+    } else {
+      p0 = ex2(x0);
+      p1 = ex2(x1);
+    }
+    if (SCALAR) {
+      fs0 += p0;
+      fs1 += p1;
+    } else {
+      if (i & 1) sum_b = add2(sum_b, pack2(p0, p1));
+      else sum_a = add2(sum_a, pack2(p0, p1));
+    }
+    s[i] = pack_bf16(p0, p1);
+    if (EARLY_ST && i == NC / 4 - 1) {
+      // first half of P leaves for tensor memory while the second half is still being exponentiated
+      if (j > 0) {
+        mbar_wait(&b->o_done, (g - 1) & 1);  // PV_{g-1} has consumed the previous P
+        tc_fence_after();
+      }
+      tmem_st32_at(p_addr, s);
+    }
+  }
+  {
+    float a0, a1;
+    unpack2(add2(sum_a, sum_b), a0, a1);
+    l += (a0 + a1) + (fs0 + fs1);
+  }
+  if constexpr (EARLY_ST) {
+    tmem_st32_at(p_addr + 32, s + 32);
+  } else {
+    if (j > 0) {
+      mbar_wait(&b->o_done, (g - 1) & 1);  // PV_{g-1} has consumed the previous P
+      tc_fence_after();
+    }
+#pragma unroll
+    for (int c = 0; c < NC / 64; ++c) tmem_st32_at(p_addr + c * 32, s + c * 32);
+  }
+  tmem_st_wait();
+  tc_fence_before();
+  __syncwarp();
+  if (lane == 0) mbar_arrive(&b->p_full);
+}
+
+template <int VAR>
 __global__ void __launch_bounds__(kThreads, 2) attn_kernel(const __grid_constant__ AttnParams p) {
   extern __shared__ __align__(1024) uint8_t smem[];
-  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + OFF_BAR);
-  uint64_t* q_full = bars;                   // 1
-  uint64_t* kv_full = bars + 1;              // KV_STAGES
-  uint64_t* kv_empty = kv_full + KV_STAGES;  // KV_STAGES
-  uint64_t* s_full = kv_empty + KV_STAGES;   // S_j in TMEM            (MMA -> softmax)
-  uint64_t* s_free = s_full + 1;             // S_j pulled to registers (softmax -> MMA), 4 warp arrivals
-  uint64_t* p_full = s_free + 1;             // P_j in TMEM             (softmax -> MMA), 4 warp arrivals
-  uint64_t* o_done = p_full + 1;             // O += P_j V_j finished   (MMA -> softmax)
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(o_done + 1);
+  Bars* b = reinterpret_cast<Bars*>(smem + OFF_BAR);
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
-  const int qblk = blockIdx.x, head = blockIdx.y, seq = blockIdx.z;
-  const int q0 = qblk * 128;
   const int n_kv = (p.seq_len + 127) / 128;
+  const int kv_tail = p.seq_len - (n_kv - 1) * 128;  // valid keys in the last K/V tile (1..128)
+  const bool tail64 = kv_tail <= 64;
+  const int n_my = (p.n_items - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;  // tiles this CTA walks (>= 1)
 
   if (threadIdx.x == 0) {
     if (smem_u32(smem) & 1023u) {
@@ -79,175 +288,171 @@ __global__ void __launch_bounds__(kThreads, 2) attn_kernel(const __grid_constant
     tma_prefetch_desc(&p.tmQKV);
   }
   if (warp == 1 && lane == 0) {
-    mbar_init(q_full, 1);
-    for (int i = 0; i < KV_STAGES; ++i) {
-      mbar_init(&kv_full[i], 1);
-      mbar_init(&kv_empty[i], 1);
+    for (int i = 0; i < Q_STAGES; ++i) {
+      mbar_init(&b->q_full[i], 1);
+      mbar_init(&b->q_free[i], 1);
     }
-    mbar_init(s_full, 1);
-    mbar_init(s_free, 4);
-    mbar_init(p_full, 4);
-    mbar_init(o_done, 1);
+    for (int i = 0; i < K_STAGES; ++i) {
+      mbar_init(&b->k_full[i], 1);
+      mbar_init(&b->k_empty[i], 1);
+    }
+    for (int i = 0; i < V_STAGES; ++i) {
+      mbar_init(&b->v_full[i], 1);
+      mbar_init(&b->v_empty[i], 1);
+    }
+    mbar_init(&b->s_full, 1);
+    mbar_init(&b->s_free, 4);
+    mbar_init(&b->p_full, 4);
+    mbar_init(&b->o_done, 1);
     fence_barrier_init();
   }
-  if (warp == 2) tmem_alloc<TMEM_COLS>(tmem_slot);
+  if (warp == 2) tmem_alloc<TMEM_COLS>(&b->tmem_slot);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
-  const uint32_t tmem_base = *tmem_slot;
+  const uint32_t tmem_base = b->tmem_slot;
 
   if (warp < 4) {
     setmaxnreg_dec<48>();
     if (warp == 0 && lane == 0) {
-      mbar_expect_tx(q_full, TILE_BYTES);
-      tma_load_4d(smem + OFF_Q, &p.tmQKV, q_full, 0, head, q0, seq);
-      int stage = 0;
-      uint32_t phase = 0;
-      for (int j = 0; j < n_kv; ++j) {
-        mbar_wait(&kv_empty[stage], phase ^ 1);
-        mbar_expect_tx(&kv_full[stage], 2 * TILE_BYTES);
-        tma_load_4d(smem + OFF_K + stage * TILE_BYTES, &p.tmQKV, &kv_full[stage], 0, p.heads + head, j * 128, seq);
-        tma_load_4d(smem + OFF_V + stage * TILE_BYTES, &p.tmQKV, &kv_full[stage], 0, 2 * p.heads + head, j * 128, seq);
-        if (++stage == KV_STAGES) {
-          stage = 0;
-          phase ^= 1;
+      // ---------------------------------------------------------------- TMA producer
+      // K runs one step ahead of V: K_{g+1} is needed when softmax step g starts (S_{g+1} is issued then), V_g only
+      // when it ends, and a V stage frees one step later than a K stage -- loading in the order K_{g+1}, V_g keeps
+      // two softmax steps of lead on both rings instead of gating K behind the V wait.
+      struct Cur { int t, j, head, seq, qblk; uint32_t g; };
+      auto decode = [&](Cur& c) {
+        const int w = blockIdx.x + c.t * gridDim.x;
+        c.qblk = w % p.n_qblk;
+        const int hs = w / p.n_qblk;
+        c.head = hs % p.heads;
+        c.seq = hs / p.heads;
+      };
+      auto advance = [&](Cur& c) {
+        ++c.g;
+        if (++c.j == n_kv) {
+          c.j = 0;
+          ++c.t;
+          if (c.t < n_my) decode(c);
         }
+      };
+      auto load_k = [&](Cur& c) {
+        if (c.j == 0) {
+          const int qs = c.t % Q_STAGES;
+          if (c.t >= Q_STAGES) mbar_wait(&b->q_free[qs], ((c.t / Q_STAGES) - 1) & 1);
+          mbar_expect_tx(&b->q_full[qs], TILE_BYTES);
+          tma_load_4d(smem + OFF_Q + qs * TILE_BYTES, &p.tmQKV, &b->q_full[qs], 0, c.head, c.qblk * 128, c.seq);
+        }
+        const int ks = c.g % K_STAGES;
+        mbar_wait(&b->k_empty[ks], ((c.g / K_STAGES) & 1) ^ 1);
+        mbar_expect_tx(&b->k_full[ks], TILE_BYTES);
+        tma_load_4d(smem + OFF_K + ks * TILE_BYTES, &p.tmQKV, &b->k_full[ks], 0, p.heads + c.head, c.j * 128, c.seq);
+        advance(c);
+      };
+      auto load_v = [&](Cur& c) {
+        const int vs = c.g % V_STAGES;
+        mbar_wait(&b->v_empty[vs], ((c.g / V_STAGES) & 1) ^ 1);
+        mbar_expect_tx(&b->v_full[vs], TILE_BYTES);
+        tma_load_4d(smem + OFF_V + vs * TILE_BYTES, &p.tmQKV, &b->v_full[vs], 0, 2 * p.heads + c.head, c.j * 128, c.seq);
+        advance(c);
+      };
+      Cur ck{0, 0, 0, 0, 0, 0}, cv{0, 0, 0, 0, 0, 0};
+      decode(ck);
+      decode(cv);
+      load_k(ck);
+      while (cv.t < n_my) {
+        if (ck.t < n_my) load_k(ck);
+        load_v(cv);
       }
     } else if (warp == 1 && lane == 0) {
-      constexpr uint32_t idesc_s = umma_idesc_bf16(128, 128, 0, 0);
+      // ---------------------------------------------------------------- MMA issuer
+      constexpr uint32_t idesc_s128 = umma_idesc_bf16(128, 128, 0, 0);
+      constexpr uint32_t idesc_s64 = umma_idesc_bf16(128, 64, 0, 0);
       constexpr uint32_t idesc_pv = umma_idesc_bf16(128, 64, 0, 1);  // B = V, MN-major
       const uint32_t q_addr = smem_u32(smem + OFF_Q);
       const uint32_t k_addr = smem_u32(smem + OFF_K);
       const uint32_t v_addr = smem_u32(smem + OFF_V);
-      auto issue_s = [&](int stage) {
+      const uint32_t G = (uint32_t)n_my * (uint32_t)n_kv;
+      uint32_t gs = 0;       // next S step to issue
+      int js = 0, ts = 0;    // its step-in-tile / tile index
+      auto issue_s = [&]() {
+        const int ks = gs % K_STAGES, qs = ts % Q_STAGES;
+        mbar_wait(&b->k_full[ks], (gs / K_STAGES) & 1);
+        if (js == 0) mbar_wait(&b->q_full[qs], (ts / Q_STAGES) & 1);
+        if (gs > 0) mbar_wait(&b->s_free, (gs - 1) & 1);  // S_{g-1} is in registers: its TMEM columns may be overwritten
+        tc_fence_after();
+        const bool last = js == n_kv - 1;
+        const uint32_t idesc = (last && tail64) ? idesc_s64 : idesc_s128;
 #pragma unroll
         for (int kk = 0; kk < 4; ++kk)
-          umma_ss(tmem_base + TM_S, umma_desc_sw128(q_addr + kk * 32),
-                  umma_desc_sw128(k_addr + stage * TILE_BYTES + kk * 32), idesc_s, kk != 0);
-        umma_commit(s_full);
-      };
-      mbar_wait(q_full, 0);
-      mbar_wait(&kv_full[0], 0);
-      tc_fence_after();
-      issue_s(0);
-      for (int j = 0; j < n_kv; ++j) {
-        const int stage = j % KV_STAGES;
-        if (j + 1 < n_kv) {
-          const int nstage = (j + 1) % KV_STAGES;
-          mbar_wait(&kv_full[nstage], ((j + 1) / KV_STAGES) & 1);
-          mbar_wait(s_free, j & 1);  // S_j is in the softmax threads' registers: its TMEM columns may be overwritten
-          tc_fence_after();
-          issue_s(nstage);
+          umma_ss(tmem_base + TM_S, umma_desc_sw128(q_addr + qs * TILE_BYTES + kk * 32),
+                  umma_desc_sw128(k_addr + ks * TILE_BYTES + kk * 32), idesc, kk != 0);
+        umma_commit(&b->s_full);
+        umma_commit(&b->k_empty[ks]);
+        if (last) umma_commit(&b->q_free[qs]);
+        ++gs;
+        if (++js == n_kv) {
+          js = 0;
+          ++ts;
         }
-        mbar_wait(p_full, j & 1);
+      };
+      issue_s();
+      int jp = 0;
+      for (uint32_t g = 0; g < G; ++g) {
+        if (gs < G) issue_s();
+        const int vs = g % V_STAGES;
+        mbar_wait(&b->v_full[vs], (g / V_STAGES) & 1);
+        mbar_wait(&b->p_full, g & 1);
         tc_fence_after();
-#pragma unroll
-        for (int ks = 0; ks < 8; ++ks)
-          umma_ts(tmem_base + TM_O, tmem_base + TM_P + ks * 8, umma_desc_sw128(v_addr + stage * TILE_BYTES + ks * 2048),
-                  idesc_pv, (j | ks) != 0);
-        umma_commit(o_done);
-        umma_commit(&kv_empty[stage]);
+        const int nks = (jp == n_kv - 1 && tail64) ? 4 : 8;
+        for (int ks = 0; ks < nks; ++ks)
+          umma_ts(tmem_base + TM_O, tmem_base + TM_P + ks * 8, umma_desc_sw128(v_addr + vs * TILE_BYTES + ks * 2048),
+                  idesc_pv, (jp | ks) != 0);
+        umma_commit(&b->o_done);
+        umma_commit(&b->v_empty[vs]);
+        if (++jp == n_kv) jp = 0;
       }
     }
   } else {
+    // ------------------------------------------------------------------ softmax warpgroup + tile epilogue
     setmaxnreg_inc<200>();
-    const int q = warp & 3;         // TMEM lane quadrant
-    const int r = q * 32 + lane;    // row within the tile
+    const int q = warp & 3;       // TMEM lane quadrant
+    const int r = q * 32 + lane;  // row within the tile
     const uint32_t lane_addr = tmem_base + (uint32_t(q * 32) << 16);
     const uint32_t s_addr = lane_addr + TM_S;
     const uint32_t p_addr = lane_addr + TM_P;
     const uint32_t o_addr = lane_addr + TM_O;
-    float m_ref = -INFINITY, l = 0.f;
     const float sl2 = p.scale_log2;
-    for (int j = 0; j < n_kv; ++j) {
-      uint32_t s[128];
-      mbar_wait(s_full, j & 1);
+    uint32_t g = 0;
+    for (int t = 0; t < n_my; ++t) {
+      const int w = blockIdx.x + t * gridDim.x;
+      const int qblk = w % p.n_qblk, hs = w / p.n_qblk;
+      const int head = hs % p.heads, seq = hs / p.heads;
+      float m_ref = -INFINITY, l = 0.f;
+      for (int j = 0; j < n_kv - 1; ++j, ++g) softmax_step<128, VAR>(b, s_addr, p_addr, o_addr, g, j, 128, sl2, m_ref, l, lane);
+      if (tail64) softmax_step<64, 0>(b, s_addr, p_addr, o_addr, g, n_kv - 1, kv_tail, sl2, m_ref, l, lane);
+      else softmax_step<128, 0>(b, s_addr, p_addr, o_addr, g, n_kv - 1, kv_tail, sl2, m_ref, l, lane);
+      // epilogue: O / l -> bf16 (PV_0 of the next tile cannot start before all four warps passed this point: it needs
+      // their p_full arrivals)
+      mbar_wait(&b->o_done, g & 1);
+      ++g;
       tc_fence_after();
-#pragma unroll
-      for (int c = 0; c < 4; ++c) tmem_ld32_at(s_addr + c * 32, s + c * 32);
+      const int row = qblk * 128 + r;
+      const float inv_l = 1.0f / l;
+      __nv_bfloat16* op = p.out + ((long long)seq * p.seq_len + row) * p.out_pitch + head * 64;
+      uint32_t v[64];
+      tmem_ld32_at(o_addr, v);
+      tmem_ld32_at(o_addr + 32, v + 32);
       tmem_ld_wait();
       tc_fence_before();
-      __syncwarp();
-      if (lane == 0) mbar_arrive(s_free);
-      const int kv_left = p.seq_len - j * 128;  // valid keys in this tile (>= 1)
-      if (kv_left < 128) {
+      if (row < p.seq_len) {
 #pragma unroll
-        for (int i = 0; i < 128; ++i)
-          if (i >= kv_left) s[i] = 0xff800000u;  // -inf
-      }
-      // 4 independent max chains (one 128-deep dependent chain keeps the warp off the MUFU pipe for ~500 clk per tile)
-      float mx[4];
+        for (int c = 0; c < 8; ++c) {
+          float f[8];
 #pragma unroll
-      for (int i = 0; i < 4; ++i) mx[i] = __uint_as_float(s[i]);
-#pragma unroll
-      for (int i = 4; i < 128; ++i) mx[i & 3] = fmaxf(mx[i & 3], __uint_as_float(s[i]));
-      const float tmax = fmaxf(fmaxf(mx[0], mx[1]), fmaxf(mx[2], mx[3]));
-      if (j == 0) {
-        m_ref = tmax;
-      } else {
-        const bool need = (tmax - m_ref) * sl2 > 8.0f;
-        if (__any_sync(0xffffffffu, need)) {
-          mbar_wait(o_done, (j - 1) & 1);  // PV_{j-1} finished: O stable
-          tc_fence_after();
-          float alpha = 1.0f;
-          if (need) {
-            alpha = ex2((m_ref - tmax) * sl2);
-            m_ref = tmax;
-          }
-          l *= alpha;
-#pragma unroll 1
-          for (int c = 0; c < 2; ++c) {
-            uint32_t v[32];
-            tmem_ld32(o_addr + c * 32, v);
-            tmem_ld_wait();
-#pragma unroll
-            for (int i = 0; i < 32; ++i) v[i] = __float_as_uint(__uint_as_float(v[i]) * alpha);
-            tmem_st32(o_addr + c * 32, v);
-          }
-          tmem_st_wait();
+          for (int i = 0; i < 8; ++i) f[i] = __uint_as_float(v[8 * c + i]) * inv_l;
+          *reinterpret_cast<uint4*>(op + c * 8) =
+              make_uint4(pack_bf16(f[0], f[1]), pack_bf16(f[2], f[3]), pack_bf16(f[4], f[5]), pack_bf16(f[6], f[7]));
         }
-      }
-      // p = exp2((s - m_ref) * scale*log2e), row sum, bf16 pairs
-      const float mb = m_ref * sl2;
-      float sum0 = 0.f, sum1 = 0.f;
-#pragma unroll
-      for (int i = 0; i < 64; ++i) {
-        const float p0 = ex2(fmaf(__uint_as_float(s[2 * i]), sl2, -mb));
-        const float p1 = ex2(fmaf(__uint_as_float(s[2 * i + 1]), sl2, -mb));
-        sum0 += p0;
-        sum1 += p1;
-        s[i] = pack_bf16(p0, p1);
-      }
-      l += sum0 + sum1;
-      if (j > 0) {
-        mbar_wait(o_done, (j - 1) & 1);  // PV_{j-1} has consumed the previous P
-        tc_fence_after();
-      }
-      tmem_st32_at(p_addr, s);
-      tmem_st32_at(p_addr + 32, s + 32);
-      tmem_st_wait();
-      tc_fence_before();
-      __syncwarp();
-      if (lane == 0) mbar_arrive(p_full);
-    }
-    // epilogue: O / l -> bf16
-    mbar_wait(o_done, (n_kv - 1) & 1);
-    tc_fence_after();
-    const int row = q0 + r;
-    const float inv_l = 1.0f / l;
-    __nv_bfloat16* op = p.out + ((long long)seq * p.seq_len + row) * p.out_pitch + head * 64;
-    uint32_t v[64];
-    tmem_ld32_at(o_addr, v);
-    tmem_ld32_at(o_addr + 32, v + 32);
-    tmem_ld_wait();
-    if (row < p.seq_len) {
-#pragma unroll
-      for (int g = 0; g < 8; ++g) {
-        float f[8];
-#pragma unroll
-        for (int i = 0; i < 8; ++i) f[i] = __uint_as_float(v[8 * g + i]) * inv_l;
-        *reinterpret_cast<uint4*>(op + g * 8) =
-            make_uint4(pack_bf16(f[0], f[1]), pack_bf16(f[2], f[3]), pack_bf16(f[4], f[5]), pack_bf16(f[6], f[7]));
       }
     }
   }
@@ -259,15 +464,31 @@ __global__ void __launch_bounds__(kThreads, 2) attn_kernel(const __grid_constant
 
 }  // namespace
 
-cudaError_t launch_attention(const AttnParams& p, cudaStream_t stream) {
-  static bool attr = false;
-  if (!attr) {
-    cudaError_t e = cudaFuncSetAttribute(attn_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES);
-    if (e != cudaSuccess) return e;
-    attr = true;
+void set_attention_poly(int every) { g_attn_poly = every; }
+
+cudaError_t launch_attention(const AttnParams& p_in, cudaStream_t stream) {
+  static int n_sm = 0;
+  if (!n_sm) {
+    cudaError_t e = cudaSuccess;
+#define UFM_ATTN_VARIANTS(X) X(0) X(4)
+#define X(v) if ((e = cudaFuncSetAttribute(attn_kernel<v>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES)) != cudaSuccess) return e;
+    UFM_ATTN_VARIANTS(X)
+#undef X
+    int dev = 0, v = 0;
+    if ((e = cudaGetDevice(&dev)) != cudaSuccess) return e;
+    if ((e = cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, dev)) != cudaSuccess) return e;
+    n_sm = v;
   }
-  dim3 grid((p.seq_len + 127) / 128, p.heads, p.n_seq);
-  attn_kernel<<<grid, kThreads, SMEM_BYTES, stream>>>(p);
+  AttnParams p = p_in;
+  p.n_qblk = (p.seq_len + 127) / 128;
+  p.n_items = p.n_seq * p.heads * p.n_qblk;
+  if (p.n_items <= 0) return cudaSuccess;
+  const int grid = p.n_items < 2 * n_sm ? p.n_items : 2 * n_sm;
+  bool launched = false;
+#define X(v) if (!launched && g_attn_poly == v) { attn_kernel<v><<<grid, kThreads, SMEM_BYTES, stream>>>(p); launched = true; }
+  UFM_ATTN_VARIANTS(X)
+#undef X
+  if (!launched) return cudaErrorInvalidValue;
   return cudaGetLastError();
 }
 

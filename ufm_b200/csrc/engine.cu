@@ -946,6 +946,10 @@ int ufm_debug_flag(int which, int value) {
     set_gemm_pair_mode(value);
     return 0;
   }
+  if (which == 2) {
+    set_attention_poly(value);
+    return 0;
+  }
   return 1;
 }
 

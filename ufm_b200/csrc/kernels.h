@@ -99,8 +99,10 @@ struct alignas(64) AttnParams {
   float scale_log2;      // scale * log2(e)
   __nv_bfloat16* out;
   long long out_pitch;   // heads*64
+  int n_qblk, n_items;   // filled by launch_attention: query tiles per sequence, work items = n_seq*heads*n_qblk
 };
 cudaError_t launch_attention(const AttnParams& p, cudaStream_t stream);
+void set_attention_poly(int every);  // tuning switch (ufm_debug_flag 2): every n-th exp2 pair on the FMA pipe, 0 = none
 
 // ------------------------------------------------------------------------------------------------
 // SIMT kernels (bandwidth-bound stages)
