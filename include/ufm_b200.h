@@ -128,7 +128,8 @@ int ufm_op_resize_ac(const float* in_f32, const void* in_bf16, int n, int h, int
                      int ow, float* out_f32, void* out_bf16, void* stream);
 int ufm_op_shuffle(const void* in, void* out, int is_f32, int n, int h, int w, int k, int C, void* stream);
 int ufm_op_im2col_s2(const void* in, void* out, int n, int h, int w, int C, int oh, int ow, void* stream);
-int ufm_op_refine(const float* desc, int B, int H, int W, const float* flow_in, const float* bias25,
+/* desc: bf16 descriptors, channel-group planar [2B images (b,view)][2][H][W][8] (16 channels) */
+int ufm_op_refine(const void* desc, int B, int H, int W, const float* flow_in, const float* bias25,
                   float inv_temperature, float* flow_out, float* residual, float* log_softmax, void* stream);
 
 #ifdef __cplusplus

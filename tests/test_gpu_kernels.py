@@ -205,10 +205,12 @@ def test_resize_align_corners(h, w, rh, rw, oh, ow):
     torch.cuda.synchronize()
     ref = F.interpolate(x.permute(0, 3, 1, 2), size=(rh, rw), mode="bilinear", align_corners=True)[:, :, :oh, :ow]
     ref = ref.permute(0, 2, 3, 1)
-    assert (of - ref).abs().max().item() < 2e-5
+    assert (of - ref).abs().max().item() < 5e-5
     assert rel(ob.float(), ref) < 3e-3
     ref2 = F.interpolate(xb.float().permute(0, 3, 1, 2), size=(rh, rw), mode="bilinear", align_corners=True)
-    assert (of2 - ref2[:, :, :oh, :ow].permute(0, 2, 3, 1)).abs().max().item() < 2e-5
+    # the kernel interpolates vertically first (column values are shared along a strip), torch horizontally first:
+    # fp32 rounding-order differences only
+    assert (of2 - ref2[:, :, :oh, :ow].permute(0, 2, 3, 1)).abs().max().item() < 5e-5
 
 
 def test_shuffle_and_convt_fold():
@@ -259,13 +261,15 @@ def test_local_refinement_vs_oracle():
     lib = _lib.load()
     B, H, W, Cc = 2, 56, 70, 16
     g = torch.Generator().manual_seed(0)
-    desc = torch.randn(B, 2, H, W, Cc, generator=g)
+    desc = torch.randn(B, 2, H, W, Cc, generator=g).bfloat16().float()  # descriptors are bf16 in the engine
     # smooth field U(-40,40) + N(0,1), with some targets far outside the image
     base = F.interpolate(torch.rand(B, 2, 4, 5, generator=g) * 80 - 40, size=(H, W), mode="bilinear", align_corners=True)
     flow = base + torch.randn(B, 2, H, W, generator=g)
     flow[0, :, :2, :2] = 1e4
     bias = torch.randn(25, generator=g) * 0.3
-    d_desc, d_flow, d_bias = desc.cuda(), flow.cuda(), bias.cuda()
+    # engine layout: channel-group planar [B, view, C/8, H, W, 8] bf16
+    d_desc = desc.view(B, 2, H, W, Cc // 8, 8).permute(0, 1, 4, 2, 3, 5).contiguous().bfloat16().cuda()
+    d_flow, d_bias = flow.cuda(), bias.cuda()
     out = torch.zeros(B, 2, H, W, device="cuda")
     res = torch.zeros(B, 2, H, W, device="cuda")
     lsm = torch.zeros(B, H, W, 25, device="cuda")

@@ -80,7 +80,8 @@ def _engine_stages(model, B, h, w):
             pass
     try:
         d = eng.stage("desc")
-        out["desc"] = d.permute(1, 0, 4, 2, 3).reshape(-1, d.shape[4], d.shape[2], d.shape[3])
+        # engine layout (B, view, C/8, H, W, 8) bf16 -> (view*B, C, H, W) fp32
+        out["desc"] = d.permute(1, 0, 2, 5, 3, 4).reshape(-1, d.shape[2] * d.shape[5], d.shape[3], d.shape[4]).float()
         out["enc_first"] = eng.stage("enc_first").float()
     except Exception:
         pass

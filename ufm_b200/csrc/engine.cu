@@ -656,16 +656,16 @@ int ufm_engine::forward(const void* src, const void* tgt, int pairs, int in_dtyp
     const int zc = c.cls_patch * c.cls_patch * c.cls_out;
     {
       Epi e;
-      e.bias = Wf("cls.lin.b"); e.out_f32 = B<float>("Z"); e.sx = zc;
+      e.bias = Wf("cls.lin.b"); e.out_bf16 = B<bf16>("Z"); e.sx = zc;
       if (!gemm(rows_view(B<bf16>("Ycls"), Mc, c.cls_in), "cls.lin.w", 1, e)) return 1;
     }
-    if (!run(UFM_CAT_MOVE, 0.0, 8.0 * Mi * zc, "shuffle desc", [&] {
-          return launch_shuffle_f32(B<float>("Z"), B<float>("desc"), 2 * Bp, hpn, wpn, c.cls_patch, c.cls_out, st);
+    if (!run(UFM_CAT_MOVE, 0.0, 4.0 * Mi * zc, "shuffle desc", [&] {
+          return launch_desc_shuffle(B<bf16>("Z"), B<bf16>("desc"), 2 * Bp, hpn, wpn, c.cls_patch, c.cls_out, st);
         }))
       return 1;
-    set_stage("desc", B<float>("desc"), UFM_F32, {Bp, 2, c.img_h, c.img_w, c.cls_out});
+    set_stage("desc", B<bf16>("desc"), UFM_BF16, {Bp, 2, c.cls_out / 8, c.img_h, c.img_w, 8});
     RefineParams rp;
-    rp.desc = B<float>("desc"); rp.B = Bp; rp.H = c.img_h; rp.W = c.img_w;
+    rp.desc = B<bf16>("desc"); rp.B = Bp; rp.H = c.img_h; rp.W = c.img_w;
     rp.flow_in = flow_reg;
     rp.bias25 = Wf("cls.bias");
     if (!rp.bias25) return 1;
@@ -674,9 +674,9 @@ int ufm_engine::forward(const void* src, const void* tgt, int pairs, int in_dtyp
     rp.residual = keep_aux ? B<float>("residual") : nullptr;
     rp.log_softmax = keep_aux ? B<float>("log_softmax") : nullptr;
     {
-      // algorithmic bytes: F1, F2 (16 ch fp32) + flow in + flow out (+ residual, log-softmax when kept)
+      // algorithmic bytes: F1, F2 (16 ch bf16) + flow in + flow out (+ residual, log-softmax when kept)
       const double plane = (double)c.img_h * c.img_w;
-      const double rb = Bp * plane * (2 * 16 * 4 + 2 * 4 + 2 * 4 + (keep_aux ? 2 * 4 + 25 * 4 : 0));
+      const double rb = Bp * plane * (2 * 16 * 2 + 2 * 4 + 2 * 4 + (keep_aux ? 2 * 4 + 25 * 4 : 0));
       if (!run(UFM_CAT_REFINE, 0.0, rb, "refine", [&] { return launch_refine(rp, st); })) return 1;
     }
     if (keep_aux) {
@@ -822,8 +822,8 @@ int ufm_prepare(ufm_engine* e, int max_pairs) {
     ok = ok && e->alloc("Xcls", UFM_BF16, Mi * c.cls_in);
     ok = ok && e->alloc("Hcls", UFM_BF16, Mi * c.cls_hidden);
     ok = ok && e->alloc("Ycls", UFM_BF16, Mi * c.cls_in);
-    ok = ok && e->alloc("Z", UFM_F32, Mi * c.cls_patch * c.cls_patch * c.cls_out);
-    ok = ok && e->alloc("desc", UFM_F32, 2 * Bp * c.img_h * c.img_w * c.cls_out);
+    ok = ok && e->alloc("Z", UFM_BF16, Mi * c.cls_patch * c.cls_patch * c.cls_out);
+    ok = ok && e->alloc("desc", UFM_BF16, 2 * Bp * c.img_h * c.img_w * c.cls_out);
     ok = ok && e->alloc("residual", UFM_F32, Bp * 2 * c.img_h * c.img_w);
     ok = ok && e->alloc("log_softmax", UFM_F32, Bp * c.img_h * c.img_w * 25);
   }
@@ -1042,10 +1042,10 @@ int ufm_op_im2col_s2(const void* in, void* out, int n, int h, int w, int C, int 
                           reinterpret_cast<cudaStream_t>(stream)) != cudaSuccess;
 }
 
-int ufm_op_refine(const float* desc, int B, int H, int W, const float* flow_in, const float* bias25, float inv_temperature,
+int ufm_op_refine(const void* desc, int B, int H, int W, const float* flow_in, const float* bias25, float inv_temperature,
                   float* flow_out, float* residual, float* log_softmax, void* stream) {
   RefineParams p;
-  p.desc = desc; p.B = B; p.H = H; p.W = W; p.flow_in = flow_in; p.bias25 = bias25; p.inv_temperature = inv_temperature;
+  p.desc = reinterpret_cast<const bf16*>(desc); p.B = B; p.H = H; p.W = W; p.flow_in = flow_in; p.bias25 = bias25; p.inv_temperature = inv_temperature;
   p.flow_out = flow_out; p.residual = residual; p.log_softmax = log_softmax;
   return launch_refine(p, reinterpret_cast<cudaStream_t>(stream)) != cudaSuccess;
 }

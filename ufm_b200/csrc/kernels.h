@@ -154,8 +154,9 @@ cudaError_t launch_resize_ac(const float* in_f32, const __nv_bfloat16* in_bf16, 
                              int oh, int ow, float* out_f32, __nv_bfloat16* out_bf16, cudaStream_t s);
 
 // Local classification refinement (ufm.py:1012-1178): desc NHWC fp32 [(b, view), H, W, C=16]; flow planar [B,2,H,W].
+// desc: channel-group planar bf16 descriptors [2B images (b,view)][2][H][W][8]
 struct RefineParams {
-  const float* desc; int B, H, W;
+  const __nv_bfloat16* desc; int B, H, W;
   const float* flow_in;       // [B,2,H,W]
   const float* bias25; float inv_temperature;
   float* flow_out;            // [B,2,H,W] = flow_in + residual
@@ -163,6 +164,8 @@ struct RefineParams {
   float* log_softmax;         // optional [B,H,W,25]
 };
 cudaError_t launch_refine(const RefineParams& p, cudaStream_t s);
+// pixel_shuffle(k) of z[(img,ty,tx)][(i,j,c)] bf16 into desc[img][C/8][h*k][w*k][8]
+cudaError_t launch_desc_shuffle(const __nv_bfloat16* z, __nv_bfloat16* desc, int n, int h, int w, int k, int C, cudaStream_t s);
 
 // NHWC fp32 [n,H,W,C] -> NCHW fp32 (stage dumps / descriptor export)
 cudaError_t launch_nhwc_to_nchw(const float* in, float* out, int n, int H, int W, int C, cudaStream_t s);

@@ -203,39 +203,72 @@ __device__ __forceinline__ Vec<8> ldv(const __nv_bfloat16* p) {
   const float2 d = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&u.w));
   return Vec<8>{{a.x, a.y, b.x, b.y, c.x, c.y, d.x, d.y}};
 }
+// One thread = one 16-byte channel group of a STRIP of RS_STRIP consecutive output pixels of one output row: the
+// vertically interpolated source columns are kept in registers and shared by consecutive outputs (x2 upsampling
+// touches a new source column only every other output pixel), and the index arithmetic is paid once per strip.  The
+// first version (one output pixel per thread, four loads each) was issue-bound at 30 % of HBM with 75-80 % issue
+// utilisation (ncu, profiles/r01_v4_simt_refine16.csv).
+constexpr int RS_STRIP = 8;
 template <typename T>
-__global__ void __launch_bounds__(256) resize_ac_kernel(const T* in, int h, int w, int C, float sy, float sx, int oh,
-                                                       int ow, float* out_f32, __nv_bfloat16* out_bf16) {
+__global__ void __launch_bounds__(256) resize_ac_kernel(const T* __restrict__ in, int h, int w, int C, float sy, float sx,
+                                                       int oh, int ow, float* __restrict__ out_f32,
+                                                       __nv_bfloat16* __restrict__ out_bf16) {
   constexpr int V = 16 / sizeof(T);
   const unsigned cg = (unsigned)C / V;
   const unsigned t = blockIdx.x * 256u + threadIdx.x;
-  const unsigned ox = t / cg;
-  if (ox >= (unsigned)ow) return;
-  const unsigned g = t - ox * cg;
+  const unsigned strip = t / cg;
+  const unsigned ox0 = strip * RS_STRIP;
+  if (ox0 >= (unsigned)ow) return;
+  const unsigned g = t - strip * cg;
   const int oy = blockIdx.y, nn = blockIdx.z;
-  const float fy = sy * oy, fx = sx * ox;
-  const int y0 = (int)fy, x0 = (int)fx;
-  const int y1 = y0 + (y0 < h - 1 ? 1 : 0), x1 = x0 + (x0 < w - 1 ? 1 : 0);
-  const float ly = fy - y0, lx = fx - x0;
-  const float hy = 1.f - ly, hx = 1.f - lx;
-  const T* b = in + (size_t)nn * h * w * C + g * V;
-  const Vec<V> a00 = ldv(b + ((size_t)y0 * w + x0) * C), a01 = ldv(b + ((size_t)y0 * w + x1) * C);
-  const Vec<V> a10 = ldv(b + ((size_t)y1 * w + x0) * C), a11 = ldv(b + ((size_t)y1 * w + x1) * C);
-  float r[V];
+  const float fy = sy * oy;
+  const int y0 = (int)fy;
+  const int y1 = y0 + (y0 < h - 1 ? 1 : 0);
+  const float ly = fy - y0, hy = 1.f - ly;
+  const T* r0 = in + ((size_t)nn * h + y0) * w * C + g * V;
+  const T* r1 = in + ((size_t)nn * h + y1) * w * C + g * V;
+  auto col = [&](int x) {
+    const Vec<V> a = ldv(r0 + (size_t)x * C), b = ldv(r1 + (size_t)x * C);
+    Vec<V> v;
 #pragma unroll
-  for (int i = 0; i < V; ++i)
-    r[i] = hy * (hx * a00.v[i] + lx * a01.v[i]) + ly * (hx * a10.v[i] + lx * a11.v[i]);
-  const size_t o = (((size_t)nn * oh + oy) * ow + ox) * C + g * V;
-  if (out_f32) {
+    for (int i = 0; i < V; ++i) v.v[i] = hy * a.v[i] + ly * b.v[i];
+    return v;
+  };
+  int c0 = -1, c1 = -1;
+  Vec<V> v0, v1;
+  size_t o = (((size_t)nn * oh + oy) * ow + ox0) * C + g * V;
 #pragma unroll
-    for (int i = 0; i < V; i += 4) *reinterpret_cast<float4*>(out_f32 + o + i) = make_float4(r[i], r[i + 1], r[i + 2], r[i + 3]);
-  }
-  if (out_bf16) {
-    if constexpr (V == 8)
-      *reinterpret_cast<uint4*>(out_bf16 + o) =
-          make_uint4(pack_bf16(r[0], r[1]), pack_bf16(r[2], r[3]), pack_bf16(r[4], r[5]), pack_bf16(r[6], r[7]));
-    else
-      *reinterpret_cast<uint2*>(out_bf16 + o) = make_uint2(pack_bf16(r[0], r[1]), pack_bf16(r[2], r[3]));
+  for (int k = 0; k < RS_STRIP; ++k, o += C) {
+    const int ox = ox0 + k;
+    if (ox >= ow) break;
+    const float fx = sx * ox;
+    const int x0 = (int)fx;
+    const int x1 = x0 + (x0 < w - 1 ? 1 : 0);
+    const float lx = fx - x0, hx = 1.f - lx;
+    if (x0 != c0) {
+      if (x0 == c1) v0 = v1;
+      else v0 = col(x0);
+      c0 = x0;
+    }
+    if (x1 != c1) {
+      if (x1 == c0) v1 = v0;
+      else v1 = col(x1);
+      c1 = x1;
+    }
+    float r[V];
+#pragma unroll
+    for (int i = 0; i < V; ++i) r[i] = hx * v0.v[i] + lx * v1.v[i];
+    if (out_f32) {
+#pragma unroll
+      for (int i = 0; i < V; i += 4) *reinterpret_cast<float4*>(out_f32 + o + i) = make_float4(r[i], r[i + 1], r[i + 2], r[i + 3]);
+    }
+    if (out_bf16) {
+      if constexpr (V == 8)
+        *reinterpret_cast<uint4*>(out_bf16 + o) =
+            make_uint4(pack_bf16(r[0], r[1]), pack_bf16(r[2], r[3]), pack_bf16(r[4], r[5]), pack_bf16(r[6], r[7]));
+      else
+        *reinterpret_cast<uint2*>(out_bf16 + o) = make_uint2(pack_bf16(r[0], r[1]), pack_bf16(r[2], r[3]));
+    }
   }
 }
 
@@ -254,20 +287,38 @@ __device__ __forceinline__ void cubic_w(float t, float (&w)[4]) {
   w[3] = ((A * x3 - 5.f * A) * x3 + 8.f * A) * x3 - 4.f * A;
 }
 
-__global__ void __launch_bounds__(128) refine_kernel(const RefineParams p) {
+// Descriptor maps are stored channel-group planar, [image][C/8][H][W][8] bf16 (the classification head runs under
+// autocast in the reference, ufm.py:949, so its output IS bf16): the 32 pixels of a warp then read 32 consecutive 16-byte
+// chunks per load instruction (4 L1 wavefronts) instead of 32 chunks 64 bytes apart (16 wavefronts) -- the gather of
+// 64 taps x 16 channels per pixel is bound by L1 wavefronts, not by HBM.
+#ifndef REFINE_MIN_BLOCKS
+#define REFINE_MIN_BLOCKS 6
+#endif
+// c + a.lo*b.lo + a.hi*b.hi for two packed bf16 pairs, accumulated in fp32 by the sm_100 mixed-precision FMA
+// (fma.rn.f32.bf16 -> FHFMA.BF16 with .H0/.H1 operand selectors): the bf16 x bf16 products are exact in fp32, so this
+// equals an fp32 dot product of the converted values without spending ALU slots on unpacking.
+__device__ __forceinline__ float dot2_bf16(uint32_t a, uint32_t b, float c) {
+  float d;
+  asm("{\n\t.reg .b16 al, ah, bl, bh;\n\t"
+      "mov.b32 {al, ah}, %1;\n\t"
+      "mov.b32 {bl, bh}, %2;\n\t"
+      "fma.rn.f32.bf16 %0, al, bl, %3;\n\t"
+      "fma.rn.f32.bf16 %0, ah, bh, %0;\n\t}"
+      : "=&f"(d)
+      : "r"(a), "r"(b), "f"(c));
+  return d;
+}
+
+__global__ void __launch_bounds__(128, REFINE_MIN_BLOCKS) refine_kernel(const RefineParams p) {
   const int x = blockIdx.x * 32 + (threadIdx.x & 31);
   const int y = blockIdx.y * 4 + (threadIdx.x >> 5);
   const int b = blockIdx.z;
   if (x >= p.W || y >= p.H) return;
   const long long plane = (long long)p.H * p.W;
-  const float* f1 = p.desc + ((long long)(2 * b) * plane + (long long)y * p.W + x) * 16;
-  const float* f2 = p.desc + (long long)(2 * b + 1) * plane * 16;
-  float q[16];
-#pragma unroll
-  for (int i = 0; i < 4; ++i) {
-    const float4 t = __ldg(reinterpret_cast<const float4*>(f1) + i);
-    q[4 * i] = t.x; q[4 * i + 1] = t.y; q[4 * i + 2] = t.z; q[4 * i + 3] = t.w;
-  }
+  const uint4* d = reinterpret_cast<const uint4*>(p.desc);
+  const uint4* f1 = d + (long long)(2 * b) * 2 * plane + (long long)y * p.W + x;  // group 0 of view 1; group 1 at +plane
+  const uint4* f2 = d + (long long)(2 * b + 1) * 2 * plane;
+  const uint4 qa = __ldg(f1), qb = __ldg(f1 + plane);  // the query stays packed: 8 registers
   const float fx = p.flow_in[(2LL * b) * plane + (long long)y * p.W + x];
   const float fy = p.flow_in[(2LL * b + 1) * plane + (long long)y * p.W + x];
   // same float sequence as the reference: normalise with align_corners=False then grid_sample's unnormalise
@@ -282,37 +333,47 @@ __global__ void __launch_bounds__(128) refine_kernel(const RefineParams p) {
   // clamp far-away targets so the integer window arithmetic cannot overflow; such windows are all-zero anyway
   const int x0 = (int)fminf(fmaxf(flx, -16.f), (float)p.W + 16.f) - 3;
   const int y0 = (int)fminf(fmaxf(fly, -16.f), (float)p.H + 16.f) - 3;
-  float E[8][5];  // E[r][bb] = sum_tx wx[tx] * D[r][bb+tx]
+  float sc[25];
+#pragma unroll
+  for (int k = 0; k < 25; ++k) sc[k] = 0.f;
 #pragma unroll
   for (int r = 0; r < 8; ++r) {
     const int yy = y0 + r;
+    const bool yin = yy >= 0 && yy < p.H;
+    const uint4* row = f2 + (long long)yy * p.W;
     float D[8];
 #pragma unroll
     for (int s = 0; s < 8; ++s) {
       const int xx = x0 + s;
-      float d = 0.f;
-      if (yy >= 0 && yy < p.H && xx >= 0 && xx < p.W) {
-        const float4* k = reinterpret_cast<const float4*>(f2 + ((long long)yy * p.W + xx) * 16);
-        const float4 k0 = __ldg(k), k1 = __ldg(k + 1), k2 = __ldg(k + 2), k3 = __ldg(k + 3);
-        d = q[0] * k0.x + q[1] * k0.y + q[2] * k0.z + q[3] * k0.w + q[4] * k1.x + q[5] * k1.y + q[6] * k1.z +
-            q[7] * k1.w + q[8] * k2.x + q[9] * k2.y + q[10] * k2.z + q[11] * k2.w + q[12] * k3.x + q[13] * k3.y +
-            q[14] * k3.z + q[15] * k3.w;
+      float dd = 0.f;
+      if (yin && xx >= 0 && xx < p.W) {
+        const uint4 k0 = __ldg(row + xx), k1 = __ldg(row + plane + xx);
+        float d0 = dot2_bf16(k0.x, qa.x, 0.f), d1 = dot2_bf16(k1.x, qb.x, 0.f);
+        d0 = dot2_bf16(k0.y, qa.y, d0);
+        d1 = dot2_bf16(k1.y, qb.y, d1);
+        d0 = dot2_bf16(k0.z, qa.z, d0);
+        d1 = dot2_bf16(k1.z, qb.z, d1);
+        d0 = dot2_bf16(k0.w, qa.w, d0);
+        d1 = dot2_bf16(k1.w, qb.w, d1);
+        dd = d0 + d1;
       }
-      D[s] = d;
+      D[s] = dd;
     }
-#pragma unroll
-    for (int bb = 0; bb < 5; ++bb) E[r][bb] = wx[0] * D[bb] + wx[1] * D[bb + 1] + wx[2] * D[bb + 2] + wx[3] * D[bb + 3];
-  }
-  float sc[25];
-  float mx = -INFINITY;
-#pragma unroll
-  for (int a = 0; a < 5; ++a)
+    // E[bb] = sum_tx wx[tx] D[bb+tx]; window row r feeds score rows a = r-3 .. r with weight wy[r-a]
 #pragma unroll
     for (int bb = 0; bb < 5; ++bb) {
-      const float s = wy[0] * E[a][bb] + wy[1] * E[a + 1][bb] + wy[2] * E[a + 2][bb] + wy[3] * E[a + 3][bb];
-      sc[a * 5 + bb] = s * p.inv_temperature + __ldg(p.bias25 + a * 5 + bb);
-      mx = fmaxf(mx, sc[a * 5 + bb]);
+      const float E = wx[0] * D[bb] + wx[1] * D[bb + 1] + wx[2] * D[bb + 2] + wx[3] * D[bb + 3];
+#pragma unroll
+      for (int a = 0; a < 5; ++a)
+        if (r - a >= 0 && r - a < 4) sc[a * 5 + bb] = fmaf(wy[r - a], E, sc[a * 5 + bb]);
     }
+  }
+  float mx = -INFINITY;
+#pragma unroll
+  for (int k = 0; k < 25; ++k) {
+    sc[k] = sc[k] * p.inv_temperature + __ldg(p.bias25 + k);
+    mx = fmaxf(mx, sc[k]);
+  }
   float sum = 0.f, rx = 0.f, ry = 0.f;
 #pragma unroll
   for (int k = 0; k < 25; ++k) {
@@ -337,6 +398,30 @@ __global__ void __launch_bounds__(128) refine_kernel(const RefineParams p) {
 #pragma unroll
     for (int k = 0; k < 25; ++k) ls[k] = sc[k] - lse;
   }
+}
+
+// pixel_shuffle(k) of the classification head output (mlp_feature.py:99) into the channel-group planar descriptor
+// layout: z[(img, ty, tx)][(i, j, c)] bf16 -> desc[img][c/8][ty*k+i][tx*k+j][c%8]; one 16-byte chunk per thread,
+// input read contiguously.
+template <int K, int CG>
+__global__ void __launch_bounds__(256) desc_shuffle_kernel(const uint4* __restrict__ z, uint4* __restrict__ desc, int n, int h,
+                                                          int w, int k_rt, int cg_rt) {
+  // one block row (blockIdx.y) = one token (img, ty, tx); threads enumerate its k*k*cg chunks contiguously.  K, CG > 0:
+  // compile-time constants (divisions by constants); K == 0: runtime values.
+  const int k = K ? K : k_rt, cg = CG ? CG : cg_rt;
+  const int per_row = k * k * cg;
+  const int c = blockIdx.x * 256 + threadIdx.x;
+  if (c >= per_row) return;
+  const unsigned row = blockIdx.y + blockIdx.z * gridDim.y;  // token index
+  if (row >= (unsigned)(n * h * w)) return;
+  const int g = c % cg;
+  const int j = (c / cg) % k;
+  const int i = c / (cg * k);
+  const unsigned tx = row % (unsigned)w;
+  const unsigned ty = (row / (unsigned)w) % (unsigned)h;
+  const unsigned img = row / (unsigned)(w * h);
+  const long long H = (long long)h * k, W = (long long)w * k;
+  desc[(((long long)img * cg + g) * H + (ty * k + i)) * W + (tx * k + j)] = z[(long long)row * per_row + c];
 }
 
 __global__ void __launch_bounds__(256) nhwc_to_nchw_kernel(const float* in, float* out, int n, int H, int W, int C) {
@@ -409,12 +494,26 @@ cudaError_t launch_resize_ac(const float* in_f32, const __nv_bfloat16* in_bf16, 
   const float sx = rw > 1 ? (float)(w - 1) / (float)(rw - 1) : 0.f;
   if (n == 0) return cudaSuccess;
   if (in_f32) {
-    dim3 grid(blocks_for((long long)ow * (C / 4), 256), oh, n);
+    dim3 grid(blocks_for((long long)((ow + RS_STRIP - 1) / RS_STRIP) * (C / 4), 256), oh, n);
     resize_ac_kernel<float><<<grid, 256, 0, s>>>(in_f32, h, w, C, sy, sx, oh, ow, out_f32, out_bf16);
   } else {
-    dim3 grid(blocks_for((long long)ow * (C / 8), 256), oh, n);
+    dim3 grid(blocks_for((long long)((ow + RS_STRIP - 1) / RS_STRIP) * (C / 8), 256), oh, n);
     resize_ac_kernel<__nv_bfloat16><<<grid, 256, 0, s>>>(in_bf16, h, w, C, sy, sx, oh, ow, out_f32, out_bf16);
   }
+  return cudaGetLastError();
+}
+
+cudaError_t launch_desc_shuffle(const __nv_bfloat16* z, __nv_bfloat16* desc, int n, int h, int w, int k, int C, cudaStream_t s) {
+  if (C % 8) return cudaErrorInvalidValue;
+  const long long rows = (long long)n * h * w;
+  if (rows == 0) return cudaSuccess;
+  const int cg = C / 8, per_row = k * k * cg;
+  const unsigned gy = rows > 32768 ? 32768u : (unsigned)rows;
+  dim3 grid((per_row + 255) / 256, gy, (unsigned)((rows + gy - 1) / gy));
+  const uint4* zi = reinterpret_cast<const uint4*>(z);
+  uint4* di = reinterpret_cast<uint4*>(desc);
+  if (k == 14 && cg == 2) desc_shuffle_kernel<14, 2><<<grid, 256, 0, s>>>(zi, di, n, h, w, k, cg);
+  else desc_shuffle_kernel<0, 0><<<grid, 256, 0, s>>>(zi, di, n, h, w, k, cg);
   return cudaGetLastError();
 }
 

@@ -143,12 +143,13 @@ class UniFlowMatchModelsBase(nn.Module):
             res.covisibility = UFMMaskFieldOutput(mask=cov.unsqueeze(1), logits=None)
         if self._refine and aux:
             cat = lambda k: torch.cat([a[k] for a in aux])
-            desc = cat("desc")  # (B, 2, H, W, C)
+            desc = cat("desc")  # (B, 2, C/8, H, W, 8) bf16: the engine's channel-group planar descriptor layout
+            fmap = lambda v: desc[:, v].permute(0, 1, 4, 2, 3).reshape(desc.shape[0], -1, desc.shape[3], desc.shape[4]).float()
             P = int(self.config.get("refinement_range", 5))
             res.classification_refinement = UFMClassificationRefinementOutput(
                 regression_flow_output=flow, residual=cat("residual"),
                 log_softmax=cat("log_softmax").reshape(flow.shape[0], flow.shape[2], flow.shape[3], P, P),
-                feature_map_0=desc[:, 0].permute(0, 3, 1, 2), feature_map_1=desc[:, 1].permute(0, 3, 1, 2))
+                feature_map_0=fmap(0), feature_map_1=fmap(1))
         return res
 
     # API shell (base.py:137-334) --------------------------------------------------------------------------------------
