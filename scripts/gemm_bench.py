@@ -38,7 +38,7 @@ def main():
            ("info.fc1", Mi, 768, 3072, "gelu"), ("info.fc2", Mi, 3072, 768, "res")]
     # name, n, H, W, Cin, Cout, kind
     conv = [("rcu@120x160", 16, 120, 160, 256, 256, "convres"), ("rcu@240x320", 4, 240, 320, 256, 256, "convres"),
-            ("proc.c1@240x320", 4, 240, 320, 256, 128, "convbf16")]
+            ("proc.c1@240x320", 4, 240, 320, 256, 128, "convbf16"), ("proc.c2@420x560", 4, 420, 560, 128, 128, "convbf16")]
     variants = [tuple(int(x) for x in v.split(":")) for v in a.variants.split(",")]
     gen = torch.Generator(device=dev).manual_seed(0)
 

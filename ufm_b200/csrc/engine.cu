@@ -94,7 +94,7 @@ bool build_gemm(GemmParams* gp, int* BN, const AView& a, const void* wt, int n_o
   *BN = (!tail && n_out % 256 == 0) ? 256 : 128;
   const uint64_t bdims[2] = {(uint64_t)taps * cin_pad, (uint64_t)n_out};
   const uint64_t bstr[2] = {2, (uint64_t)taps * cin_pad * 2};
-  gp->ctas = (*BN == 256 && gemm_pair_mode()) ? 2 : 1;
+  gp->ctas = ((*BN == 256 && (gemm_pair_mode() & 1)) || (*BN == 128 && (gemm_pair_mode() & 2))) ? 2 : 1;
   const uint32_t bbox[2] = {64, (uint32_t)(*BN / gp->ctas)};
   if (!make_tmap_bf16(&gp->tmB, wt, 2, bdims, bstr, bbox, err, errlen)) return false;
   if (tail) {

@@ -535,7 +535,7 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_kernel(const __grid_constant
 }
 
 int g_gemm_epi = 1;   // ufm_debug_flag 0: 1 = TMA-store epilogues where eligible (default), 0 = always the direct epilogue
-int g_gemm_pair = 1;  // ufm_debug_flag 1: allow CTA-pair (cta_group::2) tiles for BN = 256
+int g_gemm_pair = 1;  // ufm_debug_flag 1 (bit 1 measured neutral on the N = 128 convs: 808 vs 795 TFLOP/s): bit 0 = CTA-pair (cta_group::2) tiles for BN = 256, bit 1 = also for BN = 128
 
 template <int BN, int CTAS>
 static cudaError_t launch_one(const GemmParams& p, int grid, cudaStream_t stream) {
@@ -579,8 +579,9 @@ cudaError_t launch_gemm(const GemmParams& p, int BN, int num_sms, cudaStream_t s
   if (total <= 0) return cudaSuccess;
   int grid = total * ctas < num_sms ? total * ctas : num_sms / ctas * ctas;
   if (ctas == 2) {
-    if (BN != 256) return cudaErrorInvalidValue;
-    return launch_one<256, 2>(p, grid, stream);
+    if (BN == 256) return launch_one<256, 2>(p, grid, stream);
+    if (BN == 128) return launch_one<128, 2>(p, grid, stream);
+    return cudaErrorInvalidValue;
   }
   if (BN == 256) return launch_one<256, 1>(p, grid, stream);
   if (BN == 128) return launch_one<128, 1>(p, grid, stream);

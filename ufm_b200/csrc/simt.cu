@@ -309,6 +309,43 @@ __device__ __forceinline__ float dot2_bf16(uint32_t a, uint32_t b, float c) {
   return d;
 }
 
+template <bool INTERIOR>
+__device__ __forceinline__ void refine_rows(const uint4* __restrict__ f2, long long plane, int W, int H, int x0, int y0,
+                                            const uint4 qa, const uint4 qb, const float (&wx)[4], const float (&wy)[4],
+                                            float (&sc)[25]) {
+#pragma unroll
+  for (int r = 0; r < 8; ++r) {
+    const int yy = y0 + r;
+    if (yy < 0 || yy >= H) continue;  // the whole window row is padding: contributes zeros
+    const uint4* row = f2 + ((long long)yy * W + x0);
+    float D[8];
+#pragma unroll
+    for (int s = 0; s < 8; ++s) {
+      float dd = 0.f;
+      if (INTERIOR || (x0 + s >= 0 && x0 + s < W)) {
+        const uint4 k0 = __ldg(row + s), k1 = __ldg(row + plane + s);
+        float d0 = dot2_bf16(k0.x, qa.x, 0.f), d1 = dot2_bf16(k1.x, qb.x, 0.f);
+        d0 = dot2_bf16(k0.y, qa.y, d0);
+        d1 = dot2_bf16(k1.y, qb.y, d1);
+        d0 = dot2_bf16(k0.z, qa.z, d0);
+        d1 = dot2_bf16(k1.z, qb.z, d1);
+        d0 = dot2_bf16(k0.w, qa.w, d0);
+        d1 = dot2_bf16(k1.w, qb.w, d1);
+        dd = d0 + d1;
+      }
+      D[s] = dd;
+    }
+    // E[bb] = sum_tx wx[tx] D[bb+tx]; window row r feeds score rows a = r-3 .. r with weight wy[r-a]
+#pragma unroll
+    for (int bb = 0; bb < 5; ++bb) {
+      const float E = wx[0] * D[bb] + wx[1] * D[bb + 1] + wx[2] * D[bb + 2] + wx[3] * D[bb + 3];
+#pragma unroll
+      for (int a = 0; a < 5; ++a)
+        if (r - a >= 0 && r - a < 4) sc[a * 5 + bb] = fmaf(wy[r - a], E, sc[a * 5 + bb]);
+    }
+  }
+}
+
 __global__ void __launch_bounds__(128, REFINE_MIN_BLOCKS) refine_kernel(const RefineParams p) {
   const int x = blockIdx.x * 32 + (threadIdx.x & 31);
   const int y = blockIdx.y * 4 + (threadIdx.x >> 5);
@@ -336,38 +373,10 @@ __global__ void __launch_bounds__(128, REFINE_MIN_BLOCKS) refine_kernel(const Re
   float sc[25];
 #pragma unroll
   for (int k = 0; k < 25; ++k) sc[k] = 0.f;
-#pragma unroll
-  for (int r = 0; r < 8; ++r) {
-    const int yy = y0 + r;
-    const bool yin = yy >= 0 && yy < p.H;
-    const uint4* row = f2 + (long long)yy * p.W;
-    float D[8];
-#pragma unroll
-    for (int s = 0; s < 8; ++s) {
-      const int xx = x0 + s;
-      float dd = 0.f;
-      if (yin && xx >= 0 && xx < p.W) {
-        const uint4 k0 = __ldg(row + xx), k1 = __ldg(row + plane + xx);
-        float d0 = dot2_bf16(k0.x, qa.x, 0.f), d1 = dot2_bf16(k1.x, qb.x, 0.f);
-        d0 = dot2_bf16(k0.y, qa.y, d0);
-        d1 = dot2_bf16(k1.y, qb.y, d1);
-        d0 = dot2_bf16(k0.z, qa.z, d0);
-        d1 = dot2_bf16(k1.z, qb.z, d1);
-        d0 = dot2_bf16(k0.w, qa.w, d0);
-        d1 = dot2_bf16(k1.w, qb.w, d1);
-        dd = d0 + d1;
-      }
-      D[s] = dd;
-    }
-    // E[bb] = sum_tx wx[tx] D[bb+tx]; window row r feeds score rows a = r-3 .. r with weight wy[r-a]
-#pragma unroll
-    for (int bb = 0; bb < 5; ++bb) {
-      const float E = wx[0] * D[bb] + wx[1] * D[bb + 1] + wx[2] * D[bb + 2] + wx[3] * D[bb + 3];
-#pragma unroll
-      for (int a = 0; a < 5; ++a)
-        if (r - a >= 0 && r - a < 4) sc[a * 5 + bb] = fmaf(wy[r - a], E, sc[a * 5 + bb]);
-    }
-  }
+  // interior windows (all 8 columns inside the image) take a path without per-tap bounds predicates: one row pointer,
+  // 16 loads at immediate offsets; border windows keep the predicated path (zero padding per tap, grid_sample "zeros")
+  if (x0 >= 0 && x0 + 7 < p.W) refine_rows<true>(f2, plane, p.W, p.H, x0, y0, qa, qb, wx, wy, sc);
+  else refine_rows<false>(f2, plane, p.W, p.H, x0, y0, qa, qb, wx, wy, sc);
   float mx = -INFINITY;
 #pragma unroll
   for (int k = 0; k < 25; ++k) {
