@@ -128,6 +128,17 @@ int ufm_op_resize_ac(const float* in_f32, const void* in_bf16, int n, int h, int
                      int ow, float* out_f32, void* out_bf16, void* stream);
 int ufm_op_shuffle(const void* in, void* out, int is_f32, int n, int h, int w, int k, int C, void* stream);
 int ufm_op_im2col_s2(const void* in, void* out, int n, int h, int w, int C, int oh, int ow, void* stream);
+/* Non-native input sizes.  ufm_op_prep_resize replaces the normalisation of
+ * predict_correspondences_batched (uniflowmatch/models/base.py:215-229) fused with ResizeToFixedManipulation.__call__
+ * (uniflowmatch/utils/flow_resizing.py:276-354: bilinear, align_corners=False, antialias=True): `in` is [B,H0,W0,3]
+ * (nhwc) or [B,3,H0,W0], uint8 (mean/std used) or fp32 (v*mul+add used; NULL = identity); `out` is normalised fp32
+ * [B,3,H,W].  ufm_op_unmap replaces unmap_predicted_flow (flow_resizing.py:749-877) and unmap_predicted_channels
+ * (flow_resizing.py:955-1010): regions are [top,bottom,left,right]; src_mul/tgt_mul are (x,y) region-size ratios. */
+int ufm_op_prep_resize(const void* in, int is_u8, int nhwc, int B, int H0, int W0, int H, int W, const float* mean,
+                       const float* std, const float* mul, const float* add, float* out, void* stream);
+int ufm_op_unmap(const float* flow, const float* cov, int B, int H, int W, int H0, int W0, const int* rep, const int* src0,
+                 const int* src1, const float* src_mul, const float* tgt_mul, float* flow_out, float* cov_out,
+                 void* stream);
 /* desc: bf16 descriptors, channel-group planar [2B images (b,view)][2][H][W][8] (16 channels) */
 int ufm_op_refine(const void* desc, int B, int H, int W, const float* flow_in, const float* bias25,
                   float inv_temperature, float* flow_out, float* residual, float* log_softmax, void* stream);

@@ -283,3 +283,59 @@ def test_local_refinement_vs_oracle():
     assert (res.cpu() - r_ref).abs().max().item() < 2e-4
     assert (lsm.cpu().view(B, H, W, 5, 5) - l_ref).abs().max().item() < 2e-3
     assert (out.cpu() - (flow + r_ref)).abs()[..., 2:, 2:].max().item() < 1e-3
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# non-native sizes: normalise + anti-alias resize in, un-map out
+# ---------------------------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("H0,W0,th,tw", [(300, 400, 42, 56), (97, 131, 56, 70), (640, 853, 56, 70), (56, 70, 56, 70),
+                                         (40, 33, 84, 112)])
+def test_prep_resize_vs_torch_antialias(H0, W0, th, tw):
+    """normalise (base.py:215-229) + F.interpolate(bilinear, antialias=True) (flow_resizing.py:276-354), fp32 CPU torch as
+    the checker; uint8 BHWC / BCHW and fp32 (identity and re-normalised)."""
+    from ufm_b200 import prepost
+
+    g = torch.Generator().manual_seed(H0 * 7 + W0)
+    u8 = torch.randint(0, 256, (2, H0, W0, 3), dtype=torch.uint8, generator=g)
+    mean, std = prepost.norm_tensors("dinov2", "cpu")
+    x = (u8.permute(0, 3, 1, 2).float() / 255.0 - mean) / std
+    ref = F.interpolate(x, size=(th, tw), mode="bilinear", align_corners=False, antialias=True)
+    a = prepost.prep_resize(u8.cuda(), True, th, tw, "dinov2").cpu()
+    b = prepost.prep_resize(u8.permute(0, 3, 1, 2).contiguous().cuda(), False, th, tw, "dinov2").cpu()
+    assert torch.equal(a, b)
+    assert (a - ref).abs().max().item() < 2e-5, (a - ref).abs().max().item()
+    c = prepost.prep_resize(x.cuda(), False, th, tw, "dinov2", "dinov2").cpu()
+    assert (c - ref).abs().max().item() < 2e-5
+    # fp32 image normalised for another model family -> re-normalised to the encoder's statistics
+    pm, ps = prepost.norm_tensors("dust3r", "cpu")
+    xd = (u8.permute(0, 3, 1, 2).float() / 255.0 - pm) / ps
+    refd = F.interpolate(xd * (ps / std) + (pm - mean) / std, size=(th, tw), mode="bilinear", align_corners=False, antialias=True)
+    d = prepost.prep_resize(xd.permute(0, 2, 3, 1).contiguous().cuda(), True, th, tw, "dinov2", "dust3r").cpu()
+    assert (d - refd).abs().max().item() < 2e-5
+
+
+@pytest.mark.parametrize("H0,W0,H1,W1,H,W", [(300, 400, 300, 400, 42, 56), (97, 131, 120, 90, 56, 70), (30, 40, 30, 40, 56, 70),
+                                             (56, 70, 56, 70, 56, 70)])
+def test_unmap_vs_torch_shell(H0, W0, H1, W1, H, W):
+    """unmap_predicted_flow / unmap_predicted_channels (flow_resizing.py:749-877, 955-1010) against their torch
+    restatement (prepost.unmap_flow / unmap_channels) on the CPU."""
+    from ufm_b200 import prepost
+
+    g = torch.Generator().manual_seed(H0 + W1)
+    flow = torch.randn(2, 2, H, W, generator=g) * 10
+    cov = torch.rand(2, H, W, generator=g)
+    rep0 = prepost.scaled_region(H, W, H0, W0)
+    src0, src1 = [0, H0, 0, W0], [0, H1, 0, W1]
+    rf = prepost.unmap_flow(flow, rep0, src0, src1, (H0, W0))
+    rc = prepost.unmap_channels(cov.unsqueeze(1), rep0, src0, (H0, W0)).squeeze(1)
+    f, c = prepost.unmap(flow.cuda(), cov.cuda(), rep0, src0, src1, (H0, W0))
+    assert f.shape == rf.shape and c.shape == rc.shape
+    assert torch.equal(c.cpu(), rc)
+    assert (f.cpu() - rf).abs().max().item() < 2e-4, (f.cpu() - rf).abs().max().item()  # fp32 cancellation at |coord| ~ W
+    # a source region smaller than the image: everything outside stays zero
+    src0b = [3, H0 - 2, 5, W0 - 4]
+    rep0b = prepost.scaled_region(H, W, H0, W0)
+    rf2 = prepost.unmap_flow(flow, rep0b, src0b, src1, (H0, W0))
+    f2, _ = prepost.unmap(flow.cuda(), None, rep0b, src0b, src1, (H0, W0))
+    assert (f2.cpu() - rf2).abs().max().item() < 2e-4
+    assert f2[:, :, :3].abs().max().item() == 0 and f2[:, :, :, :5].abs().max().item() == 0

@@ -205,6 +205,15 @@ def test_api_contract_shapes_layouts_errors():
     assert o.flow.flow_output.shape == (1, 2, 300, 400) and o.covisibility.mask.shape == (1, 300, 400)
     assert rel_l2(o.flow.flow_output.cpu(), ref["flow"]) < FLOW_TOL
     assert (o.covisibility.mask.cpu() - ref["covisibility"]).abs().mean().item() < 1e-2
+    # up-scaled input, BCHW fp32 normalised for another model family (re-normalisation path), batch of 2
+    s3 = torch.randint(0, 256, (2, 3, 40, 52), dtype=torch.uint8, generator=g)
+    t3 = torch.randint(0, 256, (2, 3, 40, 52), dtype=torch.uint8, generator=g)
+    f3 = lambda u: (u.float() / 255.0 - 0.5) / 0.5
+    o3 = model.predict_correspondences_batched(f3(s3).cuda(), f3(t3).cuda(), data_norm_type="dust3r")
+    with torch.no_grad():
+        ref3 = O.predict_correspondences_batched(f3(s3), f3(t3), sd, cfg, data_norm_type="dust3r")
+    assert o3.flow.flow_output.shape == (2, 2, 40, 52)
+    assert rel_l2(o3.flow.flow_output.cpu(), ref3["flow"]) < FLOW_TOL
 
 
 def test_batch_chunking_and_determinism():

@@ -63,6 +63,8 @@ SYMBOLS = {
     "ufm_op_shuffle": (_I, [_P, _P, _I, _I, _I, _I, _I, _I, _P]),
     "ufm_op_im2col_s2": (_I, [_P, _P, _I, _I, _I, _I, _I, _I, _P]),
     "ufm_op_refine": (_I, [_P, _I, _I, _I, _P, _P, _F, _P, _P, _P, _P]),
+    "ufm_op_prep_resize": (_I, [_P, _I, _I, _I, _I, _I, _I, _I, _P, _P, _P, _P, _P, _P]),
+    "ufm_op_unmap": (_I, [_P, _P, _I, _I, _I, _I, _I, _P, _P, _P, _P, _P, _P, _P, _P]),
 }
 
 _lib = None

@@ -1042,6 +1042,43 @@ int ufm_op_im2col_s2(const void* in, void* out, int n, int h, int w, int C, int 
                           reinterpret_cast<cudaStream_t>(stream)) != cudaSuccess;
 }
 
+int ufm_op_prep_resize(const void* in, int is_u8, int nhwc, int B, int H0, int W0, int H, int W, const float* mean,
+                       const float* std, const float* mul, const float* add, float* out, void* stream) {
+  PrepParams p;
+  p.in = in; p.is_u8 = is_u8; p.nhwc = nhwc; p.B = B; p.H0 = H0; p.W0 = W0; p.H = H; p.W = W;
+  p.scale_y = (float)H0 / (float)H;
+  p.scale_x = (float)W0 / (float)W;
+  for (int c = 0; c < 3; ++c) {
+    p.mean[c] = mean ? mean[c] : 0.f;
+    p.std[c] = std ? std[c] : 1.f;
+    p.mul[c] = mul ? mul[c] : 1.f;
+    p.add[c] = add ? add[c] : 0.f;
+  }
+  p.out = out;
+  return launch_prep_resize(p, reinterpret_cast<cudaStream_t>(stream)) != cudaSuccess;
+}
+
+int ufm_op_unmap(const float* flow, const float* cov, int B, int H, int W, int H0, int W0, const int* rep, const int* src0,
+                 const int* src1, const float* src_mul, const float* tgt_mul, float* flow_out, float* cov_out,
+                 void* stream) {
+  UnmapParams p;
+  p.flow = flow; p.cov = cov; p.B = B; p.H = H; p.W = W; p.H0 = H0; p.W0 = W0;
+  for (int i = 0; i < 4; ++i) {
+    p.rep[i] = rep[i];
+    p.src0[i] = src0[i];
+    p.src1[i] = src1[i];
+  }
+  if (p.rep[0] < 0 || p.rep[1] > H || p.rep[2] < 0 || p.rep[3] > W || p.rep[1] <= p.rep[0] || p.rep[3] <= p.rep[2] ||
+      p.src0[0] < 0 || p.src0[1] > H0 || p.src0[2] < 0 || p.src0[3] > W0)
+    return 1;
+  for (int i = 0; i < 2; ++i) {
+    p.src_mul[i] = src_mul[i];
+    p.tgt_mul[i] = tgt_mul[i];
+  }
+  p.flow_out = flow_out; p.cov_out = cov_out;
+  return launch_unmap(p, reinterpret_cast<cudaStream_t>(stream)) != cudaSuccess;
+}
+
 int ufm_op_refine(const void* desc, int B, int H, int W, const float* flow_in, const float* bias25, float inv_temperature,
                   float* flow_out, float* residual, float* log_softmax, void* stream) {
   RefineParams p;

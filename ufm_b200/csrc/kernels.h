@@ -167,6 +167,27 @@ cudaError_t launch_refine(const RefineParams& p, cudaStream_t s);
 // pixel_shuffle(k) of z[(img,ty,tx)][(i,j,c)] bf16 into desc[img][C/8][h*k][w*k][8]
 cudaError_t launch_desc_shuffle(const __nv_bfloat16* z, __nv_bfloat16* desc, int n, int h, int w, int k, int C, cudaStream_t s);
 
+// ------------------------------------------------------------------------------------------------
+// Pre/post-processing for non-native input sizes (prepost.cu; flow_resizing.py:276-354, 749-877, 955-1010)
+// ------------------------------------------------------------------------------------------------
+struct PrepParams {
+  const void* in; int is_u8, nhwc;     // [B,H0,W0,3] or [B,3,H0,W0], uint8 or fp32
+  int B, H0, W0, H, W;
+  float scale_y, scale_x;              // H0 / H, W0 / W as fp32 (ATen area_pixel_compute_scale)
+  float mean[3], std[3];               // u8: (v/255 - mean) / std
+  float mul[3], add[3];                // fp32: v * mul + add (identity or re-normalisation)
+  float* out;                          // [B,3,H,W] normalised fp32
+};
+cudaError_t launch_prep_resize(const PrepParams& p, cudaStream_t s);
+struct UnmapParams {
+  const float* flow; const float* cov; // [B,2,H,W], [B,H,W] (may be null) at the inference resolution
+  int B, H, W, H0, W0;
+  int rep[4], src0[4], src1[4];        // [top, bottom, left, right]: represented region, source regions of image 0 / 1
+  float src_mul[2], tgt_mul[2];        // (x, y): source / target region size over represented region size
+  float* flow_out; float* cov_out;     // [B,2,H0,W0], [B,H0,W0] (may be null)
+};
+cudaError_t launch_unmap(const UnmapParams& p, cudaStream_t s);
+
 // NHWC fp32 [n,H,W,C] -> NCHW fp32 (stage dumps / descriptor export)
 cudaError_t launch_nhwc_to_nchw(const float* in, float* out, int n, int H, int W, int C, cudaStream_t s);
 

@@ -1,0 +1,148 @@
+// Pre/post-processing kernels for image pairs that are NOT at the inference resolution (reference:
+// uniflowmatch/utils/flow_resizing.py).  At the native resolution none of this runs (the patch gather reads the raw
+// images and the engine writes the API tensors directly).
+//
+//   prep_resize_kernel   ResizeToFixedManipulation.__call__ (flow_resizing.py:276-354): F.interpolate(bilinear,
+//                        align_corners=False, antialias=True) of the normalised image, fused with the normalisation of
+//                        predict_correspondences_batched (base.py:215-229): u8 (v/255 - mean)/std or an fp32 affine
+//                        re-normalisation, read from BHWC or BCHW, written as normalised fp32 BCHW at (H, W).
+//                        Weights follow ATen's anti-alias triangle filter (UpSampleKernel.cpp
+//                        _compute_indices_min_size_weights_aa / UpSample.cuh _compute_weights): support = max(scale, 1),
+//                        taps [int(c - s + .5), int(c + s + .5)), w = max(0, 1 - |(j + .5 - c) / max(scale, 1)|) / sum.
+//   unmap_kernel         unmap_predicted_flow (flow_resizing.py:749-877) and unmap_predicted_channels (:955-1010) in
+//                        one pass: crop the represented region, NEAREST-resample flow / covisibility onto the source
+//                        grid, bilinear-resample the (x + .5, y + .5) coordinate grid (align_corners=False), scale the
+//                        end points by the source / target size ratios, subtract, paste into zeros.
+#include "kernels.h"
+
+namespace ufm {
+
+namespace {
+
+constexpr int kMaxTaps = 64;  // per axis; a down-scale factor up to ~31x
+
+struct AaAxis {
+  int lo, n;
+  float center, invscale, inv_total;
+};
+
+// ATen: scale = in / out (float); support = scale >= 1 ? scale : 1; center = scale * (i + 0.5)
+__device__ __forceinline__ AaAxis aa_axis(int i, int in, float scale) {
+  AaAxis a;
+  const float support = scale >= 1.f ? scale : 1.f;
+  a.invscale = scale >= 1.f ? 1.f / scale : 1.f;
+  a.center = scale * ((float)i + 0.5f);
+  a.lo = max((int)(a.center - support + 0.5f), 0);
+  a.n = min((int)(a.center + support + 0.5f), in) - a.lo;
+  a.n = min(a.n, kMaxTaps);
+  float tot = 0.f;
+  for (int j = 0; j < a.n; ++j) tot += fmaxf(0.f, 1.f - fabsf(((float)(j + a.lo) - a.center + 0.5f) * a.invscale));
+  a.inv_total = tot != 0.f ? 1.f / tot : 0.f;
+  return a;
+}
+__device__ __forceinline__ float aa_w(const AaAxis& a, int j) {
+  return fmaxf(0.f, 1.f - fabsf(((float)(j + a.lo) - a.center + 0.5f) * a.invscale)) * a.inv_total;
+}
+
+template <typename T, bool NHWC>
+__global__ void __launch_bounds__(128) prep_resize_kernel(const PrepParams p) {
+  const int ox = blockIdx.x * 128 + threadIdx.x;
+  const int oy = blockIdx.y, b = blockIdx.z;
+  if (ox >= p.W) return;
+  const AaAxis ax = aa_axis(ox, p.W0, p.scale_x), ay = aa_axis(oy, p.H0, p.scale_y);
+  const T* img = reinterpret_cast<const T*>(p.in) + (size_t)b * 3 * p.H0 * p.W0;
+  const size_t plane0 = (size_t)p.H0 * p.W0;
+  float acc[3] = {0.f, 0.f, 0.f};
+  // separable like ATen's CPU kernel: horizontal pass per source row (fp32), then the vertical weights
+  for (int jy = 0; jy < ay.n; ++jy) {
+    const int y = ay.lo + jy;
+    float row[3] = {0.f, 0.f, 0.f};
+    for (int jx = 0; jx < ax.n; ++jx) {
+      const int x = ax.lo + jx;
+      const float w = aa_w(ax, jx);
+#pragma unroll
+      for (int c = 0; c < 3; ++c) {
+        const size_t idx = NHWC ? ((size_t)y * p.W0 + x) * 3 + c : c * plane0 + (size_t)y * p.W0 + x;
+        float v = (float)img[idx];
+        // base.py:215-229: (u8 / 255 - mean) / std, or an affine re-normalisation of an fp32 image
+        v = p.is_u8 ? (v / 255.0f - p.mean[c]) / p.std[c] : v * p.mul[c] + p.add[c];
+        row[c] = fmaf(w, v, row[c]);
+      }
+    }
+    const float wy = aa_w(ay, jy);
+#pragma unroll
+    for (int c = 0; c < 3; ++c) acc[c] = fmaf(wy, row[c], acc[c]);
+  }
+  const size_t plane = (size_t)p.H * p.W;
+  float* o = p.out + (size_t)b * 3 * plane + (size_t)oy * p.W + ox;
+#pragma unroll
+  for (int c = 0; c < 3; ++c) o[c * plane] = acc[c];
+}
+
+// F.interpolate(mode="nearest"): src = min(floor(dst * (in / out)), in - 1)
+__device__ __forceinline__ int nearest_src(int dst, float scale, int in) { return min((int)floorf((float)dst * scale), in - 1); }
+
+__global__ void __launch_bounds__(128) unmap_kernel(const UnmapParams p) {
+  const int X = blockIdx.x * 128 + threadIdx.x;
+  const int Y = blockIdx.y, b = blockIdx.z;
+  if (X >= p.W0) return;
+  const size_t plane0 = (size_t)p.H0 * p.W0, plane = (size_t)p.H * p.W;
+  const size_t o = (size_t)Y * p.W0 + X;
+  float fx = 0.f, fy = 0.f, cv = 0.f;
+  const int y = Y - p.src0[0], x = X - p.src0[2];
+  const int sh = p.src0[1] - p.src0[0], sw = p.src0[3] - p.src0[2];
+  if (y >= 0 && y < sh && x >= 0 && x < sw) {
+    const int rh = p.rep[1] - p.rep[0], rw = p.rep[3] - p.rep[2];
+    const float ys = (float)rh / (float)sh, xs = (float)rw / (float)sw;  // ATen: scale = in / out
+    const int iy = p.rep[0] + nearest_src(y, ys, rh), ix = p.rep[2] + nearest_src(x, xs, rw);
+    const size_t in = (size_t)iy * p.W + ix;
+    // bilinear (align_corners=False) resample of the coordinate grid sc[.., yy, xx] = (xx + 0.5, yy + 0.5)
+    float sy = ys * ((float)y + 0.5f) - 0.5f, sx = xs * ((float)x + 0.5f) - 0.5f;
+    sy = sy < 0.f ? 0.f : sy;
+    sx = sx < 0.f ? 0.f : sx;
+    const int y0 = (int)sy, x0 = (int)sx;
+    const int y1 = y0 + (y0 < rh - 1 ? 1 : 0), x1 = x0 + (x0 < rw - 1 ? 1 : 0);
+    const float ly = sy - (float)y0, lx = sx - (float)x0;
+    const float hy = 1.f - ly, hx = 1.f - lx;
+    const float gx0 = (float)x0 + 0.5f, gx1 = (float)x1 + 0.5f, gy0 = (float)y0 + 0.5f, gy1 = (float)y1 + 0.5f;
+    const float scx = hy * (hx * gx0 + lx * gx1) + ly * (hx * gx0 + lx * gx1);
+    const float scy = hy * (hx * gy0 + lx * gy0) + ly * (hx * gy1 + lx * gy1);
+    const float* fl = p.flow + (size_t)b * 2 * plane;
+    const float tx = fl[in] + scx, ty = fl[plane + in] + scy;
+    fx = (tx * p.tgt_mul[0] + (float)p.src1[2]) - (scx * p.src_mul[0] + (float)p.src0[2]);
+    fy = (ty * p.tgt_mul[1] + (float)p.src1[0]) - (scy * p.src_mul[1] + (float)p.src0[0]);
+    if (p.cov) cv = p.cov[(size_t)b * plane + in];
+  }
+  float* fo = p.flow_out + (size_t)b * 2 * plane0;
+  fo[o] = fx;
+  fo[plane0 + o] = fy;
+  if (p.cov_out) p.cov_out[(size_t)b * plane0 + o] = cv;
+}
+
+}  // namespace
+
+cudaError_t launch_prep_resize(const PrepParams& p, cudaStream_t s) {
+  if (p.B <= 0) return cudaSuccess;
+  if (p.H > 65535 || p.B > 65535) return cudaErrorInvalidValue;
+  // the tap loops are bounded by kMaxTaps per axis: refuse a down-scale they cannot represent instead of truncating it
+  if (2.f * p.scale_x + 2.f > (float)kMaxTaps || 2.f * p.scale_y + 2.f > (float)kMaxTaps) return cudaErrorInvalidValue;
+  dim3 grid((p.W + 127) / 128, p.H, p.B);
+  if (p.is_u8) {
+    if (p.nhwc) prep_resize_kernel<uint8_t, true><<<grid, 128, 0, s>>>(p);
+    else prep_resize_kernel<uint8_t, false><<<grid, 128, 0, s>>>(p);
+  } else {
+    if (p.nhwc) prep_resize_kernel<float, true><<<grid, 128, 0, s>>>(p);
+    else prep_resize_kernel<float, false><<<grid, 128, 0, s>>>(p);
+  }
+  return cudaGetLastError();
+}
+
+cudaError_t launch_unmap(const UnmapParams& p, cudaStream_t s) {
+  if (p.B <= 0) return cudaSuccess;
+  if (p.H0 > 65535 || p.B > 65535) return cudaErrorInvalidValue;
+  dim3 grid((p.W0 + 127) / 128, p.H0, p.B);
+  unmap_kernel<<<grid, 128, 0, s>>>(p);
+  return cudaGetLastError();
+}
+
+}  // namespace ufm

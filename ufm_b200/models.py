@@ -190,26 +190,18 @@ class UniFlowMatchModelsBase(nn.Module):
             # the reference's un-map at native size is the identity up to (flow + c) - c rounding
             flow, cov, _ = self._run(src.contiguous(), tgt.contiguous(), layout)
         else:
-            if layout == _lib.UFM_NHWC:
-                src, tgt = src.permute(0, 3, 1, 2), tgt.permute(0, 3, 1, 2)
-            mean, std = prepost.norm_tensors(required, dev)
-            if src.dtype == torch.uint8:
-                src = (src.float() / 255.0 - mean) / std
-                tgt = (tgt.float() / 255.0 - mean) / std
-            elif renorm:
-                pm, ps = prepost.norm_tensors(data_norm_type, dev)
-                src = src * (ps / std) + (pm - mean) / std
-                tgt = tgt * (ps / std) + (pm - mean) / std
+            # non-native size or foreign normalisation: normalise + anti-alias resize, forward, un-map -- two CUDA
+            # kernels around the engine (csrc/prepost.cu), no torch ops on the data path
             res = self.inference_resolution
             res = [res] if isinstance(res[0], int) else res
             th, tw = prepost.closest_aspect(res, hw0[0], hw0[1], hw1[0], hw1[1])
-            s0 = prepost.resize_to_fixed(src, th, tw).contiguous()
-            s1 = prepost.resize_to_fixed(tgt, th, tw).contiguous()
+            nhwc = layout == _lib.UFM_NHWC
+            s0 = prepost.prep_resize(src, nhwc, th, tw, required, data_norm_type)
+            s1 = prepost.prep_resize(tgt, nhwc, th, tw, required, data_norm_type)
             f, c, _ = self._run(s0, s1, _lib.UFM_NCHW)
             rep0 = prepost.scaled_region(th, tw, hw0[0], hw0[1])
             src0, src1 = [0, hw0[0], 0, hw0[1]], [0, hw1[0], 0, hw1[1]]
-            flow = prepost.unmap_flow(f, rep0, src0, src1, hw0)
-            cov = prepost.unmap_channels(c.unsqueeze(1), rep0, src0, hw0).squeeze(1) if c is not None else None
+            flow, cov = prepost.unmap(f, c, rep0, src0, src1, hw0)
         out = UFMOutputInterface(flow=UFMFlowFieldOutput(flow_output=flow.to(in_device)))
         if cov is not None:
             out.covisibility = UFMMaskFieldOutput(mask=cov.to(in_device), logits=None)

@@ -1,13 +1,23 @@
 """Pre/post-processing shell of ``predict_correspondences_batched`` for inputs that are NOT at the inference
-resolution (uniflowmatch/utils/flow_resizing.py:276-354, 667-744, 749-877, 955-1010).  Host-side torch ops on the
-device the data lives on; at the native resolution the engine consumes the raw images directly and none of this runs.
+resolution (uniflowmatch/utils/flow_resizing.py:276-354, 667-744, 749-877, 955-1010).  At the native resolution the
+engine consumes the raw images directly and none of this runs.
+
+The product path is ``prep_resize`` / ``unmap`` below: two CUDA kernels (csrc/prepost.cu) behind the C ABI
+(``ufm_op_prep_resize``, ``ufm_op_unmap``).  The torch functions (``resize_to_fixed``, ``unmap_flow``,
+``unmap_channels``) restate the same reference code with library ops and are kept as the checkers the GPU tests compare
+the kernels with; the model classes do not call them.
 """
 from __future__ import annotations
 
 from typing import List, Sequence, Tuple
 
+import ctypes as C
+
+import numpy as np
 import torch
 import torch.nn.functional as F
+
+from . import _lib
 
 # UC/models/encoders/image_normalizations.py:17-35
 IMAGE_NORMALIZATION = {
@@ -75,3 +85,63 @@ def unmap_channels(ch, rep0, src0, shape0):
     out = torch.zeros(ch.shape[0], ch.shape[1], shape0[0], shape0[1], dtype=ch.dtype, device=ch.device)
     out[..., src0[0]:src0[1], src0[2]:src0[3]] = r
     return out
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# kernel-backed product path
+# ---------------------------------------------------------------------------------------------------------------------
+def _f3(v):
+    return (C.c_float * 3)(*[float(x) for x in v])
+
+
+def prep_resize(img: torch.Tensor, nhwc: bool, th: int, tw: int, required: str, given: str = None) -> torch.Tensor:
+    """Normalise (base.py:215-229) and anti-alias resize (flow_resizing.py:276-354) in one kernel.
+
+    img: CUDA uint8 or fp32, [B,H0,W0,3] (nhwc) or [B,3,H0,W0]; fp32 images are already normalised with ``given`` and are
+    re-normalised to ``required`` when the two differ.  Returns normalised fp32 [B,3,th,tw]."""
+    assert img.is_cuda and img.dtype in (torch.uint8, torch.float32)
+    img = img.contiguous()
+    B = img.shape[0]
+    H0, W0 = (img.shape[1], img.shape[2]) if nhwc else (img.shape[2], img.shape[3])
+    mean, std = IMAGE_NORMALIZATION[required]
+    mul, add = (1.0, 1.0, 1.0), (0.0, 0.0, 0.0)
+    if img.dtype == torch.float32 and given is not None and given != required:
+        pm, ps = IMAGE_NORMALIZATION[given]
+        # same fp32 arithmetic as the torch expression  x * (ps / std) + (pm - mean) / std
+        mul = [float(np.float32(a) / np.float32(b)) for a, b in zip(ps, std)]
+        add = [float((np.float32(a) - np.float32(m)) / np.float32(b)) for a, m, b in zip(pm, mean, std)]
+    out = torch.empty(B, 3, th, tw, dtype=torch.float32, device=img.device)
+    lib = _lib.load()
+    with torch.cuda.device(img.device):
+        rc = lib.ufm_op_prep_resize(img.data_ptr(), int(img.dtype == torch.uint8), int(nhwc), B, H0, W0, th, tw, _f3(mean),
+                                    _f3(std), _f3(mul), _f3(add), out.data_ptr(),
+                                    torch.cuda.current_stream().cuda_stream)
+    if rc != 0:
+        raise RuntimeError(f"ufm_op_prep_resize failed for {H0}x{W0} -> {th}x{tw} (down-scale factor too large?)")
+    return out
+
+
+def unmap(flow: torch.Tensor, cov, rep0, src0, src1, shape0) -> Tuple[torch.Tensor, torch.Tensor]:
+    """``unmap_predicted_flow`` + ``unmap_predicted_channels`` (flow_resizing.py:749-877, 955-1010) in one kernel.
+
+    flow [B,2,H,W], cov [B,H,W] or None (fp32, CUDA, inference resolution) -> flow [B,2,H0,W0], cov [B,H0,W0]."""
+    flow = flow.contiguous()
+    B, _, H, W = flow.shape
+    H0, W0 = int(shape0[0]), int(shape0[1])
+    svs = [src0[1] - src0[0], src0[3] - src0[2]]
+    tvs = [src1[1] - src1[0], src1[3] - src1[2]]
+    rh, rw = rep0[1] - rep0[0], rep0[3] - rep0[2]
+    i4 = lambda v: (C.c_int * 4)(*[int(x) for x in v])
+    f2 = lambda a, b: (C.c_float * 2)(float(a), float(b))
+    out = torch.empty(B, 2, H0, W0, dtype=torch.float32, device=flow.device)
+    cout = torch.empty(B, H0, W0, dtype=torch.float32, device=flow.device) if cov is not None else None
+    if cov is not None:
+        cov = cov.contiguous()
+    lib = _lib.load()
+    with torch.cuda.device(flow.device):
+        rc = lib.ufm_op_unmap(flow.data_ptr(), None if cov is None else cov.data_ptr(), B, H, W, H0, W0, i4(rep0), i4(src0),
+                              i4(src1), f2(svs[1] / rw, svs[0] / rh), f2(tvs[1] / rw, tvs[0] / rh), out.data_ptr(),
+                              None if cout is None else cout.data_ptr(), torch.cuda.current_stream().cuda_stream)
+    if rc != 0:
+        raise RuntimeError("ufm_op_unmap: invalid regions")
+    return out, cout
