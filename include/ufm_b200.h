@@ -39,13 +39,24 @@ typedef struct ufm_config {
   int dpt_layer_dims[4];
   int dpt_feature_dim, dpt_hidden;
   int flow_out_ch;                         /* 2 */
-  int unc_out_ch;                          /* 0 = no uncertainty head, 1 = non_occluded_mask */
+  int unc_out_ch;                          /* 0 = no uncertainty head, else the sum of its adaptors' channels (<= 8) */
   float flow_scale[2], flow_shift[2];      /* FlowAdaptor: flow = raw*scale + shift (adaptors.py:77-120) */
   /* Refine (ufm.py:710-1178) */
   int refine;                              /* 0/1 */
   int cls_in, cls_hidden, cls_out, cls_patch, refine_P;
   float temperature;
+  /* uncertainty-head adaptors in AdaptorMap order (ufm.py:553-556, UC/models/prediction_heads/adaptors.py:899-985).
+   * unc_n_adaptors == 0 with unc_out_ch == 1 means the single 'non_occluded_mask' MaskAdaptor. */
+  int unc_n_adaptors;
+  int unc_kind[4];                         /* UFM_ADAPT_* */
+  float unc_vmin[4], unc_vmax[4];          /* ConfidenceAdaptor vmin / vmax */
 } ufm_config;
+
+/* adaptor kinds and their channel counts: mask 1 ('non_occluded_mask'), covariance 3 ('flow_cov'), confidence 1
+ * ('keypoint_confidence').  Outputs other than the mask are read back with ufm_stage_copy: "flow_cov", "flow_cov_inv"
+ * [B,3,H,W], "flow_cov_log_det" [B,1,H,W], "keypoint_confidence" [B,H,W]. */
+enum { UFM_ADAPT_MASK = 1, UFM_ADAPT_COV_EXP_TANH = 2, UFM_ADAPT_CONF_EXP = 3, UFM_ADAPT_CONF_SIGMOID = 4,
+       UFM_ADAPT_CONF_SOFTMAX = 5 };
 
 /* Create an engine on CUDA device `device`.  Fails (non-zero) if no sm_100 GPU is present: there is no CPU fallback. */
 int ufm_create(const ufm_config* cfg, int device, ufm_engine** out);
@@ -133,12 +144,14 @@ int ufm_op_im2col_s2(const void* in, void* out, int n, int h, int w, int C, int 
  * (uniflowmatch/utils/flow_resizing.py:276-354: bilinear, align_corners=False, antialias=True): `in` is [B,H0,W0,3]
  * (nhwc) or [B,3,H0,W0], uint8 (mean/std used) or fp32 (v*mul+add used; NULL = identity); `out` is normalised fp32
  * [B,3,H,W].  ufm_op_unmap replaces unmap_predicted_flow (flow_resizing.py:749-877) and unmap_predicted_channels
- * (flow_resizing.py:955-1010): regions are [top,bottom,left,right]; src_mul/tgt_mul are (x,y) region-size ratios. */
+ * (flow_resizing.py:955-1010): regions are [top,bottom,left,right]; src_mul/tgt_mul are (x,y) region-size ratios.  flow /
+ * flow_out may be NULL (channels only); plane b of cov_out is multiplied by cov_mul[b % cov_mul_n] (NULL = 1), which is the
+ * covariance rescaling of base.py:295-319 when the three covariance planes are passed as 3B single-channel images. */
 int ufm_op_prep_resize(const void* in, int is_u8, int nhwc, int B, int H0, int W0, int H, int W, const float* mean,
                        const float* std, const float* mul, const float* add, float* out, void* stream);
 int ufm_op_unmap(const float* flow, const float* cov, int B, int H, int W, int H0, int W0, const int* rep, const int* src0,
                  const int* src1, const float* src_mul, const float* tgt_mul, float* flow_out, float* cov_out,
-                 void* stream);
+                 const float* cov_mul, int cov_mul_n, void* stream);
 /* desc: bf16 descriptors, channel-group planar [2B images (b,view)][2][H][W][8] (16 channels) */
 int ufm_op_refine(const void* desc, int B, int H, int W, const float* flow_in, const float* bias25,
                   float inv_temperature, float* flow_out, float* residual, float* log_softmax, void* stream);

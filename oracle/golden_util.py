@@ -13,6 +13,8 @@ GOLDEN_CASES = {
     "tiny_alt_qknorm": dict(cfg="tiny_alt_qknorm", batch=2, out_gain=8.0),
     "ufm_base_assumed": dict(cfg="ufm_base_assumed", batch=1, out_gain=8.0),
     "ufm_refine_assumed": dict(cfg="ufm_refine_assumed", batch=1, out_gain=8.0),
+    # uncertainty head with Covariance2DAdaptor + ConfidenceAdaptor + MaskAdaptor; gain 1 keeps exp() sane
+    "tiny_cov": dict(cfg="tiny_cov", batch=2, out_gain=1.0),
 }
 
 

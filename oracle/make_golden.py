@@ -59,6 +59,15 @@ def run_reference(name: str):
     if hasattr(model, "uncertainty_head"):
         hk(model.uncertainty_head[0][0], lambda o: st.__setitem__("dptu", o.features_upsampled_8x))
         hk(model.uncertainty_head[0], lambda o: st.__setitem__("headu_raw", o.decoded_channels))
+
+        def unc(o):
+            if "flow_cov" in o:
+                st["flow_cov"], st["flow_cov_inv"] = o["flow_cov"].covariance, o["flow_cov"].inv_covariance
+                st["flow_cov_log_det"] = o["flow_cov"].log_det
+            if "keypoint_confidence" in o:
+                st["keypoint_confidence"] = o["keypoint_confidence"].value
+
+        hk(model.uncertainty_head[1], unc)
     if hasattr(model, "classification_head"):
         hk(model.classification_head, lambda o: st.__setitem__("desc", o.decoded_channels))
         orig = model.classification_refinement
@@ -78,6 +87,8 @@ def run_reference(name: str):
     st["api_flow"] = out.flow.flow_output
     if out.covisibility is not None:
         st["api_covis"] = out.covisibility.mask
+    if out.flow.flow_covariance is not None:
+        st["api_flow_cov"] = out.flow.flow_covariance
     return st, dt
 
 

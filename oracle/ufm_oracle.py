@@ -248,6 +248,19 @@ def covariance_adaptor(x):
     return cov, log_det, inv
 
 
+def confidence_adaptor(x, kw):
+    """``ConfidenceAdaptor.forward`` (adaptors.py:899-927)."""
+    t, vmin, vmax = kw["confidence_type"], kw["vmin"], kw["vmax"]
+    if t == "exp":
+        return vmin + x.exp().clip(max=vmax - vmin)
+    if t == "sigmoid":
+        return torch.sigmoid(x) * (vmax - vmin) + vmin
+    if t == "softmax":
+        B, C, H, W = x.shape
+        return F.softmax(x.reshape(B, C, -1), dim=-1).reshape(B, C, H, W) * (H * W)
+    raise ValueError(t)
+
+
 def run_adaptors(raw, adaptors_kwargs, out_hw) -> Dict[str, Any]:
     """``AdaptorMap.forward`` (UC/models/prediction_heads/base.py:186-210): split channels in dict order."""
     out, c = {}, 0
@@ -262,6 +275,9 @@ def run_adaptors(raw, adaptors_kwargs, out_hw) -> Dict[str, Any]:
         elif cls == "Covariance2DAdaptor":
             out[name] = covariance_adaptor(raw[:, c:c + 3])
             c += 3
+        elif cls == "ConfidenceAdaptor":
+            out[name] = confidence_adaptor(raw[:, c:c + 1], a["kwargs"])
+            c += 1
         else:
             raise NotImplementedError(cls)
     return out
@@ -382,6 +398,8 @@ def forward_stages(img1: torch.Tensor, img2: torch.Tensor, sd, cfg, stop_after: 
             st["covis_logits"] = au["non_occluded_mask"]["logits"]
         if "flow_cov" in au:
             st["flow_cov"], st["flow_cov_log_det"], st["flow_cov_inv"] = au["flow_cov"]
+        if "keypoint_confidence" in au:
+            st["keypoint_confidence"] = au["keypoint_confidence"]  # (B,1,H,W); ufm.py:654 squeezes dim 1
     st["flow"] = st["flow_reg"]
     if "classification_head_kwargs" in cfg:
         ck = cfg["classification_head_kwargs"]

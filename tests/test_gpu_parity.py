@@ -247,3 +247,52 @@ def test_north_star_absolute_tolerances(name):
     mc = max_abs(out.covisibility.mask.cpu(), ref["covisibility"])
     print(f"\n[{name} natural scale] flow max-abs {mf:.3e} px (ref max {ref['flow'].abs().max():.3f}); covis max-abs {mc:.3e}")
     assert mf <= 1e-2 and mc <= 1e-3
+
+
+@pytest.mark.parametrize("conf_type", ["sigmoid", "exp", "softmax"])
+def test_uncertainty_adaptors(conf_type):
+    """Covariance2DAdaptor + ConfidenceAdaptor + MaskAdaptor on one uncertainty head (adaptors.py:899-985,
+    consumed at ufm.py:644-660, covariance rescaled at base.py:295-319)."""
+    from ufm_b200.configs import tiny
+
+    cfg = tiny(False, unc_adaptors="cov_conf_mask", conf_type=conf_type)
+    sd = make_state_dict(cfg, seed=0, out_gain=1.0)
+    m = UniFlowMatchConfidence(**cfg).to("cuda")
+    m.load_state_dict(sd)
+    W, H = cfg["inference_resolution"]
+    src, tgt = make_inputs(3, H, W, seed=5)
+    m.max_pairs_per_call = 2  # two chunks: the per-chunk stage read-back must concatenate
+    s0, s1 = O.canonicalize_inputs(src, tgt, "dinov2", None)
+    res = m.forward({"img": s0.cuda(), "data_norm_type": "dinov2", "symmetrized": False},
+                    {"img": s1.cuda(), "data_norm_type": "dinov2", "symmetrized": False})
+    torch.cuda.synchronize()
+    assert res.flow.flow_covariance.shape == (3, 3, H, W) and res.keypoint_confidence.shape == (3, H, W)
+    assert res.covisibility.mask.shape == (3, 1, H, W)
+    # adaptor arithmetic in isolation: the oracle's AdaptorMap on the ENGINE's raw head output (last chunk)
+    eng = next(iter(m._engines.values()))
+    raw = eng.stage("headu_raw").cpu()
+    au = O.run_adaptors(raw, cfg["uncertainty_adaptors_kwargs"], (H, W))
+    cov, log_det, inv = au["flow_cov"]
+    n = raw.shape[0]
+    # element-wise error relative to |ref| + a floor (the off-diagonal terms cross zero)
+    rel = lambda a, b: ((a - b).abs() / (b.abs() + 1e-2 * b.abs().mean())).max().item()
+    assert rel(res.flow.flow_covariance[-n:].cpu(), cov) < 1e-4
+    # 1 / (1 - tanh^2 + 1e-8) is ill-conditioned near |tanh| = 1: an ulp of tanhf is amplified by 2 tanh / (1 - tanh^2)
+    assert rel(res.flow.flow_covariance_inv[-n:].cpu(), inv) < 2e-2
+    assert max_abs(res.flow.flow_covariance_log_det[-n:].cpu(), log_det) < 2e-2  # log of the same 1 - tanh^2 term
+    assert rel(res.keypoint_confidence[-n:].cpu(), au["keypoint_confidence"].squeeze(1)) < 2e-4
+    assert max_abs(res.covisibility.mask[-n:].cpu(), au["non_occluded_mask"]["mask"]) < 1e-6
+    # end to end against the fp32 oracle, native and non-native size (covariance is nearest-resampled and rescaled)
+    with torch.no_grad():
+        ref = O.predict_correspondences_batched(src, tgt, sd, cfg)
+    out = m.predict_correspondences_batched(src.cuda(), tgt.cuda())
+    assert rel_l2(out.flow.flow_covariance.cpu(), ref["flow_covariance"]) < 5e-2
+    g = torch.Generator().manual_seed(4)
+    s2 = torch.randint(0, 256, (2, 120, 150, 3), dtype=torch.uint8, generator=g)
+    t2 = torch.randint(0, 256, (2, 120, 150, 3), dtype=torch.uint8, generator=g)
+    with torch.no_grad():
+        ref2 = O.predict_correspondences_batched(s2, t2, sd, cfg)
+    out2 = m.predict_correspondences_batched(s2.cuda(), t2.cuda())
+    assert out2.flow.flow_covariance.shape == (2, 3, 120, 150)
+    assert rel_l2(out2.flow.flow_covariance.cpu(), ref2["flow_covariance"]) < 5e-2
+    assert rel_l2(out2.flow.flow_output.cpu(), ref2["flow"]) < FLOW_TOL

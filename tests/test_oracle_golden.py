@@ -43,6 +43,8 @@ def test_oracle_matches_reference_golden(name):
             mine = api["flow"] if api is not None else st["flow"]  # native size: un-map is the identity map
         elif stage == "api_covis":
             mine = api["covisibility"] if api is not None else st["covis"].squeeze(1)
+        elif stage == "api_flow_cov":
+            mine = api["flow_covariance"] if api is not None else st["flow_cov"]
         else:
             mine = st[stage]
         ref_sub = torch.from_numpy(g[key])

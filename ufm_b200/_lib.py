@@ -14,6 +14,7 @@ LIB_PATH = os.path.join(_HERE, "libufm_b200.so")
 UFM_F32, UFM_BF16, UFM_U8 = 0, 1, 2
 UFM_NCHW, UFM_NHWC = 0, 1
 GEMM_GELU, GEMM_RELU_BF16, GEMM_TAIL, GEMM_TAIL_SIGMOID = 1, 2, 4, 8
+ADAPT_MASK, ADAPT_COV_EXP_TANH, ADAPT_CONF_EXP, ADAPT_CONF_SIGMOID, ADAPT_CONF_SOFTMAX = 1, 2, 3, 4, 5
 PROFILE_CATS = ("gemm", "conv3x3", "attention", "layernorm", "resize", "move", "refine")
 
 
@@ -34,6 +35,8 @@ class UfmConfig(C.Structure):
         ("cls_in", C.c_int), ("cls_hidden", C.c_int), ("cls_out", C.c_int), ("cls_patch", C.c_int),
         ("refine_P", C.c_int),
         ("temperature", C.c_float),
+        ("unc_n_adaptors", C.c_int), ("unc_kind", C.c_int * 4),
+        ("unc_vmin", C.c_float * 4), ("unc_vmax", C.c_float * 4),
     ]
 
 
@@ -64,7 +67,7 @@ SYMBOLS = {
     "ufm_op_im2col_s2": (_I, [_P, _P, _I, _I, _I, _I, _I, _I, _P]),
     "ufm_op_refine": (_I, [_P, _I, _I, _I, _P, _P, _F, _P, _P, _P, _P]),
     "ufm_op_prep_resize": (_I, [_P, _I, _I, _I, _I, _I, _I, _I, _P, _P, _P, _P, _P, _P]),
-    "ufm_op_unmap": (_I, [_P, _P, _I, _I, _I, _I, _I, _P, _P, _P, _P, _P, _P, _P, _P]),
+    "ufm_op_unmap": (_I, [_P, _P, _I, _I, _I, _I, _I, _P, _P, _P, _P, _P, _P, _P, _P, _I, _P]),
 }
 
 _lib = None

@@ -84,7 +84,7 @@ def ufm_refine_assumed(inference_resolution=(560, 420)) -> Dict[str, Any]:
 
 
 def tiny(refine: bool = False, inference_resolution=(224, 168), info_sharing_str="global_attention",
-         qk_norm: bool = False) -> Dict[str, Any]:
+         qk_norm: bool = False, unc_adaptors: str = "mask", conf_type: str = "sigmoid") -> Dict[str, Any]:
     """A small architecture with the same topology, for fast CPU goldens and GPU parity at every
     stage boundary: ViT-S/14 truncated to 4 layers, 4x128 info sharing, slim DPT heads."""
     W, H = inference_resolution
@@ -100,6 +100,17 @@ def tiny(refine: bool = False, inference_resolution=(224, 168), info_sharing_str
         cfg["info_sharing_kwargs"].update({"use_pe_for_non_reference_views": False, "max_num_views_for_pe": 1000})
     cfg["feature_head_kwargs"] = _dpt([384, 128, 128, 128], 2, layer_dims=(64, 64, 128, 128), feature_dim=64)
     cfg["uncertainty_head_kwargs"] = _dpt([384, 128, 128, 128], 1, layer_dims=(64, 64, 128, 128), feature_dim=64)
+    if unc_adaptors == "cov_conf_mask":
+        # flow covariance + keypoint confidence + covisibility mask from one 5-channel uncertainty head
+        # (names as consumed by ufm.py:644-660)
+        vmin, vmax = (1.0, 50.0) if conf_type == "exp" else (0.0, 1.0)
+        cfg["uncertainty_head_kwargs"] = _dpt([384, 128, 128, 128], 5, layer_dims=(64, 64, 128, 128), feature_dim=64)
+        cfg["uncertainty_adaptors_kwargs"] = {
+            "flow_cov": {"class": "Covariance2DAdaptor", "kwargs": {"name": "flow_cov", "parametrization": "exp_tanh"}},
+            "keypoint_confidence": {"class": "ConfidenceAdaptor", "kwargs": {
+                "name": "keypoint_confidence", "confidence_type": conf_type, "vmin": vmin, "vmax": vmax}},
+            "non_occluded_mask": {"class": "MaskAdaptor", "kwargs": {"name": "non_occluded_mask"}},
+        }
     if refine:
         cfg["classification_head_kwargs"].update({"input_feature_dim": 384 + 128})
     return cfg
@@ -111,6 +122,7 @@ CONFIGS = {
     "ufm_base_hires": lambda: ufm_base_assumed((1120, 840)),
     "tiny_base": lambda: tiny(False),
     "tiny_refine": lambda: tiny(True),
+    "tiny_cov": lambda: tiny(False, unc_adaptors="cov_conf_mask"),
 }
 
 

@@ -74,7 +74,7 @@ struct Epi {
   long long sn = 0, sy = 0, sx = 0, out_off = 0;
   uint32_t flags = 0;
   const float* w2 = nullptr;
-  float b2[4] = {0, 0, 0, 0}, tscale[4] = {1, 1, 1, 1}, tshift[4] = {0, 0, 0, 0};
+  float b2[kTailMax] = {0, 0, 0, 0, 0, 0, 0, 0}, tscale[kTailMax] = {1, 1, 1, 1, 1, 1, 1, 1}, tshift[kTailMax] = {0, 0, 0, 0, 0, 0, 0, 0};
   int tail_out = 0;
   float* out2 = nullptr;
 };
@@ -98,7 +98,7 @@ bool build_gemm(GemmParams* gp, int* BN, const AView& a, const void* wt, int n_o
   const uint32_t bbox[2] = {64, (uint32_t)(*BN / gp->ctas)};
   if (!make_tmap_bf16(&gp->tmB, wt, 2, bdims, bstr, bbox, err, errlen)) return false;
   if (tail) {
-    if (n_out > 128 || e.tail_out < 1 || e.tail_out > 4 || n_out % 32) {
+    if (n_out > 128 || e.tail_out < 1 || e.tail_out > kTailMax || n_out % 32) {
       snprintf(err, errlen, "tail epilogue needs N<=128, N%%32==0, 1..4 outputs (N=%d out=%d)", n_out, e.tail_out);
       return false;
     }
@@ -156,7 +156,7 @@ bool build_gemm(GemmParams* gp, int* BN, const AView& a, const void* wt, int n_o
   gp->sN = e.sn; gp->sY = e.sy; gp->sX = e.sx; gp->out_off = e.out_off;
   gp->r2N = e.r2n; gp->r2Y = e.r2y; gp->r2X = e.r2x;
   gp->w2 = e.w2; gp->tail_out = e.tail_out; gp->out2 = e.out2;
-  for (int i = 0; i < 4; ++i) {
+  for (int i = 0; i < kTailMax; ++i) {
     gp->tail_b2[i] = e.b2[i];
     gp->tail_scale[i] = e.tscale[i];
     gp->tail_shift[i] = e.tshift[i];
@@ -636,7 +636,41 @@ int ufm_engine::forward(const void* src, const void* tgt, int pairs, int in_dtyp
   set_stage("flow_reg", flow_reg, UFM_F32, {Bp, 2, c.img_h, c.img_w});
   if (c.unc_out_ch > 0) {
     float* cov = covis_out ? covis_out : B<float>("covis");
-    if (!dpt_head("hu", Bp, c.unc_out_ch, true, nullptr, nullptr, B<bf16>("dptu"), cov, B<float>("headu_raw"))) return 1;
+    if (c.unc_n_adaptors == 0) {
+      // the single non_occluded_mask MaskAdaptor: sigmoid fused into the tail epilogue
+      if (!dpt_head("hu", Bp, c.unc_out_ch, true, nullptr, nullptr, B<bf16>("dptu"), cov, B<float>("headu_raw"))) return 1;
+    } else {
+      // several adaptors: the tail writes the raw channels, one elementwise kernel applies AdaptorMap (adaptors.py)
+      if (!dpt_head("hu", Bp, c.unc_out_ch, false, nullptr, nullptr, B<bf16>("dptu"), B<float>("headu_raw"), nullptr))
+        return 1;
+      UncAdaptParams up;
+      up.raw = B<float>("headu_raw"); up.B = Bp; up.C = c.unc_out_ch; up.H = c.img_h; up.W = c.img_w;
+      up.n = c.unc_n_adaptors;
+      int ch = 0;
+      bool has_cov = false, has_conf = false;
+      for (int a = 0; a < up.n; ++a) {
+        up.kind[a] = c.unc_kind[a]; up.ch[a] = ch; up.vmin[a] = c.unc_vmin[a]; up.vmax[a] = c.unc_vmax[a];
+        ch += c.unc_kind[a] == UFM_ADAPT_COV_EXP_TANH ? 3 : 1;
+        has_cov = has_cov || c.unc_kind[a] == UFM_ADAPT_COV_EXP_TANH;
+        has_conf = has_conf || c.unc_kind[a] >= UFM_ADAPT_CONF_EXP;
+      }
+      up.mask = cov;
+      up.cov = has_cov ? B<float>("flow_cov") : nullptr;
+      up.cov_inv = has_cov ? B<float>("flow_cov_inv") : nullptr;
+      up.cov_log_det = has_cov ? B<float>("flow_cov_log_det") : nullptr;
+      up.conf = has_conf ? B<float>("kp_conf") : nullptr;
+      up.conf_stats = has_conf ? B<float>("conf_stats") : nullptr;
+      const double plane = (double)c.img_h * c.img_w;
+      if (!run(UFM_CAT_MOVE, 0.0, Bp * plane * 4.0 * (c.unc_out_ch + 1 + (has_cov ? 7 : 0) + (has_conf ? 1 : 0)),
+               "unc adaptors", [&] { return launch_unc_adaptors(up, st); }))
+        return 1;
+      if (has_cov) {
+        set_stage("flow_cov", up.cov, UFM_F32, {Bp, 3, c.img_h, c.img_w});
+        set_stage("flow_cov_inv", up.cov_inv, UFM_F32, {Bp, 3, c.img_h, c.img_w});
+        set_stage("flow_cov_log_det", up.cov_log_det, UFM_F32, {Bp, 1, c.img_h, c.img_w});
+      }
+      if (has_conf) set_stage("keypoint_confidence", up.conf, UFM_F32, {Bp, c.img_h, c.img_w});
+    }
     set_stage("dptu", B<bf16>("dptu"), UFM_BF16, {Bp, H8, W8, c.dpt_feature_dim});
     set_stage("headu_raw", B<float>("headu_raw"), UFM_F32, {Bp, c.unc_out_ch, c.img_h, c.img_w});
   }
@@ -718,6 +752,26 @@ int ufm_create(const ufm_config* cfg, int device, ufm_engine** out) {
     delete e;
     fprintf(stderr, "ufm_create: dims must be multiples of 128 with head_dim 64\n");
     return 5;
+  }
+  {
+    int ch = 0, n_mask = 0, n_cov = 0, n_conf = 0;
+    bool bad = c.unc_n_adaptors < 0 || c.unc_n_adaptors > 4 || c.unc_out_ch < 0 || c.unc_out_ch > kTailMax;
+    for (int a = 0; !bad && a < c.unc_n_adaptors; ++a) {
+      const int k = c.unc_kind[a];
+      bad = k < UFM_ADAPT_MASK || k > UFM_ADAPT_CONF_SOFTMAX;
+      ch += k == UFM_ADAPT_COV_EXP_TANH ? 3 : 1;
+      n_mask += k == UFM_ADAPT_MASK;
+      n_cov += k == UFM_ADAPT_COV_EXP_TANH;
+      n_conf += k >= UFM_ADAPT_CONF_EXP;
+    }
+    bad = bad || n_mask > 1 || n_cov > 1 || n_conf > 1 || (c.unc_n_adaptors > 0 && ch != c.unc_out_ch) ||
+          (c.unc_n_adaptors == 0 && c.unc_out_ch > 1);
+    if (bad) {
+      delete e;
+      fprintf(stderr, "ufm_create: uncertainty adaptors must be at most one mask, one covariance and one confidence adaptor "
+                      "whose channels add up to unc_out_ch\n");
+      return 7;
+    }
   }
   if (c.refine && (c.cls_out != 16 || c.refine_P != 5)) {
     delete e;
@@ -815,7 +869,17 @@ int ufm_prepare(ufm_engine* e, int max_pairs) {
   if (c.unc_out_ch > 0) {
     ok = ok && e->alloc("dptu", UFM_BF16, Bp * 64 * n * fd);
     ok = ok && e->alloc("headu_raw", UFM_F32, Bp * c.unc_out_ch * c.img_h * c.img_w);
-    ok = ok && e->alloc("covis", UFM_F32, Bp * c.unc_out_ch * c.img_h * c.img_w);
+    ok = ok && e->alloc("covis", UFM_F32, Bp * c.img_h * c.img_w);
+    for (int a = 0; a < c.unc_n_adaptors; ++a) {
+      if (c.unc_kind[a] == UFM_ADAPT_COV_EXP_TANH) {
+        ok = ok && e->alloc("flow_cov", UFM_F32, Bp * 3 * c.img_h * c.img_w);
+        ok = ok && e->alloc("flow_cov_inv", UFM_F32, Bp * 3 * c.img_h * c.img_w);
+        ok = ok && e->alloc("flow_cov_log_det", UFM_F32, Bp * c.img_h * c.img_w);
+      } else if (c.unc_kind[a] >= UFM_ADAPT_CONF_EXP) {
+        ok = ok && e->alloc("kp_conf", UFM_F32, Bp * c.img_h * c.img_w);
+        ok = ok && e->alloc("conf_stats", UFM_F32, Bp * 2);
+      }
+    }
   }
   if (c.refine) {
     ok = ok && e->alloc("flow_reg", UFM_F32, Bp * 2 * c.img_h * c.img_w);
@@ -979,7 +1043,7 @@ int ufm_op_gemm(const void* a, int C, int X, int Y, int Nimg, int64_t a_sx, int6
   e.sn = sn; e.sy = sy; e.sx = sx; e.out_off = out_off;
   e.flags = flags;
   e.w2 = tail_w2; e.tail_out = tail_out; e.out2 = out2;
-  for (int i = 0; i < tail_out && i < 4; ++i) {
+  for (int i = 0; i < tail_out && i < kTailMax; ++i) {
     e.b2[i] = tail_b2 ? tail_b2[i] : 0.f;
     e.tscale[i] = tail_scale ? tail_scale[i] : 1.f;
     e.tshift[i] = tail_shift ? tail_shift[i] : 0.f;
@@ -1060,7 +1124,7 @@ int ufm_op_prep_resize(const void* in, int is_u8, int nhwc, int B, int H0, int W
 
 int ufm_op_unmap(const float* flow, const float* cov, int B, int H, int W, int H0, int W0, const int* rep, const int* src0,
                  const int* src1, const float* src_mul, const float* tgt_mul, float* flow_out, float* cov_out,
-                 void* stream) {
+                 const float* cov_mul, int cov_mul_n, void* stream) {
   UnmapParams p;
   p.flow = flow; p.cov = cov; p.B = B; p.H = H; p.W = W; p.H0 = H0; p.W0 = W0;
   for (int i = 0; i < 4; ++i) {
@@ -1076,6 +1140,9 @@ int ufm_op_unmap(const float* flow, const float* cov, int B, int H, int W, int H
     p.tgt_mul[i] = tgt_mul[i];
   }
   p.flow_out = flow_out; p.cov_out = cov_out;
+  p.cov_mul_n = (cov_mul && cov_mul_n >= 1 && cov_mul_n <= 4) ? cov_mul_n : 1;
+  for (int i = 0; i < 4; ++i) p.cov_mul[i] = (cov_mul && i < p.cov_mul_n) ? cov_mul[i] : 1.f;
+  if ((flow == nullptr) != (flow_out == nullptr)) return 1;
   return launch_unmap(p, reinterpret_cast<cudaStream_t>(stream)) != cudaSuccess;
 }
 

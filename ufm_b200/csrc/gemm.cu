@@ -38,7 +38,7 @@ struct Cfg {
   static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
   static constexpr int STAGES = (STAGE_BYTES == 49152) ? 3 : 5;
   static constexpr int BAR_BYTES = 512;
-  // epilogue slabs: 8 warps x 2 x (32 rows x 128 B); TAIL mode reuses them as [acc][half][row][4] floats
+  // epilogue slabs: 8 warps x 2 x (32 rows x 128 B); TAIL mode reuses them as [acc][half][row][kTailMax] floats
   static constexpr int SCRATCH_BYTES = kEpiWarps * 2 * 4096;
   static constexpr int SMEM_BYTES = 1024 + STAGES * STAGE_BYTES + BAR_BYTES + SCRATCH_BYTES;
   static constexpr int TMEM_COLS = 2 * BN;
@@ -402,7 +402,7 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_kernel(const __grid_constant
         }
         mbar_wait(&tfull[acc], accphase);
         tc_fence_after();
-        float part[4] = {0.f, 0.f, 0.f, 0.f};
+        float part[kTailMax] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
 #pragma unroll 1
         for (int c = 0; c < HALF_COLS / 32; ++c) {
           const int col0 = half * HALF_COLS + c * 32;
@@ -434,7 +434,9 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_kernel(const __grid_constant
           if (tail) {
 #pragma unroll
             for (int j = 0; j < 32; ++j) v[j] = fmaxf(v[j], 0.f);
-            for (int o = 0; o < p.tail_out; ++o) {
+#pragma unroll
+            for (int o = 0; o < kTailMax; ++o) {
+              if (o >= p.tail_out) break;
               const float* w = p.w2 + (long long)o * p.N + gcol;
               float s = 0.f;
 #pragma unroll
@@ -499,15 +501,20 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_kernel(const __grid_constant
 
         if (tail) {
           // combine the two column halves of each row through smem (double-buffered by accumulator stage)
-          float* sc = scratch + acc * (2 * 128 * 4);
-          float4* mine = reinterpret_cast<float4*>(sc + (half * 128 + r) * 4);
-          *mine = make_float4(part[0], part[1], part[2], part[3]);
+          float* sc = scratch + acc * (2 * 128 * kTailMax);
+          float4* mine = reinterpret_cast<float4*>(sc + (half * 128 + r) * kTailMax);
+          mine[0] = make_float4(part[0], part[1], part[2], part[3]);
+          mine[1] = make_float4(part[4], part[5], part[6], part[7]);
           asm volatile("bar.sync %0, 64;" ::"r"(1 + q) : "memory");
           if (half == 0 && valid) {
-            const float4 o4 = *reinterpret_cast<const float4*>(sc + (128 + r) * 4);
-            float yv[4] = {part[0] + o4.x, part[1] + o4.y, part[2] + o4.z, part[3] + o4.w};
+            const float4* oth = reinterpret_cast<const float4*>(sc + (128 + r) * kTailMax);
+            const float4 o4 = oth[0], o5 = oth[1];
+            float yv[kTailMax] = {part[0] + o4.x, part[1] + o4.y, part[2] + o4.z, part[3] + o4.w,
+                                  part[4] + o5.x, part[5] + o5.y, part[6] + o5.z, part[7] + o5.w};
             const long long plane = (long long)p.Y * p.X;
-            for (int o = 0; o < p.tail_out; ++o) {
+#pragma unroll
+            for (int o = 0; o < kTailMax; ++o) {
+              if (o >= p.tail_out) break;
               float t = yv[o] + p.tail_b2[o];
               const long long idx = ((long long)img * p.tail_out + o) * plane + (long long)y * p.X + x;
               if (p.out2) p.out2[idx] = t;

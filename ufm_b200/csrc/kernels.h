@@ -43,6 +43,7 @@ enum : uint32_t {
 //   EPI_TMA_BF16  bf16 output only: 64-column slabs, out by TMA store
 enum : int { EPI_DIRECT = 0, EPI_TMA_F32 = 1, EPI_TMA_BF16 = 2 };
 
+constexpr int kTailMax = 8;  // output channels of the fused TAIL epilogue
 struct alignas(64) GemmParams {
   CUtensorMap tmA;
   CUtensorMap tmB;
@@ -73,10 +74,10 @@ struct alignas(64) GemmParams {
   long long out_off;           // element offset added to out / res1 addresses
   // TAIL
   const float* w2;       // [tail_out][N]
-  float tail_b2[4];
-  float tail_scale[4];
-  float tail_shift[4];
-  int tail_out;          // <= 4
+  float tail_b2[kTailMax];
+  float tail_scale[kTailMax];
+  float tail_shift[kTailMax];
+  int tail_out;          // <= kTailMax
   float* out2;           // optional planar raw (logits) output
 };
 
@@ -184,9 +185,18 @@ struct UnmapParams {
   int B, H, W, H0, W0;
   int rep[4], src0[4], src1[4];        // [top, bottom, left, right]: represented region, source regions of image 0 / 1
   float src_mul[2], tgt_mul[2];        // (x, y): source / target region size over represented region size
-  float* flow_out; float* cov_out;     // [B,2,H0,W0], [B,H0,W0] (may be null)
+  float* flow_out; float* cov_out;     // [B,2,H0,W0], [B,H0,W0] (may be null); flow/flow_out may be null (channels only)
+  float cov_mul[4]; int cov_mul_n;     // cov_out plane b is scaled by cov_mul[b % cov_mul_n] (covariance ratios, base.py:311-315)
 };
 cudaError_t launch_unmap(const UnmapParams& p, cudaStream_t s);
+// uncertainty-head adaptors (adaptors.py:899-985): raw [B,C,H,W] -> per-adaptor outputs
+enum { ADAPT_MASK = 1, ADAPT_COV_EXP_TANH = 2, ADAPT_CONF_EXP = 3, ADAPT_CONF_SIGMOID = 4, ADAPT_CONF_SOFTMAX = 5 };
+struct UncAdaptParams {
+  const float* raw; int B, C, H, W;
+  int n, kind[4], ch[4]; float vmin[4], vmax[4];
+  float* mask; float* cov; float* cov_inv; float* cov_log_det; float* conf; float* conf_stats;
+};
+cudaError_t launch_unc_adaptors(const UncAdaptParams& p, cudaStream_t s);
 
 // NHWC fp32 [n,H,W,C] -> NCHW fp32 (stage dumps / descriptor export)
 cudaError_t launch_nhwc_to_nchw(const float* in, float* out, int n, int H, int W, int C, cudaStream_t s);

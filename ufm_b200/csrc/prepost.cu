@@ -107,16 +107,107 @@ __global__ void __launch_bounds__(128) unmap_kernel(const UnmapParams p) {
     const float gx0 = (float)x0 + 0.5f, gx1 = (float)x1 + 0.5f, gy0 = (float)y0 + 0.5f, gy1 = (float)y1 + 0.5f;
     const float scx = hy * (hx * gx0 + lx * gx1) + ly * (hx * gx0 + lx * gx1);
     const float scy = hy * (hx * gy0 + lx * gy0) + ly * (hx * gy1 + lx * gy1);
-    const float* fl = p.flow + (size_t)b * 2 * plane;
-    const float tx = fl[in] + scx, ty = fl[plane + in] + scy;
-    fx = (tx * p.tgt_mul[0] + (float)p.src1[2]) - (scx * p.src_mul[0] + (float)p.src0[2]);
-    fy = (ty * p.tgt_mul[1] + (float)p.src1[0]) - (scy * p.src_mul[1] + (float)p.src0[0]);
+    if (p.flow) {
+      const float* fl = p.flow + (size_t)b * 2 * plane;
+      const float tx = fl[in] + scx, ty = fl[plane + in] + scy;
+      fx = (tx * p.tgt_mul[0] + (float)p.src1[2]) - (scx * p.src_mul[0] + (float)p.src0[2]);
+      fy = (ty * p.tgt_mul[1] + (float)p.src1[0]) - (scy * p.src_mul[1] + (float)p.src0[0]);
+    }
     if (p.cov) cv = p.cov[(size_t)b * plane + in];
   }
-  float* fo = p.flow_out + (size_t)b * 2 * plane0;
-  fo[o] = fx;
-  fo[plane0 + o] = fy;
-  if (p.cov_out) p.cov_out[(size_t)b * plane0 + o] = cv;
+  if (p.flow_out) {
+    float* fo = p.flow_out + (size_t)b * 2 * plane0;
+    fo[o] = fx;
+    fo[plane0 + o] = fy;
+  }
+  if (p.cov_out) p.cov_out[(size_t)b * plane0 + o] = cv * p.cov_mul[b % p.cov_mul_n];
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// Uncertainty-head adaptors (UC/models/prediction_heads/adaptors.py): AdaptorMap splits the head's raw
+// channels in adaptor order (base.py:186-210); per adaptor:
+//   MaskAdaptor (:980-985)              mask = sigmoid(x)
+//   Covariance2DAdaptor exp_tanh (:944-965)  cov = (e^c1, e^c2, tanh(s) e^((c1+c2)/2)), log_det = c1 + c2 + log(1 - tanh^2 + 1e-8),
+//                                       inv = (e^-c1, e^-c2, -tanh(s) e^(-(c1+c2)/2)) / (1 - tanh^2 + 1e-8)
+//   ConfidenceAdaptor (:899-927)        exp: vmin + min(e^x, vmax - vmin); sigmoid: sigmoid(x) (vmax - vmin) + vmin;
+//                                       softmax: softmax over the H*W pixels of an image, times H*W
+__global__ void __launch_bounds__(1024) conf_softmax_stats_kernel(const float* raw, int C, int ch, long long plane, float* stats) {
+  const float* x = raw + ((long long)blockIdx.x * C + ch) * plane;
+  float m = -INFINITY, s = 0.f;
+  for (long long i = threadIdx.x; i < plane; i += 1024) {
+    const float v = x[i];
+    const float nm = fmaxf(m, v);
+    s = s * __expf(m - nm) + __expf(v - nm);
+    m = nm;
+  }
+  __shared__ float sm[32], ss[32];
+  for (int o = 16; o > 0; o >>= 1) {
+    const float om = __shfl_xor_sync(0xffffffffu, m, o), os = __shfl_xor_sync(0xffffffffu, s, o);
+    const float nm = fmaxf(m, om);
+    s = (m == -INFINITY ? 0.f : s * __expf(m - nm)) + (om == -INFINITY ? 0.f : os * __expf(om - nm));
+    m = nm;
+  }
+  if ((threadIdx.x & 31) == 0) {
+    sm[threadIdx.x >> 5] = m;
+    ss[threadIdx.x >> 5] = s;
+  }
+  __syncthreads();
+  if (threadIdx.x < 32) {
+    m = sm[threadIdx.x];
+    s = ss[threadIdx.x];
+    for (int o = 16; o > 0; o >>= 1) {
+      const float om = __shfl_xor_sync(0xffffffffu, m, o), os = __shfl_xor_sync(0xffffffffu, s, o);
+      const float nm = fmaxf(m, om);
+      s = (m == -INFINITY ? 0.f : s * __expf(m - nm)) + (om == -INFINITY ? 0.f : os * __expf(om - nm));
+      m = nm;
+    }
+    if (threadIdx.x == 0) {
+      stats[2 * blockIdx.x] = m;
+      stats[2 * blockIdx.x + 1] = s;
+    }
+  }
+}
+
+__global__ void __launch_bounds__(256) unc_adaptor_kernel(const UncAdaptParams p) {
+  const long long plane = (long long)p.H * p.W;
+  const long long i = (long long)blockIdx.x * 256 + threadIdx.x;
+  if (i >= plane) return;
+  const int b = blockIdx.y;
+  const float* raw = p.raw + (long long)b * p.C * plane + i;
+  for (int a = 0; a < p.n; ++a) {
+    const float* x = raw + (long long)p.ch[a] * plane;
+    switch (p.kind[a]) {
+      case ADAPT_MASK:
+        p.mask[(long long)b * plane + i] = 1.0f / (1.0f + expf(-x[0]));
+        break;
+      case ADAPT_COV_EXP_TANH: {
+        const float c1 = x[0], c2 = x[plane], t = tanhf(x[2 * plane]);
+        const float de = (c1 + c2) / 2, om = 1.f - t * t + 1e-8f;
+        float* cov = p.cov + (long long)b * 3 * plane + i;
+        cov[0] = expf(c1);
+        cov[plane] = expf(c2);
+        cov[2 * plane] = t * expf(de);
+        p.cov_log_det[(long long)b * plane + i] = c1 + c2 + logf(om);
+        const float ic = 1.f / om;
+        float* inv = p.cov_inv + (long long)b * 3 * plane + i;
+        inv[0] = ic * expf(-c1);
+        inv[plane] = ic * expf(-c2);
+        inv[2 * plane] = ic * (-t * expf(-de));
+        break;
+      }
+      case ADAPT_CONF_EXP:
+        p.conf[(long long)b * plane + i] = p.vmin[a] + fminf(expf(x[0]), p.vmax[a] - p.vmin[a]);
+        break;
+      case ADAPT_CONF_SIGMOID:
+        p.conf[(long long)b * plane + i] = (1.0f / (1.0f + expf(-x[0]))) * (p.vmax[a] - p.vmin[a]) + p.vmin[a];
+        break;
+      case ADAPT_CONF_SOFTMAX:
+        p.conf[(long long)b * plane + i] = expf(x[0] - p.conf_stats[2 * b]) / p.conf_stats[2 * b + 1] * (float)plane;
+        break;
+      default:
+        break;
+    }
+  }
 }
 
 }  // namespace
@@ -142,6 +233,20 @@ cudaError_t launch_unmap(const UnmapParams& p, cudaStream_t s) {
   if (p.H0 > 65535 || p.B > 65535) return cudaErrorInvalidValue;
   dim3 grid((p.W0 + 127) / 128, p.H0, p.B);
   unmap_kernel<<<grid, 128, 0, s>>>(p);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_unc_adaptors(const UncAdaptParams& p, cudaStream_t s) {
+  if (p.B <= 0 || p.n <= 0) return cudaSuccess;
+  if (p.B > 65535) return cudaErrorInvalidValue;
+  const long long plane = (long long)p.H * p.W;
+  for (int a = 0; a < p.n; ++a)
+    if (p.kind[a] == ADAPT_CONF_SOFTMAX) {
+      if (!p.conf_stats) return cudaErrorInvalidValue;
+      conf_softmax_stats_kernel<<<p.B, 1024, 0, s>>>(p.raw, p.C, p.ch[a], plane, p.conf_stats);
+    }
+  dim3 grid((unsigned)((plane + 255) / 256), p.B);
+  unc_adaptor_kernel<<<grid, 256, 0, s>>>(p);
   return cudaGetLastError();
 }
 

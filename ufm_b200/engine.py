@@ -30,6 +30,10 @@ class Engine:
         self.cfg = cfg
         self.ec = engine_config(cfg)
         self.H, self.W = self.ec.img_h, self.ec.img_w
+        kinds = [self.ec.unc_kind[i] for i in range(self.ec.unc_n_adaptors)]
+        self.has_mask = self.ec.unc_out_ch > 0 and (not kinds or _lib.ADAPT_MASK in kinds)
+        self.has_cov = _lib.ADAPT_COV_EXP_TANH in kinds
+        self.has_conf = any(k >= _lib.ADAPT_CONF_EXP for k in kinds)
         self.max_pairs = max_pairs
         h = C.c_void_p()
         rc = self.lib.ufm_create(C.byref(self.ec), self.index, C.byref(h))
@@ -66,7 +70,7 @@ class Engine:
         assert src.dtype == tgt.dtype and src.shape == tgt.shape
         B = src.shape[0]
         flow = torch.empty(B, 2, self.H, self.W, dtype=torch.float32, device=src.device)
-        cov = torch.empty(B, self.H, self.W, dtype=torch.float32, device=src.device) if self.ec.unc_out_ch else None
+        cov = torch.empty(B, self.H, self.W, dtype=torch.float32, device=src.device) if self.has_mask else None
         stream = torch.cuda.current_stream(src.device).cuda_stream
         self._ck(self.lib.ufm_forward(self.h, src.data_ptr(), tgt.data_ptr(), B, _DT[src.dtype], layout,
                                       flow.data_ptr(), cov.data_ptr() if cov is not None else None, stream))

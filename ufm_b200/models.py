@@ -118,7 +118,7 @@ class UniFlowMatchModelsBase(nn.Module):
         hw = img0.shape[1:3] if layout == _lib.UFM_NHWC else img0.shape[2:4]
         assert tuple(hw) == (H, W), f"engine prepared for {(H, W)}, got {tuple(hw)}"
         eng.set_keep_aux(keep_aux)
-        flows, covs, aux = [], [], []
+        flows, covs, aux, unc = [], [], [], []
         B = img0.shape[0]
         for s in range(0, B, self.max_pairs_per_call):
             a = img0[s:s + self.max_pairs_per_call].contiguous()
@@ -128,8 +128,14 @@ class UniFlowMatchModelsBase(nn.Module):
             covs.append(c)
             if keep_aux and self._refine:
                 aux.append({k: eng.stage(k) for k in ("flow_reg", "residual", "log_softmax", "desc")})
+            # uncertainty-head adaptors beyond the mask (ufm.py:644-660) are read back from their stage buffers
+            names = (["flow_cov", "flow_cov_inv", "flow_cov_log_det"] if eng.has_cov else []) + \
+                    (["keypoint_confidence"] if eng.has_conf else [])
+            if names:
+                unc.append({k: eng.stage(k) for k in names})
         flow = flows[0] if len(flows) == 1 else torch.cat(flows)
         cov = None if covs[0] is None else (covs[0] if len(covs) == 1 else torch.cat(covs))
+        self._last_unc = {k: torch.cat([u[k] for u in unc]) for k in unc[0]} if unc else {}
         return flow, cov, aux
 
     def forward(self, view1, view2) -> UFMOutputInterface:
@@ -141,6 +147,12 @@ class UniFlowMatchModelsBase(nn.Module):
         res = UFMOutputInterface(flow=UFMFlowFieldOutput(flow_output=flow))
         if cov is not None:
             res.covisibility = UFMMaskFieldOutput(mask=cov.unsqueeze(1), logits=None)
+        u = self._last_unc
+        if "flow_cov" in u:  # ufm.py:649-652
+            res.flow.flow_covariance, res.flow.flow_covariance_inv = u["flow_cov"], u["flow_cov_inv"]
+            res.flow.flow_covariance_log_det = u["flow_cov_log_det"]
+        if "keypoint_confidence" in u:  # ufm.py:654 (set dynamically there as well)
+            res.keypoint_confidence = u["keypoint_confidence"]
         if self._refine and aux:
             cat = lambda k: torch.cat([a[k] for a in aux])
             desc = cat("desc")  # (B, 2, C/8, H, W, 8) bf16: the engine's channel-group planar descriptor layout
@@ -189,6 +201,7 @@ class UniFlowMatchModelsBase(nn.Module):
             # the engine reads the images as they are (u8 normalisation is fused into the patch gather);
             # the reference's un-map at native size is the identity up to (flow + c) - c rounding
             flow, cov, _ = self._run(src.contiguous(), tgt.contiguous(), layout)
+            fcov = self._last_unc.get("flow_cov")  # base.py:295-319 at native size: ratios are 1
         else:
             # non-native size or foreign normalisation: normalise + anti-alias resize, forward, un-map -- two CUDA
             # kernels around the engine (csrc/prepost.cu), no torch ops on the data path
@@ -202,7 +215,15 @@ class UniFlowMatchModelsBase(nn.Module):
             rep0 = prepost.scaled_region(th, tw, hw0[0], hw0[1])
             src0, src1 = [0, hw0[0], 0, hw0[1]], [0, hw1[0], 0, hw1[1]]
             flow, cov = prepost.unmap(f, c, rep0, src0, src1, hw0)
+            fcov = self._last_unc.get("flow_cov")
+            if fcov is not None:
+                # unmap_predicted_channels + covariance rescaling (base.py:295-319): the three planes as 3B images
+                wr, hr = hw0[1] / tw, hw0[0] / th
+                _, fc = prepost.unmap(None, fcov.reshape(-1, th, tw), rep0, src0, src1, hw0, cov_mul=(wr ** 2, hr ** 2, wr * hr))
+                fcov = fc.reshape(-1, 3, hw0[0], hw0[1])
         out = UFMOutputInterface(flow=UFMFlowFieldOutput(flow_output=flow.to(in_device)))
+        if fcov is not None:
+            out.flow.flow_covariance = fcov.to(in_device)
         if cov is not None:
             out.covisibility = UFMMaskFieldOutput(mask=cov.to(in_device), logits=None)
         return out

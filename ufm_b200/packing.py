@@ -35,6 +35,29 @@ def inference_hw(cfg) -> Tuple[int, int]:
     return int(res[1]), int(res[0])  # (H, W)
 
 
+def unc_adaptor_kinds(ua):
+    """uncertainty_adaptors_kwargs -> [(engine adaptor kind, vmin, vmax)] in AdaptorMap order (adaptors.py:899-985)."""
+    want = {"non_occluded_mask": "MaskAdaptor", "flow_cov": "Covariance2DAdaptor", "keypoint_confidence": "ConfidenceAdaptor"}
+    out = []
+    for name, a in ua.items():
+        if want.get(name) != a["class"]:
+            raise NotImplementedError(f"uncertainty adaptor {name!r} of class {a['class']!r}: UFM consumes {want} (ufm.py:644-660)")
+        kw = a["kwargs"]
+        if a["class"] == "MaskAdaptor":
+            out.append((_lib.ADAPT_MASK, 0.0, 0.0))
+        elif a["class"] == "Covariance2DAdaptor":
+            if kw.get("parametrization", "exp_tanh") != "exp_tanh":
+                raise ValueError(f"Invalid parametrization: {kw.get('parametrization')}")  # adaptors.py:963
+            out.append((_lib.ADAPT_COV_EXP_TANH, 0.0, 0.0))
+        else:
+            kind = {"exp": _lib.ADAPT_CONF_EXP, "sigmoid": _lib.ADAPT_CONF_SIGMOID, "softmax": _lib.ADAPT_CONF_SOFTMAX}[kw["confidence_type"]]
+            assert kw["vmin"] < kw["vmax"], "vmin must be less than vmax"  # adaptors.py:893
+            out.append((kind, float(kw["vmin"]), float(kw["vmax"])))
+    if not out or len(out) > 4:
+        raise NotImplementedError("uncertainty head needs 1..4 adaptors")
+    return out
+
+
 def flow_affine(cfg, H, W):
     a = cfg["adaptors_kwargs"]
     if list(a.keys()) != ["flow"] or a["flow"]["class"] != "FlowAdaptor":
@@ -99,10 +122,16 @@ def engine_config(cfg: Dict[str, Any]) -> "_lib.UfmConfig":
     c.flow_scale[0], c.flow_scale[1], c.flow_shift[0], c.flow_shift[1] = s0, s1, b0, b1
     c.unc_out_ch = 0
     if cfg.get("uncertainty_head_kwargs"):
+        # AdaptorMap order (ufm.py:553-556); names are the ones ufm.py:644-660 consumes
         ua = cfg.get("uncertainty_adaptors_kwargs", {})
-        if list(ua.keys()) != ["non_occluded_mask"] or ua["non_occluded_mask"]["class"] != "MaskAdaptor":
-            raise NotImplementedError("uncertainty head supports the 'non_occluded_mask' MaskAdaptor (SURVEY.md 8f N3)")
-        c.unc_out_ch = 1
+        kinds = unc_adaptor_kinds(ua)
+        c.unc_out_ch = sum(3 if k == _lib.ADAPT_COV_EXP_TANH else 1 for k, _, _ in kinds)
+        if c.unc_out_ch != cfg["uncertainty_head_kwargs"]["dpt_processor"]["output_dim"]:
+            raise ValueError("uncertainty head output_dim does not match the channels its adaptors require")
+        if [k for k, _, _ in kinds] != [_lib.ADAPT_MASK]:
+            c.unc_n_adaptors = len(kinds)
+            for i, (k, vmin, vmax) in enumerate(kinds):
+                c.unc_kind[i], c.unc_vmin[i], c.unc_vmax[i] = k, vmin, vmax
     c.refine = int("classification_head_kwargs" in cfg)
     if c.refine:
         ck = cfg["classification_head_kwargs"]

@@ -121,27 +121,32 @@ def prep_resize(img: torch.Tensor, nhwc: bool, th: int, tw: int, required: str, 
     return out
 
 
-def unmap(flow: torch.Tensor, cov, rep0, src0, src1, shape0) -> Tuple[torch.Tensor, torch.Tensor]:
+def unmap(flow, cov, rep0, src0, src1, shape0, cov_mul=None) -> Tuple[torch.Tensor, torch.Tensor]:
     """``unmap_predicted_flow`` + ``unmap_predicted_channels`` (flow_resizing.py:749-877, 955-1010) in one kernel.
 
-    flow [B,2,H,W], cov [B,H,W] or None (fp32, CUDA, inference resolution) -> flow [B,2,H0,W0], cov [B,H0,W0]."""
-    flow = flow.contiguous()
-    B, _, H, W = flow.shape
+    flow [B,2,H,W] or None, cov [B,H,W] or None (fp32, CUDA, inference resolution) -> flow [B,2,H0,W0], cov [B,H0,W0];
+    plane b of cov is multiplied by cov_mul[b % len(cov_mul)] (the covariance rescaling of base.py:311-315)."""
+    ref = flow if flow is not None else cov
+    if flow is not None:
+        flow = flow.contiguous()
+    B, H, W = ref.shape[0], ref.shape[-2], ref.shape[-1]
     H0, W0 = int(shape0[0]), int(shape0[1])
     svs = [src0[1] - src0[0], src0[3] - src0[2]]
     tvs = [src1[1] - src1[0], src1[3] - src1[2]]
     rh, rw = rep0[1] - rep0[0], rep0[3] - rep0[2]
     i4 = lambda v: (C.c_int * 4)(*[int(x) for x in v])
     f2 = lambda a, b: (C.c_float * 2)(float(a), float(b))
-    out = torch.empty(B, 2, H0, W0, dtype=torch.float32, device=flow.device)
-    cout = torch.empty(B, H0, W0, dtype=torch.float32, device=flow.device) if cov is not None else None
+    out = torch.empty(B, 2, H0, W0, dtype=torch.float32, device=ref.device) if flow is not None else None
+    cout = torch.empty(B, H0, W0, dtype=torch.float32, device=ref.device) if cov is not None else None
+    cm = (C.c_float * len(cov_mul))(*[float(np.float32(v)) for v in cov_mul]) if cov_mul else None
     if cov is not None:
         cov = cov.contiguous()
     lib = _lib.load()
-    with torch.cuda.device(flow.device):
-        rc = lib.ufm_op_unmap(flow.data_ptr(), None if cov is None else cov.data_ptr(), B, H, W, H0, W0, i4(rep0), i4(src0),
-                              i4(src1), f2(svs[1] / rw, svs[0] / rh), f2(tvs[1] / rw, tvs[0] / rh), out.data_ptr(),
-                              None if cout is None else cout.data_ptr(), torch.cuda.current_stream().cuda_stream)
+    with torch.cuda.device(ref.device):
+        rc = lib.ufm_op_unmap(None if flow is None else flow.data_ptr(), None if cov is None else cov.data_ptr(), B, H, W, H0,
+                              W0, i4(rep0), i4(src0), i4(src1), f2(svs[1] / rw, svs[0] / rh), f2(tvs[1] / rw, tvs[0] / rh),
+                              None if out is None else out.data_ptr(), None if cout is None else cout.data_ptr(), cm,
+                              len(cov_mul) if cov_mul else 0, torch.cuda.current_stream().cuda_stream)
     if rc != 0:
         raise RuntimeError("ufm_op_unmap: invalid regions")
     return out, cout
