@@ -4,6 +4,9 @@ uniflowmatch/models/ufm.py:120-1009), with the forward pass executed by the sm_1
 """
 from __future__ import annotations
 
+import json
+import os
+
 from dataclasses import dataclass
 from typing import Any, Dict, Optional
 
@@ -47,6 +50,44 @@ class UFMOutputInterface:
     covisibility: Optional[UFMMaskFieldOutput] = None
 
 
+def modify_state_dict(original_state_dict, mappings):
+    """Rename / drop checkpoint keys: ``{substring: replacement or None}``, first matching rule wins, ``None`` drops the
+    key (semantics of ``modify_state_dict``, uniflowmatch/models/ufm.py:85-117)."""
+    out = {}
+    for k, v in original_state_dict.items():
+        new_key, skip = None, False
+        for old, new in mappings.items():
+            if old in k:
+                if new is None:
+                    skip = True
+                else:
+                    new_key = k.replace(old, new)
+                break
+        if not skip:
+            out[new_key if new_key is not None else k] = v
+    return out
+
+
+def _aliases(key: str):
+    """Other reference keys that name the same DPT tensor (dpt.py:107-172: ``scratch.layer{K}_rn``, ``scratch.layer_rn[K-1]``
+    and ``input_process[K-1][1]`` are one module)."""
+    import re
+
+    m = re.match(r"(.*\.)scratch\.layer(\d)_rn\.(.*)", key)
+    if m:
+        k = int(m.group(2)) - 1
+        return [f"{m.group(1)}scratch.layer_rn.{k}.{m.group(3)}", f"{m.group(1)}input_process.{k}.1.{m.group(3)}"]
+    m = re.match(r"(.*\.)scratch\.layer_rn\.(\d)\.(.*)", key)
+    if m:
+        k = int(m.group(2))
+        return [f"{m.group(1)}scratch.layer{k + 1}_rn.{m.group(3)}", f"{m.group(1)}input_process.{k}.1.{m.group(3)}"]
+    m = re.match(r"(.*\.)input_process\.(\d)\.1\.(.*)", key)
+    if m:
+        k = int(m.group(2))
+        return [f"{m.group(1)}scratch.layer{k + 1}_rn.{m.group(3)}", f"{m.group(1)}scratch.layer_rn.{k}.{m.group(3)}"]
+    return []
+
+
 class _EncoderShim:
     def __init__(self, data_norm_type):
         self.data_norm_type = data_norm_type
@@ -59,8 +100,8 @@ class UniFlowMatchModelsBase(nn.Module):
 
     def __init__(self, max_pairs_per_call: int = 16, seed: int = 0, **cfg):
         super().__init__()
-        cfg.pop("pretrained_checkpoint_path", None)
-        cfg.pop("pretrained_backbone_checkpoint_path", None)
+        assert cfg.pop("pretrained_checkpoint_path", None) is None, "Pretrained weights are not supported for now"  # ufm.py:558
+        backbone_ckpt = cfg.pop("pretrained_backbone_checkpoint_path", None)
         if cfg.get("info_sharing_and_head_structure", "dual+single") != "dual+single":
             raise AssertionError("Only dual+single is supported now")  # ufm.py:180
         if self._refine and "classification_head_kwargs" not in cfg:
@@ -79,6 +120,83 @@ class UniFlowMatchModelsBase(nn.Module):
             self._names[safe] = key
             self.register_buffer(safe, t)
         self._engines: Dict[Any, Engine] = {}
+        self._last_unc: Dict[str, torch.Tensor] = {}
+        if backbone_ckpt is not None:
+            self._load_backbone_checkpoint(backbone_ckpt)
+
+    # checkpoint ingestion ---------------------------------------------------------------------------
+    def _load_backbone_checkpoint(self, path: str):
+        """``UniFlowMatch.__init__`` (ufm.py:197-217): a training checkpoint ({"state_dict": {"model.<key>": ...}}, with the
+        feature-matching projection and the DINOv2 mask token dropped, strict) or an exported one ({"model": ...}, no
+        missing keys allowed).  Only the backbone keys (encoder / info_sharing / head1) are taken."""
+        ckpt = torch.load(path, map_location="cpu", weights_only=False)
+        mine = set(self._names.values())
+        backbone = {k for k in mine if k.split(".")[0] in ("encoder", "info_sharing", "head1")}
+        if "state_dict" in ckpt:
+            sd = {k[6:]: v for k, v in ckpt["state_dict"].items() if k.startswith("model.")}
+            sd = modify_state_dict(sd, {"feature_matching_proj": None, "encoder.model.mask_token": None})
+            missing, unexpected = sorted(backbone - set(sd)), sorted(set(sd) - backbone)
+            if missing or unexpected:
+                raise RuntimeError(f"backbone checkpoint: missing {missing[:5]}, unexpected {unexpected[:5]}")
+        else:
+            sd = ckpt["model"]
+            missing = sorted(backbone - set(sd))
+            assert len(missing) == 0, f"Missing keys: {missing}"
+        self.load_state_dict({**self.state_dict(), **{k: v for k, v in sd.items() if k in backbone}})
+
+    @classmethod
+    def from_pretrained_ckpt(cls, pretrained_model_name_or_path, strict=True, **kw):
+        """``UniFlowMatch.from_pretrained_ckpt`` (ufm.py:219-240): {"model_args": ctor kwargs, "model": state_dict}."""
+        if os.path.isfile(pretrained_model_name_or_path):
+            ckpt = torch.load(pretrained_model_name_or_path, map_location="cpu", weights_only=False)
+            model = cls(**ckpt["model_args"], **kw)
+            model.load_state_dict(ckpt["model"], strict=strict)
+            return model
+        raise ValueError(f"Pretrained model {pretrained_model_name_or_path} not found.")
+
+    @classmethod
+    def from_pretrained(cls, pretrained_model_name_or_path, strict: bool = True, **kw):
+        """``PyTorchModelHubMixin.from_pretrained`` for the layout the reference models are published in
+        ("infinity1096/UFM-Base", ufm.py:1254-1256): a directory holding ``config.json`` (constructor kwargs) and
+        ``model.safetensors`` (reference key names).  A hub id is resolved through the local Hugging Face cache only:
+        this build has no network access."""
+        path = str(pretrained_model_name_or_path)
+        if not os.path.isdir(path):
+            try:
+                from huggingface_hub import snapshot_download
+
+                path = snapshot_download(path, local_files_only=True)
+            except Exception as e:
+                raise ValueError(f"{pretrained_model_name_or_path!r} is neither a directory with config.json + "
+                                 f"model.safetensors nor a model in the local Hugging Face cache ({e})")
+        with open(os.path.join(path, "config.json")) as f:
+            cfg = json.load(f)
+        from safetensors.torch import load_file
+
+        sd = load_file(os.path.join(path, "model.safetensors"))
+        # the published checkpoints may carry the DINOv2 mask token the wrapper deletes (dinov2.py:93-95)
+        sd = modify_state_dict(sd, {"encoder.model.mask_token": None})
+        model = cls(**{**cfg, **kw})
+        # safetensors stores one copy of tensors that alias each other (scratch.layerK_rn == scratch.layer_rn.K-1 ==
+        # input_process.K-1.1, SURVEY.md 8b): restore the aliases before the strict check
+        for key in model._names.values():
+            if key not in sd:
+                for other in _aliases(key):
+                    if other in sd:
+                        sd[key] = sd[other]
+                        break
+        model.load_state_dict(sd, strict=strict)
+        return model
+
+    def save_pretrained(self, save_directory: str):
+        """config.json + model.safetensors in the layout ``from_pretrained`` (and the reference's hub mixin) reads."""
+        os.makedirs(save_directory, exist_ok=True)
+        from safetensors.torch import save_file
+
+        with open(os.path.join(save_directory, "config.json"), "w") as f:
+            json.dump(self.config, f, indent=1)
+        save_file({k: v.detach().cpu().contiguous().clone() for k, v in self.state_dict().items()},
+                  os.path.join(save_directory, "model.safetensors"))
 
     # reference key names in/out -------------------------------------------------------------------------------------
     def state_dict(self, *a, **k):
