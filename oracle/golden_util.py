@@ -15,6 +15,8 @@ GOLDEN_CASES = {
     "ufm_refine_assumed": dict(cfg="ufm_refine_assumed", batch=1, out_gain=8.0),
     # uncertainty head with Covariance2DAdaptor + ConfidenceAdaptor + MaskAdaptor; gain 1 keeps exp() sane
     "tiny_cov": dict(cfg="tiny_cov", batch=2, out_gain=1.0),
+    # per-view cross-attention info sharing, Refine model, qk-norm on
+    "tiny_cross": dict(cfg="tiny_cross", batch=2, out_gain=8.0),
 }
 
 

@@ -129,12 +129,66 @@ def encoder(img: torch.Tensor, sd, cfg) -> List[torch.Tensor]:
     return outs
 
 
+def cross_attention(q_in, kv_in, sd, prefix, heads, qk_norm=False):
+    """``CrossAttention.forward`` (UC/models/utils/transformer_blocks.py:190-283): separate projq / projk / projv Linears,
+    [LayerNorm over head_dim on q, k], softmax(q k^T / sqrt(hd)) v, proj."""
+    B, Nq, C = q_in.shape
+    hd = C // heads
+    split = lambda t: t.reshape(B, -1, heads, hd).permute(0, 2, 1, 3)
+    q = split(F.linear(q_in, sd[prefix + "projq.weight"], sd.get(prefix + "projq.bias")))
+    k = split(F.linear(kv_in, sd[prefix + "projk.weight"], sd.get(prefix + "projk.bias")))
+    v = split(F.linear(kv_in, sd[prefix + "projv.weight"], sd.get(prefix + "projv.bias")))
+    if qk_norm:
+        q = F.layer_norm(q, (hd,), sd[prefix + "q_norm.weight"], sd[prefix + "q_norm.bias"], 1e-6)
+        k = F.layer_norm(k, (hd,), sd[prefix + "k_norm.weight"], sd[prefix + "k_norm.bias"], 1e-6)
+    o = F.scaled_dot_product_attention(q, k, v, scale=hd ** -0.5).transpose(1, 2).reshape(B, Nq, C)
+    return F.linear(o, sd[prefix + "proj.weight"], sd[prefix + "proj.bias"])
+
+
+def cross_block(x, y, sd, prefix, heads, qk_norm=False):
+    """``CrossAttentionBlock.forward`` (transformer_blocks.py:489-519): x += ls1(attn(norm1 x));
+    x += ls2(cross_attn(norm2 x, norm_y y, norm_y y)); x += ls3(mlp(norm3 x))."""
+    g = lambda name, t: t * sd[prefix + name] if prefix + name in sd else t
+    x = x + g("ls1.gamma", attention(_ln(x, sd, prefix + "norm1."), sd, prefix + "attn.", heads, qk_norm))
+    y_ = _ln(y, sd, prefix + "norm_y.") if prefix + "norm_y.weight" in sd else y
+    x = x + g("ls2.gamma", cross_attention(_ln(x, sd, prefix + "norm2."), y_, sd, prefix + "cross_attn.", heads, qk_norm))
+    h = F.gelu(F.linear(_ln(x, sd, prefix + "norm3."), sd[prefix + "mlp.fc1.weight"], sd[prefix + "mlp.fc1.bias"]))
+    h = F.linear(h, sd[prefix + "mlp.fc2.weight"], sd[prefix + "mlp.fc2.bias"])
+    return x + g("ls3.gamma", h)
+
+
+def info_sharing_cross(f1: torch.Tensor, f2: torch.Tensor, sd, cfg):
+    """``MultiViewCrossAttentionTransformerIFR.forward`` (UC/models/info_sharing/cross_attention_transformer.py:360-478)
+    for 2 views: per-view token streams, proj_embed, then at every depth BOTH views are updated from the previous
+    depth's features (view v runs its own branch with the other view's tokens as cross tokens); final norm, and the same
+    norm on the intermediates at ``indices``.  Returns (final (2,B,D,h,w), [intermediate (2,B,D,h,w)])."""
+    ik = cfg["info_sharing_kwargs"]
+    dim, depth, heads = ik["dim"], ik["depth"], ik["num_heads"]
+    p = "info_sharing."
+    B, Cin, h, w = f1.shape
+    xs = [f.permute(0, 2, 3, 1).reshape(B, h * w, Cin) for f in (f1, f2)]
+    if p + "proj_embed.weight" in sd:
+        xs = [F.linear(x, sd[p + "proj_embed.weight"], sd[p + "proj_embed.bias"]) for x in xs]
+    idx = ik["indices"]
+    take = list(range(depth - idx, depth)) if isinstance(idx, int) else [depth + i if i < 0 else i for i in idx]
+    inter = []
+    qk_norm = bool(ik.get("qk_norm"))
+    to_views = lambda ts: torch.stack([t.reshape(B, h, w, dim).permute(0, 3, 1, 2) for t in ts], 0).contiguous()
+    for i in range(depth):
+        xs = [cross_block(xs[v], xs[1 - v], sd, f"{p}multi_view_branches.{v}.{i}.", heads, qk_norm) for v in (0, 1)]
+        if i in take:
+            inter.append(to_views([_ln(x, sd, p + "norm.") if ik.get("norm_intermediate", True) else x for x in xs]))
+    return to_views([_ln(x, sd, p + "norm.") for x in xs]), inter
+
+
 def info_sharing(f1: torch.Tensor, f2: torch.Tensor, sd, cfg):
     """``MultiViewGlobalAttentionTransformerIFR.forward`` (UC/models/info_sharing/global_attention_transformer.py:428-609)
     and ``MultiViewAlternatingAttentionTransformerIFR.forward`` (alternating_attention_transformer.py:490-728) for 2 views:
     tokens (B, 2hw, C_in) -> proj_embed -> + view_pos_table row per view -> blocks (alternating: odd layers attend
     within each view) -> final norm; intermediates at ``indices`` get the same final norm.
     Returns (final (2,B,D,h,w), [intermediate (2,B,D,h,w)])."""
+    if cfg["info_sharing_str"] == "cross_attention":
+        return info_sharing_cross(f1, f2, sd, cfg)
     ik = cfg["info_sharing_kwargs"]
     dim, depth, heads = ik["dim"], ik["depth"], ik["num_heads"]
     alternating = cfg["info_sharing_str"] == "alternating_attention"

@@ -95,6 +95,12 @@ def tiny(refine: bool = False, inference_resolution=(224, 168), info_sharing_str
     cfg["info_sharing_str"] = info_sharing_str
     cfg["info_sharing_kwargs"].update({"input_embed_dim": 384, "depth": 4, "dim": 128, "num_heads": 2,
                                        "indices": [1, 2], "qk_norm": qk_norm})
+    if info_sharing_str == "cross_attention":
+        # MultiViewCrossAttentionTransformerIFR kwargs (cross_attention_transformer.py:264-292); SURVEY.md 8f N2
+        ik = cfg["info_sharing_kwargs"]
+        for k in ("max_num_views", "use_rand_idx_pe_for_non_reference_views"):
+            ik.pop(k)
+        ik.update({"num_views": 2, "norm_cross_tokens": True})
     if info_sharing_str == "alternating_attention":
         cfg["info_sharing_kwargs"].pop("max_num_views")
         cfg["info_sharing_kwargs"].update({"use_pe_for_non_reference_views": False, "max_num_views_for_pe": 1000})
@@ -123,6 +129,7 @@ CONFIGS = {
     "tiny_base": lambda: tiny(False),
     "tiny_refine": lambda: tiny(True),
     "tiny_cov": lambda: tiny(False, unc_adaptors="cov_conf_mask"),
+    "tiny_cross": lambda: tiny(True, info_sharing_str="cross_attention", qk_norm=True),
 }
 
 

@@ -78,6 +78,37 @@ def info_sharing_spec(cfg: Dict[str, Any]) -> Spec:
     s: Spec = []
     if ik["input_embed_dim"] != dim:
         s += [(p + "proj_embed.weight", (dim, ik["input_embed_dim"]), "w"), (p + "proj_embed.bias", (dim,), "b")]
+    if cfg["info_sharing_str"] == "cross_attention":
+        # MultiViewCrossAttentionTransformer (cross_attention_transformer.py:100-135): one CrossAttentionBlock stack per
+        # view (transformer_blocks.py:406-519), no view embedding
+        ls, qkn, hd, bias = bool(ik.get("init_values")), bool(ik.get("qk_norm")), dim // heads, ik.get("qkv_bias", True)
+        for v in range(ik.get("num_views", 2)):
+            for i in range(depth):
+                q = f"{p}multi_view_branches.{v}.{i}."
+                blk = _block_spec(q, dim, hidden, ls, qkn, hd, bias)
+                # _block_spec = norm1, attn, [ls1], norm2, mlp, [ls2]; the cross block's MLP hangs off norm3 / ls3
+                first = [e for e in blk if ".norm2." not in e[0] and ".mlp." not in e[0] and ".ls2." not in e[0]]
+                s += first
+                if ik.get("norm_cross_tokens", True):
+                    s += [(q + "norm_y.weight", (dim,), "ln_w"), (q + "norm_y.bias", (dim,), "ln_b")]
+                s += [(q + "norm2.weight", (dim,), "ln_w"), (q + "norm2.bias", (dim,), "ln_b")]
+                for nm in ("projq", "projk", "projv"):
+                    s.append((f"{q}cross_attn.{nm}.weight", (dim, dim), "w"))
+                    if bias:
+                        s.append((f"{q}cross_attn.{nm}.bias", (dim,), "b"))
+                if qkn:
+                    s += [(q + "cross_attn.q_norm.weight", (hd,), "ln_w"), (q + "cross_attn.q_norm.bias", (hd,), "ln_b"),
+                          (q + "cross_attn.k_norm.weight", (hd,), "ln_w"), (q + "cross_attn.k_norm.bias", (hd,), "ln_b")]
+                s += [(q + "cross_attn.proj.weight", (dim, dim), "w"), (q + "cross_attn.proj.bias", (dim,), "b")]
+                if ls:
+                    s.append((q + "ls2.gamma", (dim,), "gamma"))
+                s += [(q + "norm3.weight", (dim,), "ln_w"), (q + "norm3.bias", (dim,), "ln_b"),
+                      (q + "mlp.fc1.weight", (hidden, dim), "w"), (q + "mlp.fc1.bias", (hidden,), "b"),
+                      (q + "mlp.fc2.weight", (dim, hidden), "w"), (q + "mlp.fc2.bias", (dim,), "b")]
+                if ls:
+                    s.append((q + "ls3.gamma", (dim,), "gamma"))
+        s += [(p + "norm.weight", (dim,), "ln_w"), (p + "norm.bias", (dim,), "ln_b")]
+        return s
     for i in range(depth):
         s += _block_spec(f"{p}self_attention_blocks.{i}.", dim, hidden, bool(ik.get("init_values")),
                          bool(ik.get("qk_norm")), dim // heads, ik.get("qkv_bias", True))
