@@ -52,10 +52,15 @@ def algorithmic_tflop_per_pair(cfg, refine: bool) -> dict:
     D, d = ec.enc_dim, ec.info_dim
     enc_gemm = ec.enc_depth * 2 * (2 * S) * D * D * 12 + 2 * (2 * n) * D * 3 * ec.patch ** 2
     enc_attn = ec.enc_depth * 4 * (2 * S) * S * D
-    info_gemm = ec.info_depth * 2 * (2 * n) * d * (4 * d + 2 * ec.info_hidden) + 2 * (2 * n) * D * d
+    # per token and layer: qkv 3d^2 + proj d^2 + MLP 2 d hidden; cross-attention branches add q d^2 + kv 2d^2 + proj d^2
+    per_tok = 4 * d + 2 * ec.info_hidden + (4 * d if ec.info_alternating == 2 else 0)
+    info_gemm = ec.info_depth * 2 * (2 * n) * d * per_tok + 2 * (2 * n) * D * d
     info_attn = 0
     for i in range(ec.info_depth):
-        span = n if (ec.info_alternating and i % 2 == 1) else 2 * n
+        if ec.info_alternating == 2:  # self-attention within the view + cross-attention to the other view
+            info_attn += 2 * 4 * (2 * n) * n * d
+            continue
+        span = n if (ec.info_alternating == 1 and i % 2 == 1) else 2 * n
         info_attn += 4 * (2 * n) * span * d
     ld = list(ec.dpt_layer_dims)
     fd, hid = ec.dpt_feature_dim, ec.dpt_hidden

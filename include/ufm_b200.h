@@ -33,7 +33,8 @@ typedef struct ufm_config {
   /* info sharing (UC/models/info_sharing/{global,alternating}_attention_transformer.py) */
   int info_dim, info_depth, info_heads, info_hidden;
   int info_take0, info_take1;              /* indices[0], indices[1] */
-  int info_alternating;                    /* 1: odd layers attend within a view */
+  int info_alternating;                    /* 0: global attention over both views; 1: alternating (odd layers attend
+                                            * within a view); 2: per-view cross-attention branches */
   int info_qk_norm, info_layerscale, info_has_proj;
   /* DPT heads (UC/models/prediction_heads/dpt.py) */
   int dpt_layer_dims[4];

@@ -369,6 +369,92 @@ struct ufm_engine {
     return true;
   }
 
+  // One depth of MultiViewCrossAttentionTransformer (UC/models/info_sharing/cross_attention_transformer.py:418-437) for two
+  // views on the VIEW-MAJOR residual stream y [2][B][n][d]: both views are updated from the previous depth's features,
+  // so the K/V projections of both branches (from norm_y of the OTHER view) are taken first; then per view
+  // CrossAttentionBlock.forward (UC/models/utils/transformer_blocks.py:489-519): self-attention, cross-attention, MLP.
+  // The cross q / k / v land in one fused [rows, 3, heads, 64] buffer, so the attention kernel is the same one.
+  bool cross_depth(int i, float* y, int Bp, int n, int D, int heads, int hidden, bool qk_norm) {
+    const long long Mv = (long long)Bp * n;
+    bf16* xn = B<bf16>("xn");
+    bf16* qkv = B<bf16>("qkv");
+    bf16* cqkv = B<bf16>("cqkv");
+    bf16* att = B<bf16>("att");
+    bf16* h = B<bf16>("h");
+    for (int v = 0; v < 2; ++v) {
+      const std::string pre = "info.v" + std::to_string(v) + "." + std::to_string(i);
+      if (!layernorm(y + (long long)(1 - v) * Mv * D, 1, (int)Mv, 0, (int)Mv, D, pre + ".lny", 0, xn, D, 0)) return false;
+      Epi e;
+      e.bias = has(pre + ".ckv.b") ? Wf(pre + ".ckv.b") : nullptr;
+      e.out_bf16 = cqkv + (long long)v * Mv * 3 * D; e.sx = 3LL * D; e.out_off = D;
+      if (!gemm(rows_view(xn, Mv, D), pre + ".ckv.w", 1, e)) return false;
+    }
+    for (int v = 0; v < 2; ++v) {
+      const std::string pre = "info.v" + std::to_string(v) + "." + std::to_string(i);
+      float* x = y + (long long)v * Mv * D;
+      bf16* cq = cqkv + (long long)v * Mv * 3 * D;
+      // x += ls1(attn(norm1 x))
+      if (!layernorm(x, 1, (int)Mv, 0, (int)Mv, D, pre + ".ln1", 0, xn, D, 0)) return false;
+      {
+        Epi e;
+        e.bias = has(pre + ".qkv.b") ? Wf(pre + ".qkv.b") : nullptr;
+        e.out_bf16 = qkv; e.sx = 3LL * D;
+        if (!gemm(rows_view(xn, Mv, D), pre + ".qkv.w", 1, e)) return false;
+      }
+      if (qk_norm && !run(UFM_CAT_LN, 0.0, (double)Mv * heads * 64 * 2 * 4, "qk_norm", [&] {
+            return launch_qk_norm(qkv, Mv, heads, Wf(pre + ".qn.w"), Wf(pre + ".qn.b"), Wf(pre + ".kn.w"), Wf(pre + ".kn.b"),
+                                  1e-6f, st);
+          }))
+        return false;
+      if (!attention(qkv, Bp, n, heads, att)) return false;
+      {
+        Epi e;
+        e.bias = Wf(pre + ".proj.b");
+        e.scale = has(pre + ".ls1") ? Wf(pre + ".ls1") : nullptr;
+        e.res1 = x; e.out_f32 = x; e.sx = D;
+        if (!gemm(rows_view(att, Mv, D), pre + ".proj.w", 1, e)) return false;
+      }
+      // x += ls2(cross_attn(norm2 x, norm_y y, norm_y y))
+      if (!layernorm(x, 1, (int)Mv, 0, (int)Mv, D, pre + ".ln2", 0, xn, D, 0)) return false;
+      {
+        Epi e;
+        e.bias = has(pre + ".cq.b") ? Wf(pre + ".cq.b") : nullptr;
+        e.out_bf16 = cq; e.sx = 3LL * D;
+        if (!gemm(rows_view(xn, Mv, D), pre + ".cq.w", 1, e)) return false;
+      }
+      if (qk_norm && !run(UFM_CAT_LN, 0.0, (double)Mv * heads * 64 * 2 * 4, "qk_norm", [&] {
+            return launch_qk_norm(cq, Mv, heads, Wf(pre + ".cqn.w"), Wf(pre + ".cqn.b"), Wf(pre + ".ckn.w"),
+                                  Wf(pre + ".ckn.b"), 1e-6f, st);
+          }))
+        return false;
+      if (!attention(cq, Bp, n, heads, att)) return false;
+      {
+        Epi e;
+        e.bias = Wf(pre + ".cproj.b");
+        e.scale = has(pre + ".ls2") ? Wf(pre + ".ls2") : nullptr;
+        e.res1 = x; e.out_f32 = x; e.sx = D;
+        if (!gemm(rows_view(att, Mv, D), pre + ".cproj.w", 1, e)) return false;
+      }
+      // x += ls3(mlp(norm3 x))
+      if (!layernorm(x, 1, (int)Mv, 0, (int)Mv, D, pre + ".ln3", 0, xn, D, 0)) return false;
+      {
+        Epi e;
+        e.bias = Wf(pre + ".fc1.b");
+        e.flags = GEMM_GELU;
+        e.out_bf16 = h; e.sx = hidden;
+        if (!gemm(rows_view(xn, Mv, D), pre + ".fc1.w", 1, e)) return false;
+      }
+      {
+        Epi e;
+        e.bias = Wf(pre + ".fc2.b");
+        e.scale = has(pre + ".ls3") ? Wf(pre + ".ls3") : nullptr;
+        e.res1 = x; e.out_f32 = x; e.sx = D;
+        if (!gemm(rows_view(h, Mv, hidden), pre + ".fc2.w", 1, e)) return false;
+      }
+    }
+    return true;
+  }
+
   // 3x3 conv (pad 1, stride 1) on an NHWC bf16 image through the implicit-GEMM kernel
   bool conv3(const bf16* in, int N, int H, int Wd, int C, const std::string& wname, const float* bias, const float* res1,
              const float* res2, float* of, bf16* ob, bool relu_bf16) {
@@ -596,34 +682,51 @@ int ufm_engine::forward(const void* src, const void* tgt, int pairs, int in_dtyp
   }
   // ---- info sharing ----
   float* y = B<float>("y");
+  const bool cross = c.info_alternating == 2;
   {
     Epi e;
     e.bias = Wf("info.proj.b");
-    e.res2 = Wf("info.viewpos");
-    if (!e.bias || !e.res2) return 1;
-    e.r2y = d; e.r2x = 0; e.r2n = 0;
-    e.out_f32 = y; e.sx = d; e.sy = (long long)n * d; e.sn = 2LL * n * d;
+    if (!e.bias) return 1;
+    if (!cross) {
+      e.res2 = Wf("info.viewpos");
+      if (!e.res2) return 1;
+      e.r2y = d; e.r2x = 0; e.r2n = 0;
+    }
+    // residual stream layout: pair-major [B][2][n][d] (one attention sequence = one pair's 2n tokens), or VIEW-major
+    // [2][B][n][d] for the per-view branches of cross-attention info sharing
+    e.out_f32 = y; e.sx = d;
+    e.sy = cross ? (long long)Bp * n * d : (long long)n * d;
+    e.sn = cross ? (long long)n * d : 2LL * n * d;
     AView a{enc_last, D, n, 2, Bp, D, (long long)n * D, 2LL * n * D, 128, 1};
     if (!gemm(a, "info.proj.w", 1, e)) return 1;
   }
+  // final LayerNorm of the stream -> a pair-major [B,2,n,*] feature buffer (the layout the heads read)
+  auto info_norm = [&](bf16* dst, long long pitch, long long col) {
+    return cross ? layernorm(y, 2 * Bp, n, 0, n, d, "info.norm", Bp, dst, pitch, col)
+                 : layernorm(y, 1, (int)Mi, 0, (int)Mi, d, "info.norm", 0, dst, pitch, col);
+  };
   for (int i = 0; i < c.info_depth; ++i) {
-    const bool per_view = c.info_alternating && (i & 1);
-    if (!block("info." + std::to_string(i), y, per_view ? 2 * Bp : Bp, per_view ? n : 2 * n, d, c.info_heads,
-               c.info_hidden, c.info_qk_norm != 0))
-      return 1;
+    if (cross) {
+      if (!cross_depth(i, y, Bp, n, d, c.info_heads, c.info_hidden, c.info_qk_norm != 0)) return 1;
+    } else {
+      const bool per_view = c.info_alternating && (i & 1);
+      if (!block("info." + std::to_string(i), y, per_view ? 2 * Bp : Bp, per_view ? n : 2 * n, d, c.info_heads,
+                 c.info_hidden, c.info_qk_norm != 0))
+        return 1;
+    }
     if (i == c.info_take0) {
-      if (!layernorm(y, 1, (int)Mi, 0, (int)Mi, d, "info.norm", 0, B<bf16>("inter0"), d, 0)) return 1;
+      if (!info_norm(B<bf16>("inter0"), d, 0)) return 1;
       set_stage("info_inter0", B<bf16>("inter0"), UFM_BF16, {Bp, 2, n, d});
     }
     if (i == c.info_take1) {
-      if (!layernorm(y, 1, (int)Mi, 0, (int)Mi, d, "info.norm", 0, B<bf16>("inter1"), d, 0)) return 1;
+      if (!info_norm(B<bf16>("inter1"), d, 0)) return 1;
       set_stage("info_inter1", B<bf16>("inter1"), UFM_BF16, {Bp, 2, n, d});
     }
   }
-  if (!layernorm(y, 1, (int)Mi, 0, (int)Mi, d, "info.norm", 0, B<bf16>("final"), d, 0)) return 1;
+  if (!info_norm(B<bf16>("final"), d, 0)) return 1;
   set_stage("info_final", B<bf16>("final"), UFM_BF16, {Bp, 2, n, d});
   if (c.refine) {
-    if (!layernorm(y, 1, (int)Mi, 0, (int)Mi, d, "info.norm", 0, B<bf16>("Xcls"), c.cls_in, D)) return 1;
+    if (!info_norm(B<bf16>("Xcls"), c.cls_in, D)) return 1;
   }
   // ---- heads (view 1 only: "dual+single", ufm.py:180,700) ----
   float* flow_reg = c.refine ? B<float>("flow_reg") : flow_out;
@@ -834,6 +937,7 @@ int ufm_prepare(ufm_engine* e, int max_pairs) {
   ok = ok && e->alloc("y", UFM_F32, Mi * d);
   ok = ok && e->alloc("xn", UFM_BF16, mx(Me * D, Mi * d));
   ok = ok && e->alloc("qkv", UFM_BF16, mx(Me * 3 * D, Mi * 3 * d));
+  if (c.info_alternating == 2) ok = ok && e->alloc("cqkv", UFM_BF16, Mi * 3 * d);
   ok = ok && e->alloc("att", UFM_BF16, mx(Me * D, Mi * d));
   ok = ok && e->alloc("h", UFM_BF16, mx(Me * 4 * D, Mi * c.info_hidden));
   ok = ok && e->alloc("enc_last", UFM_BF16, Mi * D);

@@ -77,8 +77,13 @@ def engine_config(cfg: Dict[str, Any]) -> "_lib.UfmConfig":
     ek, ik = cfg["encoder_kwargs"], cfg["info_sharing_kwargs"]
     if cfg.get("encoder_str", "dinov2") != "dinov2" or ek.get("with_registers"):
         raise NotImplementedError("engine encoder is DINOv2 ViT-S/B/L without registers")
-    if cfg["info_sharing_str"] not in ("global_attention", "alternating_attention"):
-        raise NotImplementedError(f"info_sharing_str={cfg['info_sharing_str']} (SURVEY.md 8f N2)")
+    if cfg["info_sharing_str"] not in ("global_attention", "alternating_attention", "cross_attention"):
+        raise NotImplementedError(f"info_sharing_str={cfg['info_sharing_str']}")
+    if cfg["info_sharing_str"] == "cross_attention":
+        if ik.get("num_views", 2) != 2:
+            raise AssertionError("Expected 2 views")  # cross_attention_transformer.py:382-384 with UFM's two views
+        if not ik.get("norm_cross_tokens", True):
+            raise NotImplementedError("norm_cross_tokens=False (the K/V GEMM reads the LayerNorm kernel's bf16 output)")
     if ik.get("custom_positional_encoding") is not None:
         raise NotImplementedError("custom_positional_encoding='rope' is not built yet")
     if ik.get("use_rand_idx_pe_for_non_reference_views") and cfg["info_sharing_str"] == "global_attention":
@@ -102,7 +107,7 @@ def engine_config(cfg: Dict[str, Any]) -> "_lib.UfmConfig":
     if len(it) < 2:
         raise ValueError("info_sharing indices must name at least two layers (ufm.py:605-606)")
     c.info_take0, c.info_take1 = it[0], it[1]
-    c.info_alternating = int(cfg["info_sharing_str"] == "alternating_attention")
+    c.info_alternating = {"global_attention": 0, "alternating_attention": 1, "cross_attention": 2}[cfg["info_sharing_str"]]
     c.info_qk_norm = int(bool(ik.get("qk_norm")))
     c.info_layerscale = int(bool(ik.get("init_values")))
     c.info_has_proj = 1
@@ -224,17 +229,49 @@ def pack_weights(cfg: Dict[str, Any], sd: Dict[str, torch.Tensor]) -> Dict[str, 
         out["info.proj.w"], out["info.proj.b"] = bf(sd[p + "proj_embed.weight"]), sd[p + "proj_embed.bias"]
     else:  # nn.Identity (global_attention_transformer.py:104-107) as an exact identity GEMM
         out["info.proj.w"], out["info.proj.b"] = bf(torch.eye(d)), torch.zeros(d)
-    tab = sd[p + "view_pos_table"]
-    vp = torch.zeros(2, d)
-    vp[0] = tab[0]
     ik = cfg["info_sharing_kwargs"]
-    if not ec.info_alternating or ik.get("use_pe_for_non_reference_views", False):
-        if ec.info_alternating and ik.get("use_rand_idx_pe_for_non_reference_views", True):
-            raise NotImplementedError("random view indices (SURVEY.md H7)")
-        vp[1] = tab[1]
-    out["info.viewpos"] = vp
-    for i in range(ec.info_depth):
-        block(f"info.{i}", f"{p}self_attention_blocks.{i}.", bool(ec.info_layerscale), bool(ec.info_qk_norm))
+    if ec.info_alternating == 2:
+        # per-view CrossAttentionBlock stacks (transformer_blocks.py:406-519): block() packs norm1 / attn / norm2 / mlp;
+        # here the MLP hangs off norm3 / ls3 and the cross-attention off norm2 / ls2, projk and projv are fused
+        ls, qkn = bool(ec.info_layerscale), bool(ec.info_qk_norm)
+        for v in range(2):
+            for i in range(ec.info_depth):
+                src, dst = f"{p}multi_view_branches.{v}.{i}.", f"info.v{v}.{i}"
+                g = lambda k: sd[src + k]
+                out[dst + ".ln1.w"], out[dst + ".ln1.b"] = g("norm1.weight"), g("norm1.bias")
+                out[dst + ".qkv.w"] = bf(g("attn.qkv.weight"))
+                if src + "attn.qkv.bias" in sd:
+                    out[dst + ".qkv.b"] = g("attn.qkv.bias")
+                out[dst + ".proj.w"], out[dst + ".proj.b"] = bf(g("attn.proj.weight")), g("attn.proj.bias")
+                out[dst + ".lny.w"], out[dst + ".lny.b"] = g("norm_y.weight"), g("norm_y.bias")
+                out[dst + ".ln2.w"], out[dst + ".ln2.b"] = g("norm2.weight"), g("norm2.bias")
+                out[dst + ".cq.w"] = bf(g("cross_attn.projq.weight"))
+                out[dst + ".ckv.w"] = bf(torch.cat([g("cross_attn.projk.weight"), g("cross_attn.projv.weight")], 0))
+                if src + "cross_attn.projq.bias" in sd:
+                    out[dst + ".cq.b"] = g("cross_attn.projq.bias")
+                    out[dst + ".ckv.b"] = torch.cat([g("cross_attn.projk.bias"), g("cross_attn.projv.bias")], 0)
+                out[dst + ".cproj.w"], out[dst + ".cproj.b"] = bf(g("cross_attn.proj.weight")), g("cross_attn.proj.bias")
+                out[dst + ".ln3.w"], out[dst + ".ln3.b"] = g("norm3.weight"), g("norm3.bias")
+                out[dst + ".fc1.w"], out[dst + ".fc1.b"] = bf(g("mlp.fc1.weight")), g("mlp.fc1.bias")
+                out[dst + ".fc2.w"], out[dst + ".fc2.b"] = bf(g("mlp.fc2.weight")), g("mlp.fc2.bias")
+                if qkn:
+                    out[dst + ".qn.w"], out[dst + ".qn.b"] = g("attn.q_norm.weight"), g("attn.q_norm.bias")
+                    out[dst + ".kn.w"], out[dst + ".kn.b"] = g("attn.k_norm.weight"), g("attn.k_norm.bias")
+                    out[dst + ".cqn.w"], out[dst + ".cqn.b"] = g("cross_attn.q_norm.weight"), g("cross_attn.q_norm.bias")
+                    out[dst + ".ckn.w"], out[dst + ".ckn.b"] = g("cross_attn.k_norm.weight"), g("cross_attn.k_norm.bias")
+                if ls:
+                    out[dst + ".ls1"], out[dst + ".ls2"], out[dst + ".ls3"] = g("ls1.gamma"), g("ls2.gamma"), g("ls3.gamma")
+    else:
+        tab = sd[p + "view_pos_table"]
+        vp = torch.zeros(2, d)
+        vp[0] = tab[0]
+        if not ec.info_alternating or ik.get("use_pe_for_non_reference_views", False):
+            if ec.info_alternating and ik.get("use_rand_idx_pe_for_non_reference_views", True):
+                raise NotImplementedError("random view indices (SURVEY.md H7)")
+            vp[1] = tab[1]
+        out["info.viewpos"] = vp
+        for i in range(ec.info_depth):
+            block(f"info.{i}", f"{p}self_attention_blocks.{i}.", bool(ec.info_layerscale), bool(ec.info_qk_norm))
     out["info.norm.w"], out["info.norm.b"] = sd[p + "norm.weight"], sd[p + "norm.bias"]
 
     def head(dst, src):
