@@ -199,7 +199,8 @@ def run_reference(args):
     refine = "classification_head_kwargs" in cfg
     t0 = time.perf_counter()
     v, threads, ts = cpu_reference_pairs_per_s(cfg, refine, n_calls=max(1, args.steps), warmup=min(args.warmup, 1))
-    sample = f"{len(ts)} timed call(s) of one 560x420 pair each (batch 1) of workload {args.workload}, fp32, {threads} threads"
+    Wr, Hr = cfg["inference_resolution"]
+    sample = f"{len(ts)} timed call(s) of one {Wr}x{Hr} pair each (batch 1) of workload {args.workload}, fp32, {threads} threads"
     line = {
         "impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": len(ts),
         "warmup": min(args.warmup, 1), "ms_per_step": 1e3 * statistics.median(ts), "higher_is_better": True,
@@ -347,7 +348,7 @@ def run_engine(args):
     if rank == 0 and world == 1 and not args.no_cpu:
         v, threads, ts = cpu_reference_pairs_per_s(cfg, refine, n_calls=args.cpu_calls, warmup=0)
         line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": threads, "kind": "port",
-                                "sample": f"{len(ts)} call(s) of one 560x420 pair (batch 1) of the same model, CPU fp32 oracle"}
+                                "sample": f"{len(ts)} call(s) of one {W}x{H} pair (batch 1) of the same model, CPU fp32 oracle"}
     sys.stdout.flush()
     os.dup2(saved_fd, 1)
     if rank == 0:
