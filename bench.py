@@ -1,7 +1,7 @@
 #!/usr/bin/env python
 """bench.py -- image pairs / second of the UFM dense-correspondence forward pass (BASELINE.json metric).
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl engine|reference] [--workload base16|refine16|hires4]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl engine|reference] [--workload base16|refine16|hires4|refine16_unet]
 
 A "step" is one pass of the hot path over one batch of synthetic image pairs (random-init weights of the assumed
 UFM-Base architecture; iid uint8 images of the named shape):
@@ -38,6 +38,7 @@ WORKLOADS = {
     "base16": ("ufm_base_assumed", (560, 420), 16, "UFM-Base batch 16 pairs 560x420 bf16 on 1xB200 (BASELINE.json configs[1])"),
     "refine16": ("ufm_refine_assumed", (560, 420), 16, "UFM-Refine batch 16 pairs 560x420 (configs[2])"),
     "hires4": ("ufm_base_assumed", (1120, 840), 4, "UFM-Base 1120x840 batch 4 (configs[3])"),
+    "refine16_unet": ("ufm_refine_unet", (560, 420), 16, "UFM-Refine + UNet fine-feature branch, batch 16 pairs 560x420 (SURVEY 8f N3)"),
 }
 
 
@@ -84,8 +85,23 @@ def algorithmic_tflop_per_pair(cfg, refine: bool) -> dict:
     cls = 0
     if refine:
         cls = 2 * (2 * n) * (2 * ec.cls_in * ec.cls_hidden + ec.cls_in * ec.cls_out * ec.cls_patch ** 2)
+    unet = 0
+    if ec.unet:  # unet_encoder.py:26-72 on both images + final / combine 1x1 convs
+        F = (64, 128, 256, 512)
+        lh, lw, cin = ec.img_h, ec.img_w, 3
+        dims = []
+        for f in F:
+            unet += 2 * lh * lw * 9 * (cin * f + f * f)
+            dims.append((lh, lw))
+            lh, lw, cin = lh // 2, lw // 2, f
+        unet += 2 * lh * lw * 9 * (cin * 2 * cin + 4 * cin * cin)
+        for f, (sh, sw) in zip(reversed(F), reversed(dims)):
+            unet += 2 * lh * lw * 4 * (2 * f) * f + 2 * sh * sw * 9 * (2 * f * f + f * f)
+            lh, lw = sh, sw
+        unet += 2 * ec.img_h * ec.img_w * (64 * 16 + (32 * 32 + 32 * 16 if ec.unet == 1 else 16 * 16))
+        unet *= 2
     t = {"enc_gemm": enc_gemm, "enc_attn": enc_attn, "info_gemm": info_gemm, "info_attn": info_attn, "heads": heads,
-         "cls_head": cls}
+         "cls_head": cls + unet}
     t = {k: v / 1e12 for k, v in t.items()}
     t["total"] = sum(t.values())
     t["gemm_conv"] = t["enc_gemm"] + t["info_gemm"] + t["heads"] + t["cls_head"]
@@ -160,7 +176,7 @@ def _make_cfg(workload: str):
     from ufm_b200 import configs
 
     name, res, pairs, desc = WORKLOADS[workload]
-    cfg = getattr(configs, name)(res)
+    cfg = configs.CONFIGS[name]() if name == "ufm_refine_unet" else getattr(configs, name)(res)
     return cfg, pairs, desc, name
 
 

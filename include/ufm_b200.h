@@ -51,6 +51,10 @@ typedef struct ufm_config {
   int unc_n_adaptors;
   int unc_kind[4];                         /* UFM_ADAPT_* */
   float unc_vmin[4], unc_vmax[4];          /* ConfidenceAdaptor vmin / vmax */
+  /* UNet fine-feature branch of UFM-Refine (use_unet_feature, ufm.py:817-825, 916-918, 967-982; the UNet is
+   * UNet(3, 16, [64,128,256,512]), unet_encoder.py:26-72): 0 = off, 1 = feature_combine_method "conv",
+   * 2 = "modulate".  Needs refine = 1. */
+  int unet;
 } ufm_config;
 
 /* adaptor kinds and their channel counts: mask 1 ('non_occluded_mask'), covariance 3 ('flow_cov'), confidence 1

@@ -69,10 +69,21 @@ def run_reference(name: str):
 
         hk(model.uncertainty_head[1], unc)
     if hasattr(model, "classification_head"):
-        hk(model.classification_head, lambda o: st.__setitem__("desc", o.decoded_channels))
+        unet = getattr(model, "use_unet_feature", False)
+        hk(model.classification_head, lambda o: st.__setitem__("desc_cls" if unet else "desc", o.decoded_channels))
+        if unet:
+            calls = []
+
+            def unet_out(o):  # called once per view (ufm.py:916-918)
+                calls.append(o)
+                st["unet_feat"] = torch.cat(calls, 0)
+
+            hk(model.unet_feature, unet_out)
         orig = model.classification_refinement
 
         def wrapped(flow, feats):
+            if unet:
+                st["desc"] = feats  # the combined features (ufm.py:967-982)
             r, l = orig(flow, feats)
             st["residual"], st["log_softmax"] = r, l.permute(0, 3, 4, 1, 2)  # (B,P,P,H,W) so H,W trail
             return r, l

@@ -350,6 +350,42 @@ def mlp_feature(x, sd, prefix, patch):
     return F.pixel_shuffle(t, patch)
 
 
+def _double_conv(x, sd, p):
+    """``DoubleConv.forward`` (uniflowmatch/models/unet_encoder.py:10-23)."""
+    x = F.relu(F.conv2d(x, sd[p + "conv.0.weight"], sd[p + "conv.0.bias"], padding=1))
+    return F.relu(F.conv2d(x, sd[p + "conv.2.weight"], sd[p + "conv.2.bias"], padding=1))
+
+
+def unet(img, sd, prefix="unet_feature.", n_levels=4, return_last=False):
+    """``UNet.forward`` (uniflowmatch/models/unet_encoder.py:50-72): 4 x [DoubleConv, maxpool 2], bottleneck, 4 x
+    [ConvTranspose 2x2/s2, nearest resize to the skip if the sizes differ, cat(skip, x), DoubleConv], 1x1 conv."""
+    skips = []
+    x = img
+    for k in range(n_levels):
+        x = _double_conv(x, sd, f"{prefix}downs.{k}.")
+        skips.append(x)
+        x = F.max_pool2d(x, kernel_size=2, stride=2)
+    x = _double_conv(x, sd, prefix + "bottleneck.")
+    for k in range(n_levels):
+        x = F.conv_transpose2d(x, sd[f"{prefix}ups.{2 * k}.weight"], sd[f"{prefix}ups.{2 * k}.bias"], stride=2)
+        skip = skips[n_levels - 1 - k]
+        if x.shape != skip.shape:
+            x = F.interpolate(x, size=skip.shape[2:])  # default mode: nearest
+        x = _double_conv(torch.cat((skip, x), dim=1), sd, f"{prefix}ups.{2 * k + 1}.")
+    out = F.conv2d(x, sd[prefix + "final_conv.weight"], sd[prefix + "final_conv.bias"])
+    return (out, x) if return_last else out
+
+
+def combine_unet(cls_feat, unet_feat, sd, method):
+    """ufm.py:967-982: ``conv``: conv2(relu(conv1(cat(cls, unet)))); ``modulate``: conv2(cls * tanh(unet))."""
+    if method == "conv":
+        t = F.relu(F.conv2d(torch.cat([cls_feat, unet_feat], dim=1), sd["conv1.weight"], sd["conv1.bias"]))
+        return F.conv2d(t, sd["conv2.weight"], sd["conv2.bias"])
+    if method == "modulate":
+        return F.conv2d(cls_feat * torch.tanh(unet_feat), sd["conv2.weight"], sd["conv2.bias"])
+    raise ValueError(method)
+
+
 def _cubic_weights(t: torch.Tensor, A: float = -0.75):
     """PyTorch bicubic convolution coefficients for fractional offset t (taps at -1,0,1,2)."""
     def c1(x):
@@ -460,6 +496,10 @@ def forward_stages(img1: torch.Tensor, img2: torch.Tensor, sd, cfg, stop_after: 
         cf = torch.cat([torch.cat([feats[0][:B], final[0]], dim=1),
                         torch.cat([feats[0][B:], final[1]], dim=1)], dim=0)  # ufm.py:954-963
         st["desc"] = mlp_feature(cf, sd, "classification_head.", ck["patch_size"])
+        if cfg.get("use_unet_feature"):
+            st["desc_cls"] = st["desc"]
+            st["unet_feat"], st["unet_x0"] = unet(torch.cat([img1, img2], dim=0), sd, return_last=True)  # ufm.py:916-918
+            st["desc"] = combine_unet(st["desc_cls"], st["unet_feat"], sd, cfg.get("feature_combine_method", "conv"))
         res, lsm = local_refinement(st["flow_reg"], st["desc"][:B], st["desc"][B:], sd["classification_bias"],
                                     float(cfg.get("temperature", 4)), int(cfg.get("refinement_range", 5)))
         st["residual"], st["log_softmax"] = res, lsm

@@ -89,6 +89,16 @@ def _engine_stages(model, B, h, w):
         out["log_softmax"] = eng.stage("log_softmax")
     except Exception:
         pass
+    try:
+        # UNet branch: (B, view, H, W, 64) bf16 / (B, view, 16, H, W) fp32 / planar descriptors -> (view*B, C, H, W)
+        x0 = eng.stage("unet_x0").float()
+        out["unet_x0"] = x0.permute(1, 0, 4, 2, 3).reshape(-1, x0.shape[4], x0.shape[2], x0.shape[3])
+        uf = eng.stage("unet_feat")
+        out["unet_feat"] = uf.permute(1, 0, 2, 3, 4).reshape(-1, *uf.shape[2:])
+        d = eng.stage("desc_cls")
+        out["desc_cls"] = d.permute(1, 0, 2, 5, 3, 4).reshape(-1, d.shape[2] * d.shape[5], d.shape[3], d.shape[4]).float()
+    except Exception:
+        pass
     return out
 
 
@@ -98,7 +108,7 @@ def _report(tag, rows):
         print(f"  {k:14s} rel-L2 {r:.3e}  max-abs {m:.3e}  (ref max {s:.3e})")
 
 
-@pytest.mark.parametrize("name", ["tiny_base", "tiny_refine", "tiny_alt_qknorm", "tiny_cross"])
+@pytest.mark.parametrize("name", ["tiny_base", "tiny_refine", "tiny_alt_qknorm", "tiny_cross", "tiny_unet", "tiny_unet_mod"])
 def test_tiny_stagewise_vs_oracle(name):
     model, cfg, sd = _model(name)
     W, H = cfg["inference_resolution"]
@@ -119,6 +129,9 @@ def test_tiny_stagewise_vs_oracle(name):
              ("dptu", st["dptu"], ref["dptu"]), ("headu_raw", st["headu_raw"], ref["headu_raw"])]
     if refine:
         pairs.append(("desc", st["desc"], ref["desc"]))
+    if cfg.get("use_unet_feature"):
+        pairs += [("unet_x0", st["unet_x0"], ref["unet_x0"]), ("unet_feat", st["unet_feat"], ref["unet_feat"]),
+                  ("desc_cls", st["desc_cls"], ref["desc_cls"])]
     rows = [(k, rel_l2(a.cpu(), b), max_abs(a.cpu(), b), b.abs().max().item()) for k, a, b in pairs]
     flow = res.flow.flow_output.cpu()
     rows.append(("flow", rel_l2(flow, ref["flow"]), max_abs(flow, ref["flow"]), ref["flow"].abs().max().item()))
@@ -296,3 +309,29 @@ def test_uncertainty_adaptors(conf_type):
     assert out2.flow.flow_covariance.shape == (2, 3, 120, 150)
     assert rel_l2(out2.flow.flow_covariance.cpu(), ref2["flow_covariance"]) < 5e-2
     assert rel_l2(out2.flow.flow_output.cpu(), ref2["flow"]) < FLOW_TOL
+
+
+def test_unet_branch_full_resolution():
+    """SURVEY.md 8f N3 at 560x420 (105 -> 104 -> nearest-resized 105 rows on the third level): the UNet branch and the
+    combine against the oracle, isolated from upstream bf16 noise by feeding the oracle the engine's own classification
+    features."""
+    from ufm_b200 import get_config
+
+    cfg = get_config("ufm_refine_unet")
+    sd = make_state_dict(cfg, seed=0, out_gain=8.0)
+    model = UniFlowMatchClassificationRefinement(**cfg).to("cuda")
+    model.load_state_dict(sd)
+    W, H = cfg["inference_resolution"]
+    src, tgt = make_inputs(1, H, W, seed=3)
+    s0, s1 = O.canonicalize_inputs(src, tgt, "dinov2", None)
+    model.forward({"img": s0.cuda(), "data_norm_type": "dinov2"}, {"img": s1.cuda(), "data_norm_type": "dinov2"})
+    torch.cuda.synchronize()
+    st = _engine_stages(model, 1, H // 14, W // 14)
+    with torch.no_grad():
+        uf, x0 = O.unet(torch.cat([s0, s1], dim=0), sd, return_last=True)
+        desc_ref = O.combine_unet(st["desc_cls"].cpu(), uf, sd, "conv")
+    rows = [(k, rel_l2(a.cpu(), b), max_abs(a.cpu(), b), b.abs().max().item())
+            for k, a, b in (("unet_x0", st["unet_x0"], x0), ("unet_feat", st["unet_feat"], uf), ("desc", st["desc"], desc_ref))]
+    _report("ufm_refine_unet", rows)
+    for k, r, m, s in rows:
+        assert r <= FEAT_TOL, (k, r)

@@ -37,6 +37,7 @@ class UfmConfig(C.Structure):
         ("temperature", C.c_float),
         ("unc_n_adaptors", C.c_int), ("unc_kind", C.c_int * 4),
         ("unc_vmin", C.c_float * 4), ("unc_vmax", C.c_float * 4),
+        ("unet", C.c_int),
     ]
 
 

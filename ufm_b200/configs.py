@@ -84,7 +84,8 @@ def ufm_refine_assumed(inference_resolution=(560, 420)) -> Dict[str, Any]:
 
 
 def tiny(refine: bool = False, inference_resolution=(224, 168), info_sharing_str="global_attention",
-         qk_norm: bool = False, unc_adaptors: str = "mask", conf_type: str = "sigmoid") -> Dict[str, Any]:
+         qk_norm: bool = False, unc_adaptors: str = "mask", conf_type: str = "sigmoid",
+         unet: str = "") -> Dict[str, Any]:
     """A small architecture with the same topology, for fast CPU goldens and GPU parity at every
     stage boundary: ViT-S/14 truncated to 4 layers, 4x128 info sharing, slim DPT heads."""
     W, H = inference_resolution
@@ -119,6 +120,9 @@ def tiny(refine: bool = False, inference_resolution=(224, 168), info_sharing_str
         }
     if refine:
         cfg["classification_head_kwargs"].update({"input_feature_dim": 384 + 128})
+        if unet:
+            # UNet fine-feature branch (ufm.py:817-825, 967-982); the UNet itself is not configurable
+            cfg.update({"use_unet_feature": True, "feature_combine_method": unet})
     return cfg
 
 
@@ -130,6 +134,9 @@ CONFIGS = {
     "tiny_refine": lambda: tiny(True),
     "tiny_cov": lambda: tiny(False, unc_adaptors="cov_conf_mask"),
     "tiny_cross": lambda: tiny(True, info_sharing_str="cross_attention", qk_norm=True),
+    "tiny_unet": lambda: tiny(True, unet="conv"),
+    "tiny_unet_mod": lambda: tiny(True, unet="modulate"),
+    "ufm_refine_unet": lambda: dict(ufm_refine_assumed(), use_unet_feature=True, feature_combine_method="conv"),
 }
 
 

@@ -472,6 +472,7 @@ struct ufm_engine {
 
   bool dpt_head(const std::string& hp, int Bp, int out_ch, bool sigmoid, const float* tscale, const float* tshift,
                 bf16* dpt_out, float* out_final, float* out_raw);
+  bool unet_branch(const void* src, const void* tgt, int in_dtype, int in_layout, int Bp);
   int forward(const void* src, const void* tgt, int pairs, int in_dtype, int in_layout, float* flow_out, float* covis_out,
               cudaStream_t stream);
 };
@@ -616,6 +617,95 @@ bool ufm_engine::dpt_head(const std::string& hp, int Bp, int out_ch, bool sigmoi
     e.out2 = out_raw;
     if (!gemm(image_view(rs, Bp, c.img_h, c.img_w, hid), hp + ".proc.c2.w", 9, e)) return false;
   }
+  return true;
+}
+
+// UNet fine-feature branch (uniflowmatch/models/unet_encoder.py:50-72 on both images, ufm.py:916-918) and the combine
+// with the classification features (ufm.py:967-982).  Images run in (b, view) order, NHWC bf16; every cat(skip, x) is a
+// concat buffer "ucat<l>" whose left half the encoder conv writes and whose right half the ConvTranspose scatter writes.
+bool ufm_engine::unet_branch(const void* src, const void* tgt, int in_dtype, int in_layout, int Bp) {
+  const ufm_config& c = cfg;
+  const int N2 = 2 * Bp;
+  static const int F[4] = {64, 128, 256, 512};
+  int LH[5], LW[5];
+  LH[0] = c.img_h; LW[0] = c.img_w;
+  for (int l = 1; l < 5; ++l) { LH[l] = LH[l - 1] / 2; LW[l] = LW[l - 1] / 2; }
+  bf16* cat[4] = {B<bf16>("ucat0"), B<bf16>("ucat1"), B<bf16>("ucat2"), B<bf16>("ucat3")};
+  bf16 *T = B<bf16>("uT"), *P = B<bf16>("uP"), *X = B<bf16>("uX"), *G = B<bf16>("uG");
+  // conv3x3 + bias + ReLU, dense NHWC input, output at a channel offset of a buffer with pixel pitch out_pitch
+  auto conv = [&](const bf16* in, int l, int C, const std::string& wn, bf16* out, long long out_pitch, long long off) {
+    const Tensor* wt = W(wn + ".w");
+    if (!wt) return false;
+    Epi e;
+    e.bias = Wf(wn + ".b");
+    if (!e.bias) return false;
+    e.out_bf16 = out; e.sx = out_pitch; e.sy = LW[l] * out_pitch; e.sn = (long long)LH[l] * LW[l] * out_pitch;
+    e.out_off = off;
+    e.flags = GEMM_RELU_BF16;
+    return gemm(image_view(in, N2, LH[l], LW[l], C), wn + ".w", 9, e);
+  };
+  {
+    UnetStemParams sp;
+    sp.src = src; sp.tgt = tgt; sp.B = Bp; sp.H = c.img_h; sp.W = c.img_w;
+    sp.is_u8 = in_dtype == UFM_U8; sp.is_nhwc = in_layout == UFM_NHWC;
+    const float mean[3] = {0.485f, 0.456f, 0.406f}, stdv[3] = {0.229f, 0.224f, 0.225f};
+    for (int i = 0; i < 3; ++i) { sp.mean[i] = mean[i]; sp.inv_std[i] = 1.0f / stdv[i]; }
+    sp.w = Wf("unet.stem.w"); sp.b = Wf("unet.stem.b"); sp.out = T;
+    if (!sp.w || !sp.b) return false;
+    const double px = (double)N2 * c.img_h * c.img_w;
+    if (!run(UFM_CAT_MOVE, 2.0 * px * 64 * 27, px * (3.0 * (sp.is_u8 ? 1 : 4) + 128), "unet stem",
+             [&] { return launch_unet_stem(sp, st); }))
+      return false;
+  }
+  if (!conv(T, 0, 64, "unet.d0.c2", cat[0], 128, 0)) return false;
+  for (int l = 1; l <= 4; ++l) {
+    const int Cin = F[l - 1];
+    const double pb = (double)N2 * LH[l] * LW[l] * Cin * 2;
+    if (!run(UFM_CAT_MOVE, 0.0, 5.0 * pb, "unet pool",
+             [&] { return launch_unet_pool(cat[l - 1], 2 * Cin, N2, LH[l - 1], LW[l - 1], Cin, P, st); }))
+      return false;
+    const std::string pre = l < 4 ? "unet.d" + std::to_string(l) : std::string("unet.bn");
+    const int Cout = 2 * Cin;
+    if (!conv(P, l, Cin, pre + ".c1", T, Cout, 0)) return false;
+    if (l < 4) {
+      if (!conv(T, l, Cout, pre + ".c2", cat[l], 2 * Cout, 0)) return false;
+    } else {
+      if (!conv(T, l, Cout, pre + ".c2", X, Cout, 0)) return false;
+    }
+  }
+  for (int l = 3; l >= 0; --l) {
+    const std::string pre = "unet.u" + std::to_string(l);
+    const long long rows = (long long)N2 * LH[l + 1] * LW[l + 1];
+    {
+      Epi e;
+      e.bias = Wf(pre + ".t.b");
+      if (!e.bias) return false;
+      e.out_bf16 = G; e.sx = 4LL * F[l];
+      if (!gemm(rows_view(X, rows, 2 * F[l]), pre + ".t.w", 1, e)) return false;
+    }
+    const double ub = (double)N2 * LH[l] * LW[l] * F[l] * 2;
+    if (!run(UFM_CAT_MOVE, 0.0, 2.0 * ub, "unet up", [&] {
+          return launch_unet_up(G, N2, LH[l + 1], LW[l + 1], F[l], cat[l], 2 * F[l], F[l], LH[l], LW[l], st);
+        }))
+      return false;
+    if (!conv(cat[l], l, 2 * F[l], pre + ".c1", T, F[l], 0)) return false;
+    if (!conv(T, l, F[l], pre + ".c2", X, F[l], 0)) return false;
+  }
+  set_stage("unet_x0", X, UFM_BF16, {Bp, 2, c.img_h, c.img_w, 64});
+  UnetCombineParams cp;
+  cp.x0 = X; cp.desc_cls = B<bf16>("desc_cls"); cp.desc = B<bf16>("desc");
+  cp.unet_feat = keep_aux ? B<float>("unet_feat") : nullptr;
+  cp.n = N2; cp.H = c.img_h; cp.W = c.img_w; cp.method = c.unet;
+  cp.wf = Wf("unet.final.w"); cp.bf = Wf("unet.final.b");
+  cp.w1 = c.unet == 1 ? Wf("unet.conv1.w") : nullptr; cp.b1 = c.unet == 1 ? Wf("unet.conv1.b") : nullptr;
+  cp.w2 = Wf("unet.conv2.w"); cp.b2 = Wf("unet.conv2.b");
+  if (!cp.wf || !cp.bf || !cp.w2 || !cp.b2 || (c.unet == 1 && (!cp.w1 || !cp.b1))) return false;
+  const double px = (double)N2 * c.img_h * c.img_w;
+  const double fl = 2.0 * px * (64 * 16 + (c.unet == 1 ? 32 * 32 + 32 * 16 : 16 * 16));
+  if (!run(UFM_CAT_MOVE, fl, px * (128 + 32 + 32 + (keep_aux ? 64 : 0)), "unet combine",
+           [&] { return launch_unet_combine(cp, st); }))
+    return false;
+  if (keep_aux) set_stage("unet_feat", cp.unet_feat, UFM_F32, {Bp, 2, 16, c.img_h, c.img_w});
   return true;
 }
 
@@ -796,10 +886,15 @@ int ufm_engine::forward(const void* src, const void* tgt, int pairs, int in_dtyp
       e.bias = Wf("cls.lin.b"); e.out_bf16 = B<bf16>("Z"); e.sx = zc;
       if (!gemm(rows_view(B<bf16>("Ycls"), Mc, c.cls_in), "cls.lin.w", 1, e)) return 1;
     }
+    bf16* desc_dst = c.unet ? B<bf16>("desc_cls") : B<bf16>("desc");
     if (!run(UFM_CAT_MOVE, 0.0, 4.0 * Mi * zc, "shuffle desc", [&] {
-          return launch_desc_shuffle(B<bf16>("Z"), B<bf16>("desc"), 2 * Bp, hpn, wpn, c.cls_patch, c.cls_out, st);
+          return launch_desc_shuffle(B<bf16>("Z"), desc_dst, 2 * Bp, hpn, wpn, c.cls_patch, c.cls_out, st);
         }))
       return 1;
+    if (c.unet) {
+      if (!unet_branch(src, tgt, in_dtype, in_layout, Bp)) return 1;
+      set_stage("desc_cls", desc_dst, UFM_BF16, {Bp, 2, c.cls_out / 8, c.img_h, c.img_w, 8});
+    }
     set_stage("desc", B<bf16>("desc"), UFM_BF16, {Bp, 2, c.cls_out / 8, c.img_h, c.img_w, 8});
     RefineParams rp;
     rp.desc = B<bf16>("desc"); rp.B = Bp; rp.H = c.img_h; rp.W = c.img_w;
@@ -880,6 +975,11 @@ int ufm_create(const ufm_config* cfg, int device, ufm_engine** out) {
     delete e;
     fprintf(stderr, "ufm_create: refinement kernel is specialised for 16-channel descriptors and a 5x5 window\n");
     return 6;
+  }
+  if (c.unet && (!c.refine || c.unet < 0 || c.unet > 2 || c.img_h < 16 || c.img_w < 16)) {
+    delete e;
+    fprintf(stderr, "ufm_create: unet must be 0, 1 (conv) or 2 (modulate), on a Refine config with an image of at least 16x16\n");
+    return 8;
   }
   *out = e;
   return 0;
@@ -994,6 +1094,18 @@ int ufm_prepare(ufm_engine* e, int max_pairs) {
     ok = ok && e->alloc("desc", UFM_BF16, 2 * Bp * c.img_h * c.img_w * c.cls_out);
     ok = ok && e->alloc("residual", UFM_F32, Bp * 2 * c.img_h * c.img_w);
     ok = ok && e->alloc("log_softmax", UFM_F32, Bp * c.img_h * c.img_w * 25);
+    if (c.unet) {
+      const long long N2 = 2 * Bp, HW = (long long)c.img_h * c.img_w;
+      int lh = c.img_h, lw = c.img_w;
+      for (int l = 0; l < 4; ++l) {
+        ok = ok && e->alloc("ucat" + std::to_string(l), UFM_BF16, N2 * lh * lw * (128LL << l));
+        lh /= 2; lw /= 2;
+      }
+      for (const char* nm : {"uT", "uX", "uG"}) ok = ok && e->alloc(nm, UFM_BF16, N2 * HW * 64);
+      ok = ok && e->alloc("uP", UFM_BF16, N2 * (c.img_h / 2) * (c.img_w / 2) * 64);
+      ok = ok && e->alloc("desc_cls", UFM_BF16, N2 * HW * c.cls_out);
+      ok = ok && e->alloc("unet_feat", UFM_F32, N2 * HW * 16);
+    }
   }
   // staging buffers for ufm_forward_host
   ok = ok && e->alloc("in_src", UFM_F32, Bp * 3 * c.img_h * c.img_w);

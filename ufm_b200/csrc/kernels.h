@@ -198,6 +198,36 @@ struct UncAdaptParams {
 };
 cudaError_t launch_unc_adaptors(const UncAdaptParams& p, cudaStream_t s);
 
+// ------------------------------------------------------------------------------------------------
+// UNet fine-feature branch of UFM-Refine (unet.cu; unet_encoder.py:26-72, ufm.py:817-825, 967-982)
+// ------------------------------------------------------------------------------------------------
+struct UnetStemParams {
+  const void* src; const void* tgt;    // each [B, ...] uint8 / fp32, NHWC / NCHW; output image index = b*2 + view
+  int B, H, W, is_u8, is_nhwc;
+  float mean[3], inv_std[3];
+  const float* w; const float* b;      // downs.0.conv.0: [64][3][3][3] fp32, [64]
+  __nv_bfloat16* out;                  // [2B, H, W, 64] = relu(conv3x3(normalised image))
+};
+cudaError_t launch_unet_stem(const UnetStemParams& p, cudaStream_t s);
+// 2x2/s2 max pool of the first C channels of in[n,H,W,in_pitch] -> out[n,H/2,W/2,C] (dense)
+cudaError_t launch_unet_pool(const __nv_bfloat16* in, long long in_pitch, int n, int H, int W, int C, __nv_bfloat16* out,
+                             cudaStream_t s);
+// ConvTranspose(k=s=2) GEMM result g[(n,y,x)][(ky,kx,c)] -> out[n,oy,ox,out_off + c] (pixel pitch out_pitch), nearest
+// resize from (2h, 2w) to (oh, ow) as F.interpolate does when the skip is larger (unet_encoder.py:66-67)
+cudaError_t launch_unet_up(const __nv_bfloat16* g, int n, int h, int w, int C, __nv_bfloat16* out, long long out_pitch,
+                           int out_off, int oh, int ow, cudaStream_t s);
+struct UnetCombineParams {
+  const __nv_bfloat16* x0;             // [n, H, W, 64] last DoubleConv output
+  const __nv_bfloat16* desc_cls;       // classification features, planar [n][2][H][W][8]
+  __nv_bfloat16* desc;                 // combined descriptors, same layout
+  float* unet_feat;                    // optional [n][16][H][W] fp32 (final_conv output, parity stage)
+  int n, H, W, method;                 // method 1 = "conv", 2 = "modulate"
+  const float *wf, *bf;                // final_conv transposed [64][16], [16]
+  const float *w1, *b1;                // conv1 transposed [32][32], [32] (method 1)
+  const float *w2, *b2;                // conv2 transposed [32 | 16][16], [16]
+};
+cudaError_t launch_unet_combine(const UnetCombineParams& p, cudaStream_t s);
+
 // NHWC fp32 [n,H,W,C] -> NCHW fp32 (stage dumps / descriptor export)
 cudaError_t launch_nhwc_to_nchw(const float* in, float* out, int n, int H, int W, int C, cudaStream_t s);
 

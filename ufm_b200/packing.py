@@ -90,8 +90,8 @@ def engine_config(cfg: Dict[str, Any]) -> "_lib.UfmConfig":
         raise NotImplementedError("use_rand_idx_pe_for_non_reference_views draws from the global RNG (SURVEY.md H7)")
     if cfg.get("head_type", "dpt") != "dpt":
         raise NotImplementedError("head_type must be 'dpt'")
-    if cfg.get("use_unet_feature"):
-        raise NotImplementedError("use_unet_feature (SURVEY.md 8f N3)")
+    if cfg.get("use_unet_feature") and "classification_head_kwargs" not in cfg:
+        raise ValueError("use_unet_feature belongs to UniFlowMatchClassificationRefinement (ufm.py:742)")
     dim, depth, heads = DINOV2_ARCH[ek["size"]]
     if ek.get("keep_first_n_layers") is not None:
         depth = min(depth, ek["keep_first_n_layers"])
@@ -145,6 +145,13 @@ def engine_config(cfg: Dict[str, Any]) -> "_lib.UfmConfig":
         c.cls_out, c.cls_patch = ck["output_dim"], ck["patch_size"]
         c.refine_P = cfg.get("refinement_range", 5)
         c.temperature = float(cfg.get("temperature", 4))
+        if cfg.get("use_unet_feature"):
+            method = cfg.get("feature_combine_method", "conv")
+            if method not in ("conv", "modulate"):
+                raise ValueError(f"feature_combine_method={method!r}")  # ufm.py:821-824 leaves conv2 undefined otherwise
+            if c.cls_out != 16:
+                raise ValueError("the UNet branch emits 16 channels (ufm.py:818); classification output_dim must be 16")
+            c.unet = {"conv": 1, "modulate": 2}[method]
     return c
 
 
@@ -316,4 +323,31 @@ def pack_weights(cfg: Dict[str, Any], sd: Dict[str, torch.Tensor]) -> Dict[str, 
         out["cls.lin.w"] = bf(w)
         out["cls.lin.b"] = sd[p + "linear.bias"].reshape(od, P, P).permute(1, 2, 0).reshape(-1)
         out["cls.bias"] = sd["classification_bias"]
+    if ec.unet:
+        # unet_encoder.py:26-72.  3x3 convs in the implicit-GEMM layout; ConvTranspose(k = s = 2) as a GEMM with rows
+        # ordered (ky, kx, out) and its bias replicated over the 4 taps; the per-pixel 1x1 convs transposed to [in][out].
+        u = "unet_feature."
+
+        def dconv(dst, src, first=True):
+            if first:
+                out[dst + ".c1.w"], out[dst + ".c1.b"] = _conv3_pack(sd[src + "conv.0.weight"]), sd[src + "conv.0.bias"]
+            out[dst + ".c2.w"], out[dst + ".c2.b"] = _conv3_pack(sd[src + "conv.2.weight"]), sd[src + "conv.2.bias"]
+
+        out["unet.stem.w"] = sd[u + "downs.0.conv.0.weight"].reshape(64, 27)
+        out["unet.stem.b"] = sd[u + "downs.0.conv.0.bias"]
+        dconv("unet.d0", u + "downs.0.", first=False)
+        for l in (1, 2, 3):
+            dconv(f"unet.d{l}", f"{u}downs.{l}.")
+        dconv("unet.bn", u + "bottleneck.")
+        for k in range(4):
+            l = 3 - k
+            wt = sd[f"{u}ups.{2 * k}.weight"]  # (in, out, 2, 2)
+            out[f"unet.u{l}.t.w"] = bf(wt.permute(2, 3, 1, 0).reshape(4 * wt.shape[1], wt.shape[0]))
+            out[f"unet.u{l}.t.b"] = sd[f"{u}ups.{2 * k}.bias"].repeat(4)
+            dconv(f"unet.u{l}", f"{u}ups.{2 * k + 1}.")
+        t2 = lambda w: w.reshape(w.shape[0], w.shape[1]).t()
+        out["unet.final.w"], out["unet.final.b"] = t2(sd[u + "final_conv.weight"]), sd[u + "final_conv.bias"]
+        if ec.unet == 1:
+            out["unet.conv1.w"], out["unet.conv1.b"] = t2(sd["conv1.weight"]), sd["conv1.bias"]
+        out["unet.conv2.w"], out["unet.conv2.b"] = t2(sd["conv2.weight"]), sd["conv2.bias"]
     return {k: v.contiguous() for k, v in out.items()}

@@ -191,6 +191,38 @@ def model_spec(cfg: Dict[str, Any]) -> Spec:
               (p + "linear.weight", (ck["output_dim"] * ck["patch_size"] ** 2, d, 1, 1), "w_desc"),
               (p + "linear.bias", (ck["output_dim"] * ck["patch_size"] ** 2,), "b")]
         s = [("classification_bias", (cfg.get("refinement_range", 5) ** 2,), "cls_bias")] + s
+        if cfg.get("use_unet_feature"):
+            s += unet_spec(cfg)
+    return s
+
+
+UNET_FEATURES = (64, 128, 256, 512)  # hard-coded in the reference (``ufm.py:818``)
+
+
+def unet_spec(cfg: Dict[str, Any]) -> Spec:
+    """``UNet(3, 16, [64,128,256,512])`` (``uniflowmatch/models/unet_encoder.py:26-72``) plus the two 1x1 combine convs
+    (``ufm.py:817-825``)."""
+    s: Spec = []
+
+    def double_conv(p, cin, cout):
+        return [(p + "conv.0.weight", (cout, cin, 3, 3), "w_relu"), (p + "conv.0.bias", (cout,), "b"),
+                (p + "conv.2.weight", (cout, cout, 3, 3), "w_relu"), (p + "conv.2.bias", (cout,), "b")]
+
+    u = "unet_feature."
+    cin = 3
+    for k, f in enumerate(UNET_FEATURES):
+        s += double_conv(f"{u}downs.{k}.", cin, f)
+        cin = f
+    s += double_conv(u + "bottleneck.", UNET_FEATURES[-1], 2 * UNET_FEATURES[-1])
+    for k, f in enumerate(reversed(UNET_FEATURES)):
+        s += [(f"{u}ups.{2 * k}.weight", (2 * f, f, 2, 2), "w_convt_up"), (f"{u}ups.{2 * k}.bias", (f,), "b")]
+        s += double_conv(f"{u}ups.{2 * k + 1}.", 2 * f, f)
+    od = cfg["classification_head_kwargs"]["output_dim"]
+    s += [(u + "final_conv.weight", (od, UNET_FEATURES[0], 1, 1), "w"), (u + "final_conv.bias", (od,), "b")]
+    method = cfg.get("feature_combine_method", "conv")
+    s += [("conv1.weight", (32, 32, 1, 1), "w_relu"), ("conv1.bias", (32,), "b")]
+    c2in = {"conv": 32, "modulate": 16}[method]
+    s += [("conv2.weight", (16, c2in, 1, 1), "w"), ("conv2.bias", (16,), "b")]
     return s
 
 
@@ -220,13 +252,17 @@ def make_state_dict(cfg: Dict[str, Any], seed: int = 0, out_gain: float = 1.0) -
             sd[key] = sd[kind[6:]]
             continue
         g = _gen(seed, key)
-        if kind in ("w", "w_convt", "w_out", "w_desc"):
+        if kind in ("w", "w_convt", "w_out", "w_desc", "w_relu", "w_convt_up"):
             if kind == "w_convt":  # ConvTranspose2d weight is (in, out, kh, kw)
                 fan_in, fan_out = shape[0], shape[1]
+            elif kind == "w_convt_up":  # k == stride: every output pixel sees one tap of every input channel
+                fan_in = fan_out = shape[0]
             else:
                 rf = int(np.prod(shape[2:])) if len(shape) > 2 else 1
                 fan_in, fan_out = shape[1] * rf, shape[0] * rf
             a = math.sqrt(6.0 / (fan_in + fan_out))
+            if kind == "w_relu":  # He-uniform: keeps the activation scale through the 18-conv ReLU stack of the UNet
+                a = math.sqrt(6.0 / fan_in)
             t = (torch.rand(shape, generator=g) * 2 - 1) * a
             if kind == "w_out":
                 t = t * out_gain
