@@ -39,8 +39,9 @@ __device__ __forceinline__ int nearest_src(int dst, int in, int out) {
 }
 
 // ------------------------------------------------------------------------------------------------ stem
-// 64 pixels x 4 channel quarters per block; one thread = 16 output channels of one pixel.
-__global__ void __launch_bounds__(256) unet_stem_kernel(const UnetStemParams p) {
+// Generic version (any width): 64 pixels x 4 channel quarters per block; one thread = 16 output channels of one pixel.
+// One LDS.128 feeds only 4 FMAs here, so it runs at the shared-memory rate; used when W % 4 != 0.
+__global__ void __launch_bounds__(256) unet_stem_generic_kernel(const UnetStemParams p) {
   __shared__ __align__(16) float ws[27][64];
   __shared__ float bs[64];
   for (int i = threadIdx.x; i < 27 * 64; i += 256) {
@@ -98,6 +99,112 @@ __global__ void __launch_bounds__(256) unet_stem_kernel(const UnetStemParams p) 
   dst[1] = make_uint4(u[4], u[5], u[6], u[7]);
 }
 
+// Fast version (W % 4 == 0): a block covers 256 consecutive pixels of one image; warp w computes channel quarter q = w & 3
+// (so every weight load is a warp-wide broadcast) for 4 consecutive pixels per thread -> one LDS.128 feeds 16 FMAs.
+// The 256 x 64 bf16 tile is staged in shared memory (16-byte chunks XOR-swizzled against the 512-byte lane stride)
+// and leaves as one contiguous 32 KB run.
+// Input taps are fetched branch-free (clamped address + select) so that the 18 loads of one input channel are in
+// flight together; uint8 pixels are normalised through a 3 x 256 table built per block (no per-tap division).
+template <bool U8, bool NHWC>
+__global__ void __launch_bounds__(256, 2) unet_stem_kernel(const UnetStemParams p) {
+  __shared__ __align__(16) float ws[27][64];
+  __shared__ float bs[64];
+  __shared__ float lut[U8 ? 3 * 256 : 1];
+  __shared__ __align__(16) uint4 tile[256 * 8];
+  for (int i = threadIdx.x; i < 27 * 64; i += 256) {
+    const int co = i / 27, k = i - co * 27;  // weight is [co][ci][ky][kx]
+    ws[k][co] = p.w[i];
+  }
+  if (threadIdx.x < 64) bs[threadIdx.x] = p.b[threadIdx.x];
+  if (U8) {
+    for (int i = threadIdx.x; i < 3 * 256; i += 256) {
+      const int c = i >> 8;
+      lut[i] = ((float)(i & 255) / 255.0f - p.mean[c]) * p.inv_std[c];  // base.py:215-229, as patch_im2col_kernel
+    }
+  }
+  __syncthreads();
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int q = warp & 3;
+  const int lp = ((warp >> 2) * 32 + lane) * 4;  // first of this thread's 4 pixels inside the tile
+  const int plane = p.H * p.W;
+  const int pix0 = blockIdx.x * 256 + lp;
+  const int img = blockIdx.y;  // (b, view)
+  const int b = img >> 1, view = img & 1;
+  const uint8_t* base8 = reinterpret_cast<const uint8_t*>(view ? p.tgt : p.src);
+  const float* base32 = reinterpret_cast<const float*>(view ? p.tgt : p.src);
+  if (pix0 < plane) {
+    const int y = pix0 / p.W, x0 = pix0 - y * p.W;  // W % 4 == 0: the 4 pixels share the row
+    float acc[4][16];
+#pragma unroll
+    for (int j = 0; j < 4; ++j)
+#pragma unroll
+      for (int o = 0; o < 16; ++o) acc[j][o] = bs[q * 16 + o];
+    int xc[6], yc[3];
+    bool xok[6], yok[3];
+#pragma unroll
+    for (int i = 0; i < 6; ++i) {
+      const int xx = x0 + i - 1;
+      xok[i] = (unsigned)xx < (unsigned)p.W;
+      xc[i] = min(max(xx, 0), p.W - 1);
+    }
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+      const int yy = y + k - 1;
+      yok[k] = (unsigned)yy < (unsigned)p.H;
+      yc[k] = min(max(yy, 0), p.H - 1);
+    }
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {
+      float in[3][6];
+#pragma unroll
+      for (int ky = 0; ky < 3; ++ky)
+#pragma unroll
+        for (int i = 0; i < 6; ++i) {
+          const int off = NHWC ? ((b * p.H + yc[ky]) * p.W + xc[i]) * 3 + c : ((b * 3 + c) * p.H + yc[ky]) * p.W + xc[i];
+          const float val = U8 ? lut[c * 256 + base8[off]] : base32[off];
+          in[ky][i] = (xok[i] && yok[ky]) ? val : 0.f;  // zero padding of the NORMALISED image
+        }
+#pragma unroll
+      for (int ky = 0; ky < 3; ++ky)
+#pragma unroll
+        for (int kx = 0; kx < 3; ++kx) {
+          const float4* wr = reinterpret_cast<const float4*>(&ws[c * 9 + ky * 3 + kx][q * 16]);
+#pragma unroll
+          for (int v = 0; v < 4; ++v) {
+            const float4 w4 = wr[v];
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+              acc[j][v * 4 + 0] = fmaf(in[ky][j + kx], w4.x, acc[j][v * 4 + 0]);
+              acc[j][v * 4 + 1] = fmaf(in[ky][j + kx], w4.y, acc[j][v * 4 + 1]);
+              acc[j][v * 4 + 2] = fmaf(in[ky][j + kx], w4.z, acc[j][v * 4 + 2]);
+              acc[j][v * 4 + 3] = fmaf(in[ky][j + kx], w4.w, acc[j][v * 4 + 3]);
+            }
+          }
+        }
+    }
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      uint32_t u[8];
+#pragma unroll
+      for (int i = 0; i < 8; ++i) u[i] = pack2(fmaxf(acc[j][2 * i], 0.f), fmaxf(acc[j][2 * i + 1], 0.f));
+      const int px = lp + j, sw = (px >> 2) & 7;
+      tile[px * 8 + ((q * 2) ^ sw)] = make_uint4(u[0], u[1], u[2], u[3]);
+      tile[px * 8 + ((q * 2 + 1) ^ sw)] = make_uint4(u[4], u[5], u[6], u[7]);
+    }
+  }
+  __syncthreads();
+  uint4* dst = reinterpret_cast<uint4*>(p.out + ((long long)img * plane + (long long)blockIdx.x * 256) * 64);
+  const int valid = min(256, plane - blockIdx.x * 256) * 8;  // 16-byte chunks of this tile that exist
+#pragma unroll
+  for (int it = 0; it < 8; ++it) {
+    const int i = it * 256 + threadIdx.x;
+    if (i < valid) {
+      const int px = i >> 3;
+      dst[i] = tile[px * 8 + ((i & 7) ^ ((px >> 2) & 7))];
+    }
+  }
+}
+
 // ------------------------------------------------------------------------------------------------ max pool
 __global__ void __launch_bounds__(256) unet_pool_kernel(const bf16* __restrict__ in, long long in_pitch, int n, int H, int W,
                                                        int C, bf16* __restrict__ out, int oh, int ow) {
@@ -141,6 +248,9 @@ __global__ void __launch_bounds__(256) unet_up_kernel(const bf16* __restrict__ g
 }
 
 // ------------------------------------------------------------------------------------------------ combine
+// One thread = CP pixels (128 apart, so every planar load / store stays coalesced): each broadcast weight load from
+// shared memory feeds 4 * CP FMAs instead of 4 (the one-pixel version ran at the LDS rate).
+constexpr int CP = 2;
 __global__ void __launch_bounds__(128) unet_combine_kernel(const UnetCombineParams p) {
   __shared__ __align__(16) float wf[64][16];
   __shared__ __align__(16) float w1[32][32];
@@ -157,103 +267,139 @@ __global__ void __launch_bounds__(128) unet_combine_kernel(const UnetCombinePara
   if (threadIdx.x < 32) b1[threadIdx.x] = p.method == 1 ? p.b1[threadIdx.x] : 0.f;
   __syncthreads();
   const long long plane = (long long)p.H * p.W;
-  const long long pix = (long long)blockIdx.x * 128 + threadIdx.x;
-  if (pix >= plane) return;
+  const long long pix0 = (long long)blockIdx.x * (128 * CP) + threadIdx.x;
+  if (pix0 >= plane) return;
   const int img = blockIdx.y;
-  // final_conv: 64 -> 16
-  float f[16];
+  long long pix[CP];
 #pragma unroll
-  for (int o = 0; o < 16; ++o) f[o] = bfin[o];
-  const uint4* xs = reinterpret_cast<const uint4*>(p.x0 + ((long long)img * plane + pix) * 64);
+  for (int j = 0; j < CP; ++j) pix[j] = min(pix0 + 128 * j, plane - 1);  // clamped duplicates are not stored
+  // final_conv: 64 -> 16
+  float f[CP][16];
+#pragma unroll
+  for (int j = 0; j < CP; ++j)
+#pragma unroll
+    for (int o = 0; o < 16; ++o) f[j][o] = bfin[o];
 #pragma unroll
   for (int ch = 0; ch < 8; ++ch) {
-    const uint4 v = xs[ch];
-    const uint32_t uu[4] = {v.x, v.y, v.z, v.w};
+    uint4 xv[CP];
 #pragma unroll
-    for (int j = 0; j < 4; ++j) {
-      const float2 xv = unpack2(uu[j]);
-      const int c = ch * 8 + j * 2;
+    for (int j = 0; j < CP; ++j) xv[j] = reinterpret_cast<const uint4*>(p.x0 + ((long long)img * plane + pix[j]) * 64)[ch];
+#pragma unroll
+    for (int e = 0; e < 8; ++e) {
+      float xs[CP];
+#pragma unroll
+      for (int j = 0; j < CP; ++j) {
+        const uint32_t w = e < 2 ? xv[j].x : e < 4 ? xv[j].y : e < 6 ? xv[j].z : xv[j].w;
+        const float2 t = unpack2(w);
+        xs[j] = (e & 1) ? t.y : t.x;
+      }
 #pragma unroll
       for (int o4 = 0; o4 < 4; ++o4) {
-        const float4 a = *reinterpret_cast<const float4*>(&wf[c][o4 * 4]);
-        const float4 b = *reinterpret_cast<const float4*>(&wf[c + 1][o4 * 4]);
-        f[o4 * 4 + 0] = fmaf(xv.y, b.x, fmaf(xv.x, a.x, f[o4 * 4 + 0]));
-        f[o4 * 4 + 1] = fmaf(xv.y, b.y, fmaf(xv.x, a.y, f[o4 * 4 + 1]));
-        f[o4 * 4 + 2] = fmaf(xv.y, b.z, fmaf(xv.x, a.z, f[o4 * 4 + 2]));
-        f[o4 * 4 + 3] = fmaf(xv.y, b.w, fmaf(xv.x, a.w, f[o4 * 4 + 3]));
+        const float4 a = *reinterpret_cast<const float4*>(&wf[ch * 8 + e][o4 * 4]);
+#pragma unroll
+        for (int j = 0; j < CP; ++j) {
+          f[j][o4 * 4 + 0] = fmaf(xs[j], a.x, f[j][o4 * 4 + 0]);
+          f[j][o4 * 4 + 1] = fmaf(xs[j], a.y, f[j][o4 * 4 + 1]);
+          f[j][o4 * 4 + 2] = fmaf(xs[j], a.z, f[j][o4 * 4 + 2]);
+          f[j][o4 * 4 + 3] = fmaf(xs[j], a.w, f[j][o4 * 4 + 3]);
+        }
       }
     }
   }
   if (p.unet_feat) {
 #pragma unroll
-    for (int o = 0; o < 16; ++o) p.unet_feat[((long long)img * 16 + o) * plane + pix] = f[o];
+    for (int j = 0; j < CP; ++j)
+      if (pix0 + 128 * j < plane) {
+#pragma unroll
+        for (int o = 0; o < 16; ++o) p.unet_feat[((long long)img * 16 + o) * plane + pix[j]] = f[j][o];
+      }
   }
-  // classification features of this pixel: two 16-byte chunks of the planar layout [img][2][H][W][8]
-  float v[32];
+  // classification features: two 16-byte chunks per pixel of the planar layout [img][2][H][W][8]
+  float v[CP][16];
 #pragma unroll
-  for (int g = 0; g < 2; ++g) {
-    const uint4 cv = *reinterpret_cast<const uint4*>(p.desc_cls + (((long long)img * 2 + g) * plane + pix) * 8);
-    const uint32_t uu[4] = {cv.x, cv.y, cv.z, cv.w};
+  for (int j = 0; j < CP; ++j)
 #pragma unroll
-    for (int j = 0; j < 4; ++j) {
-      const float2 t = unpack2(uu[j]);
-      v[g * 8 + j * 2] = t.x;
-      v[g * 8 + j * 2 + 1] = t.y;
+    for (int g = 0; g < 2; ++g) {
+      const uint4 cv = *reinterpret_cast<const uint4*>(p.desc_cls + (((long long)img * 2 + g) * plane + pix[j]) * 8);
+      const uint32_t uu[4] = {cv.x, cv.y, cv.z, cv.w};
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        const float2 t = unpack2(uu[k]);
+        v[j][g * 8 + k * 2] = t.x;
+        v[j][g * 8 + k * 2 + 1] = t.y;
+      }
     }
-  }
-  float o[16];
+  float o[CP][16];
 #pragma unroll
-  for (int k = 0; k < 16; ++k) o[k] = b2[k];
+  for (int j = 0; j < CP; ++j)
+#pragma unroll
+    for (int k = 0; k < 16; ++k) o[j][k] = b2[k];
   if (p.method == 1) {
     // conv2(relu(conv1(cat(cls, unet))))
+    float h[CP][32];
 #pragma unroll
-    for (int k = 0; k < 16; ++k) v[16 + k] = f[k];
-    float h[32];
+    for (int j = 0; j < CP; ++j)
 #pragma unroll
-    for (int k = 0; k < 32; ++k) h[k] = b1[k];
+      for (int k = 0; k < 32; ++k) h[j][k] = b1[k];
 #pragma unroll
     for (int i = 0; i < 32; ++i) {
 #pragma unroll
       for (int o4 = 0; o4 < 8; ++o4) {
         const float4 a = *reinterpret_cast<const float4*>(&w1[i][o4 * 4]);
-        h[o4 * 4 + 0] = fmaf(v[i], a.x, h[o4 * 4 + 0]);
-        h[o4 * 4 + 1] = fmaf(v[i], a.y, h[o4 * 4 + 1]);
-        h[o4 * 4 + 2] = fmaf(v[i], a.z, h[o4 * 4 + 2]);
-        h[o4 * 4 + 3] = fmaf(v[i], a.w, h[o4 * 4 + 3]);
+#pragma unroll
+        for (int j = 0; j < CP; ++j) {
+          const float vi = i < 16 ? v[j][i & 15] : f[j][i & 15];
+          h[j][o4 * 4 + 0] = fmaf(vi, a.x, h[j][o4 * 4 + 0]);
+          h[j][o4 * 4 + 1] = fmaf(vi, a.y, h[j][o4 * 4 + 1]);
+          h[j][o4 * 4 + 2] = fmaf(vi, a.z, h[j][o4 * 4 + 2]);
+          h[j][o4 * 4 + 3] = fmaf(vi, a.w, h[j][o4 * 4 + 3]);
+        }
       }
     }
 #pragma unroll
     for (int i = 0; i < 32; ++i) {
-      const float hv = fmaxf(h[i], 0.f);
 #pragma unroll
       for (int o4 = 0; o4 < 4; ++o4) {
         const float4 a = *reinterpret_cast<const float4*>(&w2[i][o4 * 4]);
-        o[o4 * 4 + 0] = fmaf(hv, a.x, o[o4 * 4 + 0]);
-        o[o4 * 4 + 1] = fmaf(hv, a.y, o[o4 * 4 + 1]);
-        o[o4 * 4 + 2] = fmaf(hv, a.z, o[o4 * 4 + 2]);
-        o[o4 * 4 + 3] = fmaf(hv, a.w, o[o4 * 4 + 3]);
+#pragma unroll
+        for (int j = 0; j < CP; ++j) {
+          const float hv = fmaxf(h[j][i], 0.f);
+          o[j][o4 * 4 + 0] = fmaf(hv, a.x, o[j][o4 * 4 + 0]);
+          o[j][o4 * 4 + 1] = fmaf(hv, a.y, o[j][o4 * 4 + 1]);
+          o[j][o4 * 4 + 2] = fmaf(hv, a.z, o[j][o4 * 4 + 2]);
+          o[j][o4 * 4 + 3] = fmaf(hv, a.w, o[j][o4 * 4 + 3]);
+        }
       }
     }
   } else {
     // conv2(cls * tanh(unet))
 #pragma unroll
     for (int i = 0; i < 16; ++i) {
-      const float m = v[i] * tanhf(f[i]);
+      float m[CP];
+#pragma unroll
+      for (int j = 0; j < CP; ++j) m[j] = v[j][i] * tanhf(f[j][i]);
 #pragma unroll
       for (int o4 = 0; o4 < 4; ++o4) {
         const float4 a = *reinterpret_cast<const float4*>(&w2[i][o4 * 4]);
-        o[o4 * 4 + 0] = fmaf(m, a.x, o[o4 * 4 + 0]);
-        o[o4 * 4 + 1] = fmaf(m, a.y, o[o4 * 4 + 1]);
-        o[o4 * 4 + 2] = fmaf(m, a.z, o[o4 * 4 + 2]);
-        o[o4 * 4 + 3] = fmaf(m, a.w, o[o4 * 4 + 3]);
+#pragma unroll
+        for (int j = 0; j < CP; ++j) {
+          o[j][o4 * 4 + 0] = fmaf(m[j], a.x, o[j][o4 * 4 + 0]);
+          o[j][o4 * 4 + 1] = fmaf(m[j], a.y, o[j][o4 * 4 + 1]);
+          o[j][o4 * 4 + 2] = fmaf(m[j], a.z, o[j][o4 * 4 + 2]);
+          o[j][o4 * 4 + 3] = fmaf(m[j], a.w, o[j][o4 * 4 + 3]);
+        }
       }
     }
   }
 #pragma unroll
-  for (int g = 0; g < 2; ++g)
-    *reinterpret_cast<uint4*>(p.desc + (((long long)img * 2 + g) * plane + pix) * 8) =
-        make_uint4(pack2(o[g * 8 + 0], o[g * 8 + 1]), pack2(o[g * 8 + 2], o[g * 8 + 3]), pack2(o[g * 8 + 4], o[g * 8 + 5]),
-                   pack2(o[g * 8 + 6], o[g * 8 + 7]));
+  for (int j = 0; j < CP; ++j)
+    if (pix0 + 128 * j < plane) {
+#pragma unroll
+      for (int g = 0; g < 2; ++g)
+        *reinterpret_cast<uint4*>(p.desc + (((long long)img * 2 + g) * plane + pix[j]) * 8) =
+            make_uint4(pack2(o[j][g * 8 + 0], o[j][g * 8 + 1]), pack2(o[j][g * 8 + 2], o[j][g * 8 + 3]),
+                       pack2(o[j][g * 8 + 4], o[j][g * 8 + 5]), pack2(o[j][g * 8 + 6], o[j][g * 8 + 7]));
+    }
 }
 
 inline unsigned blocks_for(long long total, int per) { return (unsigned)((total + per - 1) / per); }
@@ -261,8 +407,18 @@ inline unsigned blocks_for(long long total, int per) { return (unsigned)((total 
 }  // namespace
 
 cudaError_t launch_unet_stem(const UnetStemParams& p, cudaStream_t s) {
-  dim3 grid(blocks_for((long long)p.H * p.W, 64), 2 * p.B);
-  unet_stem_kernel<<<grid, 256, 0, s>>>(p);
+  if (p.W % 4 == 0) {
+    // 32-bit input offsets in the fast kernel
+    if ((long long)p.B * p.H * p.W * 3 >= (1LL << 31)) return cudaErrorInvalidValue;
+    dim3 grid(blocks_for((long long)p.H * p.W, 256), 2 * p.B);
+    if (p.is_u8 && p.is_nhwc) unet_stem_kernel<true, true><<<grid, 256, 0, s>>>(p);
+    else if (p.is_u8) unet_stem_kernel<true, false><<<grid, 256, 0, s>>>(p);
+    else if (p.is_nhwc) unet_stem_kernel<false, true><<<grid, 256, 0, s>>>(p);
+    else unet_stem_kernel<false, false><<<grid, 256, 0, s>>>(p);
+  } else {
+    dim3 grid(blocks_for((long long)p.H * p.W, 64), 2 * p.B);
+    unet_stem_generic_kernel<<<grid, 256, 0, s>>>(p);
+  }
   return cudaGetLastError();
 }
 
@@ -284,7 +440,7 @@ cudaError_t launch_unet_up(const __nv_bfloat16* g, int n, int h, int w, int C, _
 
 cudaError_t launch_unet_combine(const UnetCombineParams& p, cudaStream_t s) {
   if (p.method != 1 && p.method != 2) return cudaErrorInvalidValue;
-  dim3 grid(blocks_for((long long)p.H * p.W, 128), p.n);
+  dim3 grid(blocks_for((long long)p.H * p.W, 128 * CP), p.n);
   unet_combine_kernel<<<grid, 128, 0, s>>>(p);
   return cudaGetLastError();
 }
