@@ -79,16 +79,23 @@ struct Epi {
   float* out2 = nullptr;
 };
 
-bool build_gemm(GemmParams* gp, int* BN, const AView& a, const void* wt, int n_out, int taps, int cin_pad, const Epi& e,
+bool build_gemm(GemmParams* gp, int* BN, const AView& a_in, const void* wt, int n_out, int taps, int cin_pad, const Epi& e,
                 char* err, int errlen) {
   memset(gp, 0, sizeof(*gp));
+  AView a = a_in;
+  const bool halo = taps == 9 && (gemm_halo_mode() & 1);
+  if (halo) {  // gemm.cu HALO: 8 x 16-pixel tiles, one (8+2) x (16+2) halo box per channel chunk
+    a.tw = 8;
+    a.th = 16;
+  }
+  gp->halo = halo ? 1 : 0;
   if (a.tw * a.th != 128 || (a.tw & (a.tw - 1))) {
     snprintf(err, errlen, "tile %dx%d must cover 128 rows with a power-of-two width", a.tw, a.th);
     return false;
   }
   const uint64_t adims[4] = {(uint64_t)a.C, (uint64_t)a.X, (uint64_t)a.Y, (uint64_t)a.N};
   const uint64_t astr[4] = {2, (uint64_t)a.sx * 2, (uint64_t)a.sy * 2, (uint64_t)a.sn * 2};
-  const uint32_t abox[4] = {64, (uint32_t)a.tw, (uint32_t)a.th, 1};
+  const uint32_t abox[4] = {64, (uint32_t)a.tw + (halo ? 2u : 0u), (uint32_t)a.th + (halo ? 2u : 0u), 1};
   if (!make_tmap_bf16(&gp->tmA, a.p, 4, adims, astr, abox, err, errlen)) return false;
   const bool tail = (e.flags & GEMM_TAIL) != 0;
   *BN = (!tail && n_out % 256 == 0) ? 256 : 128;
@@ -1228,6 +1235,10 @@ int ufm_debug_flag(int which, int value) {
   }
   if (which == 2) {
     set_attention_poly(value);
+    return 0;
+  }
+  if (which == 3) {
+    set_gemm_halo_mode(value);
     return 0;
   }
   return 1;

@@ -30,17 +30,31 @@ constexpr int kThreads = 128 + kEpiWarps * 32;
 // CTAS = 2: a CTA pair (cluster of 2, tcgen05 cta_group::2) computes a 256 x BN tile; each CTA stages its own 128 rows
 // of A and only HALF of the B tile, which cuts the L2 -> SM operand traffic per FLOP by a third (the single-CTA
 // 128 x 256 tile needs 96 B/clk/SM at the MMA floor; the chip-wide L2 cap is about 43 B/clk/SM).
-template <int BN, int CTAS>
+//
+// HALO (3x3 convs): the A operand of all 9 taps comes from ONE resident (8+2) x (16+2)-pixel x 64-channel halo tile per
+// channel chunk instead of 9 shifted 8 x 16 boxes: the tile's 128 rows are 16 image rows of 8 pixels, one 128B-swizzle
+// atom (8 rows x 128 B) per image row, so the operand of tap (dy, dx) is the same smem with the descriptor start moved
+// by ((dy+1)*10 + dx+1) * 128 bytes and an atom stride (SBO) of one halo row, 10 * 128 bytes.  The swizzle XOR is a
+// function of the shared-memory address bits, which TMA (writing) and the MMA unit (reading) share, so a start that is
+// only 128-byte aligned reads back consistently.  L2 -> SM operand traffic per (tile, chunk): 23 KB + 9 B tiles instead
+// of 9 x (16 KB + B tile); the A ring and the B ring are then independent pipelines.
+constexpr int HALO_TW = 8, HALO_TH = 16;
+constexpr int HALO_ROW_BYTES = (HALO_TW + 2) * 128;
+constexpr int HALO_TX_BYTES = (HALO_TH + 2) * HALO_ROW_BYTES;  // 23040
+
+template <int BN, int CTAS, bool HALO>
 struct Cfg {
-  static constexpr int A_BYTES = BM * BK * 2;
+  static constexpr int A_BYTES = HALO ? 24576 : BM * BK * 2;    // halo tile padded to the 1024-byte swizzle period
+  static constexpr int A_TX = HALO ? HALO_TX_BYTES : BM * BK * 2;
   static constexpr int B_ROWS = BN / CTAS;
   static constexpr int B_BYTES = B_ROWS * BK * 2;
   static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
-  static constexpr int STAGES = (STAGE_BYTES == 49152) ? 3 : 5;
+  static constexpr int STAGES = HALO ? (B_BYTES == 32768 ? 2 : 5) : (STAGE_BYTES == 49152) ? 3 : 5;  // B (and A) ring
+  static constexpr int A_STAGES = HALO ? 3 : STAGES;  // a halo lasts 36 MMAs: three in flight cover the TMA latency
   static constexpr int BAR_BYTES = 512;
   // epilogue slabs: 8 warps x 2 x (32 rows x 128 B); TAIL mode reuses them as [acc][half][row][kTailMax] floats
   static constexpr int SCRATCH_BYTES = kEpiWarps * 2 * 4096;
-  static constexpr int SMEM_BYTES = 1024 + STAGES * STAGE_BYTES + BAR_BYTES + SCRATCH_BYTES;
+  static constexpr int SMEM_BYTES = 1024 + A_STAGES * A_BYTES + STAGES * B_BYTES + BAR_BYTES + SCRATCH_BYTES;
   static constexpr int TMEM_COLS = 2 * BN;
 };
 
@@ -61,23 +75,25 @@ __device__ __forceinline__ float gelu_erf(float x) {
   return fmaf(-ax * 0.3989422804014327f, pl * e, fmaxf(x, 0.f));
 }
 
-template <int BN, int CTAS>
+template <int BN, int CTAS, bool HALO>
 __global__ void __launch_bounds__(kThreads, 1) gemm_kernel(const __grid_constant__ GemmParams p) {
-  using C = Cfg<BN, CTAS>;
+  using C = Cfg<BN, CTAS, HALO>;
   const uint32_t cta_rank = (CTAS == 2) ? cluster_ctarank() : 0u;
   const int unit = blockIdx.x / CTAS;          // scheduling unit: a CTA (CTAS 1) or a CTA pair (CTAS 2)
   const int num_units = gridDim.x / CTAS;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* sA = smem;
-  uint8_t* sB = smem + C::STAGES * C::A_BYTES;
-  uint8_t* epi_smem = smem + C::STAGES * C::STAGE_BYTES;  // 8 warps x 2 x 4 KB TMA slabs (1024-byte aligned)
+  uint8_t* sB = smem + C::A_STAGES * C::A_BYTES;
+  uint8_t* epi_smem = sB + C::STAGES * C::B_BYTES;  // 8 warps x 2 x 4 KB TMA slabs (1024-byte aligned)
   uint64_t* full = reinterpret_cast<uint64_t*>(epi_smem + C::SCRATCH_BYTES);
   uint64_t* empty = full + C::STAGES;
   uint64_t* tfull = empty + C::STAGES;
   uint64_t* tempty = tfull + 2;
   uint64_t* resbar = tempty + 2;  // [8 warps][2 slabs] residual-slab "full" barriers
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(resbar + 2 * kEpiWarps);
+  uint64_t* afull = resbar + 2 * kEpiWarps;  // HALO: the A ring's own barriers (full/empty then belong to the B ring)
+  uint64_t* aempty = afull + 3;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(aempty + 3);
   float* scratch = reinterpret_cast<float*>(epi_smem);  // TAIL mode: [acc][half][row][4] floats
 
   const int warp = threadIdx.x >> 5;
@@ -99,6 +115,10 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_kernel(const __grid_constant
       mbar_init(&tempty[i], kEpiWarps * CTAS);  // pair: the leader's barrier also collects the peer's epilogue warps
     }
     for (int i = 0; i < 2 * kEpiWarps; ++i) mbar_init(&resbar[i], 1);
+    for (int i = 0; i < 3; ++i) {
+      mbar_init(&afull[i], 1);
+      mbar_init(&aempty[i], 1);
+    }
     fence_barrier_init();
   }
   if (warp == 2) {
@@ -120,8 +140,8 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_kernel(const __grid_constant
 
   if (warp == 0) {
     if (lane == 0) {
-      int stage = 0;
-      uint32_t phase = 0;
+      int stage = 0, astage = 0;
+      uint32_t phase = 0, aphase = 0;
       for (int tile = unit; tile < total_tiles; tile += num_units) {
         const int tn = tile % p.tiles_n;
         const int tm = (tile / p.tiles_n) * CTAS + (int)cta_rank;
@@ -129,6 +149,39 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_kernel(const __grid_constant
         const int ty = (tm / p.tiles_x) % p.tiles_y;
         const int img = tm / (p.tiles_x * p.tiles_y);
         const int x0 = tx * p.tw, y0 = ty * p.th, n0 = tn * BN + (int)cta_rank * C::B_ROWS;
+        if constexpr (HALO) {
+          for (int cc = 0; cc < p.cchunks; ++cc) {
+            mbar_wait(&aempty[astage], aphase ^ 1);
+            if constexpr (CTAS == 2) {
+              if (cta_rank == 0) mbar_expect_tx(&afull[astage], 2 * C::A_TX);
+              tma2_load_4d(sA + astage * C::A_BYTES, &p.tmA, smem_u32(&afull[astage]) & kPeerBitMask, cc * BK, x0 - 1,
+                           y0 - 1, img);
+            } else {
+              mbar_expect_tx(&afull[astage], C::A_TX);
+              tma_load_4d(sA + astage * C::A_BYTES, &p.tmA, &afull[astage], cc * BK, x0 - 1, y0 - 1, img);
+            }
+            if (++astage == C::A_STAGES) {
+              astage = 0;
+              aphase ^= 1;
+            }
+            for (int tap = 0; tap < 9; ++tap) {
+              mbar_wait(&empty[stage], phase ^ 1);
+              if constexpr (CTAS == 2) {
+                if (cta_rank == 0) mbar_expect_tx(&full[stage], 2 * C::B_BYTES);
+                tma2_load_2d(sB + stage * C::B_BYTES, &p.tmB, smem_u32(&full[stage]) & kPeerBitMask,
+                             tap * p.cin_pad + cc * BK, n0);
+              } else {
+                mbar_expect_tx(&full[stage], C::B_BYTES);
+                tma_load_2d(sB + stage * C::B_BYTES, &p.tmB, &full[stage], tap * p.cin_pad + cc * BK, n0);
+              }
+              if (++stage == C::STAGES) {
+                stage = 0;
+                phase ^= 1;
+              }
+            }
+          }
+          continue;
+        }
         for (int k = 0; k < k_iters; ++k) {
           const int tap = k / p.cchunks;
           const int cc = k - tap * p.cchunks;
@@ -140,12 +193,12 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_kernel(const __grid_constant
           mbar_wait(&empty[stage], phase ^ 1);
           if constexpr (CTAS == 2) {
             // both CTAs' boxes complete on the LEADER's full barrier, which expects the bytes of the whole pair
-            if (cta_rank == 0) mbar_expect_tx(&full[stage], 2 * C::STAGE_BYTES);
+            if (cta_rank == 0) mbar_expect_tx(&full[stage], 2 * (C::A_TX + C::B_BYTES));
             const uint32_t lbar = smem_u32(&full[stage]) & kPeerBitMask;
             tma2_load_4d(sA + stage * C::A_BYTES, &p.tmA, lbar, cc * BK, x0 + dx, y0 + dy, img);
             tma2_load_2d(sB + stage * C::B_BYTES, &p.tmB, lbar, tap * p.cin_pad + cc * BK, n0);
           } else {
-            mbar_expect_tx(&full[stage], C::STAGE_BYTES);
+            mbar_expect_tx(&full[stage], C::A_TX + C::B_BYTES);
             tma_load_4d(sA + stage * C::A_BYTES, &p.tmA, &full[stage], cc * BK, x0 + dx, y0 + dy, img);
             tma_load_2d(sB + stage * C::B_BYTES, &p.tmB, &full[stage], tap * p.cin_pad + cc * BK, n0);
           }
@@ -157,40 +210,96 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_kernel(const __grid_constant
       }
     }
   } else if (warp == 1) {
-    if (lane == 0 && cta_rank == 0) {
+    // The whole warp walks the loops (uniform control flow keeps the operand descriptors in uniform registers); one
+    // elected lane issues the MMAs and commits.  With `if (lane == 0)` around the loop instead, every tcgen05.mma cost
+    // an ELECT / R2UR.BROADCAST / branch sequence and ~25 dependent uniform-datapath instructions: ~600 clk per group of
+    // four MMAs, more than the 256-512 clk the tensor pipe needs for them.
+    if (cta_rank == 0) {
       constexpr uint32_t idesc = umma_idesc_bf16(BM * CTAS, BN, 0, 0);
+      constexpr uint32_t hi_b = umma_desc_hi_sw128(1024);
+      constexpr uint32_t hi_a = umma_desc_hi_sw128(HALO ? HALO_ROW_BYTES : 1024);
+      const uint32_t a_lo0 = umma_desc_lo(smem_u32(sA));
+      const uint32_t b_lo0 = umma_desc_lo(smem_u32(sB));
+      const bool leader = elect_one();
       int stage = 0;
       uint32_t phase = 0;
-      int acc = 0;
-      uint32_t accphase = 0;
+      int acc = 0, astage = 0;
+      uint32_t accphase = 0, aphase = 0;
       for (int tile = unit; tile < total_tiles; tile += num_units) {
         mbar_wait(&tempty[acc], accphase ^ 1);
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + acc * BN;
-        for (int k = 0; k < k_iters; ++k) {
-          mbar_wait(&full[stage], phase);
-          tc_fence_after();
-          const uint32_t a_addr = smem_u32(sA + stage * C::A_BYTES);
-          const uint32_t b_addr = smem_u32(sB + stage * C::B_BYTES);
+        if constexpr (HALO) {
+          for (int cc = 0; cc < p.cchunks; ++cc) {
+            mbar_wait(&afull[astage], aphase);
+            const uint32_t halo_lo = a_lo0 + astage * (C::A_BYTES >> 4);
+#pragma unroll 1
+            for (int ty3 = 0; ty3 < 3; ++ty3) {
 #pragma unroll
-          for (int kk = 0; kk < BK / 16; ++kk) {
-            if constexpr (CTAS == 2)
-              umma2_ss(d_tmem, umma_desc_sw128(a_addr + kk * 32), umma_desc_sw128(b_addr + kk * 32), idesc,
-                       (k | kk) != 0 ? 1u : 0u);
-            else
-              umma_ss(d_tmem, umma_desc_sw128(a_addr + kk * 32), umma_desc_sw128(b_addr + kk * 32), idesc,
-                      (k | kk) != 0 ? 1u : 0u);
+              for (int tx3 = 0; tx3 < 3; ++tx3) {
+                mbar_wait(&full[stage], phase);
+                tc_fence_after();
+                if (leader) {
+                  const uint32_t a_lo = halo_lo + (ty3 * (HALO_TW + 2) + tx3) * (128 >> 4);
+                  const uint32_t b_lo = b_lo0 + stage * (C::B_BYTES >> 4);
+#pragma unroll
+                  for (int kk = 0; kk < BK / 16; ++kk) {
+                    const uint32_t accum = (cc | ty3 | tx3 | kk) != 0 ? 1u : 0u;
+                    if constexpr (CTAS == 2)
+                      umma2_ss(d_tmem, umma_desc_words(a_lo + kk * 2, hi_a), umma_desc_words(b_lo + kk * 2, hi_b), idesc, accum);
+                    else
+                      umma_ss(d_tmem, umma_desc_words(a_lo + kk * 2, hi_a), umma_desc_words(b_lo + kk * 2, hi_b), idesc, accum);
+                  }
+                  if constexpr (CTAS == 2) umma2_commit_mc(&empty[stage]);
+                  else umma_commit(&empty[stage]);
+                }
+                if (++stage == C::STAGES) {
+                  stage = 0;
+                  phase ^= 1;
+                }
+              }
+            }
+            if (leader) {
+              if constexpr (CTAS == 2) {
+                umma2_commit_mc(&aempty[astage]);
+                if (cc == p.cchunks - 1) umma2_commit_mc(&tfull[acc]);
+              } else {
+                umma_commit(&aempty[astage]);
+                if (cc == p.cchunks - 1) umma_commit(&tfull[acc]);
+              }
+            }
+            if (++astage == C::A_STAGES) {
+              astage = 0;
+              aphase ^= 1;
+            }
           }
-          if constexpr (CTAS == 2) {
-            umma2_commit_mc(&empty[stage]);
-            if (k == k_iters - 1) umma2_commit_mc(&tfull[acc]);
-          } else {
-            umma_commit(&empty[stage]);
-            if (k == k_iters - 1) umma_commit(&tfull[acc]);
-          }
-          if (++stage == C::STAGES) {
-            stage = 0;
-            phase ^= 1;
+        } else {
+          for (int k = 0; k < k_iters; ++k) {
+            mbar_wait(&full[stage], phase);
+            tc_fence_after();
+            if (leader) {
+              const uint32_t a_lo = a_lo0 + stage * (C::A_BYTES >> 4);
+              const uint32_t b_lo = b_lo0 + stage * (C::B_BYTES >> 4);
+#pragma unroll
+              for (int kk = 0; kk < BK / 16; ++kk) {
+                const uint32_t accum = (k | kk) != 0 ? 1u : 0u;
+                if constexpr (CTAS == 2)
+                  umma2_ss(d_tmem, umma_desc_words(a_lo + kk * 2, hi_a), umma_desc_words(b_lo + kk * 2, hi_b), idesc, accum);
+                else
+                  umma_ss(d_tmem, umma_desc_words(a_lo + kk * 2, hi_a), umma_desc_words(b_lo + kk * 2, hi_b), idesc, accum);
+              }
+              if constexpr (CTAS == 2) {
+                umma2_commit_mc(&empty[stage]);
+                if (k == k_iters - 1) umma2_commit_mc(&tfull[acc]);
+              } else {
+                umma_commit(&empty[stage]);
+                if (k == k_iters - 1) umma_commit(&tfull[acc]);
+              }
+            }
+            if (++stage == C::STAGES) {
+              stage = 0;
+              phase ^= 1;
+            }
           }
         }
         acc ^= 1;
@@ -544,17 +653,17 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_kernel(const __grid_constant
 int g_gemm_epi = 1;   // ufm_debug_flag 0: 1 = TMA-store epilogues where eligible (default), 0 = always the direct epilogue
 int g_gemm_pair = 1;  // ufm_debug_flag 1 (bit 1 measured neutral on the N = 128 convs: 808 vs 795 TFLOP/s): bit 0 = CTA-pair (cta_group::2) tiles for BN = 256, bit 1 = also for BN = 128
 
-template <int BN, int CTAS>
+template <int BN, int CTAS, bool HALO>
 static cudaError_t launch_one(const GemmParams& p, int grid, cudaStream_t stream) {
-  using C = Cfg<BN, CTAS>;
+  using C = Cfg<BN, CTAS, HALO>;
   static bool attr = false;
   if (!attr) {
-    cudaError_t err = cudaFuncSetAttribute(gemm_kernel<BN, CTAS>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM_BYTES);
+    cudaError_t err = cudaFuncSetAttribute(gemm_kernel<BN, CTAS, HALO>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM_BYTES);
     if (err != cudaSuccess) return err;
     attr = true;
   }
   if (CTAS == 1) {
-    gemm_kernel<BN, CTAS><<<grid, kThreads, C::SMEM_BYTES, stream>>>(p);
+    gemm_kernel<BN, CTAS, HALO><<<grid, kThreads, C::SMEM_BYTES, stream>>>(p);
     return cudaGetLastError();
   }
   cudaLaunchConfig_t cfg = {};
@@ -569,7 +678,7 @@ static cudaError_t launch_one(const GemmParams& p, int grid, cudaStream_t stream
   at[0].val.clusterDim.z = 1;
   cfg.attrs = at;
   cfg.numAttrs = 1;
-  return cudaLaunchKernelEx(&cfg, gemm_kernel<BN, CTAS>, p);
+  return cudaLaunchKernelEx(&cfg, gemm_kernel<BN, CTAS, HALO>, p);
 }
 
 }  // namespace
@@ -577,6 +686,11 @@ static cudaError_t launch_one(const GemmParams& p, int grid, cudaStream_t stream
 void set_gemm_epilogue_variant(int v) { g_gemm_epi = v; }
 int gemm_epilogue_variant() { return g_gemm_epi; }
 void set_gemm_pair_mode(int v) { g_gemm_pair = v; }
+// ufm_debug_flag 3: 1 = halo-resident A operand for the 3x3 convs.  (Bring-up note: the operand descriptors must NOT set
+// the base-offset field for the 128-byte-aligned tap starts; with it set every tap but the centre one reads garbage.)
+int g_gemm_halo = 1;
+void set_gemm_halo_mode(int v) { g_gemm_halo = v; }
+int gemm_halo_mode() { return g_gemm_halo; }
 int gemm_pair_mode() { return g_gemm_pair; }
 
 cudaError_t launch_gemm(const GemmParams& p, int BN, int num_sms, cudaStream_t stream) {
@@ -585,13 +699,21 @@ cudaError_t launch_gemm(const GemmParams& p, int BN, int num_sms, cudaStream_t s
   const int total = ((tiles_m1 + ctas - 1) / ctas) * p.tiles_n;
   if (total <= 0) return cudaSuccess;
   int grid = total * ctas < num_sms ? total * ctas : num_sms / ctas * ctas;
-  if (ctas == 2) {
-    if (BN == 256) return launch_one<256, 2>(p, grid, stream);
-    if (BN == 128) return launch_one<128, 2>(p, grid, stream);
+  if (p.halo) {
+    if (p.taps != 9 || p.tw != HALO_TW || p.th != HALO_TH) return cudaErrorInvalidValue;
+    if (ctas == 2 && BN == 256) return launch_one<256, 2, true>(p, grid, stream);
+    if (ctas == 2 && BN == 128) return launch_one<128, 2, true>(p, grid, stream);
+    if (BN == 256) return launch_one<256, 1, true>(p, grid, stream);
+    if (BN == 128) return launch_one<128, 1, true>(p, grid, stream);
     return cudaErrorInvalidValue;
   }
-  if (BN == 256) return launch_one<256, 1>(p, grid, stream);
-  if (BN == 128) return launch_one<128, 1>(p, grid, stream);
+  if (ctas == 2) {
+    if (BN == 256) return launch_one<256, 2, false>(p, grid, stream);
+    if (BN == 128) return launch_one<128, 2, false>(p, grid, stream);
+    return cudaErrorInvalidValue;
+  }
+  if (BN == 256) return launch_one<256, 1, false>(p, grid, stream);
+  if (BN == 128) return launch_one<128, 1, false>(p, grid, stream);
   return cudaErrorInvalidValue;
 }
 

@@ -54,6 +54,7 @@ struct alignas(64) GemmParams {
   int tw, th;            // A box extents, tw*th == 128, tw a power of two
   int tw_log2;
   int ctas;              // 1, or 2 = CTA-pair tiles (tmB box is then BN/2 rows)
+  int halo;              // 1 = 3x3 conv with the halo-resident A operand: tw x th = 8 x 16, tmA box (64, 10, 18, 1)
   int X, Y, Nimg;        // logical output extents per image
   int tiles_x, tiles_y;  // ceil(X/tw), ceil(Y/th)
   int N;                 // output channels (multiple of 32, or anything in TAIL mode with N <= 128)
@@ -87,6 +88,8 @@ void set_gemm_epilogue_variant(int v);  // tuning hook: 1 = TMA-store epilogues 
 int gemm_epilogue_variant();
 void set_gemm_pair_mode(int v);         // tuning hook: 1 = CTA-pair (cta_group::2) tiles where BN = 256 (default)
 int gemm_pair_mode();
+void set_gemm_halo_mode(int v);         // tuning hook: bit 0 = halo-resident A operand for the 3x3 convs (default on)
+int gemm_halo_mode();
 
 // ------------------------------------------------------------------------------------------------
 // Flash-style attention forward, head_dim 64, non-causal: O = softmax(Q K^T * scale) V per (sequence, head).
