@@ -363,14 +363,18 @@ __global__ void __launch_bounds__(kThreads, 2) attn_kernel(const __grid_constant
         if (ck.t < n_my) load_k(ck);
         load_v(cv);
       }
-    } else if (warp == 1 && lane == 0) {
+    } else if (warp == 1) {
       // ---------------------------------------------------------------- MMA issuer
+      // The whole warp walks the loop (uniform control flow keeps descriptors in uniform registers, see gemm.cu); one
+      // elected lane issues the MMAs and the commits.
       constexpr uint32_t idesc_s128 = umma_idesc_bf16(128, 128, 0, 0);
       constexpr uint32_t idesc_s64 = umma_idesc_bf16(128, 64, 0, 0);
       constexpr uint32_t idesc_pv = umma_idesc_bf16(128, 64, 0, 1);  // B = V, MN-major
-      const uint32_t q_addr = smem_u32(smem + OFF_Q);
-      const uint32_t k_addr = smem_u32(smem + OFF_K);
-      const uint32_t v_addr = smem_u32(smem + OFF_V);
+      constexpr uint32_t hi = umma_desc_hi_sw128(1024);
+      const uint32_t q_lo0 = umma_desc_lo(smem_u32(smem + OFF_Q));
+      const uint32_t k_lo0 = umma_desc_lo(smem_u32(smem + OFF_K));
+      const uint32_t v_lo0 = umma_desc_lo(smem_u32(smem + OFF_V));
+      const bool leader = elect_one();
       const uint32_t G = (uint32_t)n_my * (uint32_t)n_kv;
       uint32_t gs = 0;       // next S step to issue
       int js = 0, ts = 0;    // its step-in-tile / tile index
@@ -381,14 +385,16 @@ __global__ void __launch_bounds__(kThreads, 2) attn_kernel(const __grid_constant
         if (gs > 0) mbar_wait(&b->s_free, (gs - 1) & 1);  // S_{g-1} is in registers: its TMEM columns may be overwritten
         tc_fence_after();
         const bool last = js == n_kv - 1;
-        const uint32_t idesc = (last && tail64) ? idesc_s64 : idesc_s128;
+        if (leader) {
+          const uint32_t idesc = (last && tail64) ? idesc_s64 : idesc_s128;
+          const uint32_t q_lo = q_lo0 + qs * (TILE_BYTES >> 4), k_lo = k_lo0 + ks * (TILE_BYTES >> 4);
 #pragma unroll
-        for (int kk = 0; kk < 4; ++kk)
-          umma_ss(tmem_base + TM_S, umma_desc_sw128(q_addr + qs * TILE_BYTES + kk * 32),
-                  umma_desc_sw128(k_addr + ks * TILE_BYTES + kk * 32), idesc, kk != 0);
-        umma_commit(&b->s_full);
-        umma_commit(&b->k_empty[ks]);
-        if (last) umma_commit(&b->q_free[qs]);
+          for (int kk = 0; kk < 4; ++kk)
+            umma_ss(tmem_base + TM_S, umma_desc_words(q_lo + kk * 2, hi), umma_desc_words(k_lo + kk * 2, hi), idesc, kk != 0);
+          umma_commit(&b->s_full);
+          umma_commit(&b->k_empty[ks]);
+          if (last) umma_commit(&b->q_free[qs]);
+        }
         ++gs;
         if (++js == n_kv) {
           js = 0;
@@ -403,12 +409,22 @@ __global__ void __launch_bounds__(kThreads, 2) attn_kernel(const __grid_constant
         mbar_wait(&b->v_full[vs], (g / V_STAGES) & 1);
         mbar_wait(&b->p_full, g & 1);
         tc_fence_after();
-        const int nks = (jp == n_kv - 1 && tail64) ? 4 : 8;
-        for (int ks = 0; ks < nks; ++ks)
-          umma_ts(tmem_base + TM_O, tmem_base + TM_P + ks * 8, umma_desc_sw128(v_addr + vs * TILE_BYTES + ks * 2048),
-                  idesc_pv, (jp | ks) != 0);
-        umma_commit(&b->o_done);
-        umma_commit(&b->v_empty[vs]);
+        if (leader) {
+          const uint32_t v_lo = v_lo0 + vs * (TILE_BYTES >> 4);
+          if (jp == n_kv - 1 && tail64) {
+#pragma unroll
+            for (int ks = 0; ks < 4; ++ks)
+              umma_ts(tmem_base + TM_O, tmem_base + TM_P + ks * 8, umma_desc_words(v_lo + ks * (2048 >> 4), hi), idesc_pv,
+                      (jp | ks) != 0);
+          } else {
+#pragma unroll
+            for (int ks = 0; ks < 8; ++ks)
+              umma_ts(tmem_base + TM_O, tmem_base + TM_P + ks * 8, umma_desc_words(v_lo + ks * (2048 >> 4), hi), idesc_pv,
+                      (jp | ks) != 0);
+          }
+          umma_commit(&b->o_done);
+          umma_commit(&b->v_empty[vs]);
+        }
         if (++jp == n_kv) jp = 0;
       }
     }

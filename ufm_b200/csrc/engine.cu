@@ -98,7 +98,7 @@ bool build_gemm(GemmParams* gp, int* BN, const AView& a_in, const void* wt, int 
   const uint32_t abox[4] = {64, (uint32_t)a.tw + (halo ? 2u : 0u), (uint32_t)a.th + (halo ? 2u : 0u), 1};
   if (!make_tmap_bf16(&gp->tmA, a.p, 4, adims, astr, abox, err, errlen)) return false;
   const bool tail = (e.flags & GEMM_TAIL) != 0;
-  *BN = (!tail && n_out % 256 == 0) ? 256 : 128;
+  *BN = (!tail && n_out % 256 == 0) ? 256 : (halo && !tail && n_out <= 64) ? 64 : 128;
   const uint64_t bdims[2] = {(uint64_t)taps * cin_pad, (uint64_t)n_out};
   const uint64_t bstr[2] = {2, (uint64_t)taps * cin_pad * 2};
   gp->ctas = ((*BN == 256 && (gemm_pair_mode() & 1)) || (*BN == 128 && (gemm_pair_mode() & 2))) ? 2 : 1;

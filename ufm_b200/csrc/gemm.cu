@@ -49,7 +49,7 @@ struct Cfg {
   static constexpr int B_ROWS = BN / CTAS;
   static constexpr int B_BYTES = B_ROWS * BK * 2;
   static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
-  static constexpr int STAGES = HALO ? (B_BYTES == 32768 ? 2 : 5) : (STAGE_BYTES == 49152) ? 3 : 5;  // B (and A) ring
+  static constexpr int STAGES = HALO ? (B_BYTES == 32768 ? 2 : B_BYTES == 8192 ? 9 : 5) : (STAGE_BYTES == 49152) ? 3 : 5;  // B (and A) ring
   static constexpr int A_STAGES = HALO ? 3 : STAGES;  // a halo lasts 36 MMAs: three in flight cover the TMA latency
   static constexpr int BAR_BYTES = 512;
   // epilogue slabs: 8 warps x 2 x (32 rows x 128 B); TAIL mode reuses them as [acc][half][row][kTailMax] floats
@@ -310,7 +310,9 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_kernel(const __grid_constant
     const int e = warp - 4;
     const int q = warp & 3;  // TMEM lane quadrant this warp may access
     const int half = e >> 2;
-    constexpr int HALF_COLS = BN / 2;
+    // BN = 64 (thin convs): the four half-0 warps take all 64 columns, the half-1 warps only keep the barrier protocol
+    constexpr int HALF_COLS = BN == 64 ? 64 : BN / 2;
+    const int Nlim = (BN == 64 && half == 1) ? 0 : p.N;  // column bound of this warp
     const bool tail = (p.flags & GEMM_TAIL) != 0;
     const int emode = p.epi_mode;
     // TMA epilogues: two 4 KB slabs per warp = 32 rows x 128 bytes in the 128B-swizzle pattern (16-byte chunk j of row r
@@ -341,7 +343,7 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_kernel(const __grid_constant
         // ---- fp32 output (+ optional fp32 residual) through TMA: 32-column slabs -------------------------------------
         const int wx = tx * p.tw + ((32 * q) & (p.tw - 1));
         const int wy = ty * p.th + ((32 * q) >> p.tw_log2);
-        int nch = (p.N - c0 + 31) >> 5;
+        int nch = (Nlim - c0 + 31) >> 5;
         nch = nch < 0 ? 0 : (nch > HALF_COLS / 32 ? HALF_COLS / 32 : nch);
         const bool has_res = p.res1 != nullptr;
         if (lane == 0) {
@@ -424,7 +426,7 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_kernel(const __grid_constant
         // ---- bf16 output through TMA: 64-column slabs ----------------------------------------------------------------
         const int wx = tx * p.tw + ((32 * q) & (p.tw - 1));
         const int wy = ty * p.th + ((32 * q) >> p.tw_log2);
-        int nch = (p.N - c0 + 63) >> 6;
+        int nch = (Nlim - c0 + 63) >> 6;
         nch = nch < 0 ? 0 : (nch > HALF_COLS / 64 ? HALF_COLS / 64 : nch);
         if (lane == 0) bulk_wait_read<0>();
         __syncwarp();
@@ -440,7 +442,7 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_kernel(const __grid_constant
             uint32_t vr[32];
             tmem_ld32(acc_addr + c * 64 + h2 * 32, vr);
             tmem_ld_wait();
-            if (gcol + h2 * 32 < p.N) {
+            if (gcol + h2 * 32 < Nlim) {
 #pragma unroll
               for (int j = 0; j < 4; ++j) {
                 float v[8];
@@ -501,12 +503,12 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_kernel(const __grid_constant
           if (p.res1) {
 #pragma unroll
             for (int c = 0; c < HALF_COLS / 32; ++c)
-              if (pc0 + c * 32 < p.N) prefetch_l2(p.res1 + off + pc0 + c * 32);
+              if (pc0 + c * 32 < Nlim) prefetch_l2(p.res1 + off + pc0 + c * 32);
           }
           if (p.res2) {
 #pragma unroll
             for (int c = 0; c < HALF_COLS / 32; ++c)
-              if (pc0 + c * 32 < p.N) prefetch_l2(p.res2 + off2 + pc0 + c * 32);
+              if (pc0 + c * 32 < Nlim) prefetch_l2(p.res2 + off2 + pc0 + c * 32);
           }
         }
         mbar_wait(&tfull[acc], accphase);
@@ -516,7 +518,7 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_kernel(const __grid_constant
         for (int c = 0; c < HALF_COLS / 32; ++c) {
           const int col0 = half * HALF_COLS + c * 32;
           const int gcol = n0 + col0;
-          if (gcol >= p.N) break;
+          if (gcol >= Nlim) break;
           uint32_t vr[32];
           __syncwarp();  // tcgen05.ld is .sync.aligned: reconverge after the per-row predicated body
           // issue the residual loads first so that their latency overlaps the TMEM read
@@ -705,6 +707,7 @@ cudaError_t launch_gemm(const GemmParams& p, int BN, int num_sms, cudaStream_t s
     if (ctas == 2 && BN == 128) return launch_one<128, 2, true>(p, grid, stream);
     if (BN == 256) return launch_one<256, 1, true>(p, grid, stream);
     if (BN == 128) return launch_one<128, 1, true>(p, grid, stream);
+    if (BN == 64) return launch_one<64, 1, true>(p, grid, stream);
     return cudaErrorInvalidValue;
   }
   if (ctas == 2) {
