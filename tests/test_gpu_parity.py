@@ -240,6 +240,11 @@ def test_batch_chunking_and_determinism():
     assert torch.equal(a, b)
     one = model.predict_correspondences_batched(src[4:5].cuda(), tgt[4:5].cuda()).flow.flow_output
     assert torch.equal(one, a[4:5])  # pairs are independent: batching must not change a pair's result
+    # host tensors (pageable and pinned) take the ufm_forward_host path: same bits, results on the host
+    for hs, ht in ((src, tgt), (src.pin_memory(), tgt.pin_memory())):
+        o = model.predict_correspondences_batched(hs, ht)
+        assert o.flow.flow_output.device.type == "cpu" and o.covisibility.mask.device.type == "cpu"
+        assert torch.equal(o.flow.flow_output, a.cpu())
 
 
 @pytest.mark.parametrize("name", ["tiny_base", "ufm_base_assumed"])

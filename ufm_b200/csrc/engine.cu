@@ -202,6 +202,11 @@ struct ufm_engine {
   std::map<std::string, Tensor> buf;    // workspace
   std::map<std::string, Tensor> stage;  // views of the last forward (not owned)
   cudaStream_t st = nullptr;
+  // ufm_forward_host: result copies run on their own stream as soon as each output is final (flow after the flow head
+  // or the refinement, covisibility after the uncertainty head), under the rest of the pass
+  cudaStream_t copy_st = nullptr;
+  cudaEvent_t ev_flow = nullptr, ev_cov = nullptr;
+  bool mark_outputs = false;
 
   // ---- per-kernel-family timing (CUDA events on the launching stream; read by bench.py for the roofline) ----
   bool profile = false;
@@ -834,6 +839,7 @@ int ufm_engine::forward(const void* src, const void* tgt, int pairs, int in_dtyp
   set_stage("dpt1", B<bf16>("dpt1"), UFM_BF16, {Bp, H8, W8, c.dpt_feature_dim});
   set_stage("head1_raw", B<float>("head1_raw"), UFM_F32, {Bp, c.flow_out_ch, c.img_h, c.img_w});
   set_stage("flow_reg", flow_reg, UFM_F32, {Bp, 2, c.img_h, c.img_w});
+  if (mark_outputs && !c.refine) cudaEventRecord(ev_flow, st);
   if (c.unc_out_ch > 0) {
     float* cov = covis_out ? covis_out : B<float>("covis");
     if (c.unc_n_adaptors == 0) {
@@ -873,6 +879,7 @@ int ufm_engine::forward(const void* src, const void* tgt, int pairs, int in_dtyp
     }
     set_stage("dptu", B<bf16>("dptu"), UFM_BF16, {Bp, H8, W8, c.dpt_feature_dim});
     set_stage("headu_raw", B<float>("headu_raw"), UFM_F32, {Bp, c.unc_out_ch, c.img_h, c.img_w});
+    if (mark_outputs) cudaEventRecord(ev_cov, st);
   }
   // ---- Refine: classification head + local refinement (ufm.py:954-991) ----
   if (c.refine) {
@@ -922,6 +929,7 @@ int ufm_engine::forward(const void* src, const void* tgt, int pairs, int in_dtyp
       set_stage("residual", B<float>("residual"), UFM_F32, {Bp, 2, c.img_h, c.img_w});
       set_stage("log_softmax", B<float>("log_softmax"), UFM_F32, {Bp, c.img_h, c.img_w, 25});
     }
+    if (mark_outputs) cudaEventRecord(ev_flow, st);
   }
   return 0;
 }
@@ -996,6 +1004,11 @@ void ufm_destroy(ufm_engine* e) {
   if (!e) return;
   cudaSetDevice(e->device);
   for (auto ev : e->ev_pool) cudaEventDestroy(ev);
+  if (e->copy_st) {
+    cudaStreamDestroy(e->copy_st);
+    cudaEventDestroy(e->ev_flow);
+    cudaEventDestroy(e->ev_cov);
+  }
   for (auto& kv : e->w) cudaFree(kv.second.ptr);
   for (auto& kv : e->buf) cudaFree(kv.second.ptr);
   delete e;
@@ -1148,11 +1161,29 @@ int ufm_forward_host(ufm_engine* e, const void* src, const void* tgt, int pairs,
   float* dcov = c.unc_out_ch > 0 ? reinterpret_cast<float*>(e->buf["covis"].ptr) : nullptr;
   if (!e->ck(cudaMemcpyAsync(dsrc, src, in_bytes, cudaMemcpyHostToDevice, st), "H2D src")) return 1;
   if (!e->ck(cudaMemcpyAsync(dtgt, tgt, in_bytes, cudaMemcpyHostToDevice, st), "H2D tgt")) return 1;
-  if (e->forward(dsrc, dtgt, pairs, in_dtype, in_layout, dflow, dcov, st)) return 1;
+  if (!e->copy_st) {
+    if (!e->ck(cudaStreamCreateWithFlags(&e->copy_st, cudaStreamNonBlocking), "copy stream")) return 1;
+    if (!e->ck(cudaEventCreateWithFlags(&e->ev_flow, cudaEventDisableTiming), "event")) return 1;
+    if (!e->ck(cudaEventCreateWithFlags(&e->ev_cov, cudaEventDisableTiming), "event")) return 1;
+  }
+  e->mark_outputs = true;
+  const int rc = e->forward(dsrc, dtgt, pairs, in_dtype, in_layout, dflow, dcov, st);
+  e->mark_outputs = false;
+  if (rc) return 1;
   const size_t plane = (size_t)c.img_h * c.img_w;
-  if (!e->ck(cudaMemcpyAsync(flow_out, dflow, pairs * 2 * plane * 4, cudaMemcpyDeviceToHost, st), "D2H flow")) return 1;
-  if (covis_out && dcov)
-    if (!e->ck(cudaMemcpyAsync(covis_out, dcov, pairs * plane * 4, cudaMemcpyDeviceToHost, st), "D2H covis")) return 1;
+  const bool want_cov = covis_out && dcov;
+  // queue the copies in the order the outputs become final: Base = flow, then covisibility; Refine = the reverse
+  for (int k = 0; k < 2; ++k) {
+    const bool do_flow = (k == 0) != (c.refine != 0);
+    if (do_flow) {
+      if (!e->ck(cudaStreamWaitEvent(e->copy_st, e->ev_flow, 0), "wait flow")) return 1;
+      if (!e->ck(cudaMemcpyAsync(flow_out, dflow, pairs * 2 * plane * 4, cudaMemcpyDeviceToHost, e->copy_st), "D2H flow")) return 1;
+    } else if (want_cov) {
+      if (!e->ck(cudaStreamWaitEvent(e->copy_st, e->ev_cov, 0), "wait covis")) return 1;
+      if (!e->ck(cudaMemcpyAsync(covis_out, dcov, pairs * plane * 4, cudaMemcpyDeviceToHost, e->copy_st), "D2H covis")) return 1;
+    }
+  }
+  if (!e->ck(cudaStreamSynchronize(e->copy_st), "sync copies")) return 1;
   if (!e->ck(cudaStreamSynchronize(st), "sync")) return 1;
   return 0;
 }

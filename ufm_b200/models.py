@@ -256,6 +256,26 @@ class UniFlowMatchModelsBase(nn.Module):
         self._last_unc = {k: torch.cat([u[k] for u in unc]) for k in unc[0]} if unc else {}
         return flow, cov, aux
 
+    def _run_host(self, img0: torch.Tensor, img1: torch.Tensor, layout: int):
+        """Host uint8 / normalised fp32 images at the inference resolution -> pinned host (flow, covisibility)."""
+        if img0.shape != img1.shape:
+            raise NotImplementedError("Unequal Image sizes are not supported now")  # ufm.py:316-317
+        eng = self._engine(self._device())
+        eng.set_keep_aux(False)
+        B = img0.shape[0]
+        flow = torch.empty(B, 2, eng.H, eng.W, dtype=torch.float32, pin_memory=True)
+        cov = torch.empty(B, eng.H, eng.W, dtype=torch.float32, pin_memory=True) if eng.has_mask else None
+        unc = []
+        for s in range(0, B, self.max_pairs_per_call):
+            e = min(B, s + self.max_pairs_per_call)
+            eng.forward_host(img0[s:e], img1[s:e], layout, flow[s:e], cov[s:e] if cov is not None else None)
+            names = (["flow_cov", "flow_cov_inv", "flow_cov_log_det"] if eng.has_cov else []) + \
+                    (["keypoint_confidence"] if eng.has_conf else [])
+            if names:
+                unc.append({k: eng.stage(k) for k in names})
+        self._last_unc = {k: torch.cat([u[k] for u in unc]) for k in unc[0]} if unc else {}
+        return flow, cov
+
     def forward(self, view1, view2) -> UFMOutputInterface:
         img1, img2 = view1["img"], view2["img"]
         assert view1.get("data_norm_type", self.encoder.data_norm_type) == self.encoder.data_norm_type
@@ -308,13 +328,25 @@ class UniFlowMatchModelsBase(nn.Module):
         dev = self._device()
         if dev.type != "cuda":
             raise RuntimeError("ufm_b200 models run on CUDA only: call .to('cuda') (there is no CPU fallback)")
+        H, W = inference_hw(self.config) if isinstance(self.inference_resolution[0], int) else (None, None)
+        hw0 = tuple(source_image.shape[1:3] if layout == _lib.UFM_NHWC else source_image.shape[2:4])
+        hw1 = tuple(target_image.shape[1:3] if layout == _lib.UFM_NHWC else target_image.shape[2:4])
+        native = hw0 == (H, W) and hw1 == (H, W)
+        renorm = source_image.dtype == torch.float32 and data_norm_type != required
+        if native and not renorm and in_device.type == "cpu" and target_image.device.type == "cpu" \
+                and source_image.dtype == target_image.dtype:
+            # host tensors at the native size: one ufm_forward_host call per chunk -- H2D, forward and the D2H copies
+            # (overlapped with the tail of the pass) inside the C ABI, results land in pinned host tensors
+            flow, cov = self._run_host(source_image.contiguous(), target_image.contiguous(), layout)
+            out = UFMOutputInterface(flow=UFMFlowFieldOutput(flow_output=flow))
+            fcov = self._last_unc.get("flow_cov")
+            if fcov is not None:
+                out.flow.flow_covariance = fcov.to(in_device)
+            if cov is not None:
+                out.covisibility = UFMMaskFieldOutput(mask=cov, logits=None)
+            return out
         src = source_image.to(dev, non_blocking=True)
         tgt = target_image.to(dev, non_blocking=True)
-        H, W = inference_hw(self.config) if isinstance(self.inference_resolution[0], int) else (None, None)
-        hw0 = tuple(src.shape[1:3] if layout == _lib.UFM_NHWC else src.shape[2:4])
-        hw1 = tuple(tgt.shape[1:3] if layout == _lib.UFM_NHWC else tgt.shape[2:4])
-        native = hw0 == (H, W) and hw1 == (H, W)
-        renorm = src.dtype == torch.float32 and data_norm_type != required
         if native and not renorm:
             # the engine reads the images as they are (u8 normalisation is fused into the patch gather);
             # the reference's un-map at native size is the identity up to (flow + c) - c rounding
