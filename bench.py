@@ -302,8 +302,10 @@ def run_engine(args):
 
     # ---- e2e: public API, pinned host tensors in, host tensors out ---------------------------------------------------
     hsrc, htgt = src.pin_memory(), tgt.pin_memory()
-    for _ in range(max(1, min(args.warmup, 2))):
-        model.predict_correspondences_batched(hsrc, htgt)
+    # warm-up calls keep their outputs alive so that the pinned-host allocator's cache holds the two result blocks the
+    # timed loop alternates between (a first-use cudaHostAlloc of 45 MB costs 10-20 ms)
+    keep = [model.predict_correspondences_batched(hsrc, htgt) for _ in range(max(2, min(args.warmup, 3)))]
+    del keep
     barrier()
     t0 = time.perf_counter()
     e0.record()
