@@ -55,6 +55,9 @@ typedef struct ufm_config {
    * UNet(3, 16, [64,128,256,512]), unet_encoder.py:26-72): 0 = off, 1 = feature_combine_method "conv",
    * 2 = "modulate".  Needs refine = 1. */
   int unet;
+  /* custom_positional_encoding="rope" of the global-attention info sharing (global_attention_transformer.py:110-113:
+   * RoPE2D(freq=100, F0=1) on q and k of every block, positions = the patch grid of each view). 0/1. */
+  int info_rope;
 } ufm_config;
 
 /* adaptor kinds and their channel counts: mask 1 ('non_occluded_mask'), covariance 3 ('flow_cov'), confidence 1
@@ -142,6 +145,9 @@ int ufm_op_layernorm(const float* x, int n_seq, int src_seq_len, int src_skip, i
                      float* out_f32, int64_t of_pitch, int64_t of_col, void* stream);
 int ufm_op_qk_norm(void* qkv, int64_t rows, int heads, const float* qw, const float* qb, const float* kw,
                    const float* kb, float eps, void* stream);
+/* RoPE2D (UC/models/libs/croco/pos_embed.py:108-155, base 100) on the q and k columns of a fused qkv buffer, in place:
+ * token (y, x) = ((row mod tokens_per_view) / grid_w, (row mod tokens_per_view) mod grid_w). */
+int ufm_op_rope(void* qkv, int64_t rows, int heads, int tokens_per_view, int grid_w, void* stream);
 int ufm_op_resize_ac(const float* in_f32, const void* in_bf16, int n, int h, int w, int C, int rh, int rw, int oh,
                      int ow, float* out_f32, void* out_bf16, void* stream);
 int ufm_op_shuffle(const void* in, void* out, int is_f32, int n, int h, int w, int k, int C, void* stream);

@@ -17,6 +17,8 @@ GOLDEN_CASES = {
     "tiny_cov": dict(cfg="tiny_cov", batch=2, out_gain=1.0),
     # per-view cross-attention info sharing, Refine model, qk-norm on
     "tiny_cross": dict(cfg="tiny_cross", batch=2, out_gain=8.0),
+    # RoPE2D on the global-attention info sharing (custom_positional_encoding="rope"), with qk-norm
+    "tiny_rope": dict(cfg="tiny_rope", batch=2, out_gain=8.0),
     # UNet fine-feature branch of UFM-Refine, both combine methods
     "tiny_unet": dict(cfg="tiny_unet", batch=2, out_gain=8.0),
     "tiny_unet_mod": dict(cfg="tiny_unet_mod", batch=1, out_gain=8.0),

@@ -48,9 +48,33 @@ def _ln(x, sd, prefix, eps=1e-6):
     return F.layer_norm(x, (x.shape[-1],), sd[prefix + "weight"], sd[prefix + "bias"], eps)
 
 
-def attention(x, sd, prefix, heads, qk_norm=False):
+def rope2d(t, pos, base=100.0):
+    """``RoPE2D.forward`` (UC/models/libs/croco/pos_embed.py:108-155; the compiled cuRoPE2D computes the same):
+    t (B, heads, N, hd), pos (B, N, 2) = (y, x) of each token.  The first hd/2 dims rotate by y, the last hd/2 by x."""
+    D = t.shape[-1] // 2
+    inv_freq = 1.0 / (base ** (torch.arange(0, D, 2).float() / D))
+
+    def rope1d(v, p1):
+        fr = torch.einsum("bn,j->bnj", p1.float(), inv_freq)
+        fr = torch.cat((fr, fr), dim=-1)[:, None]  # (B, 1, N, D)
+        v1, v2 = v[..., : D // 2], v[..., D // 2:]
+        return v * fr.cos() + torch.cat((-v2, v1), dim=-1) * fr.sin()
+
+    y, x = t.chunk(2, dim=-1)
+    return torch.cat((rope1d(y, pos[:, :, 0]), rope1d(x, pos[:, :, 1])), dim=-1)
+
+
+def grid_positions(B, h, w, views=1):
+    """``PositionGetter`` (UC/models/utils/positional_encoding.py:8-23), repeated per view
+    (global_attention_transformer.py:499-503)."""
+    g = torch.cartesian_prod(torch.arange(h), torch.arange(w)).view(1, h * w, 2)
+    return g.repeat(B, views, 1)
+
+
+def attention(x, sd, prefix, heads, qk_norm=False, pos=None):
     """UC/models/utils/transformer_blocks.py:150-187 (and the DINOv2 SDPA wrapper, dinov2.py:128-141):
-    fused qkv Linear -> (B, heads, N, hd) -> [LayerNorm over head_dim on q,k] -> softmax(q k^T / sqrt(hd)) v -> proj."""
+    fused qkv Linear -> (B, heads, N, hd) -> [LayerNorm over head_dim on q,k] -> [RoPE2D on q,k] ->
+    softmax(q k^T / sqrt(hd)) v -> proj."""
     B, N, C = x.shape
     hd = C // heads
     qkv = F.linear(x, sd[prefix + "qkv.weight"], sd.get(prefix + "qkv.bias"))
@@ -60,15 +84,17 @@ def attention(x, sd, prefix, heads, qk_norm=False):
         # norm_layer = partial(nn.LayerNorm, eps=1e-6) is handed down to q_norm/k_norm (transformer_blocks.py:142-143)
         q = F.layer_norm(q, (hd,), sd[prefix + "q_norm.weight"], sd[prefix + "q_norm.bias"], 1e-6)
         k = F.layer_norm(k, (hd,), sd[prefix + "k_norm.weight"], sd[prefix + "k_norm.bias"], 1e-6)
+    if pos is not None:
+        q, k = rope2d(q, pos), rope2d(k, pos)
     o = F.scaled_dot_product_attention(q, k, v, scale=hd ** -0.5)
     o = o.transpose(1, 2).reshape(B, N, C)
     return F.linear(o, sd[prefix + "proj.weight"], sd[prefix + "proj.bias"])
 
 
-def block(x, sd, prefix, heads, qk_norm=False):
+def block(x, sd, prefix, heads, qk_norm=False, pos=None):
     """Pre-LN block: ``x += ls1(attn(norm1 x)); x += ls2(mlp(norm2 x))``
     (transformer_blocks.py:386-403; hub DINOv2 ``Block.forward``; LayerScale = ``x * gamma`` :315-317)."""
-    a = attention(_ln(x, sd, prefix + "norm1."), sd, prefix + "attn.", heads, qk_norm)
+    a = attention(_ln(x, sd, prefix + "norm1."), sd, prefix + "attn.", heads, qk_norm, pos)
     if prefix + "ls1.gamma" in sd:
         a = a * sd[prefix + "ls1.gamma"]
     x = x + a
@@ -208,12 +234,14 @@ def info_sharing(f1: torch.Tensor, f2: torch.Tensor, sd, cfg):
     take = list(range(depth - idx, depth)) if isinstance(idx, int) else [depth + i if i < 0 else i for i in idx]
     inter = []
     qk_norm = bool(ik.get("qk_norm"))
+    # custom_positional_encoding="rope" (global_attention_transformer.py:110-113): RoPE2D on q, k of every block
+    pos = grid_positions(B, h, w, views=2) if ik.get("custom_positional_encoding") == "rope" and not alternating else None
     for i in range(depth):
         pre = f"{p}self_attention_blocks.{i}."
         if alternating and i % 2 == 1:
             x = block(x.reshape(B * 2, n, dim), sd, pre, heads, qk_norm).reshape(B, 2 * n, dim)
         else:
-            x = block(x, sd, pre, heads, qk_norm)
+            x = block(x, sd, pre, heads, qk_norm, pos)
         if i in take:
             inter.append(_ln(x, sd, p + "norm.") if ik.get("norm_intermediate", True) else x)
 

@@ -190,6 +190,29 @@ def test_qk_norm():
     assert torch.equal(got[:, 2], o[:, 2])
 
 
+def test_rope2d_vs_oracle():
+    """RoPE2D on q and k of a fused qkv buffer (2 sequences x 2 views x a 30 x 40 patch grid) vs the oracle's restatement
+    of pos_embed.py:108-155; v untouched."""
+    from oracle import ufm_oracle as O
+
+    lib = _lib.load()
+    h, w, heads, B = 30, 40, 3, 2
+    n = h * w
+    rows = B * 2 * n
+    qkv = _rand(rows, 3 * heads * 64, seed=7).bfloat16()
+    orig = qkv.clone()
+    assert lib.ufm_op_rope(qkv.data_ptr(), rows, heads, n, w, torch.cuda.current_stream().cuda_stream) == 0
+    torch.cuda.synchronize()
+    o = orig.float().cpu().view(B, 2 * n, 3, heads, 64).permute(2, 0, 3, 1, 4)  # (3, B, heads, 2n, 64)
+    pos = O.grid_positions(B, h, w, views=2)
+    got = qkv.float().cpu().view(B, 2 * n, 3, heads, 64).permute(2, 0, 3, 1, 4)
+    for i in (0, 1):
+        ref = O.rope2d(o[i], pos)
+        assert rel(got[i], ref) < 4e-3, (i, rel(got[i], ref))
+        assert rel(got[i], o[i]) > 0.5  # the rotation is far from the identity on this grid
+    assert torch.equal(got[2], o[2])
+
+
 @pytest.mark.parametrize("h,w,rh,rw,oh,ow", [(15, 20, 30, 40, 30, 40), (8, 10, 16, 20, 15, 19), (96, 128, 168, 224, 168, 224)])
 def test_resize_align_corners(h, w, rh, rw, oh, ow):
     lib = _lib.load()

@@ -38,6 +38,7 @@ class UfmConfig(C.Structure):
         ("unc_n_adaptors", C.c_int), ("unc_kind", C.c_int * 4),
         ("unc_vmin", C.c_float * 4), ("unc_vmax", C.c_float * 4),
         ("unet", C.c_int),
+        ("info_rope", C.c_int),
     ]
 
 
@@ -63,6 +64,7 @@ SYMBOLS = {
     "ufm_op_attention": (_I, [_P, _I, _I, _I, _F, _P, _P, C.c_char_p, _I]),
     "ufm_op_layernorm": (_I, [_P, _I, _I, _I, _I, _I, _P, _P, _F, _I, _P, _L, _L, _P, _L, _L, _P]),
     "ufm_op_qk_norm": (_I, [_P, _L, _I, _P, _P, _P, _P, _F, _P]),
+    "ufm_op_rope": (_I, [_P, _L, _I, _I, _I, _P]),
     "ufm_op_resize_ac": (_I, [_P, _P, _I, _I, _I, _I, _I, _I, _I, _I, _P, _P, _P]),
     "ufm_op_shuffle": (_I, [_P, _P, _I, _I, _I, _I, _I, _I, _P]),
     "ufm_op_im2col_s2": (_I, [_P, _P, _I, _I, _I, _I, _I, _I, _P]),

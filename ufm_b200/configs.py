@@ -85,7 +85,7 @@ def ufm_refine_assumed(inference_resolution=(560, 420)) -> Dict[str, Any]:
 
 def tiny(refine: bool = False, inference_resolution=(224, 168), info_sharing_str="global_attention",
          qk_norm: bool = False, unc_adaptors: str = "mask", conf_type: str = "sigmoid",
-         unet: str = "") -> Dict[str, Any]:
+         unet: str = "", rope: bool = False) -> Dict[str, Any]:
     """A small architecture with the same topology, for fast CPU goldens and GPU parity at every
     stage boundary: ViT-S/14 truncated to 4 layers, 4x128 info sharing, slim DPT heads."""
     W, H = inference_resolution
@@ -96,6 +96,8 @@ def tiny(refine: bool = False, inference_resolution=(224, 168), info_sharing_str
     cfg["info_sharing_str"] = info_sharing_str
     cfg["info_sharing_kwargs"].update({"input_embed_dim": 384, "depth": 4, "dim": 128, "num_heads": 2,
                                        "indices": [1, 2], "qk_norm": qk_norm})
+    if rope:
+        cfg["info_sharing_kwargs"]["custom_positional_encoding"] = "rope"  # global_attention_transformer.py:110-113
     if info_sharing_str == "cross_attention":
         # MultiViewCrossAttentionTransformerIFR kwargs (cross_attention_transformer.py:264-292); SURVEY.md 8f N2
         ik = cfg["info_sharing_kwargs"]
@@ -134,6 +136,7 @@ CONFIGS = {
     "tiny_refine": lambda: tiny(True),
     "tiny_cov": lambda: tiny(False, unc_adaptors="cov_conf_mask"),
     "tiny_cross": lambda: tiny(True, info_sharing_str="cross_attention", qk_norm=True),
+    "tiny_rope": lambda: tiny(False, qk_norm=True, rope=True),
     "tiny_unet": lambda: tiny(True, unet="conv"),
     "tiny_unet_mod": lambda: tiny(True, unet="modulate"),
     "ufm_refine_unet": lambda: dict(ufm_refine_assumed(), use_unet_feature=True, feature_combine_method="conv"),

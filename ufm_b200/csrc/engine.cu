@@ -335,7 +335,8 @@ struct ufm_engine {
   }
 
   // One pre-LN transformer block over x [n_rows, D] (fp32 residual stream), attention over n_seq sequences of seq_len.
-  bool block(const std::string& pre, float* x, int n_seq, int seq_len, int D, int heads, int hidden, bool qk_norm) {
+  bool block(const std::string& pre, float* x, int n_seq, int seq_len, int D, int heads, int hidden, bool qk_norm,
+             int rope_n = 0, int rope_w = 0) {
     const long long M = (long long)n_seq * seq_len;
     bf16* xn = B<bf16>("xn");
     bf16* qkv = B<bf16>("qkv");
@@ -348,10 +349,15 @@ struct ufm_engine {
       e.out_bf16 = qkv; e.sx = 3LL * D; e.sy = e.sn = 0;
       if (!gemm(rows_view(xn, M, D), pre + ".qkv.w", 1, e)) return false;
     }
-    if (qk_norm) {
-      if (!run(UFM_CAT_LN, 0.0, (double)M * heads * 64 * 2 * 4, "qk_norm", [&] {
-            return launch_qk_norm(qkv, M, heads, Wf(pre + ".qn.w"), Wf(pre + ".qn.b"), Wf(pre + ".kn.w"),
-                                  Wf(pre + ".kn.b"), 1e-6f, st);
+    if (qk_norm || rope_n > 0) {
+      // q/k LayerNorm (transformer_blocks.py:164) and RoPE2D (:166-171) in one in-place pass over the q and k columns
+      const float *qw = nullptr, *qb = nullptr, *kw = nullptr, *kb = nullptr;
+      if (qk_norm) {
+        qw = Wf(pre + ".qn.w"); qb = Wf(pre + ".qn.b"); kw = Wf(pre + ".kn.w"); kb = Wf(pre + ".kn.b");
+        if (!qw || !qb || !kw || !kb) return false;
+      }
+      if (!run(UFM_CAT_LN, 0.0, (double)M * heads * 64 * 2 * 4, "qk_norm/rope", [&] {
+            return launch_qk_norm(qkv, M, heads, qw, qb, kw, kb, 1e-6f, st, qk_norm ? 1 : 0, rope_n, rope_w);
           }))
         return false;
     }
@@ -813,7 +819,7 @@ int ufm_engine::forward(const void* src, const void* tgt, int pairs, int in_dtyp
     } else {
       const bool per_view = c.info_alternating && (i & 1);
       if (!block("info." + std::to_string(i), y, per_view ? 2 * Bp : Bp, per_view ? n : 2 * n, d, c.info_heads,
-                 c.info_hidden, c.info_qk_norm != 0))
+                 c.info_hidden, c.info_qk_norm != 0, c.info_rope ? n : 0, wpn))
         return 1;
     }
     if (i == c.info_take0) {
@@ -990,6 +996,11 @@ int ufm_create(const ufm_config* cfg, int device, ufm_engine** out) {
     delete e;
     fprintf(stderr, "ufm_create: refinement kernel is specialised for 16-channel descriptors and a 5x5 window\n");
     return 6;
+  }
+  if (c.info_rope && c.info_alternating != 0) {
+    delete e;
+    fprintf(stderr, "ufm_create: info_rope is defined for global-attention info sharing only\n");
+    return 9;
   }
   if (c.unet && (!c.refine || c.unet < 0 || c.unet > 2 || c.img_h < 16 || c.img_w < 16)) {
     delete e;
@@ -1344,6 +1355,11 @@ int ufm_op_qk_norm(void* qkv, int64_t rows, int heads, const float* qw, const fl
                    const float* kb, float eps, void* stream) {
   return launch_qk_norm(reinterpret_cast<bf16*>(qkv), rows, heads, qw, qb, kw, kb, eps,
                         reinterpret_cast<cudaStream_t>(stream)) != cudaSuccess;
+}
+
+int ufm_op_rope(void* qkv, int64_t rows, int heads, int tokens_per_view, int grid_w, void* stream) {
+  return launch_qk_norm(reinterpret_cast<bf16*>(qkv), rows, heads, nullptr, nullptr, nullptr, nullptr, 0.f,
+                        reinterpret_cast<cudaStream_t>(stream), 0, tokens_per_view, grid_w) != cudaSuccess;
 }
 
 int ufm_op_resize_ac(const float* in_f32, const void* in_bf16, int n, int h, int w, int C, int rh, int rw, int oh, int ow,

@@ -125,9 +125,11 @@ struct LNParams {
 };
 cudaError_t launch_layernorm(const LNParams& p, cudaStream_t stream);
 
-// per-head LayerNorm of q and k inside the fused qkv buffer (in place, bf16), head_dim 64
+// per-head LayerNorm of q and k (do_norm) and / or RoPE2D with base 100 (rope_n = tokens per view > 0, rope_w = patch
+// grid width; pos_embed.py:108-155) inside the fused qkv buffer (in place, bf16), head_dim 64
 cudaError_t launch_qk_norm(__nv_bfloat16* qkv, long long rows, int heads, const float* qw, const float* qb,
-                           const float* kw, const float* kb, float eps, cudaStream_t stream);
+                           const float* kw, const float* kb, float eps, cudaStream_t stream, int do_norm = 1,
+                           int rope_n = 0, int rope_w = 0);
 
 // Patch im2col: image (uint8 or fp32, NHWC or NCHW) -> A[(img, py, px), Kpad] bf16 with
 // k = c*P*P + ky*P + kx (conv weight flatten order), zero padded to Kpad.  uint8 pixels are normalised

@@ -74,9 +74,16 @@ __global__ void __launch_bounds__(256) layernorm_kernel(const LNParams p) {
     }
 }
 
-// per-head LayerNorm of q and k (head_dim 64) in place inside the fused qkv buffer; one warp per (row, head, q|k)
+// per-head LayerNorm of q and k (head_dim 64) and / or 2-D RoPE, in place inside the fused qkv buffer; one warp per
+// (row, head, q|k), two elements per lane.
+// RoPE2D (UC/models/libs/croco/pos_embed.py:108-155; curope/kernels.cu computes the same): the first 32 dims rotate by
+// the token's grid row y, the last 32 by its column x; inside a 32-dim half, element i < 16 pairs with i + 16:
+//   out[i] = t[i] cos(a_i) - t[i+16] sin(a_i),  out[i+16] = t[i+16] cos(a_i) + t[i] sin(a_i),  a_i = pos * 100^(-i/16).
+// Token (y, x) = ((row mod rope_n) / rope_w, (row mod rope_n) mod rope_w): every view carries the same patch grid
+// (global_attention_transformer.py:499-503).
 __global__ void __launch_bounds__(256) qk_norm_kernel(__nv_bfloat16* qkv, long long rows, int heads, const float* qw,
-                                                     const float* qb, const float* kw, const float* kb, float eps) {
+                                                     const float* qb, const float* kw, const float* kb, float eps,
+                                                     int do_norm, int rope_n, int rope_w) {
   const long long wid = (long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
   const long long total = rows * heads * 2;
   if (wid >= total) return;
@@ -86,13 +93,27 @@ __global__ void __launch_bounds__(256) qk_norm_kernel(__nv_bfloat16* qkv, long l
   const long long row = wid / (2 * heads);
   __nv_bfloat162* ptr =
       reinterpret_cast<__nv_bfloat162*>(qkv + row * (3LL * heads * 64) + (long long)which * heads * 64 + head * 64) + lane;
-  const float2 x = __bfloat1622float2(*ptr);
-  const float mean = warp_sum(x.x + x.y) * (1.f / 64.f);
-  const float a = x.x - mean, b = x.y - mean;
-  const float rstd = rsqrtf(warp_sum(a * a + b * b) * (1.f / 64.f) + eps);
-  const float* w = which ? kw : qw;
-  const float* bb = which ? kb : qb;
-  *ptr = __floats2bfloat162_rn(a * rstd * w[2 * lane] + bb[2 * lane], b * rstd * w[2 * lane + 1] + bb[2 * lane + 1]);
+  float2 v = __bfloat1622float2(*ptr);
+  if (do_norm) {
+    const float mean = warp_sum(v.x + v.y) * (1.f / 64.f);
+    const float a = v.x - mean, b = v.y - mean;
+    const float rstd = rsqrtf(warp_sum(a * a + b * b) * (1.f / 64.f) + eps);
+    const float* w = which ? kw : qw;
+    const float* bb = which ? kb : qb;
+    v = make_float2(a * rstd * w[2 * lane] + bb[2 * lane], b * rstd * w[2 * lane + 1] + bb[2 * lane + 1]);
+  }
+  if (rope_n > 0) {
+    const int t = (int)(row % rope_n);
+    const float pos = (float)((lane & 16) ? t % rope_w : t / rope_w);
+    const float ox = __shfl_xor_sync(0xffffffffu, v.x, 8), oy = __shfl_xor_sync(0xffffffffu, v.y, 8);
+    const int j = 2 * (lane & 7);
+    float s0, c0, s1, c1;
+    sincosf(pos * exp2f(-(float)j * (6.643856189774724f / 16.f)), &s0, &c0);        // 100^(-j/16)
+    sincosf(pos * exp2f(-(float)(j + 1) * (6.643856189774724f / 16.f)), &s1, &c1);
+    const float sg = (lane & 8) ? 1.f : -1.f;  // first half of the pair: - partner * sin, second half: + partner * sin
+    v = make_float2(v.x * c0 + sg * ox * s0, v.y * c1 + sg * oy * s1);
+  }
+  *ptr = __floats2bfloat162_rn(v.x, v.y);
 }
 
 // ------------------------------------------------------------------------------------------------ patch im2col
@@ -457,9 +478,12 @@ cudaError_t launch_layernorm(const LNParams& p, cudaStream_t stream) {
 }
 
 cudaError_t launch_qk_norm(__nv_bfloat16* qkv, long long rows, int heads, const float* qw, const float* qb,
-                           const float* kw, const float* kb, float eps, cudaStream_t stream) {
+                           const float* kw, const float* kb, float eps, cudaStream_t stream, int do_norm, int rope_n,
+                           int rope_w) {
+  if (!do_norm && rope_n <= 0) return cudaSuccess;
+  if (rope_n > 0 && rope_w <= 0) return cudaErrorInvalidValue;
   const long long warps = rows * heads * 2;
-  qk_norm_kernel<<<blocks_for(warps, 8), 256, 0, stream>>>(qkv, rows, heads, qw, qb, kw, kb, eps);
+  qk_norm_kernel<<<blocks_for(warps, 8), 256, 0, stream>>>(qkv, rows, heads, qw, qb, kw, kb, eps, do_norm, rope_n, rope_w);
   return cudaGetLastError();
 }
 

@@ -84,8 +84,14 @@ def engine_config(cfg: Dict[str, Any]) -> "_lib.UfmConfig":
             raise AssertionError("Expected 2 views")  # cross_attention_transformer.py:382-384 with UFM's two views
         if not ik.get("norm_cross_tokens", True):
             raise NotImplementedError("norm_cross_tokens=False (the K/V GEMM reads the LayerNorm kernel's bf16 output)")
-    if ik.get("custom_positional_encoding") is not None:
-        raise NotImplementedError("custom_positional_encoding='rope' is not built yet")
+    cpe = ik.get("custom_positional_encoding")
+    if cpe is not None:
+        # only the global-attention transformer maps the string "rope" to RoPE2D (global_attention_transformer.py:110-115);
+        # the other two take a callable, which a config.json cannot carry
+        if cfg["info_sharing_str"] != "global_attention" or not isinstance(cpe, str):
+            raise NotImplementedError("custom_positional_encoding must be the string 'rope' with global_attention")
+        if cpe != "rope":
+            raise ValueError(f"Unknown custom positional encoding: {cpe}")  # global_attention_transformer.py:115
     if ik.get("use_rand_idx_pe_for_non_reference_views") and cfg["info_sharing_str"] == "global_attention":
         raise NotImplementedError("use_rand_idx_pe_for_non_reference_views draws from the global RNG (SURVEY.md H7)")
     if cfg.get("head_type", "dpt") != "dpt":
@@ -109,6 +115,7 @@ def engine_config(cfg: Dict[str, Any]) -> "_lib.UfmConfig":
     c.info_take0, c.info_take1 = it[0], it[1]
     c.info_alternating = {"global_attention": 0, "alternating_attention": 1, "cross_attention": 2}[cfg["info_sharing_str"]]
     c.info_qk_norm = int(bool(ik.get("qk_norm")))
+    c.info_rope = int(cpe == "rope")
     c.info_layerscale = int(bool(ik.get("init_values")))
     c.info_has_proj = 1
     f = cfg["feature_head_kwargs"]["dpt_feature"]
