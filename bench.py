@@ -172,6 +172,22 @@ def _peaks() -> dict:
     return {"bf16_burst": 1590.0, "bf16_sustained": 1400.0, "hbm": 6650.0, "source": "fallback"}
 
 
+def _ncu_traffic(workload: str):
+    """DRAM bytes per launch of the dominant kernel from the committed `ncu --set full` summary (profiles/*_traffic.json,
+    written when a capture is summarised); None when no capture of this workload is committed."""
+    import glob
+
+    for path in sorted(glob.glob(os.path.join(ROOT, "profiles", "*_traffic.json")), reverse=True):
+        try:
+            with open(path) as f:
+                d = json.load(f)
+            if d.get("workload") == workload:
+                return d["dram_bytes_per_launch"]
+        except Exception:
+            continue
+    return None
+
+
 def _make_cfg(workload: str):
     from ufm_b200 import configs
 
@@ -347,7 +363,7 @@ def run_engine(args):
     g_n = sum(v["launches"] for v in gm.values())
     roofline = {"kernel": "gemm_kernel<BN> (tcgen05 GEMM + implicit-GEMM 3x3 conv)", "bound": "tensor",
                 "achieved": g_fl / (g_ms * 1e-3) / 1e12, "peak": peaks["bf16_sustained"], "unit": "TFLOP/s",
-                "peak_source": f"{peaks['source']} bf16 sustained", "traffic": None,
+                "peak_source": f"{peaks['source']} bf16 sustained", "traffic": _ncu_traffic(args.workload),
                 "avg_launch_ms": g_ms / g_n, "flops_per_launch": g_fl / g_n, "share_of_step": g_ms / tot_ms}
     roofline["frac"] = roofline["achieved"] / roofline["peak"]
     whole = {"tflop_per_pair": fl["total"], "achieved_tflops_per_gpu": value / world * fl["total"],
