@@ -18,6 +18,7 @@ def main():
     ap.add_argument("--workload", default="base16")
     ap.add_argument("--chunk", type=int, default=32)
     ap.add_argument("--batches", default="1,2,4,8,16,32,64,128")
+    ap.add_argument("--host", action="store_true", help="pinned host tensors in, host tensors out (ufm_forward_host)")
     a = ap.parse_args()
     import torch
 
@@ -36,11 +37,11 @@ def main():
     model.load_state_dict(make_state_dict(cfg, seed=0))
     model = model.to("cuda:0")
     W, H = cfg["inference_resolution"]
-    print(f"# {desc}; engine calls of <= {a.chunk} pairs; device tensors in/out")
+    print(f"# {desc}; engine calls of <= {a.chunk} pairs; {'pinned host' if a.host else 'device'} tensors in/out")
     print("B,ms_per_call,pairs_per_s")
     for B in [int(b) for b in a.batches.split(",")]:
         src, tgt = make_inputs(B, H, W, seed=1)
-        dsrc, dtgt = src.cuda(), tgt.cuda()
+        dsrc, dtgt = (src.pin_memory(), tgt.pin_memory()) if a.host else (src.cuda(), tgt.cuda())
         reps = max(3, min(20, 256 // B))
         for _ in range(2):
             model.predict_correspondences_batched(dsrc, dtgt)
@@ -52,6 +53,13 @@ def main():
         e1.record()
         torch.cuda.synchronize()
         ms = e0.elapsed_time(e1) / reps
+        if a.host:
+            import time
+
+            t0 = time.perf_counter()
+            for _ in range(reps):
+                model.predict_correspondences_batched(dsrc, dtgt)
+            ms = (time.perf_counter() - t0) * 1e3 / reps  # the host path synchronises inside the call
         print(f"{B},{ms:.2f},{B / ms * 1e3:.1f}", flush=True)
 
 
