@@ -26,6 +26,7 @@
 #include <stdio.h>
 
 #include "kernels.h"
+#include "launch.cuh"
 #include "ptx.cuh"
 
 namespace ufm {
@@ -311,6 +312,7 @@ __global__ void __launch_bounds__(kThreads, 2) attn_kernel(const __grid_constant
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = b->tmem_slot;
+  pdl_wait();  // barrier init + TMEM allocation above overlap the previous kernel's tail (launch.cuh)
 
   if (warp < 4) {
     setmaxnreg_dec<48>();
@@ -501,7 +503,7 @@ cudaError_t launch_attention(const AttnParams& p_in, cudaStream_t stream) {
   if (p.n_items <= 0) return cudaSuccess;
   const int grid = p.n_items < 2 * n_sm ? p.n_items : 2 * n_sm;
   bool launched = false;
-#define X(v) if (!launched && g_attn_poly == v) { attn_kernel<v><<<grid, kThreads, SMEM_BYTES, stream>>>(p); launched = true; }
+#define X(v) if (!launched && g_attn_poly == v) { launch_k(attn_kernel<v>, dim3(grid), dim3(kThreads), SMEM_BYTES, stream, p); launched = true; }
   UFM_ATTN_VARIANTS(X)
 #undef X
   if (!launched) return cudaErrorInvalidValue;

@@ -17,6 +17,7 @@
 
 #include "../../include/ufm_b200.h"
 #include "kernels.h"
+#include "launch.cuh"
 
 using namespace ufm;
 typedef __nv_bfloat16 bf16;
@@ -1329,6 +1330,10 @@ int ufm_debug_flag(int which, int value) {
   }
   if (which == 3) {
     set_gemm_halo_mode(value);
+    return 0;
+  }
+  if (which == 4) {
+    set_pdl_mode(value);
     return 0;
   }
   return 1;

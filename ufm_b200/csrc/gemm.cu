@@ -16,6 +16,7 @@
 #include <stdio.h>
 
 #include "kernels.h"
+#include "launch.cuh"
 #include "ptx.cuh"
 
 namespace ufm {
@@ -130,6 +131,8 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_kernel(const __grid_constant
   else __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  // everything above (barrier init, TMEM allocation, descriptor prefetch) overlapped the tail of the previous kernel
+  pdl_wait();
 
   // a scheduling unit owns CTAS consecutive 128-row tiles (one per CTA) x one BN-wide column tile; a CTA whose row tile
   // lies past the end loads zero-filled boxes (image index out of range) and stores nothing
@@ -664,23 +667,7 @@ static cudaError_t launch_one(const GemmParams& p, int grid, cudaStream_t stream
     if (err != cudaSuccess) return err;
     attr = true;
   }
-  if (CTAS == 1) {
-    gemm_kernel<BN, CTAS, HALO><<<grid, kThreads, C::SMEM_BYTES, stream>>>(p);
-    return cudaGetLastError();
-  }
-  cudaLaunchConfig_t cfg = {};
-  cfg.gridDim = dim3(grid, 1, 1);
-  cfg.blockDim = dim3(kThreads, 1, 1);
-  cfg.dynamicSmemBytes = C::SMEM_BYTES;
-  cfg.stream = stream;
-  cudaLaunchAttribute at[1];
-  at[0].id = cudaLaunchAttributeClusterDimension;
-  at[0].val.clusterDim.x = CTAS;
-  at[0].val.clusterDim.y = 1;
-  at[0].val.clusterDim.z = 1;
-  cfg.attrs = at;
-  cfg.numAttrs = 1;
-  return cudaLaunchKernelEx(&cfg, gemm_kernel<BN, CTAS, HALO>, p);
+  return launch_kc(gemm_kernel<BN, CTAS, HALO>, CTAS, dim3(grid), dim3(kThreads), C::SMEM_BYTES, stream, p);
 }
 
 }  // namespace

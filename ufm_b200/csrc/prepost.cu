@@ -14,6 +14,7 @@
 //                        grid, bilinear-resample the (x + .5, y + .5) coordinate grid (align_corners=False), scale the
 //                        end points by the source / target size ratios, subtract, paste into zeros.
 #include "kernels.h"
+#include "launch.cuh"
 
 namespace ufm {
 
@@ -46,6 +47,7 @@ __device__ __forceinline__ float aa_w(const AaAxis& a, int j) {
 
 template <typename T, bool NHWC>
 __global__ void __launch_bounds__(128) prep_resize_kernel(const PrepParams p) {
+  pdl_wait();
   const int ox = blockIdx.x * 128 + threadIdx.x;
   const int oy = blockIdx.y, b = blockIdx.z;
   if (ox >= p.W) return;
@@ -83,6 +85,7 @@ __global__ void __launch_bounds__(128) prep_resize_kernel(const PrepParams p) {
 __device__ __forceinline__ int nearest_src(int dst, float scale, int in) { return min((int)floorf((float)dst * scale), in - 1); }
 
 __global__ void __launch_bounds__(128) unmap_kernel(const UnmapParams p) {
+  pdl_wait();
   const int X = blockIdx.x * 128 + threadIdx.x;
   const int Y = blockIdx.y, b = blockIdx.z;
   if (X >= p.W0) return;
@@ -132,6 +135,7 @@ __global__ void __launch_bounds__(128) unmap_kernel(const UnmapParams p) {
 //   ConfidenceAdaptor (:899-927)        exp: vmin + min(e^x, vmax - vmin); sigmoid: sigmoid(x) (vmax - vmin) + vmin;
 //                                       softmax: softmax over the H*W pixels of an image, times H*W
 __global__ void __launch_bounds__(1024) conf_softmax_stats_kernel(const float* raw, int C, int ch, long long plane, float* stats) {
+  pdl_wait();
   const float* x = raw + ((long long)blockIdx.x * C + ch) * plane;
   float m = -INFINITY, s = 0.f;
   for (long long i = threadIdx.x; i < plane; i += 1024) {
@@ -169,6 +173,7 @@ __global__ void __launch_bounds__(1024) conf_softmax_stats_kernel(const float* r
 }
 
 __global__ void __launch_bounds__(256) unc_adaptor_kernel(const UncAdaptParams p) {
+  pdl_wait();
   const long long plane = (long long)p.H * p.W;
   const long long i = (long long)blockIdx.x * 256 + threadIdx.x;
   if (i >= plane) return;
@@ -219,11 +224,11 @@ cudaError_t launch_prep_resize(const PrepParams& p, cudaStream_t s) {
   if (2.f * p.scale_x + 2.f > (float)kMaxTaps || 2.f * p.scale_y + 2.f > (float)kMaxTaps) return cudaErrorInvalidValue;
   dim3 grid((p.W + 127) / 128, p.H, p.B);
   if (p.is_u8) {
-    if (p.nhwc) prep_resize_kernel<uint8_t, true><<<grid, 128, 0, s>>>(p);
-    else prep_resize_kernel<uint8_t, false><<<grid, 128, 0, s>>>(p);
+    if (p.nhwc) launch_k(prep_resize_kernel<uint8_t, true>, grid, 128, 0, s, p);
+    else launch_k(prep_resize_kernel<uint8_t, false>, grid, 128, 0, s, p);
   } else {
-    if (p.nhwc) prep_resize_kernel<float, true><<<grid, 128, 0, s>>>(p);
-    else prep_resize_kernel<float, false><<<grid, 128, 0, s>>>(p);
+    if (p.nhwc) launch_k(prep_resize_kernel<float, true>, grid, 128, 0, s, p);
+    else launch_k(prep_resize_kernel<float, false>, grid, 128, 0, s, p);
   }
   return cudaGetLastError();
 }
@@ -232,7 +237,7 @@ cudaError_t launch_unmap(const UnmapParams& p, cudaStream_t s) {
   if (p.B <= 0) return cudaSuccess;
   if (p.H0 > 65535 || p.B > 65535) return cudaErrorInvalidValue;
   dim3 grid((p.W0 + 127) / 128, p.H0, p.B);
-  unmap_kernel<<<grid, 128, 0, s>>>(p);
+  launch_k(unmap_kernel, grid, 128, 0, s, p);
   return cudaGetLastError();
 }
 
@@ -243,10 +248,10 @@ cudaError_t launch_unc_adaptors(const UncAdaptParams& p, cudaStream_t s) {
   for (int a = 0; a < p.n; ++a)
     if (p.kind[a] == ADAPT_CONF_SOFTMAX) {
       if (!p.conf_stats) return cudaErrorInvalidValue;
-      conf_softmax_stats_kernel<<<p.B, 1024, 0, s>>>(p.raw, p.C, p.ch[a], plane, p.conf_stats);
+      launch_k(conf_softmax_stats_kernel, p.B, 1024, 0, s, p.raw, p.C, p.ch[a], plane, p.conf_stats);
     }
   dim3 grid((unsigned)((plane + 255) / 256), p.B);
-  unc_adaptor_kernel<<<grid, 256, 0, s>>>(p);
+  launch_k(unc_adaptor_kernel, grid, 256, 0, s, p);
   return cudaGetLastError();
 }
 

@@ -5,7 +5,10 @@
 #include <math.h>
 #include <type_traits>
 
+#include <stdlib.h>
+
 #include "kernels.h"
+#include "launch.cuh"
 #include "ptx.cuh"
 
 namespace ufm {
@@ -23,6 +26,7 @@ __device__ __forceinline__ float warp_sum(float v) {
 // (transformer_blocks.py norm1/norm2, final `norm` on returned layers: global_attention_transformer.py:546-550,586).
 constexpr int LN_MAXV = 8;
 __global__ void __launch_bounds__(256) layernorm_kernel(const LNParams p) {
+  pdl_wait();
   const int warps_per_block = blockDim.x >> 5;
   const long long row = (long long)blockIdx.x * warps_per_block + (threadIdx.x >> 5);
   const long long rows = (long long)p.n_seq * p.tokens;
@@ -84,6 +88,7 @@ __global__ void __launch_bounds__(256) layernorm_kernel(const LNParams p) {
 __global__ void __launch_bounds__(256) qk_norm_kernel(__nv_bfloat16* qkv, long long rows, int heads, const float* qw,
                                                      const float* qb, const float* kw, const float* kb, float eps,
                                                      int do_norm, int rope_n, int rope_w) {
+  pdl_wait();
   const long long wid = (long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
   const long long total = rows * heads * 2;
   if (wid >= total) return;
@@ -118,6 +123,7 @@ __global__ void __launch_bounds__(256) qk_norm_kernel(__nv_bfloat16* qkv, long l
 
 // ------------------------------------------------------------------------------------------------ patch im2col
 __global__ void __launch_bounds__(256) patch_im2col_kernel(const PatchParams p) {
+  pdl_wait();
   const int hp = p.H / p.P, wp = p.W / p.P;
   const int kgroups = p.Kpad >> 3;
   const long long total = 2LL * p.B * hp * wp * kgroups;
@@ -158,6 +164,7 @@ __global__ void __launch_bounds__(256) patch_im2col_kernel(const PatchParams p) 
 }
 
 __global__ void cls_rows_kernel(float* x, const float* cls, const float* pos, int n_img, int seq_len, int D) {
+  pdl_wait();
   const int idx = blockIdx.x * blockDim.x + threadIdx.x;
   if (idx >= n_img * D) return;
   const int img = idx / D, d = idx - img * D;
@@ -167,6 +174,7 @@ __global__ void cls_rows_kernel(float* x, const float* cls, const float* pos, in
 // ------------------------------------------------------------------------------------------------ pixel shuffle
 template <typename T, int VEC>
 __global__ void __launch_bounds__(256) shuffle_kernel(const T* in, T* out, int n, int h, int w, int k, int C) {
+  pdl_wait();
   const int cg = C / VEC;
   const long long total = (long long)n * h * w * k * k * cg;
   const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
@@ -188,6 +196,7 @@ __global__ void __launch_bounds__(256) shuffle_kernel(const T* in, T* out, int n
 // ------------------------------------------------------------------------------------------------ 3x3 s2 im2col
 __global__ void __launch_bounds__(256) im2col_s2_kernel(const __nv_bfloat16* in, __nv_bfloat16* out, int n, int h, int w,
                                                        int C, int oh, int ow) {
+  pdl_wait();
   const int cg = C >> 3;
   const long long total = (long long)n * oh * ow * 9 * cg;
   const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
@@ -234,6 +243,7 @@ template <typename T>
 __global__ void __launch_bounds__(256) resize_ac_kernel(const T* __restrict__ in, int h, int w, int C, float sy, float sx,
                                                        int oh, int ow, float* __restrict__ out_f32,
                                                        __nv_bfloat16* __restrict__ out_bf16) {
+  pdl_wait();
   constexpr int V = 16 / sizeof(T);
   const unsigned cg = (unsigned)C / V;
   const unsigned t = blockIdx.x * 256u + threadIdx.x;
@@ -368,6 +378,7 @@ __device__ __forceinline__ void refine_rows(const uint4* __restrict__ f2, long l
 }
 
 __global__ void __launch_bounds__(128, REFINE_MIN_BLOCKS) refine_kernel(const RefineParams p) {
+  pdl_wait();
   const int x = blockIdx.x * 32 + (threadIdx.x & 31);
   const int y = blockIdx.y * 4 + (threadIdx.x >> 5);
   const int b = blockIdx.z;
@@ -436,6 +447,7 @@ __global__ void __launch_bounds__(128, REFINE_MIN_BLOCKS) refine_kernel(const Re
 template <int K, int CG>
 __global__ void __launch_bounds__(256) desc_shuffle_kernel(const uint4* __restrict__ z, uint4* __restrict__ desc, int n, int h,
                                                           int w, int k_rt, int cg_rt) {
+  pdl_wait();
   // one block row (blockIdx.y) = one token (img, ty, tx); threads enumerate its k*k*cg chunks contiguously.  K, CG > 0:
   // compile-time constants (divisions by constants); K == 0: runtime values.
   const int k = K ? K : k_rt, cg = CG ? CG : cg_rt;
@@ -455,6 +467,7 @@ __global__ void __launch_bounds__(256) desc_shuffle_kernel(const uint4* __restri
 }
 
 __global__ void __launch_bounds__(256) nhwc_to_nchw_kernel(const float* in, float* out, int n, int H, int W, int C) {
+  pdl_wait();
   const long long total = (long long)n * H * W * C;
   const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;  // output index (n,c,y,x)
   if (idx >= total) return;
@@ -467,13 +480,21 @@ __global__ void __launch_bounds__(256) nhwc_to_nchw_kernel(const float* in, floa
 
 inline unsigned blocks_for(long long total, int per) { return (unsigned)((total + per - 1) / per); }
 
+int g_pdl = -1;  // -1: not decided yet (UFM_NO_PDL in the environment turns programmatic launches off)
+
 }  // namespace
+
+int pdl_mode() {
+  if (g_pdl < 0) g_pdl = getenv("UFM_NO_PDL") ? 0 : 1;
+  return g_pdl;
+}
+void set_pdl_mode(int v) { g_pdl = v ? 1 : 0; }
 
 cudaError_t launch_layernorm(const LNParams& p, cudaStream_t stream) {
   if ((p.D & 127) || p.D > 128 * LN_MAXV) return cudaErrorInvalidValue;
   const long long rows = (long long)p.n_seq * p.tokens;
   if (rows == 0) return cudaSuccess;
-  layernorm_kernel<<<blocks_for(rows, 8), 256, 0, stream>>>(p);
+  launch_k(layernorm_kernel, blocks_for(rows, 8), 256, 0, stream, p);
   return cudaGetLastError();
 }
 
@@ -483,18 +504,18 @@ cudaError_t launch_qk_norm(__nv_bfloat16* qkv, long long rows, int heads, const 
   if (!do_norm && rope_n <= 0) return cudaSuccess;
   if (rope_n > 0 && rope_w <= 0) return cudaErrorInvalidValue;
   const long long warps = rows * heads * 2;
-  qk_norm_kernel<<<blocks_for(warps, 8), 256, 0, stream>>>(qkv, rows, heads, qw, qb, kw, kb, eps, do_norm, rope_n, rope_w);
+  launch_k(qk_norm_kernel, blocks_for(warps, 8), 256, 0, stream, qkv, rows, heads, qw, qb, kw, kb, eps, do_norm, rope_n, rope_w);
   return cudaGetLastError();
 }
 
 cudaError_t launch_patch_im2col(const PatchParams& p, cudaStream_t stream) {
   const long long total = 2LL * p.B * (p.H / p.P) * (p.W / p.P) * (p.Kpad / 8);
-  patch_im2col_kernel<<<blocks_for(total, 256), 256, 0, stream>>>(p);
+  launch_k(patch_im2col_kernel, blocks_for(total, 256), 256, 0, stream, p);
   return cudaGetLastError();
 }
 
 cudaError_t launch_cls_rows(float* x, const float* cls, const float* pos, int n_img, int seq_len, int D, cudaStream_t s) {
-  cls_rows_kernel<<<blocks_for((long long)n_img * D, 256), 256, 0, s>>>(x, cls, pos, n_img, seq_len, D);
+  launch_k(cls_rows_kernel, blocks_for((long long)n_img * D, 256), 256, 0, s, x, cls, pos, n_img, seq_len, D);
   return cudaGetLastError();
 }
 
@@ -502,13 +523,13 @@ cudaError_t launch_shuffle_bf16(const __nv_bfloat16* in, __nv_bfloat16* out, int
                                 cudaStream_t s) {
   if (C % 8) return cudaErrorInvalidValue;
   const long long total = (long long)n * h * w * k * k * (C / 8);
-  shuffle_kernel<__nv_bfloat16, 8><<<blocks_for(total, 256), 256, 0, s>>>(in, out, n, h, w, k, C);
+  launch_k(shuffle_kernel<__nv_bfloat16, 8>, blocks_for(total, 256), 256, 0, s, in, out, n, h, w, k, C);
   return cudaGetLastError();
 }
 cudaError_t launch_shuffle_f32(const float* in, float* out, int n, int h, int w, int k, int C, cudaStream_t s) {
   if (C % 4) return cudaErrorInvalidValue;
   const long long total = (long long)n * h * w * k * k * (C / 4);
-  shuffle_kernel<float, 4><<<blocks_for(total, 256), 256, 0, s>>>(in, out, n, h, w, k, C);
+  launch_k(shuffle_kernel<float, 4>, blocks_for(total, 256), 256, 0, s, in, out, n, h, w, k, C);
   return cudaGetLastError();
 }
 
@@ -516,7 +537,7 @@ cudaError_t launch_im2col_s2(const __nv_bfloat16* in, __nv_bfloat16* out, int n,
                              cudaStream_t s) {
   if (C % 8) return cudaErrorInvalidValue;
   const long long total = (long long)n * oh * ow * 9 * (C / 8);
-  im2col_s2_kernel<<<blocks_for(total, 256), 256, 0, s>>>(in, out, n, h, w, C, oh, ow);
+  launch_k(im2col_s2_kernel, blocks_for(total, 256), 256, 0, s, in, out, n, h, w, C, oh, ow);
   return cudaGetLastError();
 }
 
@@ -528,10 +549,10 @@ cudaError_t launch_resize_ac(const float* in_f32, const __nv_bfloat16* in_bf16, 
   if (n == 0) return cudaSuccess;
   if (in_f32) {
     dim3 grid(blocks_for((long long)((ow + RS_STRIP - 1) / RS_STRIP) * (C / 4), 256), oh, n);
-    resize_ac_kernel<float><<<grid, 256, 0, s>>>(in_f32, h, w, C, sy, sx, oh, ow, out_f32, out_bf16);
+    launch_k(resize_ac_kernel<float>, grid, 256, 0, s, in_f32, h, w, C, sy, sx, oh, ow, out_f32, out_bf16);
   } else {
     dim3 grid(blocks_for((long long)((ow + RS_STRIP - 1) / RS_STRIP) * (C / 8), 256), oh, n);
-    resize_ac_kernel<__nv_bfloat16><<<grid, 256, 0, s>>>(in_bf16, h, w, C, sy, sx, oh, ow, out_f32, out_bf16);
+    launch_k(resize_ac_kernel<__nv_bfloat16>, grid, 256, 0, s, in_bf16, h, w, C, sy, sx, oh, ow, out_f32, out_bf16);
   }
   return cudaGetLastError();
 }
@@ -545,20 +566,20 @@ cudaError_t launch_desc_shuffle(const __nv_bfloat16* z, __nv_bfloat16* desc, int
   dim3 grid((per_row + 255) / 256, gy, (unsigned)((rows + gy - 1) / gy));
   const uint4* zi = reinterpret_cast<const uint4*>(z);
   uint4* di = reinterpret_cast<uint4*>(desc);
-  if (k == 14 && cg == 2) desc_shuffle_kernel<14, 2><<<grid, 256, 0, s>>>(zi, di, n, h, w, k, cg);
-  else desc_shuffle_kernel<0, 0><<<grid, 256, 0, s>>>(zi, di, n, h, w, k, cg);
+  if (k == 14 && cg == 2) launch_k(desc_shuffle_kernel<14, 2>, grid, 256, 0, s, zi, di, n, h, w, k, cg);
+  else launch_k(desc_shuffle_kernel<0, 0>, grid, 256, 0, s, zi, di, n, h, w, k, cg);
   return cudaGetLastError();
 }
 
 cudaError_t launch_refine(const RefineParams& p, cudaStream_t s) {
   dim3 grid((p.W + 31) / 32, (p.H + 3) / 4, p.B);
-  refine_kernel<<<grid, 128, 0, s>>>(p);
+  launch_k(refine_kernel, grid, 128, 0, s, p);
   return cudaGetLastError();
 }
 
 cudaError_t launch_nhwc_to_nchw(const float* in, float* out, int n, int H, int W, int C, cudaStream_t s) {
   const long long total = (long long)n * H * W * C;
-  nhwc_to_nchw_kernel<<<blocks_for(total, 256), 256, 0, s>>>(in, out, n, H, W, C);
+  launch_k(nhwc_to_nchw_kernel, blocks_for(total, 256), 256, 0, s, in, out, n, H, W, C);
   return cudaGetLastError();
 }
 

@@ -11,6 +11,7 @@
 #include <stdint.h>
 
 #include "kernels.h"
+#include "launch.cuh"
 
 namespace ufm {
 namespace {
@@ -42,6 +43,7 @@ __device__ __forceinline__ int nearest_src(int dst, int in, int out) {
 // Generic version (any width): 64 pixels x 4 channel quarters per block; one thread = 16 output channels of one pixel.
 // One LDS.128 feeds only 4 FMAs here, so it runs at the shared-memory rate; used when W % 4 != 0.
 __global__ void __launch_bounds__(256) unet_stem_generic_kernel(const UnetStemParams p) {
+  pdl_wait();
   __shared__ __align__(16) float ws[27][64];
   __shared__ float bs[64];
   for (int i = threadIdx.x; i < 27 * 64; i += 256) {
@@ -107,6 +109,7 @@ __global__ void __launch_bounds__(256) unet_stem_generic_kernel(const UnetStemPa
 // flight together; uint8 pixels are normalised through a 3 x 256 table built per block (no per-tap division).
 template <bool U8, bool NHWC>
 __global__ void __launch_bounds__(256, 2) unet_stem_kernel(const UnetStemParams p) {
+  pdl_wait();
   __shared__ __align__(16) float ws[27][64];
   __shared__ float bs[64];
   __shared__ float lut[U8 ? 3 * 256 : 1];
@@ -208,6 +211,7 @@ __global__ void __launch_bounds__(256, 2) unet_stem_kernel(const UnetStemParams 
 // ------------------------------------------------------------------------------------------------ max pool
 __global__ void __launch_bounds__(256) unet_pool_kernel(const bf16* __restrict__ in, long long in_pitch, int n, int H, int W,
                                                        int C, bf16* __restrict__ out, int oh, int ow) {
+  pdl_wait();
   const int cg = C >> 3;
   const long long total = (long long)n * oh * ow * cg;
   const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
@@ -231,6 +235,7 @@ __global__ void __launch_bounds__(256) unet_pool_kernel(const bf16* __restrict__
 __global__ void __launch_bounds__(256) unet_up_kernel(const bf16* __restrict__ g, int n, int h, int w, int C,
                                                      bf16* __restrict__ out, long long out_pitch, int out_off, int oh,
                                                      int ow) {
+  pdl_wait();
   const int cg = C >> 3;
   const long long total = (long long)n * oh * ow * cg;
   const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
@@ -252,6 +257,7 @@ __global__ void __launch_bounds__(256) unet_up_kernel(const bf16* __restrict__ g
 // shared memory feeds 4 * CP FMAs instead of 4 (the one-pixel version ran at the LDS rate).
 constexpr int CP = 2;
 __global__ void __launch_bounds__(128) unet_combine_kernel(const UnetCombineParams p) {
+  pdl_wait();
   __shared__ __align__(16) float wf[64][16];
   __shared__ __align__(16) float w1[32][32];
   __shared__ __align__(16) float w2[32][16];
@@ -411,13 +417,13 @@ cudaError_t launch_unet_stem(const UnetStemParams& p, cudaStream_t s) {
     // 32-bit input offsets in the fast kernel
     if ((long long)p.B * p.H * p.W * 3 >= (1LL << 31)) return cudaErrorInvalidValue;
     dim3 grid(blocks_for((long long)p.H * p.W, 256), 2 * p.B);
-    if (p.is_u8 && p.is_nhwc) unet_stem_kernel<true, true><<<grid, 256, 0, s>>>(p);
-    else if (p.is_u8) unet_stem_kernel<true, false><<<grid, 256, 0, s>>>(p);
-    else if (p.is_nhwc) unet_stem_kernel<false, true><<<grid, 256, 0, s>>>(p);
-    else unet_stem_kernel<false, false><<<grid, 256, 0, s>>>(p);
+    if (p.is_u8 && p.is_nhwc) launch_k(unet_stem_kernel<true, true>, grid, 256, 0, s, p);
+    else if (p.is_u8) launch_k(unet_stem_kernel<true, false>, grid, 256, 0, s, p);
+    else if (p.is_nhwc) launch_k(unet_stem_kernel<false, true>, grid, 256, 0, s, p);
+    else launch_k(unet_stem_kernel<false, false>, grid, 256, 0, s, p);
   } else {
     dim3 grid(blocks_for((long long)p.H * p.W, 64), 2 * p.B);
-    unet_stem_generic_kernel<<<grid, 256, 0, s>>>(p);
+    launch_k(unet_stem_generic_kernel, grid, 256, 0, s, p);
   }
   return cudaGetLastError();
 }
@@ -426,14 +432,14 @@ cudaError_t launch_unet_pool(const __nv_bfloat16* in, long long in_pitch, int n,
                              cudaStream_t s) {
   if (C % 8 || in_pitch % 8) return cudaErrorInvalidValue;
   const int oh = H / 2, ow = W / 2;
-  unet_pool_kernel<<<blocks_for((long long)n * oh * ow * (C / 8), 256), 256, 0, s>>>(in, in_pitch, n, H, W, C, out, oh, ow);
+  launch_k(unet_pool_kernel, blocks_for((long long)n * oh * ow * (C / 8), 256), 256, 0, s, in, in_pitch, n, H, W, C, out, oh, ow);
   return cudaGetLastError();
 }
 
 cudaError_t launch_unet_up(const __nv_bfloat16* g, int n, int h, int w, int C, __nv_bfloat16* out, long long out_pitch,
                            int out_off, int oh, int ow, cudaStream_t s) {
   if (C % 8 || out_pitch % 8 || out_off % 8) return cudaErrorInvalidValue;
-  unet_up_kernel<<<blocks_for((long long)n * oh * ow * (C / 8), 256), 256, 0, s>>>(g, n, h, w, C, out, out_pitch, out_off,
+  launch_k(unet_up_kernel, blocks_for((long long)n * oh * ow * (C / 8), 256), 256, 0, s, g, n, h, w, C, out, out_pitch, out_off,
                                                                                  oh, ow);
   return cudaGetLastError();
 }
@@ -441,7 +447,7 @@ cudaError_t launch_unet_up(const __nv_bfloat16* g, int n, int h, int w, int C, _
 cudaError_t launch_unet_combine(const UnetCombineParams& p, cudaStream_t s) {
   if (p.method != 1 && p.method != 2) return cudaErrorInvalidValue;
   dim3 grid(blocks_for((long long)p.H * p.W, 128 * CP), p.n);
-  unet_combine_kernel<<<grid, 128, 0, s>>>(p);
+  launch_k(unet_combine_kernel, grid, 128, 0, s, p);
   return cudaGetLastError();
 }
 
