@@ -141,7 +141,8 @@ def test_conv3x3_tail_epilogue():
     assert (y1 - ref1).abs().max().item() < 1e-5
 
 
-@pytest.mark.parametrize("n_seq,seq_len,heads", [(2, 193, 6), (3, 1201, 2), (1, 2400, 3), (2, 130, 2), (1, 256, 1), (2, 384, 2)])
+@pytest.mark.parametrize("n_seq,seq_len,heads", [(2, 193, 6), (3, 1201, 2), (1, 2400, 3), (2, 130, 2), (1, 256, 1), (2, 384, 2),
+                                                   (1, 4801, 2), (1, 9600, 1)])  # the last two: 1120x840 encoder / info sharing
 def test_attention(n_seq, seq_len, heads):
     import gpu_ops as ops
 

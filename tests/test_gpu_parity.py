@@ -340,3 +340,32 @@ def test_unet_branch_full_resolution():
     _report("ufm_refine_unet", rows)
     for k, r, m, s in rows:
         assert r <= FEAT_TOL, (k, r)
+
+
+def test_tiny_hires_vs_oracle():
+    """BASELINE.json configs[3] geometry (1120x840: 4801-token encoder attention, 9600-token global attention, convs up
+    to 840x1120) on the slim architecture, so the CPU oracle finishes in seconds: every kernel at its largest tiling."""
+    from ufm_b200.configs import tiny
+
+    cfg = tiny(False, inference_resolution=(1120, 840))
+    sd = make_state_dict(cfg, seed=0, out_gain=8.0)
+    model = UniFlowMatchConfidence(max_pairs_per_call=1, **cfg).to("cuda")
+    model.load_state_dict(sd)
+    src, tgt = make_inputs(1, 840, 1120, seed=9)
+    s0, s1 = O.canonicalize_inputs(src, tgt, "dinov2", None)
+    with torch.no_grad():
+        ref = O.forward_stages(s0, s1, sd, cfg)
+    out = model.predict_correspondences_batched(src.cuda(), tgt.cuda())
+    torch.cuda.synchronize()
+    eng = next(iter(model._engines.values()))
+    rows = []
+    for k in ("head1_raw", "headu_raw"):
+        a = eng.stage(k).cpu()
+        rows.append((k, rel_l2(a, ref[k]), max_abs(a, ref[k]), ref[k].abs().max().item()))
+    flow = out.flow.flow_output.cpu()
+    rows.append(("flow", rel_l2(flow, ref["flow"]), max_abs(flow, ref["flow"]), ref["flow"].abs().max().item()))
+    _report("tiny@1120x840", rows)
+    for k, r, m, s in rows:
+        assert r <= FLOW_TOL, (k, r)
+    cov = out.covisibility.mask.cpu()
+    assert max_abs(cov, ref["covis"].squeeze(1)) <= 0.25 * rows[1][2] + 1e-5
