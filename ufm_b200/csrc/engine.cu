@@ -208,6 +208,7 @@ struct ufm_engine {
   cudaStream_t copy_st = nullptr;
   cudaEvent_t ev_flow = nullptr, ev_cov = nullptr;
   bool mark_outputs = false;
+  int ln_reverse = getenv("UFM_LN_FWD") ? 0 : 1;
   // ufm_forward_host, small batches (launch-bound: ~330 launches and as many tensor-map encodes per pass): the pass is
   // captured once per (pairs, dtype, layout, keep_aux) into a CUDA graph over the engine-owned staging buffers and replayed
   struct GraphEntry { cudaGraphExec_t exec = nullptr; std::map<std::string, Tensor> stage; int launches = 0; };
@@ -333,6 +334,7 @@ struct ufm_engine {
     p.w = Wf(pre + ".w"); p.b = Wf(pre + ".b");
     if (!p.w || !p.b) return false;
     p.n_seq = n_seq; p.src_seq_len = src_seq_len; p.src_skip = skip; p.tokens = tokens; p.remap_B = remap_B;
+    p.reverse = ln_reverse;
     p.out_bf16 = ob; p.ob_pitch = ob_pitch; p.ob_col = ob_col;
     p.out_f32 = of; p.of_pitch = of_pitch; p.of_col = of_col;
     const double rows = (double)n_seq * tokens;
@@ -1399,6 +1401,7 @@ int ufm_op_layernorm(const float* x, int n_seq, int src_seq_len, int src_skip, i
   LNParams p;
   p.x = x; p.D = D; p.eps = eps; p.w = w; p.b = b;
   p.n_seq = n_seq; p.src_seq_len = src_seq_len; p.src_skip = src_skip; p.tokens = tokens; p.remap_B = remap_B;
+  p.reverse = 1;
   p.out_bf16 = reinterpret_cast<bf16*>(out_bf16); p.ob_pitch = ob_pitch; p.ob_col = ob_col;
   p.out_f32 = out_f32; p.of_pitch = of_pitch; p.of_col = of_col;
   return launch_layernorm(p, reinterpret_cast<cudaStream_t>(stream)) != cudaSuccess;

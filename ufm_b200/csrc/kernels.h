@@ -119,6 +119,7 @@ struct LNParams {
   const float* w; const float* b;
   int n_seq, src_seq_len, src_skip, tokens;   // rows processed: n_seq * tokens
   // destination sequence remap: dseq = (seq / swap_inner) + (seq % swap_inner) * swap_outer_stride ... (see kernel)
+  int reverse;            // 1: process rows last-to-first (L2 reuse between consecutive kernels, see simt.cu)
   int remap_B;            // 0: dseq = seq.  B>0: seq = v*B + b  ->  dseq = b*2 + v   (encoder (view,b) -> info (b,view))
   __nv_bfloat16* out_bf16; long long ob_pitch; long long ob_col;   // element pitch/offset
   float* out_f32; long long of_pitch; long long of_col;

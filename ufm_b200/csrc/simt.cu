@@ -28,9 +28,13 @@ constexpr int LN_MAXV = 8;
 __global__ void __launch_bounds__(256) layernorm_kernel(const LNParams p) {
   pdl_wait();
   const int warps_per_block = blockDim.x >> 5;
-  const long long row = (long long)blockIdx.x * warps_per_block + (threadIdx.x >> 5);
   const long long rows = (long long)p.n_seq * p.tokens;
+  long long row = (long long)blockIdx.x * warps_per_block + (threadIdx.x >> 5);
   if (row >= rows) return;
+  // rows are walked from the last to the first: the kernel before this one (a residual GEMM) wrote x in ascending row
+  // order and x (fp32) is larger than L2, so the rows written last are the ones still resident; and the GEMM after this
+  // one reads the normalised rows in ascending order, i.e. starts with what was written last here
+  if (p.reverse) row = rows - 1 - row;
   const int lane = threadIdx.x & 31;
   const int seq = (int)(row / p.tokens);
   const int t = (int)(row - (long long)seq * p.tokens);
