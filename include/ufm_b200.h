@@ -58,6 +58,9 @@ typedef struct ufm_config {
   /* custom_positional_encoding="rope" of the global-attention info sharing (global_attention_transformer.py:110-113:
    * RoPE2D(freq=100, F0=1) on q and k of every block, positions = the patch grid of each view). 0/1. */
   int info_rope;
+  /* FlowAdaptor.output_normalized_coordinate (adaptors.py:110-118): flow = raw * flow_scale + flow_shift - (x, y) of the
+   * pixel, with flow_scale = flow_shift = (W/2, H/2).  0/1. */
+  int flow_coord;
 } ufm_config;
 
 /* adaptor kinds and their channel counts: mask 1 ('non_occluded_mask'), covariance 3 ('flow_cov'), confidence 1

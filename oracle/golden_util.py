@@ -19,6 +19,9 @@ GOLDEN_CASES = {
     "tiny_cross": dict(cfg="tiny_cross", batch=2, out_gain=8.0),
     # RoPE2D on the global-attention info sharing (custom_positional_encoding="rope"), with qk-norm
     "tiny_rope": dict(cfg="tiny_rope", batch=2, out_gain=8.0),
+    # FlowAdaptor.output_normalized_coordinate on the Refine model (the head predicts normalised landing positions);
+    # a small head gain keeps the predicted positions inside the image
+    "tiny_coord": dict(cfg="tiny_coord", batch=2, out_gain=0.05),
     # UNet fine-feature branch of UFM-Refine, both combine methods
     "tiny_unet": dict(cfg="tiny_unet", batch=2, out_gain=8.0),
     "tiny_unet_mod": dict(cfg="tiny_unet_mod", batch=1, out_gain=8.0),

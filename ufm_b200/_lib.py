@@ -13,7 +13,7 @@ LIB_PATH = os.path.join(_HERE, "libufm_b200.so")
 
 UFM_F32, UFM_BF16, UFM_U8 = 0, 1, 2
 UFM_NCHW, UFM_NHWC = 0, 1
-GEMM_GELU, GEMM_RELU_BF16, GEMM_TAIL, GEMM_TAIL_SIGMOID = 1, 2, 4, 8
+GEMM_GELU, GEMM_RELU_BF16, GEMM_TAIL, GEMM_TAIL_SIGMOID, GEMM_TAIL_COORD = 1, 2, 4, 8, 16
 ADAPT_MASK, ADAPT_COV_EXP_TANH, ADAPT_CONF_EXP, ADAPT_CONF_SIGMOID, ADAPT_CONF_SOFTMAX = 1, 2, 3, 4, 5
 PROFILE_CATS = ("gemm", "conv3x3", "attention", "layernorm", "resize", "move", "refine")
 
@@ -39,6 +39,7 @@ class UfmConfig(C.Structure):
         ("unc_vmin", C.c_float * 4), ("unc_vmax", C.c_float * 4),
         ("unet", C.c_int),
         ("info_rope", C.c_int),
+        ("flow_coord", C.c_int),
     ]
 
 

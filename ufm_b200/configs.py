@@ -128,6 +128,12 @@ def tiny(refine: bool = False, inference_resolution=(224, 168), info_sharing_str
     return cfg
 
 
+def _coord(cfg):
+    """FlowAdaptor predicting the landing position (output_normalized_coordinate, adaptors.py:110-118)."""
+    cfg["adaptors_kwargs"]["flow"]["kwargs"]["output_normalized_coordinate"] = True
+    return cfg
+
+
 CONFIGS = {
     "ufm_base_assumed": ufm_base_assumed,
     "ufm_refine_assumed": ufm_refine_assumed,
@@ -137,6 +143,7 @@ CONFIGS = {
     "tiny_cov": lambda: tiny(False, unc_adaptors="cov_conf_mask"),
     "tiny_cross": lambda: tiny(True, info_sharing_str="cross_attention", qk_norm=True),
     "tiny_rope": lambda: tiny(False, qk_norm=True, rope=True),
+    "tiny_coord": lambda: _coord(tiny(True)),
     "tiny_unet": lambda: tiny(True, unet="conv"),
     "tiny_unet_mod": lambda: tiny(True, unet="modulate"),
     "ufm_refine_unet": lambda: dict(ufm_refine_assumed(), use_unet_feature=True, feature_combine_method="conv"),

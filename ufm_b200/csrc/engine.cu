@@ -625,7 +625,7 @@ bool ufm_engine::dpt_head(const std::string& hp, int Bp, int out_ch, bool sigmoi
   {
     Epi e;
     e.bias = Wf(hp + ".proc.c2.b");
-    e.flags = GEMM_TAIL | (sigmoid ? GEMM_TAIL_SIGMOID : 0);
+    e.flags = GEMM_TAIL | (sigmoid ? GEMM_TAIL_SIGMOID : 0) | ((hp == "h1" && cfg.flow_coord) ? GEMM_TAIL_COORD : 0);
     e.w2 = Wf(hp + ".proc.out.w");
     const Tensor* b2 = W(hp + ".proc.out.b");
     if (!e.w2 || !b2) return false;

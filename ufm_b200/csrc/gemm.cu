@@ -634,6 +634,8 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_kernel(const __grid_constant
               if (p.out2) p.out2[idx] = t;
               if (p.flags & GEMM_TAIL_SIGMOID) t = 1.0f / (1.0f + __expf(-t));
               else t = t * p.tail_scale[o] + p.tail_shift[o];
+              // FlowAdaptor.output_normalized_coordinate (adaptors.py:110-118): the head predicts the landing position
+              if ((p.flags & GEMM_TAIL_COORD) && o < 2) t -= (float)(o == 0 ? x : y);
               p.out_f32[idx] = t;
             }
           }

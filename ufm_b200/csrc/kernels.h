@@ -33,6 +33,7 @@ enum : uint32_t {
   GEMM_RELU_BF16 = 1u << 1,
   GEMM_TAIL = 1u << 2,
   GEMM_TAIL_SIGMOID = 1u << 3,
+  GEMM_TAIL_COORD = 1u << 4,   // TAIL: after the affine, subtract the pixel's (x, y) from channels (0, 1)
 };
 
 // Epilogue paths of the GEMM kernel (chosen per launch by the host, engine.cu build_gemm):

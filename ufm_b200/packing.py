@@ -64,7 +64,9 @@ def flow_affine(cfg, H, W):
         raise NotImplementedError("engine flow head supports a single FlowAdaptor named 'flow' (ufm.py:645)")
     kw = a["flow"]["kwargs"]
     if kw.get("output_normalized_coordinate", False):
-        raise NotImplementedError("FlowAdaptor.output_normalized_coordinate is not built into the tail epilogue")
+        # adaptors.py:110-118: 0.5 (x + 1) (W, H) + 0.5 - (px + 0.5, py + 0.5) = x W/2 + W/2 - px; the tail epilogue
+        # subtracts the pixel index (ufm_config.flow_coord)
+        return (0.5 * W, 0.5 * H), (0.5 * W, 0.5 * H)
     bh, bw = kw["base_shape"]
     sx, sy = {"none": (1.0, 1.0), "scale_width": (W / bw, W / bw), "scale_height": (H / bh, H / bh),
               "scale_both": (W / bw, H / bh)}[kw.get("scale_strategy", "none")]
@@ -132,6 +134,7 @@ def engine_config(cfg: Dict[str, Any]) -> "_lib.UfmConfig":
     c.flow_out_ch = pr["output_dim"]
     (s0, s1), (b0, b1) = flow_affine(cfg, H, W)
     c.flow_scale[0], c.flow_scale[1], c.flow_shift[0], c.flow_shift[1] = s0, s1, b0, b1
+    c.flow_coord = int(bool(cfg["adaptors_kwargs"]["flow"]["kwargs"].get("output_normalized_coordinate", False)))
     c.unc_out_ch = 0
     if cfg.get("uncertainty_head_kwargs"):
         # AdaptorMap order (ufm.py:553-556); names are the ones ufm.py:644-660 consumes
