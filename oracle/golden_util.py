@@ -17,6 +17,8 @@ GOLDEN_CASES = {
     "tiny_cov": dict(cfg="tiny_cov", batch=2, out_gain=1.0),
     # per-view cross-attention info sharing, Refine model, qk-norm on
     "tiny_cross": dict(cfg="tiny_cross", batch=2, out_gain=8.0),
+    # cross-attention info sharing with norm_cross_tokens=False (norm_y = Identity)
+    "tiny_cross_raw": dict(cfg="tiny_cross_raw", batch=2, out_gain=8.0),
     # RoPE2D on the global-attention info sharing (custom_positional_encoding="rope"), with qk-norm
     "tiny_rope": dict(cfg="tiny_rope", batch=2, out_gain=8.0),
     # FlowAdaptor.output_normalized_coordinate on the Refine model (the head predicts normalised landing positions);

@@ -128,6 +128,12 @@ def tiny(refine: bool = False, inference_resolution=(224, 168), info_sharing_str
     return cfg
 
 
+def _raw_cross(cfg):
+    """Cross-attention info sharing without the norm on the cross tokens (norm_cross_tokens=False)."""
+    cfg["info_sharing_kwargs"]["norm_cross_tokens"] = False
+    return cfg
+
+
 def _coord(cfg):
     """FlowAdaptor predicting the landing position (output_normalized_coordinate, adaptors.py:110-118)."""
     cfg["adaptors_kwargs"]["flow"]["kwargs"]["output_normalized_coordinate"] = True
@@ -142,6 +148,7 @@ CONFIGS = {
     "tiny_refine": lambda: tiny(True),
     "tiny_cov": lambda: tiny(False, unc_adaptors="cov_conf_mask"),
     "tiny_cross": lambda: tiny(True, info_sharing_str="cross_attention", qk_norm=True),
+    "tiny_cross_raw": lambda: _raw_cross(tiny(False, info_sharing_str="cross_attention")),
     "tiny_rope": lambda: tiny(False, qk_norm=True, rope=True),
     "tiny_coord": lambda: _coord(tiny(True)),
     "tiny_unet": lambda: tiny(True, unet="conv"),

@@ -331,8 +331,11 @@ struct ufm_engine {
                  long long of_col = 0) {
     LNParams p;
     p.x = x; p.D = D; p.eps = 1e-6f;
-    p.w = Wf(pre + ".w"); p.b = Wf(pre + ".b");
-    if (!p.w || !p.b) return false;
+    // an absent norm (CrossAttentionBlock.norm_y = nn.Identity() when norm_cross_tokens=False, transformer_blocks.py:458)
+    // runs the same kernel as a plain fp32 -> bf16 conversion
+    const bool identity = pre.size() > 4 && pre.compare(pre.size() - 4, 4, ".lny") == 0 && !has(pre + ".w");
+    p.w = identity ? nullptr : Wf(pre + ".w"); p.b = identity ? nullptr : Wf(pre + ".b");
+    if (!identity && (!p.w || !p.b)) return false;
     p.n_seq = n_seq; p.src_seq_len = src_seq_len; p.src_skip = skip; p.tokens = tokens; p.remap_B = remap_B;
     p.reverse = ln_reverse;
     p.out_bf16 = ob; p.ob_pitch = ob_pitch; p.ob_col = ob_col;

@@ -67,13 +67,15 @@ __global__ void __launch_bounds__(256) layernorm_kernel(const LNParams p) {
   for (int i = 0; i < LN_MAXV; ++i)
     if (i < nv) {
       const int col = (i * 32 + lane) * 4;
-      const float4 w = __ldg(reinterpret_cast<const float4*>(p.w + col));
-      const float4 b = __ldg(reinterpret_cast<const float4*>(p.b + col));
-      float4 y;
-      y.x = (v[i].x - mean) * rstd * w.x + b.x;
-      y.y = (v[i].y - mean) * rstd * w.y + b.y;
-      y.z = (v[i].z - mean) * rstd * w.z + b.z;
-      y.w = (v[i].w - mean) * rstd * w.w + b.w;
+      float4 y = v[i];  // p.w == nullptr: nn.Identity in place of the norm (a dtype / layout conversion only)
+      if (p.w) {
+        const float4 w = __ldg(reinterpret_cast<const float4*>(p.w + col));
+        const float4 b = __ldg(reinterpret_cast<const float4*>(p.b + col));
+        y.x = (v[i].x - mean) * rstd * w.x + b.x;
+        y.y = (v[i].y - mean) * rstd * w.y + b.y;
+        y.z = (v[i].z - mean) * rstd * w.z + b.z;
+        y.w = (v[i].w - mean) * rstd * w.w + b.w;
+      }
       if (p.out_bf16) {
         uint2 o = make_uint2(pack_bf16(y.x, y.y), pack_bf16(y.z, y.w));
         *reinterpret_cast<uint2*>(p.out_bf16 + drow * p.ob_pitch + p.ob_col + col) = o;

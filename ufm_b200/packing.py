@@ -84,8 +84,6 @@ def engine_config(cfg: Dict[str, Any]) -> "_lib.UfmConfig":
     if cfg["info_sharing_str"] == "cross_attention":
         if ik.get("num_views", 2) != 2:
             raise AssertionError("Expected 2 views")  # cross_attention_transformer.py:382-384 with UFM's two views
-        if not ik.get("norm_cross_tokens", True):
-            raise NotImplementedError("norm_cross_tokens=False (the K/V GEMM reads the LayerNorm kernel's bf16 output)")
     cpe = ik.get("custom_positional_encoding")
     if cpe is not None:
         # only the global-attention transformer maps the string "rope" to RoPE2D (global_attention_transformer.py:110-115);
@@ -260,7 +258,8 @@ def pack_weights(cfg: Dict[str, Any], sd: Dict[str, torch.Tensor]) -> Dict[str, 
                 if src + "attn.qkv.bias" in sd:
                     out[dst + ".qkv.b"] = g("attn.qkv.bias")
                 out[dst + ".proj.w"], out[dst + ".proj.b"] = bf(g("attn.proj.weight")), g("attn.proj.bias")
-                out[dst + ".lny.w"], out[dst + ".lny.b"] = g("norm_y.weight"), g("norm_y.bias")
+                if src + "norm_y.weight" in sd:  # nn.Identity() when norm_cross_tokens=False (transformer_blocks.py:463)
+                    out[dst + ".lny.w"], out[dst + ".lny.b"] = g("norm_y.weight"), g("norm_y.bias")
                 out[dst + ".ln2.w"], out[dst + ".ln2.b"] = g("norm2.weight"), g("norm2.bias")
                 out[dst + ".cq.w"] = bf(g("cross_attn.projq.weight"))
                 out[dst + ".ckv.w"] = bf(torch.cat([g("cross_attn.projk.weight"), g("cross_attn.projv.weight")], 0))
