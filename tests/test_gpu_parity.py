@@ -369,3 +369,27 @@ def test_tiny_hires_vs_oracle():
         assert r <= FLOW_TOL, (k, r)
     cov = out.covisibility.mask.cpu()
     assert max_abs(cov, ref["covis"].squeeze(1)) <= 0.25 * rows[1][2] + 1e-5
+
+
+def test_multiple_inference_resolutions():
+    """base.py:86-98: a list of trained resolutions; AutomaticShapeSelection picks the closest aspect (first on ties).
+    One engine per resolution behind the same model object; checked against the oracle's API shell."""
+    from ufm_b200.configs import tiny
+
+    cfg = tiny(False)
+    cfg["inference_resolution"] = [[224, 168], [168, 224]]  # (W, H): landscape and portrait
+    sd = make_state_dict(cfg, seed=0, out_gain=8.0)
+    model = UniFlowMatchConfidence(**cfg).to("cuda")
+    model.load_state_dict(sd)
+    for (H0, W0) in [(168, 224), (224, 168), (300, 200), (120, 200)]:
+        src, tgt = make_inputs(2, H0, W0, seed=H0)
+        with torch.no_grad():
+            ref = O.predict_correspondences_batched(src, tgt, sd, cfg)
+        out = model.predict_correspondences_batched(src.cuda(), tgt.cuda())
+        flow = out.flow.flow_output.cpu()
+        assert flow.shape == (2, 2, H0, W0)
+        r = rel_l2(flow, ref["flow"])
+        print(f"\n[multi-res {H0}x{W0}] flow rel-L2 {r:.3e}")
+        assert r <= FLOW_TOL, (H0, W0, r)
+        assert (out.covisibility.mask.cpu() - ref["covisibility"]).abs().mean().item() < 1e-2
+    assert len(model._engines) == 2

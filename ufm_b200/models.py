@@ -216,11 +216,21 @@ class UniFlowMatchModelsBase(nn.Module):
         self._engines = {}
         return torch.nn.modules.module._IncompatibleKeys(missing, unexpected)
 
-    def _engine(self, device) -> Engine:
+    def _resolutions(self):
+        """Trained resolutions as (H, W) (base.py:86-98 accepts one (W, H) or a list of them)."""
+        res = self.inference_resolution
+        res = [res] if isinstance(res[0], int) else res
+        return [(int(r[1]), int(r[0])) for r in res]
+
+    def _engine(self, device, hw=None) -> Engine:
+        """One engine (weight replica + workspace) per device and trained resolution, created on first use."""
         device = torch.device(device)
-        key = (device.type, device.index if device.index is not None else torch.cuda.current_device())
+        hw = tuple(hw) if hw is not None else self._resolutions()[0]
+        assert hw in self._resolutions(), f"{hw} is not one of the model's inference resolutions {self._resolutions()}"
+        key = (device.type, device.index if device.index is not None else torch.cuda.current_device(), hw)
         if key not in self._engines:
-            self._engines[key] = Engine(self.config, self.state_dict(), device, self.max_pairs_per_call)
+            cfg = dict(self.config, inference_resolution=[hw[1], hw[0]])
+            self._engines[key] = Engine(cfg, self.state_dict(), device, self.max_pairs_per_call)
         return self._engines[key]
 
     def _device(self):
@@ -231,10 +241,8 @@ class UniFlowMatchModelsBase(nn.Module):
         """img0/img1 at the inference resolution, uint8 or normalised fp32, on CUDA."""
         if img0.shape != img1.shape:
             raise NotImplementedError("Unequal Image sizes are not supported now")  # ufm.py:316-317
-        eng = self._engine(img0.device)
-        H, W = eng.H, eng.W
-        hw = img0.shape[1:3] if layout == _lib.UFM_NHWC else img0.shape[2:4]
-        assert tuple(hw) == (H, W), f"engine prepared for {(H, W)}, got {tuple(hw)}"
+        hw = tuple(img0.shape[1:3] if layout == _lib.UFM_NHWC else img0.shape[2:4])
+        eng = self._engine(img0.device, hw)
         eng.set_keep_aux(keep_aux)
         flows, covs, aux, unc = [], [], [], []
         B = img0.shape[0]
@@ -260,7 +268,8 @@ class UniFlowMatchModelsBase(nn.Module):
         """Host uint8 / normalised fp32 images at the inference resolution -> pinned host (flow, covisibility)."""
         if img0.shape != img1.shape:
             raise NotImplementedError("Unequal Image sizes are not supported now")  # ufm.py:316-317
-        eng = self._engine(self._device())
+        hw = tuple(img0.shape[1:3] if layout == _lib.UFM_NHWC else img0.shape[2:4])
+        eng = self._engine(self._device(), hw)
         eng.set_keep_aux(False)
         B = img0.shape[0]
         flow = torch.empty(B, 2, eng.H, eng.W, dtype=torch.float32, pin_memory=True)
@@ -328,10 +337,12 @@ class UniFlowMatchModelsBase(nn.Module):
         dev = self._device()
         if dev.type != "cuda":
             raise RuntimeError("ufm_b200 models run on CUDA only: call .to('cuda') (there is no CPU fallback)")
-        H, W = inference_hw(self.config) if isinstance(self.inference_resolution[0], int) else (None, None)
         hw0 = tuple(source_image.shape[1:3] if layout == _lib.UFM_NHWC else source_image.shape[2:4])
         hw1 = tuple(target_image.shape[1:3] if layout == _lib.UFM_NHWC else target_image.shape[2:4])
-        native = hw0 == (H, W) and hw1 == (H, W)
+        # AutomaticShapeSelection (flow_resizing.py:667-694): the trained resolution of closest aspect, first entry on ties
+        res_wh = [(w, h) for h, w in self._resolutions()]
+        pick = prepost.closest_aspect(res_wh, hw0[0], hw0[1], hw1[0], hw1[1])
+        native = hw0 == hw1 == tuple(pick)  # resize and un-map are then the identity
         renorm = source_image.dtype == torch.float32 and data_norm_type != required
         if native and not renorm and in_device.type == "cpu" and target_image.device.type == "cpu" \
                 and source_image.dtype == target_image.dtype:
@@ -355,9 +366,7 @@ class UniFlowMatchModelsBase(nn.Module):
         else:
             # non-native size or foreign normalisation: normalise + anti-alias resize, forward, un-map -- two CUDA
             # kernels around the engine (csrc/prepost.cu), no torch ops on the data path
-            res = self.inference_resolution
-            res = [res] if isinstance(res[0], int) else res
-            th, tw = prepost.closest_aspect(res, hw0[0], hw0[1], hw1[0], hw1[1])
+            th, tw = pick
             nhwc = layout == _lib.UFM_NHWC
             s0 = prepost.prep_resize(src, nhwc, th, tw, required, data_norm_type)
             s1 = prepost.prep_resize(tgt, nhwc, th, tw, required, data_norm_type)

@@ -29,9 +29,7 @@ def _norm_indices(indices, depth):
 def inference_hw(cfg) -> Tuple[int, int]:
     res = cfg.get("inference_resolution") or [560, 420]
     if not isinstance(res[0], int):
-        if len(res) != 1:
-            raise NotImplementedError("the engine is prepared for one inference resolution per model instance")
-        res = res[0]
+        res = res[0]  # a list of trained resolutions (base.py:86-98): one engine per entry, this is the first
     return int(res[1]), int(res[0])  # (H, W)
 
 
