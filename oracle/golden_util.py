@@ -19,6 +19,8 @@ GOLDEN_CASES = {
     "tiny_cross": dict(cfg="tiny_cross", batch=2, out_gain=8.0),
     # cross-attention info sharing with norm_cross_tokens=False (norm_y = Identity)
     "tiny_cross_raw": dict(cfg="tiny_cross_raw", batch=2, out_gain=8.0),
+    # DPT fusion blocks with (eval-mode) BatchNorm
+    "tiny_bn": dict(cfg="tiny_bn", batch=2, out_gain=8.0),
     # RoPE2D on the global-attention info sharing (custom_positional_encoding="rope"), with qk-norm
     "tiny_rope": dict(cfg="tiny_rope", batch=2, out_gain=8.0),
     # FlowAdaptor.output_normalized_coordinate on the Refine model (the head predicts normalised landing positions);

@@ -255,9 +255,16 @@ def info_sharing(f1: torch.Tensor, f2: torch.Tensor, sd, cfg):
 # DPT head
 # ----------------------------------------------------------------------------------------------
 def _rcu(x, sd, prefix):
-    """``ResidualConvUnit_custom.forward`` (UC/models/libs/croco/dpt_block.py:156-177): x + conv2(relu(conv1(relu(x))))."""
-    o = F.conv2d(F.relu(x), sd[prefix + "conv1.weight"], sd[prefix + "conv1.bias"], padding=1)
-    o = F.conv2d(F.relu(o), sd[prefix + "conv2.weight"], sd[prefix + "conv2.bias"], padding=1)
+    """``ResidualConvUnit_custom.forward`` (UC/models/libs/croco/dpt_block.py:156-177): x + conv2(relu(conv1(relu(x))));
+    with ``use_bn`` the convs have no bias and an eval-mode BatchNorm follows each (:134-149, 164-171)."""
+    def bn(o, k):
+        if prefix + k + ".weight" not in sd:
+            return o
+        return F.batch_norm(o, sd[prefix + k + ".running_mean"], sd[prefix + k + ".running_var"], sd[prefix + k + ".weight"],
+                            sd[prefix + k + ".bias"], training=False, eps=1e-5)
+
+    o = bn(F.conv2d(F.relu(x), sd[prefix + "conv1.weight"], sd.get(prefix + "conv1.bias"), padding=1), "bn1")
+    o = bn(F.conv2d(F.relu(o), sd[prefix + "conv2.weight"], sd.get(prefix + "conv2.bias"), padding=1), "bn2")
     return o + x
 
 

@@ -134,6 +134,13 @@ def _raw_cross(cfg):
     return cfg
 
 
+def _use_bn(cfg):
+    """DPT fusion blocks with BatchNorm (use_bn=True, dpt_block.py:134-149); inference = eval-mode statistics."""
+    for k in ("feature_head_kwargs", "uncertainty_head_kwargs"):
+        cfg[k]["dpt_feature"]["use_bn"] = True
+    return cfg
+
+
 def _coord(cfg):
     """FlowAdaptor predicting the landing position (output_normalized_coordinate, adaptors.py:110-118)."""
     cfg["adaptors_kwargs"]["flow"]["kwargs"]["output_normalized_coordinate"] = True
@@ -150,6 +157,7 @@ CONFIGS = {
     "tiny_cross": lambda: tiny(True, info_sharing_str="cross_attention", qk_norm=True),
     "tiny_cross_raw": lambda: _raw_cross(tiny(False, info_sharing_str="cross_attention")),
     "tiny_rope": lambda: tiny(False, qk_norm=True, rope=True),
+    "tiny_bn": lambda: _use_bn(tiny(False)),
     "tiny_coord": lambda: _coord(tiny(True)),
     "tiny_unet": lambda: tiny(True, unet="conv"),
     "tiny_unet_mod": lambda: tiny(True, unet="modulate"),

@@ -118,8 +118,8 @@ def engine_config(cfg: Dict[str, Any]) -> "_lib.UfmConfig":
     c.info_has_proj = 1
     f = cfg["feature_head_kwargs"]["dpt_feature"]
     pr = cfg["feature_head_kwargs"]["dpt_processor"]
-    if f.get("use_bn") or list(f.get("hooks", [0, 1, 2, 3])) != [0, 1, 2, 3]:
-        raise NotImplementedError("DPT use_bn / hooks != [0,1,2,3]")
+    if list(f.get("hooks", [0, 1, 2, 3])) != [0, 1, 2, 3]:
+        raise NotImplementedError("DPT hooks != [0,1,2,3]")
     for i in range(4):
         c.dpt_layer_dims[i] = f["layer_dims"][i]
     c.dpt_feature_dim = f["feature_dim"]
@@ -310,8 +310,17 @@ def pack_weights(cfg: Dict[str, Any], sd: Dict[str, torch.Tensor]) -> Dict[str, 
             out[f"{dst}.ref{r}.out.w"], out[f"{dst}.ref{r}.out.b"] = bf(w.reshape(w.shape[0], -1)), sd[q + "out_conv.bias"]
             for u in ((1, 2) if r != 4 else (2,)):
                 for cc in (1, 2):
-                    out[f"{dst}.ref{r}.rcu{u}.c{cc}.w"] = _conv3_pack(sd[f"{q}resConfUnit{u}.conv{cc}.weight"])
-                    out[f"{dst}.ref{r}.rcu{u}.c{cc}.b"] = sd[f"{q}resConfUnit{u}.conv{cc}.bias"]
+                    w = sd[f"{q}resConfUnit{u}.conv{cc}.weight"]
+                    bnp = f"{q}resConfUnit{u}.bn{cc}."
+                    if bnp + "weight" in sd:
+                        # use_bn (dpt_block.py:134-149): eval-mode BatchNorm folded into the bias-free conv
+                        g_ = sd[bnp + "weight"].double() / torch.sqrt(sd[bnp + "running_var"].double() + 1e-5)
+                        b = (sd[bnp + "bias"].double() - g_ * sd[bnp + "running_mean"].double()).float()
+                        w = (w.double() * g_.view(-1, 1, 1, 1)).float()
+                    else:
+                        b = sd[f"{q}resConfUnit{u}.conv{cc}.bias"]
+                    out[f"{dst}.ref{r}.rcu{u}.c{cc}.w"] = _conv3_pack(w)
+                    out[f"{dst}.ref{r}.rcu{u}.c{cc}.b"] = b
         q = src + "0.1."
         out[dst + ".proc.c1.w"], out[dst + ".proc.c1.b"] = _conv3_pack(sd[q + "conv1.weight"]), sd[q + "conv1.bias"]
         out[dst + ".proc.c2.w"], out[dst + ".proc.c2.b"] = _conv3_pack(sd[q + "conv2.0.weight"]), sd[q + "conv2.0.bias"]

@@ -140,8 +140,14 @@ def dpt_head_spec(prefix: str, hk: Dict[str, Any]) -> Spec:
         s += [(q + "out_conv.weight", (fd, fd, 1, 1), "w"), (q + "out_conv.bias", (fd,), "b")]
         for u in ((1, 2) if r != 4 else (2,)):
             for c in (1, 2):
-                s += [(f"{q}resConfUnit{u}.conv{c}.weight", (fd, fd, 3, 3), "w"),
-                      (f"{q}resConfUnit{u}.conv{c}.bias", (fd,), "b")]
+                s += [(f"{q}resConfUnit{u}.conv{c}.weight", (fd, fd, 3, 3), "w")]
+                if not f.get("use_bn"):
+                    s += [(f"{q}resConfUnit{u}.conv{c}.bias", (fd,), "b")]
+            if f.get("use_bn"):  # dpt_block.py:134-149: bias-free convs, each followed by a BatchNorm2d
+                for c in (1, 2):
+                    b = f"{q}resConfUnit{u}.bn{c}."
+                    s += [(b + "weight", (fd,), "ln_w"), (b + "bias", (fd,), "ln_b"), (b + "running_mean", (fd,), "bn_mean"),
+                          (b + "running_var", (fd,), "bn_var"), (b + "num_batches_tracked", (), "bn_count")]
     # input_process.k = Sequential(act_k_postprocess, layer_rn[k])
     ip = p + "input_process."
     s += [(ip + "0.0.0.weight", (ld[0], in_dims[0], 1, 1), "w"), (ip + "0.0.0.bias", (ld[0],), "b"),
@@ -276,6 +282,12 @@ def make_state_dict(cfg: Dict[str, Any], seed: int = 0, out_gain: float = 1.0) -
             t = 0.05 * torch.randn(shape, generator=g)
         elif kind == "gamma":
             t = 0.5 + 0.1 * torch.randn(shape, generator=g)
+        elif kind == "bn_mean":
+            t = 0.1 * torch.randn(shape, generator=g)
+        elif kind == "bn_var":
+            t = 0.5 + torch.rand(shape, generator=g)
+        elif kind == "bn_count":
+            t = torch.tensor(100, dtype=torch.long)
         elif kind == "cls":
             t = 0.02 * torch.randn(shape, generator=g)
         elif kind == "pos":
