@@ -214,7 +214,9 @@ def test_rope2d_vs_oracle():
     assert torch.equal(got[2], o[2])
 
 
-@pytest.mark.parametrize("h,w,rh,rw,oh,ow", [(15, 20, 30, 40, 30, 40), (8, 10, 16, 20, 15, 19), (96, 128, 168, 224, 168, 224)])
+@pytest.mark.parametrize("h,w,rh,rw,oh,ow", [(15, 20, 30, 40, 30, 40), (8, 10, 16, 20, 15, 19), (96, 128, 168, 224, 168, 224),
+                                             (30, 40, 15, 20, 15, 20), (20, 30, 25, 37, 25, 37), (48, 64, 84, 112, 84, 112),
+                                             (6, 7, 40, 61, 40, 61)])
 def test_resize_align_corners(h, w, rh, rw, oh, ow):
     lib = _lib.load()
     n, Cc = 2, 64
@@ -235,6 +237,31 @@ def test_resize_align_corners(h, w, rh, rw, oh, ow):
     # the kernel interpolates vertically first (column values are shared along a strip), torch horizontally first:
     # fp32 rounding-order differences only
     assert (of2 - ref2[:, :, :oh, :ow].permute(0, 2, 3, 1)).abs().max().item() < 5e-5
+
+
+def test_resize_upsampling_kernel_matches_generic(monkeypatch):
+    """The up-front-load kernel used for 7*sx < 4 performs the generic strip kernel's arithmetic: identical bits."""
+    lib = _lib.load()
+    st = torch.cuda.current_stream().cuda_stream
+    for (h, w, oh, ow, Cc) in ((15, 20, 30, 40, 64), (24, 32, 42, 56, 128), (9, 11, 18, 21, 32), (5, 3, 40, 23, 8)):
+        x = _rand(2, h, w, Cc, seed=3)
+        xb = x.bfloat16()
+        outs = []
+        for generic in (False, True):
+            if generic:
+                monkeypatch.setenv("UFM_RESIZE_GENERIC", "1")
+            else:
+                monkeypatch.delenv("UFM_RESIZE_GENERIC", raising=False)
+            of = torch.zeros(2, oh, ow, Cc, device="cuda")
+            ob = torch.zeros(2, oh, ow, Cc, dtype=torch.bfloat16, device="cuda")
+            ob2 = torch.zeros_like(ob)
+            assert lib.ufm_op_resize_ac(x.data_ptr(), None, 2, h, w, Cc, oh, ow, oh, ow, of.data_ptr(), ob.data_ptr(), st) == 0
+            assert lib.ufm_op_resize_ac(None, xb.data_ptr(), 2, h, w, Cc, oh, ow, oh, ow, None, ob2.data_ptr(), st) == 0
+            torch.cuda.synchronize()
+            outs.append((of, ob, ob2))
+        for a, b in zip(*outs):
+            assert torch.equal(a, b)
+        assert outs[0][0].abs().max().item() > 0
 
 
 def test_shuffle_and_convt_fold():

@@ -25,36 +25,39 @@ __device__ __forceinline__ float warp_sum(float v) {
 // One warp per row, the row held in registers (D <= 1024, D % 128 == 0): fp32 two-pass statistics as nn.LayerNorm
 // (transformer_blocks.py norm1/norm2, final `norm` on returned layers: global_attention_transformer.py:546-550,586).
 constexpr int LN_MAXV = 8;
-__global__ void __launch_bounds__(256) layernorm_kernel(const LNParams p) {
-  pdl_wait();
-  const int warps_per_block = blockDim.x >> 5;
-  const long long rows = (long long)p.n_seq * p.tokens;
-  long long row = (long long)blockIdx.x * warps_per_block + (threadIdx.x >> 5);
-  if (row >= rows) return;
+constexpr int LN_BLOCKS_PER_SM = 2;
+struct LNRow {
+  float4 v[LN_MAXV];
+};
+
+__device__ __forceinline__ void ln_load(const LNParams& p, long long rows, long long r, int nv, int lane, LNRow& a) {
   // rows are walked from the last to the first: the kernel before this one (a residual GEMM) wrote x in ascending row
   // order and x (fp32) is larger than L2, so the rows written last are the ones still resident; and the GEMM after this
   // one reads the normalised rows in ascending order, i.e. starts with what was written last here
-  if (p.reverse) row = rows - 1 - row;
-  const int lane = threadIdx.x & 31;
+  const long long row = p.reverse ? rows - 1 - r : r;
   const int seq = (int)(row / p.tokens);
   const int t = (int)(row - (long long)seq * p.tokens);
-  const float* xr = p.x + ((long long)seq * p.src_seq_len + p.src_skip + t) * p.D;
-  const int nv = p.D >> 7;
-  float4 v[LN_MAXV];
+  const float4* xr = reinterpret_cast<const float4*>(p.x + ((long long)seq * p.src_seq_len + p.src_skip + t) * p.D) + lane;
+#pragma unroll
+  for (int i = 0; i < LN_MAXV; ++i)
+    if (i < nv) a.v[i] = __ldg(xr + i * 32);
+}
+
+__device__ __forceinline__ void ln_row(const LNParams& p, long long rows, long long r, int nv, int lane, const LNRow& a) {
+  const long long row = p.reverse ? rows - 1 - r : r;
+  const int seq = (int)(row / p.tokens);
+  const int t = (int)(row - (long long)seq * p.tokens);
   float s = 0.f;
 #pragma unroll
   for (int i = 0; i < LN_MAXV; ++i)
-    if (i < nv) {
-      v[i] = __ldg(reinterpret_cast<const float4*>(xr) + i * 32 + lane);
-      s += v[i].x + v[i].y + v[i].z + v[i].w;
-    }
+    if (i < nv) s += a.v[i].x + a.v[i].y + a.v[i].z + a.v[i].w;
   const float mean = warp_sum(s) / p.D;
   float q = 0.f;
 #pragma unroll
   for (int i = 0; i < LN_MAXV; ++i)
     if (i < nv) {
-      const float a = v[i].x - mean, b = v[i].y - mean, c = v[i].z - mean, d = v[i].w - mean;
-      q += a * a + b * b + c * c + d * d;
+      const float e = a.v[i].x - mean, f = a.v[i].y - mean, g = a.v[i].z - mean, h = a.v[i].w - mean;
+      q += e * e + f * f + g * g + h * h;
     }
   const float rstd = rsqrtf(warp_sum(q) / p.D + p.eps);
   int dseq = seq;
@@ -67,14 +70,14 @@ __global__ void __launch_bounds__(256) layernorm_kernel(const LNParams p) {
   for (int i = 0; i < LN_MAXV; ++i)
     if (i < nv) {
       const int col = (i * 32 + lane) * 4;
-      float4 y = v[i];  // p.w == nullptr: nn.Identity in place of the norm (a dtype / layout conversion only)
+      float4 y = a.v[i];  // p.w == nullptr: nn.Identity in place of the norm (a dtype / layout conversion only)
       if (p.w) {
         const float4 w = __ldg(reinterpret_cast<const float4*>(p.w + col));
         const float4 b = __ldg(reinterpret_cast<const float4*>(p.b + col));
-        y.x = (v[i].x - mean) * rstd * w.x + b.x;
-        y.y = (v[i].y - mean) * rstd * w.y + b.y;
-        y.z = (v[i].z - mean) * rstd * w.z + b.z;
-        y.w = (v[i].w - mean) * rstd * w.w + b.w;
+        y.x = (a.v[i].x - mean) * rstd * w.x + b.x;
+        y.y = (a.v[i].y - mean) * rstd * w.y + b.y;
+        y.z = (a.v[i].z - mean) * rstd * w.z + b.z;
+        y.w = (a.v[i].w - mean) * rstd * w.w + b.w;
       }
       if (p.out_bf16) {
         uint2 o = make_uint2(pack_bf16(y.x, y.y), pack_bf16(y.z, y.w));
@@ -82,6 +85,32 @@ __global__ void __launch_bounds__(256) layernorm_kernel(const LNParams p) {
       }
       if (p.out_f32) *reinterpret_cast<float4*>(p.out_f32 + drow * p.of_pitch + p.of_col + col) = y;
     }
+}
+
+// Persistent: LN_BLOCKS_PER_SM blocks per SM, every warp strides over the rows with the next row's loads in flight
+// while the current one is reduced and stored (two register row buffers, loop unrolled by two so they never move).
+__global__ void __launch_bounds__(256, LN_BLOCKS_PER_SM) layernorm_kernel(const LNParams p) {
+  pdl_wait();
+  const long long rows = (long long)p.n_seq * p.tokens;
+  const long long nw = (long long)gridDim.x * (blockDim.x >> 5);
+  long long r = (long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (r >= rows) return;
+  const int lane = threadIdx.x & 31;
+  const int nv = p.D >> 7;
+  LNRow a, b;
+  ln_load(p, rows, r, nv, lane, a);
+  for (;;) {
+    long long rn = r + nw;
+    if (rn < rows) ln_load(p, rows, rn, nv, lane, b);
+    ln_row(p, rows, r, nv, lane, a);
+    if (rn >= rows) break;
+    r = rn;
+    rn = r + nw;
+    if (rn < rows) ln_load(p, rows, rn, nv, lane, a);
+    ln_row(p, rows, r, nv, lane, b);
+    if (rn >= rows) break;
+    r = rn;
+  }
 }
 
 // per-head LayerNorm of q and k (head_dim 64) and / or 2-D RoPE, in place inside the fused qkv buffer; one warp per
@@ -227,6 +256,9 @@ __global__ void __launch_bounds__(256) im2col_s2_kernel(const __nv_bfloat16* in,
 // channels (4 fp32 / 8 bf16) of one output pixel; a warp covers consecutive channels, then consecutive pixels.
 template <int N>
 struct Vec { float v[N]; };
+// wa * a + wb * b with the contraction spelled out (one rounding of wa * a, then one fused multiply-add), so that every
+// resize kernel produces the same bits whatever the compiler would have chosen to fuse
+__device__ __forceinline__ float blend2(float wa, float a, float wb, float b) { return __fmaf_rn(wb, b, __fmul_rn(wa, a)); }
 __device__ __forceinline__ Vec<4> ldv(const float* p) {
   const float4 t = __ldg(reinterpret_cast<const float4*>(p));
   return Vec<4>{{t.x, t.y, t.z, t.w}};
@@ -268,7 +300,7 @@ __global__ void __launch_bounds__(256) resize_ac_kernel(const T* __restrict__ in
     const Vec<V> a = ldv(r0 + (size_t)x * C), b = ldv(r1 + (size_t)x * C);
     Vec<V> v;
 #pragma unroll
-    for (int i = 0; i < V; ++i) v.v[i] = hy * a.v[i] + ly * b.v[i];
+    for (int i = 0; i < V; ++i) v.v[i] = blend2(hy, a.v[i], ly, b.v[i]);
     return v;
   };
   int c0 = -1, c1 = -1;
@@ -294,7 +326,7 @@ __global__ void __launch_bounds__(256) resize_ac_kernel(const T* __restrict__ in
     }
     float r[V];
 #pragma unroll
-    for (int i = 0; i < V; ++i) r[i] = hx * v0.v[i] + lx * v1.v[i];
+    for (int i = 0; i < V; ++i) r[i] = blend2(hx, v0.v[i], lx, v1.v[i]);
     if (out_f32) {
 #pragma unroll
       for (int i = 0; i < V; i += 4) *reinterpret_cast<float4*>(out_f32 + o + i) = make_float4(r[i], r[i + 1], r[i + 2], r[i + 3]);
@@ -305,6 +337,75 @@ __global__ void __launch_bounds__(256) resize_ac_kernel(const T* __restrict__ in
             make_uint4(pack_bf16(r[0], r[1]), pack_bf16(r[2], r[3]), pack_bf16(r[4], r[5]), pack_bf16(r[6], r[7]));
       else
         *reinterpret_cast<uint2*>(out_bf16 + o) = make_uint2(pack_bf16(r[0], r[1]), pack_bf16(r[2], r[3]));
+    }
+  }
+}
+
+// Upsampling fast path (7 * sx < 4: the eight outputs of a strip touch at most five source columns, six with the +1
+// neighbour).  All twelve source loads of the strip are issued up front (the generic kernel above fetches a column only
+// when an output first needs it: five dependent round trips per thread, long-scoreboard-bound at 50-60 % of HBM with
+// 146 instructions per 16-byte output, ncu simt_v6), the columns are blended vertically once, and the outputs are then
+// emitted source column by source column, so every register index is static and nothing is moved or re-tested.
+// Arithmetic (fy, fx, the two blends and their order) is the generic kernel's: results are bit-identical.
+constexpr int RS_NC = 6;
+template <typename T>
+__global__ void __launch_bounds__(256, 3) resize_ac_up_kernel(const T* __restrict__ in, int h, int w, int C, float sy, float sx,
+                                                             int oh, int ow, float* __restrict__ out_f32,
+                                                             __nv_bfloat16* __restrict__ out_bf16) {
+  pdl_wait();
+  constexpr int V = 16 / sizeof(T);
+  const unsigned cg = (unsigned)C / V;
+  const unsigned t = blockIdx.x * 256u + threadIdx.x;
+  const unsigned strip = t / cg;
+  const int ox0 = (int)(strip * RS_STRIP);
+  if (ox0 >= ow) return;
+  const unsigned g = t - strip * cg;
+  const int oy = blockIdx.y, nn = blockIdx.z;
+  const float fy = sy * oy;
+  const int y0 = (int)fy;
+  const int y1 = y0 + (y0 < h - 1 ? 1 : 0);
+  const float ly = fy - y0, hy = 1.f - ly;
+  const T* r0 = in + ((size_t)nn * h + y0) * w * C + g * V;
+  const T* r1 = in + ((size_t)nn * h + y1) * w * C + g * V;
+  const int xb = (int)(sx * ox0);
+  Vec<V> a[RS_NC], b[RS_NC];
+#pragma unroll
+  for (int j = 0; j < RS_NC; ++j) {
+    const int x = min(xb + j, w - 1);
+    a[j] = ldv(r0 + (size_t)x * C);
+    b[j] = ldv(r1 + (size_t)x * C);
+  }
+#pragma unroll
+  for (int j = 0; j < RS_NC; ++j)
+#pragma unroll
+    for (int i = 0; i < V; ++i) a[j].v[i] = blend2(hy, a[j].v[i], ly, b[j].v[i]);
+  const int kend = min(RS_STRIP, ow - ox0);
+  size_t o = (((size_t)nn * oh + oy) * ow + ox0) * C + g * V;
+  int k = 0;
+  float fx = sx * ox0;
+  int x0 = xb;
+#pragma unroll
+  for (int j = 0; j < RS_NC - 1; ++j) {
+    while (k < kend && x0 == xb + j) {
+      const float lx = fx - x0, hx = 1.f - lx;
+      float r[V];
+#pragma unroll
+      for (int i = 0; i < V; ++i) r[i] = blend2(hx, a[j].v[i], lx, a[j + 1].v[i]);
+      if (out_f32) {
+#pragma unroll
+        for (int i = 0; i < V; i += 4) *reinterpret_cast<float4*>(out_f32 + o + i) = make_float4(r[i], r[i + 1], r[i + 2], r[i + 3]);
+      }
+      if (out_bf16) {
+        if constexpr (V == 8)
+          *reinterpret_cast<uint4*>(out_bf16 + o) =
+              make_uint4(pack_bf16(r[0], r[1]), pack_bf16(r[2], r[3]), pack_bf16(r[4], r[5]), pack_bf16(r[6], r[7]));
+        else
+          *reinterpret_cast<uint2*>(out_bf16 + o) = make_uint2(pack_bf16(r[0], r[1]), pack_bf16(r[2], r[3]));
+      }
+      ++k;
+      o += C;
+      fx = sx * (ox0 + k);
+      x0 = (int)fx;
     }
   }
 }
@@ -485,6 +586,18 @@ __global__ void __launch_bounds__(256) nhwc_to_nchw_kernel(const float* in, floa
 }
 
 inline unsigned blocks_for(long long total, int per) { return (unsigned)((total + per - 1) / per); }
+inline int sm_count() {  // of the current device (persistent SIMT grids); cached per device
+  static int cached[64] = {0};
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (dev < 0 || dev >= 64) return 148;
+  if (!cached[dev]) {
+    int n = 0;
+    if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0) n = 148;
+    cached[dev] = n;
+  }
+  return cached[dev];
+}
 
 int g_pdl = -1;  // -1: not decided yet (UFM_NO_PDL in the environment turns programmatic launches off)
 
@@ -500,7 +613,9 @@ cudaError_t launch_layernorm(const LNParams& p, cudaStream_t stream) {
   if ((p.D & 127) || p.D > 128 * LN_MAXV) return cudaErrorInvalidValue;
   const long long rows = (long long)p.n_seq * p.tokens;
   if (rows == 0) return cudaSuccess;
-  launch_k(layernorm_kernel, blocks_for(rows, 8), 256, 0, stream, p);
+  static const int per_sm = getenv("UFM_LN_BLOCKS") ? atoi(getenv("UFM_LN_BLOCKS")) : LN_BLOCKS_PER_SM;  // tuning knob
+  const unsigned need = blocks_for(rows, 8), cap = per_sm > 0 ? (unsigned)(sm_count() * per_sm) : need;
+  launch_k(layernorm_kernel, need < cap ? need : cap, 256, 0, stream, p);
   return cudaGetLastError();
 }
 
@@ -553,12 +668,16 @@ cudaError_t launch_resize_ac(const float* in_f32, const __nv_bfloat16* in_bf16, 
   const float sy = rh > 1 ? (float)(h - 1) / (float)(rh - 1) : 0.f;
   const float sx = rw > 1 ? (float)(w - 1) / (float)(rw - 1) : 0.f;
   if (n == 0) return cudaSuccess;
+  // a strip's last source column is at most floor(7 sx) + 1 past its first: the up-sampling kernel holds RS_NC = 6
+  const bool up = 7.f * sx < 3.998f && !getenv("UFM_RESIZE_GENERIC");
   if (in_f32) {
     dim3 grid(blocks_for((long long)((ow + RS_STRIP - 1) / RS_STRIP) * (C / 4), 256), oh, n);
-    launch_k(resize_ac_kernel<float>, grid, 256, 0, s, in_f32, h, w, C, sy, sx, oh, ow, out_f32, out_bf16);
+    if (up) launch_k(resize_ac_up_kernel<float>, grid, 256, 0, s, in_f32, h, w, C, sy, sx, oh, ow, out_f32, out_bf16);
+    else launch_k(resize_ac_kernel<float>, grid, 256, 0, s, in_f32, h, w, C, sy, sx, oh, ow, out_f32, out_bf16);
   } else {
     dim3 grid(blocks_for((long long)((ow + RS_STRIP - 1) / RS_STRIP) * (C / 8), 256), oh, n);
-    launch_k(resize_ac_kernel<__nv_bfloat16>, grid, 256, 0, s, in_bf16, h, w, C, sy, sx, oh, ow, out_f32, out_bf16);
+    if (up) launch_k(resize_ac_up_kernel<__nv_bfloat16>, grid, 256, 0, s, in_bf16, h, w, C, sy, sx, oh, ow, out_f32, out_bf16);
+    else launch_k(resize_ac_kernel<__nv_bfloat16>, grid, 256, 0, s, in_bf16, h, w, C, sy, sx, oh, ow, out_f32, out_bf16);
   }
   return cudaGetLastError();
 }
