@@ -89,6 +89,11 @@ __device__ __forceinline__ void ln_row(const LNParams& p, long long rows, long l
 
 // Persistent: LN_BLOCKS_PER_SM blocks per SM, every warp strides over the rows with the next row's loads in flight
 // while the current one is reduced and stored (two register row buffers, loop unrolled by two so they never move).
+// 38432 x 1024 fp32 -> bf16 in the ncu launch list: 42.1-42.8 us (5.5 TB/s, 84 % of the measured copy bandwidth)
+// against 43.2-44.4 us for the earlier one-row-per-warp grid of 4804 short-lived blocks (profiles/r01_v5 / r01_v6
+// launches): a small gain, the kernel was already close to the HBM roofline; what the in-step figure (4.4-4.5 TB/s)
+// adds is the launch gap around a 40 us kernel.  Three blocks per SM (85 registers, spills) and one block per SM are
+// both slower (61 / 66 us event-timed against 49).
 __global__ void __launch_bounds__(256, LN_BLOCKS_PER_SM) layernorm_kernel(const LNParams p) {
   pdl_wait();
   const long long rows = (long long)p.n_seq * p.tokens;
