@@ -127,7 +127,8 @@ int ufm_profile_read(ufm_engine* e, double* ms, double* flops, double* bytes, in
 /* Process-wide tuning switches for kernel experiments (no reference counterpart).  which = 0: GEMM epilogue variant
  * (0 = row-per-thread stores, 1 = shared-memory transposed, coalesced stores); which = 1: CTA-pair (cta_group::2) GEMM
  * tiles on/off; which = 2: attention, every n-th exp2 pair on the FMA pipe; which = 3: 1 = halo-resident A operand
- * for the 3x3 convolutions (default), 0 = nine shifted boxes; which = 4: 1 = programmatic dependent launches (default).  Returns non-zero for an
+ * for the 3x3 convolutions (default), 0 = nine shifted boxes; which = 4: 1 = programmatic dependent launches (default); which = 5: 1 = column slices for
+ * the tiles of a GEMM's partly filled last wave (default).  Returns non-zero for an
  * unknown switch. */
 int ufm_debug_flag(int which, int value);
 

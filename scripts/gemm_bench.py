@@ -16,7 +16,7 @@ sys.path.insert(0, os.path.join(ROOT, "tests"))
 
 def main():
     ap = argparse.ArgumentParser()
-    ap.add_argument("--variants", default="0:1,1:1", help="comma list of epilogue:pair")
+    ap.add_argument("--variants", default="0:1,1:1", help="comma list of epilogue:pair[:split]  (split: last-wave column slices, default 1)")
     ap.add_argument("--reps", type=int, default=20)
     ap.add_argument("--only", default="")
     a = ap.parse_args()
@@ -40,6 +40,7 @@ def main():
     conv = [("rcu@120x160", 16, 120, 160, 256, 256, "convres"), ("rcu@240x320", 4, 240, 320, 256, 256, "convres"),
             ("proc.c1@240x320", 4, 240, 320, 256, 128, "convbf16"), ("proc.c2@420x560", 4, 420, 560, 128, 128, "convbf16")]
     variants = [tuple(int(x) for x in v.split(":")) for v in a.variants.split(",")]
+    variants = [v if len(v) > 2 else v + (1,) for v in variants]
     gen = torch.Generator(device=dev).manual_seed(0)
 
     def timeit(fn):
@@ -54,7 +55,7 @@ def main():
         torch.cuda.synchronize()
         return e0.elapsed_time(e1) / a.reps
 
-    print(f"{'shape':18s} {'M':>7s} {'K':>5s} {'N':>5s} " + "   ".join(f"e{v[0]}p{v[1]}: ms TFLOP/s" for v in variants))
+    print(f"{'shape':18s} {'M':>7s} {'K':>5s} {'N':>5s} " + "   ".join(f"e{v[0]}p{v[1]}s{v[2]}: ms TFLOP/s" for v in variants))
     for name, M, K, N, kind in lin:
         if a.only and a.only not in name:
             continue
@@ -67,6 +68,7 @@ def main():
         for v in variants:
             lib.ufm_debug_flag(0, v[0])
             lib.ufm_debug_flag(1, v[1])
+            lib.ufm_debug_flag(5, v[2])
             if kind == "res":
                 fn = lambda: ops.linear(A, Wt, bias=bias, res1=x, out_f32=x)
             elif kind == "gelu":
@@ -99,6 +101,7 @@ def main():
         print(f"{name:18s} {n * H * W:7d} {9 * Ci:5d} {Co:5d} " + "   ".join(res))
     lib.ufm_debug_flag(0, 1)
     lib.ufm_debug_flag(1, 1)
+    lib.ufm_debug_flag(5, 1)
 
 
 if __name__ == "__main__":

@@ -70,6 +70,45 @@ def test_gemm_gelu_scale_residual_inplace():
     assert rel(x, ref) < 1e-5
 
 
+# Last-wave column slices (gemm.cu tile_ref / engine.cu build_gemm) on a 148-SM part: pair tiles 256 x 256 on 74 units,
+# single-CTA tiles 128 x 128 on 148.  (M, K, N): 86 row tiles x 1 -> R = 12 -> quarter slices; 104 -> R = 30 -> halves;
+# 151 x 4 = 604 -> R = 12 (the UFM-Base encoder proj shape, ragged last row tile); N = 384: BN = 128, 60 x 3 = 180 ->
+# R = 32 -> 64-column halves taken by one warp half.
+SLICED = [(86 * 256, 128, 256), (104 * 256 - 24, 192, 256), (32 * 1201, 256, 1024), (60 * 128, 128, 384)]
+
+
+@pytest.mark.parametrize("M,K,N", SLICED)
+def test_gemm_last_wave_slices(M, K, N):
+    import gpu_ops as ops
+
+    lib = _lib.load()
+    a = _rand(M, K, seed=1).bfloat16()
+    w = _rand(N, K, scale=K ** -0.5, seed=2).bfloat16()
+    bias, gamma = _rand(N, seed=3), _rand(N, seed=4)
+    x0 = _rand(M, N, seed=5)
+    ref_lin = a.float() @ w.float().t() + bias
+    res = {}
+    for split in (1, 0):
+        assert lib.ufm_debug_flag(5, split) == 0
+        ob = torch.zeros(M, N, dtype=torch.bfloat16, device="cuda")
+        ops.linear(a, w, bias=bias, out_bf16=ob, flags=_lib.GEMM_GELU)  # TMA bf16 epilogue
+        x = x0.clone()
+        ops.linear(a, w, bias=bias, scale=gamma, res1=x, out_f32=x)  # TMA fp32 epilogue, in-place residual
+        of = torch.zeros(M, N, device="cuda")
+        ob2 = torch.zeros(M, N, dtype=torch.bfloat16, device="cuda")
+        ops.linear(a, w, bias=bias, res1=x0, out_f32=of, out_bf16=ob2)  # direct epilogue (two outputs)
+        torch.cuda.synchronize()
+        res[split] = (ob, x, of, ob2)
+    lib.ufm_debug_flag(5, 1)
+    ob, x, of, ob2 = res[1]
+    assert rel(ob.float(), F.gelu(ref_lin)) < 4e-3
+    assert rel(x, x0 + gamma * ref_lin) < 1e-5
+    assert rel(of, x0 + ref_lin) < 1e-5
+    assert rel(ob2.float(), x0 + ref_lin) < 4e-3
+    for t1, t0 in zip(res[1], res[0]):  # a slice accumulates the same K sequence as the whole tile: identical bits
+        assert torch.equal(t1, t0)
+
+
 def test_gemm_patch_embed_addressing():
     """3-D A view (K, tokens, images), output shifted one row (cls slot) and a row-broadcast positional add."""
     import gpu_ops as ops

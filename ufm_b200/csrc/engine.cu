@@ -81,7 +81,7 @@ struct Epi {
 };
 
 bool build_gemm(GemmParams* gp, int* BN, const AView& a_in, const void* wt, int n_out, int taps, int cin_pad, const Epi& e,
-                char* err, int errlen) {
+                char* err, int errlen, int num_sms = 0) {
   memset(gp, 0, sizeof(*gp));
   AView a = a_in;
   const bool halo = taps == 9 && (gemm_halo_mode() & 1);
@@ -125,6 +125,26 @@ bool build_gemm(GemmParams* gp, int* BN, const AView& a_in, const void* wt, int 
   gp->taps = taps;
   gp->cchunks = (a.C + 63) / 64;
   gp->cin_pad = cin_pad;
+  // ---- last-wave column slices (gemm.cu tile_ref): the static schedule runs ceil(T / U) waves of T tiles on U units; when
+  // the last wave holds R <= U/4 (U/2) tiles, each is cut into 4 (2) column slices of >= 64 columns so that the wave
+  // costs a fraction of a tile time (UFM-Base encoder proj / fc2: 604 tiles on 74 pairs, R = 12 -> 48 quarter tiles) ----
+  if (!halo && !tail && taps == 1 && num_sms > 0 && gemm_split_mode()) {
+    const int tiles_m1 = a.N * gp->tiles_y * gp->tiles_x;
+    const int T = ((tiles_m1 + gp->ctas - 1) / gp->ctas) * gp->tiles_n;
+    const int U = num_sms / gp->ctas;
+    const int R = U > 0 ? T % U : 0;
+    int sl = 0;
+    if (T > U && R > 0) {
+      if (*BN / 4 >= 64 && R * 4 <= U) sl = 2;
+      else if (*BN / 2 >= 64 && R * 2 <= U) sl = 1;
+    }
+    if (sl) {
+      gp->split_from = T - R;
+      gp->split_log2 = sl;
+      const uint32_t sbox[2] = {64, (uint32_t)((*BN / gp->ctas) >> sl)};
+      if (!make_tmap_bf16(&gp->tmBs, wt, 2, bdims, bstr, sbox, err, errlen)) return false;
+    }
+  }
   if (gp->cchunks * 64 > cin_pad && taps > 1) {
     snprintf(err, errlen, "conv weight pitch %d too small for C=%d", cin_pad, a.C);
     return false;
@@ -306,7 +326,7 @@ struct ufm_engine {
     GemmParams gp;
     int BN;
     char eb[512];
-    if (!build_gemm(&gp, &BN, a, wt->ptr, n_out, taps, ktot / taps, e, eb, sizeof(eb))) {
+    if (!build_gemm(&gp, &BN, a, wt->ptr, n_out, taps, ktot / taps, e, eb, sizeof(eb), num_sms)) {
       fail("gemm %s: %s", wname.c_str(), eb);
       return false;
     }
@@ -1341,6 +1361,10 @@ int ufm_debug_flag(int which, int value) {
     set_pdl_mode(value);
     return 0;
   }
+  if (which == 5) {
+    set_gemm_split_mode(value);
+    return 0;
+  }
   return 1;
 }
 
@@ -1377,7 +1401,7 @@ int ufm_op_gemm(const void* a, int C, int X, int Y, int Nimg, int64_t a_sx, int6
   }
   GemmParams gp;
   int BN;
-  if (!build_gemm(&gp, &BN, av, wt, n_out, taps, cin_pad, e, err, errlen)) return 1;
+  if (!build_gemm(&gp, &BN, av, wt, n_out, taps, cin_pad, e, err, errlen, g_num_sms())) return 1;
   cudaError_t ce = launch_gemm(gp, BN, g_num_sms(), reinterpret_cast<cudaStream_t>(stream));
   if (ce != cudaSuccess) {
     snprintf(err, errlen, "launch_gemm: %s", cudaGetErrorString(ce));

@@ -76,6 +76,25 @@ __device__ __forceinline__ float gelu_erf(float x) {
   return fmaf(-ax * 0.3989422804014327f, pl * e, fmaxf(x, 0.f));
 }
 
+// Work item -> (row-tile index, first column, width).  Items below split_from are whole BN-wide tiles; the tiles of the
+// last, partly filled wave (item >= split_from) are cut into 2^split_log2 column slices so that they spread over the idle
+// scheduling units: with 604 tiles on 74 CTA pairs the ninth wave holds 12 tiles, as 48 quarter tiles it costs about a
+// third of a wave instead of a whole one (host side: engine.cu build_gemm).
+struct TileRef {
+  int mt, n0, ncols;
+};
+__device__ __forceinline__ TileRef tile_ref(const GemmParams& p, int item, int split_from, int BN) {
+  int tile = item, sub = 0, ncols = BN;
+  if (item >= split_from) {
+    const int r = item - split_from;
+    tile = split_from + (r >> p.split_log2);
+    sub = r & ((1 << p.split_log2) - 1);
+    ncols = BN >> p.split_log2;
+  }
+  const int tn = tile % p.tiles_n;
+  return TileRef{tile / p.tiles_n, tn * BN + sub * ncols, ncols};
+}
+
 template <int BN, int CTAS, bool HALO>
 __global__ void __launch_bounds__(kThreads, 1) gemm_kernel(const __grid_constant__ GemmParams p) {
   using C = Cfg<BN, CTAS, HALO>;
@@ -139,19 +158,25 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_kernel(const __grid_constant
   const int tiles_m1 = p.Nimg * p.tiles_y * p.tiles_x;
   const int tiles_m = (tiles_m1 + CTAS - 1) / CTAS;
   const int total_tiles = tiles_m * p.tiles_n;
+  const int split_from = p.split_log2 ? p.split_from : total_tiles;
+  const int total_items = split_from + ((total_tiles - split_from) << p.split_log2);
   const int k_iters = p.taps * p.cchunks;
 
   if (warp == 0) {
     if (lane == 0) {
       int stage = 0, astage = 0;
       uint32_t phase = 0, aphase = 0;
-      for (int tile = unit; tile < total_tiles; tile += num_units) {
-        const int tn = tile % p.tiles_n;
-        const int tm = (tile / p.tiles_n) * CTAS + (int)cta_rank;
+      for (int item = unit; item < total_items; item += num_units) {
+        const TileRef tr = tile_ref(p, item, split_from, BN);
+        const int tm = tr.mt * CTAS + (int)cta_rank;
         const int tx = tm % p.tiles_x;
         const int ty = (tm / p.tiles_x) % p.tiles_y;
         const int img = tm / (p.tiles_x * p.tiles_y);
-        const int x0 = tx * p.tw, y0 = ty * p.th, n0 = tn * BN + (int)cta_rank * C::B_ROWS;
+        const int x0 = tx * p.tw, y0 = ty * p.th, n0 = tr.n0 + (int)cta_rank * (tr.ncols / CTAS);
+        // a column slice loads only its own rows of B (tmBs: the same weight matrix with a (BN / CTAS) >> split box)
+        const bool sliced = tr.ncols != BN;
+        const CUtensorMap* tmB = sliced ? &p.tmBs : &p.tmB;
+        const uint32_t b_tx = sliced ? (uint32_t)(C::B_BYTES >> p.split_log2) : (uint32_t)C::B_BYTES;
         if constexpr (HALO) {
           for (int cc = 0; cc < p.cchunks; ++cc) {
             mbar_wait(&aempty[astage], aphase ^ 1);
@@ -196,14 +221,14 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_kernel(const __grid_constant
           mbar_wait(&empty[stage], phase ^ 1);
           if constexpr (CTAS == 2) {
             // both CTAs' boxes complete on the LEADER's full barrier, which expects the bytes of the whole pair
-            if (cta_rank == 0) mbar_expect_tx(&full[stage], 2 * (C::A_TX + C::B_BYTES));
+            if (cta_rank == 0) mbar_expect_tx(&full[stage], 2 * (C::A_TX + b_tx));
             const uint32_t lbar = smem_u32(&full[stage]) & kPeerBitMask;
             tma2_load_4d(sA + stage * C::A_BYTES, &p.tmA, lbar, cc * BK, x0 + dx, y0 + dy, img);
-            tma2_load_2d(sB + stage * C::B_BYTES, &p.tmB, lbar, tap * p.cin_pad + cc * BK, n0);
+            tma2_load_2d(sB + stage * C::B_BYTES, tmB, lbar, tap * p.cin_pad + cc * BK, n0);
           } else {
-            mbar_expect_tx(&full[stage], C::A_TX + C::B_BYTES);
+            mbar_expect_tx(&full[stage], C::A_TX + b_tx);
             tma_load_4d(sA + stage * C::A_BYTES, &p.tmA, &full[stage], cc * BK, x0 + dx, y0 + dy, img);
-            tma_load_2d(sB + stage * C::B_BYTES, &p.tmB, &full[stage], tap * p.cin_pad + cc * BK, n0);
+            tma_load_2d(sB + stage * C::B_BYTES, tmB, &full[stage], tap * p.cin_pad + cc * BK, n0);
           }
           if (++stage == C::STAGES) {
             stage = 0;
@@ -218,7 +243,8 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_kernel(const __grid_constant
     // an ELECT / R2UR.BROADCAST / branch sequence and ~25 dependent uniform-datapath instructions: ~600 clk per group of
     // four MMAs, more than the 256-512 clk the tensor pipe needs for them.
     if (cta_rank == 0) {
-      constexpr uint32_t idesc = umma_idesc_bf16(BM * CTAS, BN, 0, 0);
+      constexpr uint32_t idesc_full = umma_idesc_bf16(BM * CTAS, BN, 0, 0);
+      const uint32_t idesc_slice = umma_idesc_bf16(BM * CTAS, BN >> p.split_log2, 0, 0);
       constexpr uint32_t hi_b = umma_desc_hi_sw128(1024);
       constexpr uint32_t hi_a = umma_desc_hi_sw128(HALO ? HALO_ROW_BYTES : 1024);
       const uint32_t a_lo0 = umma_desc_lo(smem_u32(sA));
@@ -228,7 +254,8 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_kernel(const __grid_constant
       uint32_t phase = 0;
       int acc = 0, astage = 0;
       uint32_t accphase = 0, aphase = 0;
-      for (int tile = unit; tile < total_tiles; tile += num_units) {
+      for (int item = unit; item < total_items; item += num_units) {
+        const uint32_t idesc = (HALO || item < split_from) ? idesc_full : idesc_slice;  // a slice fills the first columns
         mbar_wait(&tempty[acc], accphase ^ 1);
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + acc * BN;
@@ -332,21 +359,26 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_kernel(const __grid_constant
     }
     int acc = 0;
     uint32_t accphase = 0;
-    for (int tile = unit; tile < total_tiles; tile += num_units) {
-      const int tn = tile % p.tiles_n;
-      const int tm = (tile / p.tiles_n) * CTAS + (int)cta_rank;
+    for (int item = unit; item < total_items; item += num_units) {
+      const TileRef tr = tile_ref(p, item, split_from, BN);
+      const int tm = tr.mt * CTAS + (int)cta_rank;
       const int tx = tm % p.tiles_x;
       const int ty = (tm / p.tiles_x) % p.tiles_y;
       const int img = tm / (p.tiles_x * p.tiles_y);
-      const int n0 = tn * BN;
-      const int c0 = n0 + half * HALF_COLS;  // first column of this warp
-      const uint32_t acc_addr = tmem_base + (uint32_t(q * 32) << 16) + uint32_t(acc * BN + half * HALF_COLS);
+      const int n0 = tr.n0;
+      // columns of this warp: a tile (or slice) of 128+ columns is shared by the two warp halves, a 64-column one is
+      // taken by half 0 alone (half 1 only keeps the barrier protocol)
+      const int per_half = tr.ncols >= 128 ? (tr.ncols >> 1) : tr.ncols;
+      const int col_off = tr.ncols >= 128 ? half * per_half : 0;
+      const int c0 = n0 + col_off;  // first column of this warp
+      const int Nl = (tr.ncols < 128 && half == 1) ? 0 : (Nlim < c0 + per_half ? Nlim : c0 + per_half);  // its column bound
+      const uint32_t acc_addr = tmem_base + (uint32_t(q * 32) << 16) + uint32_t(acc * BN + col_off);
 
       if (emode == EPI_TMA_F32) {
         // ---- fp32 output (+ optional fp32 residual) through TMA: 32-column slabs -------------------------------------
         const int wx = tx * p.tw + ((32 * q) & (p.tw - 1));
         const int wy = ty * p.th + ((32 * q) >> p.tw_log2);
-        int nch = (Nlim - c0 + 31) >> 5;
+        int nch = (Nl - c0 + 31) >> 5;
         nch = nch < 0 ? 0 : (nch > HALF_COLS / 32 ? HALF_COLS / 32 : nch);
         const bool has_res = p.res1 != nullptr;
         if (lane == 0) {
@@ -429,7 +461,7 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_kernel(const __grid_constant
         // ---- bf16 output through TMA: 64-column slabs ----------------------------------------------------------------
         const int wx = tx * p.tw + ((32 * q) & (p.tw - 1));
         const int wy = ty * p.th + ((32 * q) >> p.tw_log2);
-        int nch = (Nlim - c0 + 63) >> 6;
+        int nch = (Nl - c0 + 63) >> 6;
         nch = nch < 0 ? 0 : (nch > HALF_COLS / 64 ? HALF_COLS / 64 : nch);
         if (lane == 0) bulk_wait_read<0>();
         __syncwarp();
@@ -445,7 +477,7 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_kernel(const __grid_constant
             uint32_t vr[32];
             tmem_ld32(acc_addr + c * 64 + h2 * 32, vr);
             tmem_ld_wait();
-            if (gcol + h2 * 32 < Nlim) {
+            if (gcol + h2 * 32 < Nl) {
 #pragma unroll
               for (int j = 0; j < 4; ++j) {
                 float v[8];
@@ -502,16 +534,16 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_kernel(const __grid_constant
 
         // the residual rows of this tile do not depend on the accumulator: pull them into L2 while the MMAs still run
         if (valid && !tail) {
-          const int pc0 = n0 + half * HALF_COLS;
+          const int pc0 = c0;
           if (p.res1) {
 #pragma unroll
             for (int c = 0; c < HALF_COLS / 32; ++c)
-              if (pc0 + c * 32 < Nlim) prefetch_l2(p.res1 + off + pc0 + c * 32);
+              if (pc0 + c * 32 < Nl) prefetch_l2(p.res1 + off + pc0 + c * 32);
           }
           if (p.res2) {
 #pragma unroll
             for (int c = 0; c < HALF_COLS / 32; ++c)
-              if (pc0 + c * 32 < Nlim) prefetch_l2(p.res2 + off2 + pc0 + c * 32);
+              if (pc0 + c * 32 < Nl) prefetch_l2(p.res2 + off2 + pc0 + c * 32);
           }
         }
         mbar_wait(&tfull[acc], accphase);
@@ -519,9 +551,9 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_kernel(const __grid_constant
         float part[kTailMax] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
 #pragma unroll 1
         for (int c = 0; c < HALF_COLS / 32; ++c) {
-          const int col0 = half * HALF_COLS + c * 32;
+          const int col0 = col_off + c * 32;
           const int gcol = n0 + col0;
-          if (gcol >= Nlim) break;
+          if (gcol >= Nl) break;
           uint32_t vr[32];
           __syncwarp();  // tcgen05.ld is .sync.aligned: reconverge after the per-row predicated body
           // issue the residual loads first so that their latency overlaps the TMEM read
@@ -683,6 +715,9 @@ int g_gemm_halo = 1;
 void set_gemm_halo_mode(int v) { g_gemm_halo = v; }
 int gemm_halo_mode() { return g_gemm_halo; }
 int gemm_pair_mode() { return g_gemm_pair; }
+int g_gemm_split = 1;  // ufm_debug_flag 5
+void set_gemm_split_mode(int v) { g_gemm_split = v; }
+int gemm_split_mode() { return g_gemm_split; }
 
 cudaError_t launch_gemm(const GemmParams& p, int BN, int num_sms, cudaStream_t stream) {
   const int ctas = p.ctas == 2 ? 2 : 1;

@@ -50,7 +50,11 @@ struct alignas(64) GemmParams {
   CUtensorMap tmB;
   CUtensorMap tmOut;     // EPI_TMA_*: 4-D (N, X, Y, Nimg) over the output, box (32 fp32 | 64 bf16, bw, 32/bw, 1)
   CUtensorMap tmRes;     // EPI_TMA_F32 with res1: same geometry over the residual
+  CUtensorMap tmBs;      // split_log2 > 0: tmB with a box of (BN / ctas) >> split_log2 rows (column slices of the last wave)
   int epi_mode;
+  // tiles with index >= split_from (the last, partly filled wave of the static schedule) are computed as 2^split_log2
+  // column slices each; split_log2 = 0: none
+  int split_from, split_log2;
   // tile geometry
   int tw, th;            // A box extents, tw*th == 128, tw a power of two
   int tw_log2;
@@ -91,6 +95,8 @@ void set_gemm_pair_mode(int v);         // tuning hook: 1 = CTA-pair (cta_group:
 int gemm_pair_mode();
 void set_gemm_halo_mode(int v);         // tuning hook: bit 0 = halo-resident A operand for the 3x3 convs (default on)
 int gemm_halo_mode();
+void set_gemm_split_mode(int v);        // tuning hook: 1 = column-slice the tiles of a partly filled last wave (default on)
+int gemm_split_mode();
 
 // ------------------------------------------------------------------------------------------------
 // Flash-style attention forward, head_dim 64, non-causal: O = softmax(Q K^T * scale) V per (sequence, head).
