@@ -38,6 +38,8 @@ def main():
            ("info.fc1", Mi, 768, 3072, "gelu"), ("info.fc2", Mi, 3072, 768, "res")]
     # name, n, H, W, Cin, Cout, kind
     conv = [("rcu@120x160", 16, 120, 160, 256, 256, "convres"), ("rcu@240x320", 4, 240, 320, 256, 256, "convres"),
+            ("rcu1.c2@120x160", 16, 120, 160, 256, 256, "convres2"), ("rcu2.c2@120x160", 16, 120, 160, 256, 256, "convresbf"),
+            ("rcu2.c2@60x80", 32, 60, 80, 256, 256, "convresbf"),
             ("proc.c1@240x320", 4, 240, 320, 256, 128, "convbf16"), ("proc.c2@420x560", 4, 420, 560, 128, 128, "convbf16")]
     variants = [tuple(int(x) for x in v.split(":")) for v in a.variants.split(",")]
     variants = [v if len(v) > 2 else v + (1,) for v in variants]
@@ -86,13 +88,19 @@ def main():
         Wp = (torch.randn(Co, 9 * Ci, device=dev, generator=gen) * 0.02).bfloat16()
         bias = torch.randn(Co, device=dev, generator=gen)
         r = torch.randn(n, H, W, Co, device=dev, generator=gen)
+        r2 = torch.randn(n, H, W, Co, device=dev, generator=gen)
         of = torch.empty(n, H, W, Co, device=dev)
         ob = torch.empty(n, H, W, Co, dtype=torch.bfloat16, device=dev)
         res = []
         for v in variants:
             lib.ufm_debug_flag(0, v[0])
             lib.ufm_debug_flag(1, v[1])
-            if kind == "convres":
+            if kind == "convres2":  # fusion block: path + skip + conv, fp32 sum + ReLU'd bf16 copy
+                fn = lambda: ops.conv3x3(X, Wp, bias=bias, res1=r, res2=r2, r2=(H * W * Co, W * Co, Co), out_f32=of,
+                                         out_bf16=ob, flags=_lib.GEMM_RELU_BF16)
+            elif kind == "convresbf":  # x + conv, bf16 only
+                fn = lambda: ops.conv3x3(X, Wp, bias=bias, res1=r, out_bf16=ob)
+            elif kind == "convres":
                 fn = lambda: ops.conv3x3(X, Wp, bias=bias, res1=r, out_f32=of, out_bf16=ob, flags=_lib.GEMM_RELU_BF16)
             else:
                 fn = lambda: ops.conv3x3(X, Wp, bias=bias, out_bf16=ob)

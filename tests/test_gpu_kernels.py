@@ -109,6 +109,71 @@ def test_gemm_last_wave_slices(M, K, N):
         assert torch.equal(t1, t0)
 
 
+# EPI_TMA_MIX (gemm.cu): the layers with two residuals and / or a bf16 copy next to the fp32 result (RCU convs of the DPT
+# fusion blocks, ref:dpt_block.py:156-177, 225-255) take res1 / the fp32 output through TMA slabs and res2 / the bf16 output
+# through a coalesced second pass; the adds keep the direct epilogue's order, so ufm_debug_flag(0, 0) gives the same bits.
+@pytest.mark.parametrize("n,H,W,Ci,Co,mode", [(2, 30, 40, 256, 256, "rcu1"), (1, 60, 80, 256, 256, "rcu1"),
+                                               (2, 15, 20, 256, 256, "rcu1"), (2, 30, 40, 128, 256, "rcu2"),
+                                               (1, 24, 32, 64, 64, "rcu1"), (1, 42, 56, 96, 128, "dual")])
+def test_conv3x3_mixed_epilogue(n, H, W, Ci, Co, mode):
+    import gpu_ops as ops
+
+    lib = _lib.load()
+    x = _rand(n, H, W, Ci, seed=1).bfloat16()
+    w = _rand(Co, Ci, 3, 3, scale=(9 * Ci) ** -0.5, seed=2).bfloat16().float()
+    bias = _rand(Co, seed=3)
+    r1, r2 = _rand(n, H, W, Co, seed=4), _rand(n, H, W, Co, seed=5)
+    conv = F.conv2d(x.float().permute(0, 3, 1, 2), w, bias, padding=1).permute(0, 2, 3, 1)
+    res = {}
+    for variant in (1, 0):
+        assert lib.ufm_debug_flag(0, variant) == 0
+        of = torch.zeros(n, H, W, Co, device="cuda")
+        ob = torch.zeros(n, H, W, Co, dtype=torch.bfloat16, device="cuda")
+        wp = _pack3(w)
+        if mode == "rcu1":  # path + skip + conv: fp32 sum and its ReLU'd bf16 copy
+            ops.conv3x3(x, wp, bias=bias, res1=r1, res2=r2, r2=(H * W * Co, W * Co, Co), out_f32=of, out_bf16=ob,
+                        flags=_lib.GEMM_RELU_BF16)
+        elif mode == "rcu2":  # x + conv, bf16 only
+            ops.conv3x3(x, wp, bias=bias, res1=r1, out_bf16=ob)
+        else:  # two outputs, no residual
+            ops.conv3x3(x, wp, bias=bias, out_f32=of, out_bf16=ob)
+        torch.cuda.synchronize()
+        res[variant] = (of, ob)
+    lib.ufm_debug_flag(0, 1)
+    of, ob = res[1]
+    want = conv + (r1 if mode != "dual" else 0) + (r2 if mode == "rcu1" else 0)
+    if mode != "rcu2":
+        assert rel(of, want) < 1e-5
+    assert rel(ob.float(), F.relu(want) if mode == "rcu1" else want) < 4e-3
+    for t1, t0 in zip(res[1], res[0]):
+        assert torch.equal(t1, t0)
+
+
+def test_gemm_mixed_epilogue_broadcast_residual():
+    """Linear with a row-broadcast res2 (view embedding, ref:global_attention_transformer.py:168-178) and in-place res1."""
+    import gpu_ops as ops
+
+    lib = _lib.load()
+    M, K, N = 2 * 1200 + 37, 256, 768
+    a = _rand(M, K, seed=1).bfloat16()
+    w = _rand(N, K, scale=K ** -0.5, seed=2).bfloat16()
+    bias, row = _rand(N, seed=3), _rand(N, seed=4)
+    x0 = _rand(M, N, seed=5)
+    outs = []
+    for variant in (1, 0):
+        lib.ufm_debug_flag(0, variant)
+        x = x0.clone()
+        ob = torch.zeros(M, N, dtype=torch.bfloat16, device="cuda")
+        ops.linear(a, w, bias=bias, res1=x, res2=row, r2=(0, 0, 0), out_f32=x, out_bf16=ob)
+        torch.cuda.synchronize()
+        outs.append((x, ob))
+    lib.ufm_debug_flag(0, 1)
+    want = a.float() @ w.float().t() + bias + x0 + row
+    assert rel(outs[0][0], want) < 1e-5
+    assert rel(outs[0][1].float(), want) < 4e-3
+    assert torch.equal(outs[0][0], outs[1][0]) and torch.equal(outs[0][1], outs[1][1])
+
+
 def test_gemm_patch_embed_addressing():
     """3-D A view (K, tokens, images), output shifted one row (cls slot) and a row-broadcast positional add."""
     import gpu_ops as ops

@@ -122,8 +122,8 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_kernel(const __grid_constant
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&p.tmA);
     tma_prefetch_desc(&p.tmB);
-    if (p.epi_mode != EPI_DIRECT) tma_prefetch_desc(&p.tmOut);
-    if (p.epi_mode == EPI_TMA_F32 && p.res1) tma_prefetch_desc(&p.tmRes);
+    if (p.epi_mode != EPI_DIRECT && !(p.epi_mode == EPI_TMA_MIX && !p.out_f32)) tma_prefetch_desc(&p.tmOut);
+    if ((p.epi_mode == EPI_TMA_F32 || p.epi_mode == EPI_TMA_MIX) && p.res1) tma_prefetch_desc(&p.tmRes);
   }
   if (warp == 1 && lane == 0) {
     for (int i = 0; i < C::STAGES; ++i) {
@@ -374,8 +374,11 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_kernel(const __grid_constant
       const int Nl = (tr.ncols < 128 && half == 1) ? 0 : (Nlim < c0 + per_half ? Nlim : c0 + per_half);  // its column bound
       const uint32_t acc_addr = tmem_base + (uint32_t(q * 32) << 16) + uint32_t(acc * BN + col_off);
 
-      if (emode == EPI_TMA_F32) {
+      if (emode == EPI_TMA_F32 || emode == EPI_TMA_MIX) {
         // ---- fp32 output (+ optional fp32 residual) through TMA: 32-column slabs -------------------------------------
+        // EPI_TMA_MIX adds a second, coalesced pass over the finished slab (second residual with its own strides, bf16
+        // copy of the result) so that layers with two residuals / two outputs leave the row-per-thread direct path too.
+        const bool mix = emode == EPI_TMA_MIX;
         const int wx = tx * p.tw + ((32 * q) & (p.tw - 1));
         const int wy = ty * p.th + ((32 * q) >> p.tw_log2);
         int nch = (Nl - c0 + 31) >> 5;
@@ -394,6 +397,16 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_kernel(const __grid_constant
             }
           }
         }
+        if (mix && p.res2) {
+          // res2 rows of this tile do not depend on the accumulator: pull them into L2 while the MMAs still run
+          const int li = 32 * q + lane;
+          const int ly = li >> p.tw_log2, lx = li & (p.tw - 1);
+          const int x = tx * p.tw + lx, y = ty * p.th + ly;
+          if (x < p.X && y < p.Y && img < p.Nimg) {
+            const float* rp2 = p.res2 + (long long)img * p.r2N + (long long)y * p.r2Y + (long long)x * p.r2X + c0;
+            for (int c = 0; c < nch; ++c) prefetch_l2(rp2 + 32 * c);
+          }
+        }
         __syncwarp();
         mbar_wait(&tfull[acc], accphase);
         tc_fence_after();
@@ -401,6 +414,21 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_kernel(const __grid_constant
         for (int c = 0; c < nch; ++c) {
           uint8_t* buf = wbuf + (c & 1) * 4096;
           uint8_t* rowp = buf + lane * 128;
+          // EPI_TMA_MIX: second-pass addressing (8 lanes per slab row, 4 rows per warp instruction); the res2 loads are
+          // issued here so that their latency runs under the residual wait, the TMEM read and the first pass
+          float4 r2v[8];
+          const int colg = c0 + 32 * c + 4 * (lane & 7);
+          if (mix && p.res2) {
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+              const int li = 32 * q + 4 * i + (lane >> 3);
+              const int x = tx * p.tw + (li & (p.tw - 1)), y = ty * p.th + (li >> p.tw_log2);
+              r2v[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+              if (colg < Nl && x < p.X && y < p.Y && img < p.Nimg)
+                r2v[i] = *reinterpret_cast<const float4*>(p.res2 + (long long)img * p.r2N + (long long)y * p.r2Y +
+                                                          (long long)x * p.r2X + colg);
+            }
+          }
           if (has_res) {
             if (c >= 1 && c + 1 < nch && lane == 0) {
               bulk_wait_read<0>();  // slab (c+1)&1 was stored by chunk c-1
@@ -444,11 +472,42 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_kernel(const __grid_constant
             }
             *sp = v;
           }
-          fence_proxy_async_smem();
-          __syncwarp();
-          if (lane == 0) {
-            tma_store_4d(&p.tmOut, buf, gcol, wx, wy, img);
-            bulk_commit_group();
+          if (mix) {
+            // transposed pass: 8 lanes cover the 128 bytes of one slab row, a warp instruction 4 rows -> full-line global
+            // accesses for res2 (fp32, own strides) and the bf16 output; the fp32 sum goes back into the slab.  The adds
+            // keep the direct epilogue's order ((acc + bias) * scale + res1) + res2, so both paths give the same bits.
+            __syncwarp();
+            const int ch = lane & 7;
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+              const int row = 4 * i + (lane >> 3);
+              const int li = 32 * q + row;
+              const int x = tx * p.tw + (li & (p.tw - 1)), y = ty * p.th + (li >> p.tw_log2);
+              if (!(colg < Nl && x < p.X && y < p.Y && img < p.Nimg)) continue;
+              float4* sp = reinterpret_cast<float4*>(buf + row * 128 + ((uint32_t(ch) ^ uint32_t(row & 7)) << 4));
+              float4 v = *sp;
+              if (p.res2) {
+                v.x += r2v[i].x; v.y += r2v[i].y; v.z += r2v[i].z; v.w += r2v[i].w;
+                if (p.out_f32) *sp = v;
+              }
+              if (p.out_bf16) {
+                if (p.flags & GEMM_RELU_BF16) {
+                  v.x = fmaxf(v.x, 0.f); v.y = fmaxf(v.y, 0.f); v.z = fmaxf(v.z, 0.f); v.w = fmaxf(v.w, 0.f);
+                }
+                *reinterpret_cast<uint2*>(p.out_bf16 + (long long)img * p.sN + (long long)y * p.sY + (long long)x * p.sX +
+                                          p.out_off + colg) = make_uint2(pack_bf16(v.x, v.y), pack_bf16(v.z, v.w));
+              }
+            }
+          }
+          if (!mix || p.out_f32) {
+            fence_proxy_async_smem();
+            __syncwarp();
+            if (lane == 0) {
+              tma_store_4d(&p.tmOut, buf, gcol, wx, wy, img);
+              bulk_commit_group();
+            }
+          } else {
+            __syncwarp();  // the slab may be refilled (TMA residual load) once every lane has read it
           }
         }
         tc_fence_before();

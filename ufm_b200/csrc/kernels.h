@@ -42,14 +42,17 @@ enum : uint32_t {
 //   EPI_TMA_F32   fp32 output, optional fp32 residual with the same addressing (in-place residual stream): 32-column
 //                 slabs staged in swizzled smem, residual slab in by TMA load, result out by TMA store
 //   EPI_TMA_BF16  bf16 output only: 64-column slabs, out by TMA store
-enum : int { EPI_DIRECT = 0, EPI_TMA_F32 = 1, EPI_TMA_BF16 = 2 };
+//   EPI_TMA_MIX   EPI_TMA_F32's slabs (res1 in by TMA load, fp32 result - if any - out by TMA store) plus a coalesced
+//                 second pass over each slab for a res2 with its own strides and / or a bf16 copy of the result (the RCU
+//                 convs of the DPT fusion blocks: two residuals, fp32 + ReLU'd bf16 outputs)
+enum : int { EPI_DIRECT = 0, EPI_TMA_F32 = 1, EPI_TMA_BF16 = 2, EPI_TMA_MIX = 3 };
 
 constexpr int kTailMax = 8;  // output channels of the fused TAIL epilogue
 struct alignas(64) GemmParams {
   CUtensorMap tmA;
   CUtensorMap tmB;
   CUtensorMap tmOut;     // EPI_TMA_*: 4-D (N, X, Y, Nimg) over the output, box (32 fp32 | 64 bf16, bw, 32/bw, 1)
-  CUtensorMap tmRes;     // EPI_TMA_F32 with res1: same geometry over the residual
+  CUtensorMap tmRes;     // EPI_TMA_F32 / EPI_TMA_MIX with res1: same geometry over the residual
   CUtensorMap tmBs;      // split_log2 > 0: tmB with a box of (BN / ctas) >> split_log2 rows (column slices of the last wave)
   int epi_mode;
   // tiles with index >= split_from (the last, partly filled wave of the static schedule) are computed as 2^split_log2
