@@ -174,6 +174,30 @@ def test_gemm_mixed_epilogue_broadcast_residual():
     assert torch.equal(outs[0][0], outs[1][0]) and torch.equal(outs[0][1], outs[1][1])
 
 
+@pytest.mark.parametrize("M,K,N", [(32 * 1201, 256, 1024), (2400 * 3 + 5, 192, 768), (300, 128, 128)])
+def test_gemm_inplace_residual_reduce_add(M, K, N):
+    """The in-place residual add x += gamma * (a W^T + b) (ref:transformer_blocks.py:386-403) is done by the L2 through a
+    TMA reduce-add store; ufm_debug_flag(0, 5) switches back to the residual slab (TMA load, add in the SM).  One fp32
+    rounding either way -> same bits."""
+    import gpu_ops as ops
+
+    lib = _lib.load()
+    a = _rand(M, K, seed=1).bfloat16()
+    w = _rand(N, K, scale=K ** -0.5, seed=2).bfloat16()
+    bias, gamma = _rand(N, seed=3), _rand(N, seed=4)
+    x0 = _rand(M, N, seed=5)
+    outs = []
+    for variant in (1, 5):
+        lib.ufm_debug_flag(0, variant)
+        x = x0.clone()
+        ops.linear(a, w, bias=bias, scale=gamma, res1=x, out_f32=x)
+        torch.cuda.synchronize()
+        outs.append(x)
+    lib.ufm_debug_flag(0, 1)
+    assert rel(outs[0], x0 + gamma * (a.float() @ w.float().t() + bias)) < 1e-5
+    assert torch.equal(outs[0], outs[1])
+
+
 def test_gemm_patch_embed_addressing():
     """3-D A view (K, tokens, images), output shifted one row (cls slot) and a row-broadcast positional add."""
     import gpu_ops as ops

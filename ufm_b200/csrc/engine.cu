@@ -151,6 +151,7 @@ bool build_gemm(GemmParams* gp, int* BN, const AView& a_in, const void* wt, int 
   }
   // ---- epilogue path: TMA slabs when the output (and residual) is one dense-row tensor the box geometry can address ----
   gp->epi_mode = EPI_DIRECT;
+  bool red_inplace = false;
   if (!tail && gemm_epilogue_variant() && !e.res2 && (e.out_f32 != nullptr) != (e.out_bf16 != nullptr) &&
       !(e.out_bf16 && e.res1)) {
     const bool f32 = e.out_f32 != nullptr;
@@ -176,6 +177,7 @@ bool build_gemm(GemmParams* gp, int* BN, const AView& a_in, const void* wt, int 
         if (!make_tmap(&gp->tmRes, true, rb, 4, od, os, ob, err, errlen)) return false;
       }
       gp->epi_mode = f32 ? EPI_TMA_F32 : EPI_TMA_BF16;
+      red_inplace = f32 && e.res1 && e.res1 == e.out_f32 && !(gemm_epilogue_variant() & 4);
     }
   }
   // EPI_TMA_MIX: what the two plain TMA modes cannot take (a second residual, a bf16 copy next to / instead of the fp32
@@ -205,7 +207,7 @@ bool build_gemm(GemmParams* gp, int* BN, const AView& a_in, const void* wt, int 
       gp->epi_mode = EPI_TMA_MIX;
     }
   }
-  gp->flags = e.flags;
+  gp->flags = e.flags | (red_inplace ? GEMM_RED_INPLACE : 0u);
   gp->bias = e.bias; gp->scale = e.scale; gp->res1 = e.res1; gp->res2 = e.res2;
   gp->out_f32 = e.out_f32; gp->out_bf16 = e.out_bf16;
   gp->sN = e.sn; gp->sY = e.sy; gp->sX = e.sx; gp->out_off = e.out_off;

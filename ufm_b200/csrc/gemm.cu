@@ -123,7 +123,8 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_kernel(const __grid_constant
     tma_prefetch_desc(&p.tmA);
     tma_prefetch_desc(&p.tmB);
     if (p.epi_mode != EPI_DIRECT && !(p.epi_mode == EPI_TMA_MIX && !p.out_f32)) tma_prefetch_desc(&p.tmOut);
-    if ((p.epi_mode == EPI_TMA_F32 || p.epi_mode == EPI_TMA_MIX) && p.res1) tma_prefetch_desc(&p.tmRes);
+    if ((p.epi_mode == EPI_TMA_F32 || p.epi_mode == EPI_TMA_MIX) && p.res1 && !(p.flags & GEMM_RED_INPLACE))
+      tma_prefetch_desc(&p.tmRes);
   }
   if (warp == 1 && lane == 0) {
     for (int i = 0; i < C::STAGES; ++i) {
@@ -383,7 +384,8 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_kernel(const __grid_constant
         const int wy = ty * p.th + ((32 * q) >> p.tw_log2);
         int nch = (Nl - c0 + 31) >> 5;
         nch = nch < 0 ? 0 : (nch > HALF_COLS / 32 ? HALF_COLS / 32 : nch);
-        const bool has_res = p.res1 != nullptr;
+        const bool red = (p.flags & GEMM_RED_INPLACE) != 0;  // x += v by the L2 (TMA reduce-add): no residual slab
+        const bool has_res = p.res1 != nullptr && !red;
         if (lane == 0) {
           bulk_wait_read<0>();  // the previous tile's stores have left both slabs
           if (has_res) {
@@ -503,7 +505,8 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_kernel(const __grid_constant
             fence_proxy_async_smem();
             __syncwarp();
             if (lane == 0) {
-              tma_store_4d(&p.tmOut, buf, gcol, wx, wy, img);
+              if (red) tma_reduce_add_4d(&p.tmOut, buf, gcol, wx, wy, img);
+              else tma_store_4d(&p.tmOut, buf, gcol, wx, wy, img);
               bulk_commit_group();
             }
           } else {
@@ -748,7 +751,10 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_kernel(const __grid_constant
   }
 }
 
-int g_gemm_epi = 1;   // ufm_debug_flag 0: 1 = TMA-store epilogues where eligible (default), 0 = always the direct epilogue
+// ufm_debug_flag 0: 0 = always the direct epilogue; 1 = TMA epilogues where eligible, EPI_TMA_MIX and the reduce-add in-place
+// residual included (default); 2 = TMA epilogues without EPI_TMA_MIX; | 4 = in-place residuals through a residual slab
+// (TMA load + add in the SM) instead of the TMA reduce-add store
+int g_gemm_epi = 1;
 int g_gemm_pair = 1;  // ufm_debug_flag 1 (bit 1 measured neutral on the N = 128 convs: 808 vs 795 TFLOP/s): bit 0 = CTA-pair (cta_group::2) tiles for BN = 256, bit 1 = also for BN = 128
 
 template <int BN, int CTAS, bool HALO>

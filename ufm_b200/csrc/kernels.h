@@ -34,6 +34,9 @@ enum : uint32_t {
   GEMM_TAIL = 1u << 2,
   GEMM_TAIL_SIGMOID = 1u << 3,
   GEMM_TAIL_COORD = 1u << 4,   // TAIL: after the affine, subtract the pixel's (x, y) from channels (0, 1)
+  // set by build_gemm only (EPI_TMA_F32, res1 == out_f32): the in-place residual add is done by the L2 through a TMA
+  // reduce-add store (x += v) instead of loading the residual slab into the SM; one fp32 rounding either way
+  GEMM_RED_INPLACE = 1u << 8,
 };
 
 // Epilogue paths of the GEMM kernel (chosen per launch by the host, engine.cu build_gemm):
