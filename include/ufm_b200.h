@@ -125,7 +125,9 @@ int ufm_set_profile(ufm_engine* e, int on);
 int ufm_profile_read(ufm_engine* e, double* ms, double* flops, double* bytes, int64_t* launches);
 
 /* Process-wide tuning switches for kernel experiments (no reference counterpart).  which = 0: GEMM epilogue variant
- * (0 = row-per-thread stores, 1 = shared-memory transposed, coalesced stores); which = 1: CTA-pair (cta_group::2) GEMM
+ * (0 = row-per-thread direct epilogue everywhere; 1 = TMA slab epilogues where the output geometry allows, including the
+ * mixed second-residual / dual-output mode and the TMA reduce-add in-place residual (default); 2 = as 1 without the mixed mode;
+ * | 4 = in-place residuals through a TMA-loaded residual slab instead of the reduce-add store); which = 1: CTA-pair (cta_group::2) GEMM
  * tiles on/off; which = 2: attention, every n-th exp2 pair on the FMA pipe; which = 3: 1 = halo-resident A operand
  * for the 3x3 convolutions (default), 0 = nine shifted boxes; which = 4: 1 = programmatic dependent launches (default); which = 5: 1 = column slices for
  * the tiles of a GEMM's partly filled last wave (default).  Returns non-zero for an
