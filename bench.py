@@ -10,9 +10,12 @@ UFM-Base architecture; iid uint8 images of the named shape
              HOST tensors out (one `ufm_forward_host` C-ABI call per step: H2D + forward + D2H inside the timed region)
   * roofline: the dominant kernel family (the tcgen05 GEMM / implicit-GEMM conv kernel), algorithmic FLOPs / summed
              launch durations measured with CUDA events on the launching stream during the timed steps
-  * cpu_baseline: the CPU fp32 oracle (port of the reference path) timed on this box's host cores on a bounded sample
-`--impl reference` times that CPU path alone (the reference is pure Python + an un-vendored torch.hub model and cannot
-travel to the GPU box; the oracle restates it and is pinned against it by tests/golden).
+  * cpu_baseline: the reference's own CPU fp32 path timed on this box's host cores on a bounded sample (kind
+             "reference": the unmodified reference classes from oracle/_ref, staged byte for byte by oracle/build_ref.py;
+             kind "port": the oracle restatement, only when no staged reference is present)
+  * torch_gpu_baseline (informational): the unmodified reference's eager PyTorch forward on the same B200 under its own
+             recipe (bf16 autocast for encoder + info sharing, fp32 / TF32 heads), same batch, CUDA-event timed
+`--impl reference` times that CPU path alone, on the engine arm's config; `--impl torch_gpu` the eager GPU forward alone.
 Multi-GPU: one process per GPU (torchrun), each rank runs its own batch (weak scaling, no data-path collective).
 """
 from __future__ import annotations
@@ -196,54 +199,153 @@ def _make_cfg(workload: str):
     return cfg, pairs, desc, name
 
 
-def cpu_reference_pairs_per_s(cfg, refine: bool, n_calls: int = 1, warmup: int = 0):
-    """The CPU fp32 path (oracle port of the reference forward) on this box's host cores: one pair per call.
-    Returns (pairs/s, threads, seconds per pair list)."""
+def _config_dict(desc, pairs, W, H, world):
+    """`config` of the JSON line -- the same dict for the engine and the reference arm (the reference arm times a
+    bounded sample of this workload and says so in `cpu_baseline.sample`)."""
+    return {"workload": desc, "pairs_per_step_per_gpu": pairs, "resolution": [W, H], "weights": "random-init seed 0",
+            "l2": "no flush needed: per-step working set (0.9 GB weights + >10 GB activations) exceeds the 126 MB L2",
+            "parallelism": f"dp{world} (independent pairs, no data-path collective)"}
+
+
+def _reference_callable(cfg, device="cpu"):
+    """(callable(src, tgt) -> result, kind).  kind "reference": the UNMODIFIED reference classes (oracle/_ref staged by
+    oracle/build_ref.py, or /root/reference in the build container) with the seed-0 state dict; kind "port": the
+    oracle restatement (CPU only), used when no reference tree is present."""
     import torch
 
-    from oracle import ufm_oracle as O
-    from oracle.golden_util import make_inputs
     from ufm_b200.weights import make_state_dict
+
+    sd = make_state_dict(cfg, seed=0)
+    from oracle import ref_harness as R
+
+    if R.reference_available():
+        model = R.build_reference(cfg, sd).to(device)
+
+        def call(src, tgt):
+            with torch.no_grad():
+                return model.predict_correspondences_batched(src, tgt)
+
+        return call, "reference"
+    if device != "cpu":
+        raise SystemExit("bench.py: no staged reference (oracle/_ref) for the torch GPU baseline")
+    from oracle import ufm_oracle as O
+
+    def call(src, tgt):
+        with torch.no_grad():
+            return O.predict_correspondences_batched(src, tgt, sd, cfg)
+
+    return call, "port"
+
+
+def cpu_reference_pairs_per_s(cfg, n_calls: int = 1, warmup: int = 1, pairs_per_call: int = 1):
+    """The reference's CPU fp32 path on this box's host cores, `pairs_per_call` pairs per call (a bounded sample of the
+    workload).  Returns (pairs/s, threads, seconds per call list, kind)."""
+    import torch
+
+    from oracle.golden_util import make_inputs
 
     threads = len(os.sched_getaffinity(0))
     torch.set_num_threads(threads)
-    sd = make_state_dict(cfg, seed=0)
+    call, kind = _reference_callable(cfg, "cpu")
     W, H = cfg["inference_resolution"]
-    src, tgt = make_inputs(1, H, W, seed=1)
+    src, tgt = make_inputs(pairs_per_call, H, W, seed=1)
     ts = []
-    with torch.no_grad():
-        for i in range(warmup + n_calls):
-            t0 = time.perf_counter()
-            O.predict_correspondences_batched(src, tgt, sd, cfg)
-            dt = time.perf_counter() - t0
-            if i >= warmup:
-                ts.append(dt)
-    return 1.0 / statistics.median(ts), threads, ts
+    for i in range(warmup + n_calls):
+        t0 = time.perf_counter()
+        call(src, tgt)
+        dt = time.perf_counter() - t0
+        if i >= warmup:
+            ts.append(dt)
+    return pairs_per_call / statistics.median(ts), threads, ts, kind
 
 
 def run_reference(args):
-    """--impl reference: the reference's CPU fp32 path for the same metric/config.  The reference itself (pure Python +
-    un-vendored torch.hub DINOv2) cannot travel to the GPU box, so its oracle port is what is timed (kind = "port")."""
+    """--impl reference: the reference's own CPU fp32 implementation of the path (unmodified classes, all host threads)
+    for the engine arm's metric and config; each step is a bounded sample of the workload (one pair per call)."""
     rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
     if rank != 0:
         return 0
     cfg, pairs, desc, name = _make_cfg(args.workload)
-    refine = "classification_head_kwargs" in cfg
+    if args.pairs:
+        pairs = args.pairs
     t0 = time.perf_counter()
-    v, threads, ts = cpu_reference_pairs_per_s(cfg, refine, n_calls=max(1, args.steps), warmup=min(args.warmup, 1))
+    steps, warmup = max(1, args.steps), max(0, args.warmup)
+    v, threads, ts, kind = cpu_reference_pairs_per_s(cfg, n_calls=steps, warmup=warmup)
     Wr, Hr = cfg["inference_resolution"]
-    sample = f"{len(ts)} timed call(s) of one {Wr}x{Hr} pair each (batch 1) of workload {args.workload}, fp32, {threads} threads"
+    what = "unmodified reference classes (oracle/_ref)" if kind == "reference" else "oracle port of the reference path"
+    sample = (f"{len(ts)} timed step(s) after {warmup} warm-up, each ONE {Wr}x{Hr} pair (batch 1) of the workload's "
+              f"{pairs}-pair batch, CPU fp32, {threads} threads, {what}")
     line = {
         "impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": len(ts),
-        "warmup": min(args.warmup, 1), "ms_per_step": 1e3 * statistics.median(ts), "higher_is_better": True,
+        "warmup": warmup, "ms_per_step": 1e3 * statistics.median(ts), "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": desc, "pairs_per_step": 1, "resolution": cfg["inference_resolution"], "weights": "random-init seed 0"},
-        "cpu_baseline": {"value": v, "unit": UNIT, "cores": threads, "kind": "port", "sample": sample},
+        "config": _config_dict(desc, pairs, Wr, Hr, world),
+        "cpu_baseline": {"value": v, "unit": UNIT, "cores": threads, "kind": kind, "sample": sample},
         "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0, "wall_s": time.perf_counter() - t0,
     }
     print(json.dumps(line))
     return 0
+
+
+def run_torch_gpu(args):
+    """--impl torch_gpu: the UNMODIFIED reference's eager PyTorch forward on one B200 under its own recipe
+    (ref base.py:272-274 bf16 autocast; ufm.py:635 / :921 fp32 heads; TF32 matmul as transformer_blocks.py:20), same
+    batch as the engine arm, device-resident uint8 inputs, CUDA-event timed.  Informational: the same-box PyTorch
+    number BASELINE.md section 2 names.  No engine code runs in this process."""
+    import torch
+
+    from oracle.golden_util import make_inputs
+
+    cfg, pairs, desc, name = _make_cfg(args.workload)
+    if args.pairs:
+        pairs = args.pairs
+    dev = torch.device("cuda", int(os.environ.get("LOCAL_RANK", "0")))
+    torch.cuda.set_device(dev)
+    call, kind = _reference_callable(cfg, dev)
+    W, H = cfg["inference_resolution"]
+    src, tgt = make_inputs(pairs, H, W, seed=1)
+    src, tgt = src.to(dev), tgt.to(dev)
+    for _ in range(max(2, args.warmup)):
+        call(src, tgt)
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(args.steps):
+        out = call(src, tgt)
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / args.steps
+    line = {"impl": "torch_gpu", "metric": METRIC, "value": pairs / (ms / 1e3), "unit": UNIT, "ms_per_step": ms,
+            "steps": args.steps, "warmup": max(2, args.warmup), "dtype": "bf16 autocast + fp32/TF32 heads",
+            "config": _config_dict(desc, pairs, W, H, 1), "kind": kind,
+            "what": "unmodified reference, eager PyTorch (cuBLAS / cuDNN / SDPA), predict_correspondences_batched on device uint8",
+            "peak_mem_gb": torch.cuda.max_memory_allocated() / 1e9}
+    print(json.dumps(line))
+    return 0
+
+
+def _torch_gpu_baseline_subprocess(args, local: int):
+    """Run `--impl torch_gpu` in a fresh process (the engine's process never loads the reference or its libraries)."""
+    from oracle import ref_harness as R
+
+    if not R.reference_available():
+        return {"unavailable": "no staged reference (oracle/_ref) on this box"}
+    env = dict(os.environ, LOCAL_RANK=str(local))
+    for k in ("RANK", "WORLD_SIZE", "MASTER_ADDR", "MASTER_PORT"):
+        env.pop(k, None)
+    cmd = [sys.executable, os.path.abspath(__file__), "--impl", "torch_gpu", "--workload", args.workload, "--steps",
+           str(max(3, min(args.steps, 5))), "--warmup", "2"] + (["--pairs", str(args.pairs)] if args.pairs else [])
+    try:
+        p = subprocess.run(cmd, env=env, capture_output=True, text=True, timeout=600)
+        for ln in reversed(p.stdout.strip().splitlines()):
+            if ln.startswith("{"):
+                d = json.loads(ln)
+                return {k: d[k] for k in ("value", "unit", "ms_per_step", "steps", "dtype", "what", "kind", "peak_mem_gb")}
+        return {"unavailable": f"exit {p.returncode}: {p.stderr.strip().splitlines()[-1] if p.stderr.strip() else 'no output'}"}
+    except Exception as e:  # noqa: BLE001
+        return {"unavailable": repr(e)}
 
 
 def run_engine(args):
@@ -373,16 +475,22 @@ def run_engine(args):
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "bf16",
         "data": "synthetic",
-        "config": {"workload": desc, "pairs_per_step_per_gpu": pairs, "resolution": [W, H], "weights": "random-init seed 0",
-                   "l2": "no flush needed: per-step working set (0.9 GB weights + >10 GB activations) exceeds the 126 MB L2",
-                   "parallelism": f"dp{world} (independent pairs, no data-path collective)"},
+        "config": _config_dict(desc, pairs, W, H, world),
         "step_ms": step_ms, "e2e": e2e, "gpu_launches": launches, "clocks": clocks, "roofline": roofline, "kernel_families": fam,
         "whole_pass": whole,
     }
+    if rank == 0 and world == 1 and not args.no_torch_gpu:
+        # a fresh process: the engine's process never imports the reference or loads cuBLAS / cuDNN
+        tg = _torch_gpu_baseline_subprocess(args, local)
+        line["torch_gpu_baseline"] = tg
+        if "value" in tg:
+            line["vs_torch_gpu"] = value / tg["value"]
     if rank == 0 and world == 1 and not args.no_cpu:
-        v, threads, ts = cpu_reference_pairs_per_s(cfg, refine, n_calls=args.cpu_calls, warmup=0)
-        line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": threads, "kind": "port",
-                                "sample": f"{len(ts)} call(s) of one {W}x{H} pair (batch 1) of the same model, CPU fp32 oracle"}
+        v, threads, ts, kind = cpu_reference_pairs_per_s(cfg, n_calls=args.cpu_calls, warmup=1)
+        what = "unmodified reference classes (oracle/_ref)" if kind == "reference" else "oracle port of the reference path"
+        line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": threads, "kind": kind,
+                                "sample": f"{len(ts)} timed call(s) after 1 warm-up, each ONE {W}x{H} pair (batch 1) of the "
+                                          f"workload's {pairs}-pair batch, CPU fp32, {what}"}
     sys.stdout.flush()
     os.dup2(saved_fd, 1)
     if rank == 0:
@@ -398,14 +506,19 @@ def main():
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
-    ap.add_argument("--impl", default="engine", choices=["engine", "reference"])
+    ap.add_argument("--impl", default="engine", choices=["engine", "reference", "torch_gpu"])
     ap.add_argument("--workload", default="base16", choices=list(WORKLOADS))
     ap.add_argument("--pairs", type=int, default=0, help="override pairs per step per GPU")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--no-torch-gpu", action="store_true", help="skip the informational eager-PyTorch GPU baseline")
     ap.add_argument("--cpu-calls", type=int, default=3)
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "engine" else args.warmup
-    return run_reference(args) if args.impl == "reference" else run_engine(args)
+    if args.impl == "reference":
+        return run_reference(args)
+    if args.impl == "torch_gpu":
+        return run_torch_gpu(args)
+    return run_engine(args)
 
 
 if __name__ == "__main__":

@@ -1,7 +1,8 @@
-"""Run the UNMODIFIED reference classes from /root/reference (build container only).
+"""Run the UNMODIFIED reference classes from /root/reference (build container) or from the staged byte-for-byte copy
+of its import closure under ``oracle/_ref`` (GPU box; made by ``oracle/build_ref.py``).
 
-Test infrastructure: used by ``oracle/make_golden.py`` and by tests that are skipped when
-``/root/reference`` is absent (it does not exist on the GPU box).  The single substitution is
+Test infrastructure: used by ``oracle/make_golden.py``, ``bench.py``'s reference legs and by tests that are skipped
+when neither location exists.  The single substitution is
 ``torch.hub.load`` (reference ``UniCeption/uniception/models/encoders/dinov2.py:85-91``), which has
 no network here; it is replaced by :class:`HubDinoVisionTransformer`, a restatement of the published
 ``facebookresearch/dinov2`` ``DinoVisionTransformer`` (``dinov2/models/vision_transformer.py``,
@@ -21,7 +22,22 @@ import torch
 import torch.nn as nn
 import torch.nn.functional as F
 
-REFERENCE_ROOT = os.environ.get("UFM_REFERENCE_ROOT", "/root/reference")
+_STAGED = os.path.join(os.path.dirname(os.path.abspath(__file__)), "_ref")
+
+
+def _find_root() -> str:
+    """$UFM_REFERENCE_ROOT, else /root/reference (build container), else the byte-for-byte import closure that
+    ``oracle/build_ref.py`` staged under ``oracle/_ref`` (git-ignored; it travels to the GPU box with gpurun)."""
+    env = os.environ.get("UFM_REFERENCE_ROOT")
+    if env:
+        return env
+    for cand in ("/root/reference", _STAGED):
+        if os.path.isdir(os.path.join(cand, "uniflowmatch")):
+            return cand
+    return "/root/reference"
+
+
+REFERENCE_ROOT = _find_root()
 
 
 def reference_available() -> bool:
