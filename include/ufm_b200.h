@@ -61,6 +61,14 @@ typedef struct ufm_config {
   /* FlowAdaptor.output_normalized_coordinate (adaptors.py:110-118): flow = raw * flow_scale + flow_shift - (x, y) of the
    * pixel, with flow_scale = flow_shift = (W/2, H/2).  0/1. */
   int flow_coord;
+  /* norm_intermediate of the encoder (dinov2.py:259-261: applies to EVERY returned index, the last one included) and of
+   * the info-sharing transformer (global_attention_transformer.py:549, alternating:666, cross:449: intermediates only,
+   * the final features are always normed).  1 = apply the final LayerNorm (the default), 0 = return the raw residual
+   * stream (a plain fp32 -> bf16 conversion pass). */
+  int enc_norm_intermediate, info_norm_intermediate;
+  /* (mean, std) of the encoder's data_norm_type (UC/models/encoders/image_normalizations.py:17-35) applied to uint8
+   * inputs as (v / 255 - mean) / std (base.py:215-229).  All zero = the "dinov2" constants. */
+  float img_mean[3], img_std[3];
 } ufm_config;
 
 /* adaptor kinds and their channel counts: mask 1 ('non_occluded_mask'), covariance 3 ('flow_cov'), confidence 1

@@ -308,8 +308,9 @@ def dpt_processor(x, sd, prefix, out_hw) -> torch.Tensor:
     return F.conv2d(x, sd[prefix + "conv2.2.weight"], sd[prefix + "conv2.2.bias"])
 
 
-def flow_adaptor(x, kw, out_hw):
-    """``FlowAdaptor.forward`` (UC/models/prediction_heads/adaptors.py:77-141)."""
+def flow_adaptor(x, kw, out_hw, buffers=None):
+    """``FlowAdaptor.forward`` (UC/models/prediction_heads/adaptors.py:77-141).  ``buffers`` = (flow_mean, flow_std) as
+    loaded from the state_dict: they are registered buffers (:70-71), so a checkpoint's values replace the kwargs."""
     H, W = out_hw
     if kw.get("output_normalized_coordinate", False):
         x = 0.5 * (x + 1) * torch.tensor([W, H], dtype=torch.float32).view(1, 2, 1, 1) + 0.5
@@ -323,6 +324,9 @@ def flow_adaptor(x, kw, out_hw):
     s = torch.tensor([sx, sy], dtype=torch.float32).view(1, 2, 1, 1)
     mean = torch.tensor(kw["flow_mean"], dtype=torch.float32).view(1, 2, 1, 1)
     std = torch.tensor(kw["flow_std"], dtype=torch.float32).view(1, 2, 1, 1)
+    if buffers is not None:
+        mean = buffers[0].float().view(1, 2, 1, 1) if buffers[0] is not None else mean
+        std = buffers[1].float().view(1, 2, 1, 1) if buffers[1] is not None else std
     return x * (std * s) + mean * s
 
 
@@ -350,13 +354,14 @@ def confidence_adaptor(x, kw):
     raise ValueError(t)
 
 
-def run_adaptors(raw, adaptors_kwargs, out_hw) -> Dict[str, Any]:
+def run_adaptors(raw, adaptors_kwargs, out_hw, sd=None, prefix="head1.1.adaptors.") -> Dict[str, Any]:
     """``AdaptorMap.forward`` (UC/models/prediction_heads/base.py:186-210): split channels in dict order."""
     out, c = {}, 0
     for name, a in adaptors_kwargs.items():
         cls = a["class"]
         if cls == "FlowAdaptor":
-            out[name] = flow_adaptor(raw[:, c:c + 2], a["kwargs"], out_hw)
+            buf = None if sd is None else (sd.get(f"{prefix}{name}.flow_mean"), sd.get(f"{prefix}{name}.flow_std"))
+            out[name] = flow_adaptor(raw[:, c:c + 2], a["kwargs"], out_hw, buf)
             c += 2
         elif cls == "MaskAdaptor":
             out[name] = {"logits": raw[:, c:c + 1], "mask": torch.sigmoid(raw[:, c:c + 1])}
@@ -512,7 +517,7 @@ def forward_stages(img1: torch.Tensor, img2: torch.Tensor, sd, cfg, stop_after: 
     head_in = [f1, inter[0][0], inter[1][0], final[0]]  # ufm.py:602-608, view 1 only
     st["dpt1"] = dpt_feature(head_in, sd, "head1.0.0.")
     st["head1_raw"] = dpt_processor(st["dpt1"], sd, "head1.0.1.", (H, W))
-    a1 = run_adaptors(st["head1_raw"], cfg["adaptors_kwargs"], (H, W))
+    a1 = run_adaptors(st["head1_raw"], cfg["adaptors_kwargs"], (H, W), sd)
     st["flow_reg"] = a1["flow"]
     if cfg.get("uncertainty_head_kwargs"):
         st["dptu"] = dpt_feature(head_in, sd, "uncertainty_head.0.0.")

@@ -75,7 +75,48 @@ def test_from_pretrained_ckpt_and_backbone_checkpoint(tmp_path):
         UniFlowMatchConfidence(pretrained_checkpoint_path=pb, **cfg)  # ufm.py:558
 
 
-@pytest.mark.skipif(not os.path.isdir("/root/reference/uniflowmatch"), reason="reference tree only exists in the build container")
+def _has_reference():
+    from oracle.ref_harness import reference_available
+
+    return reference_available()
+
+
+def test_flow_adaptor_buffers_win_over_kwargs():
+    """FlowAdaptor.flow_mean / flow_std are registered buffers (adaptors.py:70-71): the engine's affine comes from the
+    state_dict, the constructor kwargs are only the fallback."""
+    from ufm_b200.packing import engine_config
+
+    cfg = get_config("tiny_base")
+    sd = make_state_dict(cfg, seed=0)
+    c0 = engine_config(cfg, sd)
+    assert (c0.flow_scale[0], c0.flow_scale[1], c0.flow_shift[0], c0.flow_shift[1]) == (1.0, 1.0, 0.0, 0.0)
+    sd["head1.1.adaptors.flow.flow_mean"] = torch.tensor([3.0, -2.0]).view(1, 2, 1, 1)
+    sd["head1.1.adaptors.flow.flow_std"] = torch.tensor([2.0, 0.5]).view(1, 2, 1, 1)
+    c1 = engine_config(cfg, sd)
+    assert (c1.flow_scale[0], c1.flow_scale[1], c1.flow_shift[0], c1.flow_shift[1]) == (2.0, 0.5, 3.0, -2.0)
+    c2 = engine_config(cfg)
+    assert (c2.flow_scale[0], c2.flow_shift[0]) == (1.0, 0.0)
+
+
+def test_config_rejections_are_loud():
+    """Configurations the engine does not implement raise at construction instead of loading and mis-computing."""
+    from ufm_b200.packing import engine_config
+
+    cfg = get_config("tiny_base")
+    cfg["feature_head_kwargs"]["dpt_feature"]["nonlinearity"] = "gelu"
+    with pytest.raises(NotImplementedError):
+        engine_config(cfg)
+    cfg = get_config("tiny_base")
+    cfg["encoder_kwargs"]["data_norm_type"] = "no_such_norm"
+    with pytest.raises(ValueError):
+        engine_config(cfg)
+    c = engine_config(get_config("tiny_nonorm"))
+    assert c.enc_norm_intermediate == 0 and c.info_norm_intermediate == 0 and abs(c.img_mean[0] - 0.5) < 1e-7
+    c = engine_config(get_config("tiny_base"))
+    assert c.enc_norm_intermediate == 1 and c.info_norm_intermediate == 1 and abs(c.img_std[2] - 0.225) < 1e-7
+
+
+@pytest.mark.skipif(not _has_reference(), reason="no reference tree (/root/reference or the staged oracle/_ref)")
 def test_from_pretrained_reads_what_the_reference_saves(tmp_path):
     """The unmodified reference class (hub mixin) writes config.json + model.safetensors; ours must read it back."""
     from oracle.ref_harness import build_reference

@@ -497,7 +497,8 @@ def test_prep_resize_vs_torch_antialias(H0, W0, th, tw):
                                              (56, 70, 56, 70, 56, 70)])
 def test_unmap_vs_torch_shell(H0, W0, H1, W1, H, W):
     """unmap_predicted_flow / unmap_predicted_channels (flow_resizing.py:749-877, 955-1010) against their torch
-    restatement (prepost.unmap_flow / unmap_channels) on the CPU."""
+    restatement (oracle.ufm_oracle.unmap_flow / unmap_channels) on the CPU."""
+    from oracle import ufm_oracle as O
     from ufm_b200 import prepost
 
     g = torch.Generator().manual_seed(H0 + W1)
@@ -505,8 +506,8 @@ def test_unmap_vs_torch_shell(H0, W0, H1, W1, H, W):
     cov = torch.rand(2, H, W, generator=g)
     rep0 = prepost.scaled_region(H, W, H0, W0)
     src0, src1 = [0, H0, 0, W0], [0, H1, 0, W1]
-    rf = prepost.unmap_flow(flow, rep0, src0, src1, (H0, W0))
-    rc = prepost.unmap_channels(cov.unsqueeze(1), rep0, src0, (H0, W0)).squeeze(1)
+    rf = O.unmap_flow(flow, rep0, src0, src1, (H0, W0))
+    rc = O.unmap_channels(cov.unsqueeze(1), rep0, src0, (H0, W0)).squeeze(1)
     f, c = prepost.unmap(flow.cuda(), cov.cuda(), rep0, src0, src1, (H0, W0))
     assert f.shape == rf.shape and c.shape == rc.shape
     assert torch.equal(c.cpu(), rc)
@@ -514,7 +515,7 @@ def test_unmap_vs_torch_shell(H0, W0, H1, W1, H, W):
     # a source region smaller than the image: everything outside stays zero
     src0b = [3, H0 - 2, 5, W0 - 4]
     rep0b = prepost.scaled_region(H, W, H0, W0)
-    rf2 = prepost.unmap_flow(flow, rep0b, src0b, src1, (H0, W0))
+    rf2 = O.unmap_flow(flow, rep0b, src0b, src1, (H0, W0))
     f2, _ = prepost.unmap(flow.cuda(), None, rep0b, src0b, src1, (H0, W0))
     assert (f2.cpu() - rf2).abs().max().item() < 2e-4
     assert f2[:, :, :3].abs().max().item() == 0 and f2[:, :, :, :5].abs().max().item() == 0

@@ -5,9 +5,11 @@ Tolerances (BASELINE.json: "flow within 1e-2 px max-abs, or a stated relative to
 1e-3"): the engine follows the reference's GPU recipe (bf16 operands, fp32 accumulation / LayerNorm / residuals) and
 additionally keeps the DPT conv operands in bf16, so against the fp32 oracle the stated tolerances are
   stage features   rel-L2 <= 2e-2     (reference fp32<->bf16 autocast itself: 6.7e-3 / 6.4e-3)
-  final flow       rel-L2 <= 2e-2 and max-abs <= 2e-2 * max|flow|
-  Refine flow      rel-L2 <= 4e-2 (the 25-way softmax expectation, residual in [-2, 2] px, amplifies descriptor noise; the
-                   refinement kernel itself is checked to 5e-4 px by feeding the oracle the engine's own descriptors)
+  final flow       rel-L2 <= 1.6e-2 (measured <= 1.35e-2 over all cases)
+  Refine flow      rel-L2 <= 3e-2 (measured <= 2.1e-2; the 25-way softmax expectation, residual in [-2, 2] px, amplifies
+                   descriptor noise -- the unmodified reference under its OWN GPU recipe is 1.4e-2 / 4.1 px max-abs away
+                   from its fp32 run on ufm_refine_assumed, tests/test_gpu_vs_reference.py; the refinement kernel itself is
+                   checked to 5e-4 px by feeding the oracle the engine's own descriptors)
   covisibility     logits rel-L2 <= 2e-2 and |mask - ref| <= 0.25 * max|logit - ref logit| (sigmoid is 1/4-Lipschitz): the
                    fixtures amplify the random-init outputs (out_gain=8, logits up to +-80) so that errors are visible.
 At the natural random-init output scale (test_north_star_absolute_tolerances) the absolute north-star tolerances hold:
@@ -27,7 +29,7 @@ from ufm_b200 import UniFlowMatchClassificationRefinement, UniFlowMatchConfidenc
 from ufm_b200.weights import make_state_dict  # noqa: E402
 
 GOLDEN = os.path.join(os.path.dirname(__file__), "golden")
-FEAT_TOL, FLOW_TOL, REFINE_FLOW_TOL = 2e-2, 2e-2, 4e-2
+FEAT_TOL, FLOW_TOL, REFINE_FLOW_TOL = 2e-2, 1.6e-2, 3e-2
 
 
 @pytest.fixture(scope="module", autouse=True)
@@ -108,17 +110,18 @@ def _report(tag, rows):
         print(f"  {k:14s} rel-L2 {r:.3e}  max-abs {m:.3e}  (ref max {s:.3e})")
 
 
-@pytest.mark.parametrize("name", ["tiny_base", "tiny_refine", "tiny_alt_qknorm", "tiny_cross", "tiny_unet", "tiny_unet_mod", "tiny_rope", "tiny_coord", "tiny_cross_raw", "tiny_bn"])
+@pytest.mark.parametrize("name", ["tiny_base", "tiny_refine", "tiny_alt_qknorm", "tiny_cross", "tiny_unet", "tiny_unet_mod", "tiny_rope", "tiny_coord", "tiny_cross_raw", "tiny_bn", "tiny_nonorm"])
 def test_tiny_stagewise_vs_oracle(name):
     model, cfg, sd = _model(name)
     W, H = cfg["inference_resolution"]
     B = 3
     src, tgt = make_inputs(B, H, W, seed=5)
     refine = "classification_head_kwargs" in cfg
-    s0, s1 = O.canonicalize_inputs(src, tgt, "dinov2", None)
+    nt = cfg["encoder_kwargs"]["data_norm_type"]
+    s0, s1 = O.canonicalize_inputs(src, tgt, nt, None)
     with torch.no_grad():
         ref = O.forward_stages(s0, s1, sd, cfg)
-    res = model.forward({"img": s0.cuda(), "data_norm_type": "dinov2"}, {"img": s1.cuda(), "data_norm_type": "dinov2"})
+    res = model.forward({"img": s0.cuda(), "data_norm_type": nt}, {"img": s1.cuda(), "data_norm_type": nt})
     torch.cuda.synchronize()
     st = _engine_stages(model, B, H // 14, W // 14)
     enc_last = torch.stack([ref[f"enc{len(cfg['encoder_kwargs']['indices']) - 1}"][:B],
@@ -393,3 +396,36 @@ def test_multiple_inference_resolutions():
         assert r <= FLOW_TOL, (H0, W0, r)
         assert (out.covisibility.mask.cpu() - ref["covisibility"]).abs().mean().item() < 1e-2
     assert len(model._engines) == 2
+
+
+def test_ingested_checkpoint_matches_oracle(tmp_path):
+    """SURVEY.md 8f N4 on the GPU: a checkpoint written by the UNMODIFIED reference class through its hub mixin
+    (config.json + model.safetensors, ufm.py:120) -- or by save_pretrained when no reference tree is staged -- is read by
+    from_pretrained and must produce the oracle's output for those weights.  The checkpoint carries FlowAdaptor buffers
+    that differ from the constructor kwargs (adaptors.py:70-71): the buffers must win."""
+    from oracle import ref_harness as R
+
+    cfg = case_config("tiny_refine")
+    sd = make_state_dict(cfg, seed=4, out_gain=8.0)
+    sd["head1.1.adaptors.flow.flow_mean"] = torch.tensor([1.5, -0.75]).view(1, 2, 1, 1)
+    sd["head1.1.adaptors.flow.flow_std"] = torch.tensor([1.25, 0.5]).view(1, 2, 1, 1)
+    path = str(tmp_path / "ckpt")
+    if R.reference_available():
+        R.build_reference(cfg, sd).save_pretrained(path)
+    else:
+        m0 = UniFlowMatchClassificationRefinement(**cfg)
+        m0.load_state_dict(sd)
+        m0.save_pretrained(path)
+    model = UniFlowMatchClassificationRefinement.from_pretrained(path).to("cuda")
+    W, H = cfg["inference_resolution"]
+    src, tgt = make_inputs(2, H, W, seed=13)
+    out = model.predict_correspondences_batched(src.cuda(), tgt.cuda())
+    torch.cuda.synchronize()
+    with torch.no_grad():
+        ref = O.predict_correspondences_batched(src, tgt, sd, cfg)
+        plain = O.predict_correspondences_batched(src, tgt, {k: v for k, v in sd.items() if "adaptors.flow" not in k}, cfg)
+    r = rel_l2(out.flow.flow_output.cpu(), ref["flow"])
+    print(f"\n[ingested checkpoint] flow rel-L2 {r:.3e} (kwargs-only affine would be {rel_l2(plain['flow'], ref['flow']):.3e} off)")
+    assert r <= REFINE_FLOW_TOL
+    assert rel_l2(plain["flow"], ref["flow"]) > 0.1  # the perturbed buffers matter
+    assert (out.covisibility.mask.cpu() - ref["covisibility"]).abs().mean().item() < 1e-2

@@ -21,7 +21,7 @@ def _run_oracle(name):
     W, H = cfg["inference_resolution"]
     src, tgt = make_inputs(case["batch"], H, W)
     with torch.no_grad():
-        s0, s1 = O.canonicalize_inputs(src, tgt, "dinov2", None)
+        s0, s1 = O.canonicalize_inputs(src, tgt, cfg["encoder_kwargs"]["data_norm_type"], None)
         st = O.forward_stages(s0, s1, sd, cfg)
         api = O.predict_correspondences_batched(src, tgt, sd, cfg) if name.startswith("tiny") else None
     if "log_softmax" in st:

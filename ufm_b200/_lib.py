@@ -40,6 +40,8 @@ class UfmConfig(C.Structure):
         ("unet", C.c_int),
         ("info_rope", C.c_int),
         ("flow_coord", C.c_int),
+        ("enc_norm_intermediate", C.c_int), ("info_norm_intermediate", C.c_int),
+        ("img_mean", C.c_float * 3), ("img_std", C.c_float * 3),
     ]
 
 

@@ -141,6 +141,14 @@ def _use_bn(cfg):
     return cfg
 
 
+def _nonorm(cfg):
+    """norm_intermediate=False on the encoder (dinov2.py:259-261: every returned index stays un-normed) and on the info
+    sharing (intermediates only, global_attention_transformer.py:549), with a non-default encoder data_norm_type."""
+    cfg["encoder_kwargs"].update({"norm_intermediate": False, "data_norm_type": "dust3r"})
+    cfg["info_sharing_kwargs"]["norm_intermediate"] = False
+    return cfg
+
+
 def _coord(cfg):
     """FlowAdaptor predicting the landing position (output_normalized_coordinate, adaptors.py:110-118)."""
     cfg["adaptors_kwargs"]["flow"]["kwargs"]["output_normalized_coordinate"] = True
@@ -159,6 +167,7 @@ CONFIGS = {
     "tiny_rope": lambda: tiny(False, qk_norm=True, rope=True),
     "tiny_bn": lambda: _use_bn(tiny(False)),
     "tiny_coord": lambda: _coord(tiny(True)),
+    "tiny_nonorm": lambda: _nonorm(tiny(True)),
     "tiny_unet": lambda: tiny(True, unet="conv"),
     "tiny_unet_mod": lambda: tiny(True, unet="modulate"),
     "ufm_refine_unet": lambda: dict(ufm_refine_assumed(), use_unet_feature=True, feature_combine_method="conv"),

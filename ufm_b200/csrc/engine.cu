@@ -238,6 +238,19 @@ bool build_attn(AttnParams* ap, const void* qkv, int n_seq, int seq_len, int hea
 
 }  // namespace
 
+// C-ABI entry points run on the engine's device and restore the caller's current device on return (a multi-GPU
+// process must not find its current device switched by a predict on another GPU).
+struct DevGuard {
+  int prev = -1, dev;
+  explicit DevGuard(int d) : dev(d) {
+    if (cudaGetDevice(&prev) != cudaSuccess) prev = -1;
+    if (prev != dev) cudaSetDevice(dev);
+  }
+  ~DevGuard() {
+    if (prev >= 0 && prev != dev) cudaSetDevice(prev);
+  }
+};
+
 struct ufm_engine {
   ufm_config cfg;
   int device = 0;
@@ -252,12 +265,42 @@ struct ufm_engine {
   std::map<std::string, Tensor> buf;    // workspace
   std::map<std::string, Tensor> stage;  // views of the last forward (not owned)
   cudaStream_t st = nullptr;
+  // Every pass shares one workspace: a pass on a different stream than the previous one first waits for the event the
+  // previous pass recorded at its end (ufm_forward on the caller's stream, ufm_forward_host on the legacy stream or
+  // the private graph stream may follow each other in any order).
+  cudaEvent_t ev_done = nullptr;
+  cudaStream_t done_stream = nullptr;
+  bool have_done = false, capturing = false;
+  bool order_after_previous(cudaStream_t s) {
+    if (capturing) return true;
+    if (have_done && s != done_stream) return ck(cudaStreamWaitEvent(s, ev_done, 0), "order after the previous pass");
+    return true;
+  }
+  bool mark_done(cudaStream_t s) {
+    if (capturing) return true;
+    if (!ev_done && !ck(cudaEventCreateWithFlags(&ev_done, cudaEventDisableTiming), "event")) return false;
+    if (!ck(cudaEventRecord(ev_done, s), "record end of pass")) return false;
+    done_stream = s;
+    have_done = true;
+    return true;
+  }
+  int forward_impl(const void* src, const void* tgt, int pairs, int in_dtype, int in_layout, float* flow_out,
+                   float* covis_out, cudaStream_t stream);
   // ufm_forward_host: result copies run on their own stream as soon as each output is final (flow after the flow head
   // or the refinement, covisibility after the uncertainty head), under the rest of the pass
   cudaStream_t copy_st = nullptr;
   cudaEvent_t ev_flow = nullptr, ev_cov = nullptr;
   bool mark_outputs = false;
   int ln_reverse = getenv("UFM_LN_FWD") ? 0 : 1;
+  // (mean, std) of the encoder's data_norm_type; an all-zero config entry means the "dinov2" constants
+  float img_mean(int i) const {
+    static const float m[3] = {0.485f, 0.456f, 0.406f};
+    return cfg.img_std[0] == 0.f ? m[i] : cfg.img_mean[i];
+  }
+  float img_std(int i) const {
+    static const float s[3] = {0.229f, 0.224f, 0.225f};
+    return cfg.img_std[0] == 0.f ? s[i] : cfg.img_std[i];
+  }
   // ufm_forward_host, small batches (launch-bound: ~330 launches and as many tensor-map encodes per pass): the pass is
   // captured once per (pairs, dtype, layout, keep_aux) into a CUDA graph over the engine-owned staging buffers and replayed
   struct GraphEntry { cudaGraphExec_t exec = nullptr; std::map<std::string, Tensor> stage; int launches = 0; };
@@ -377,12 +420,13 @@ struct ufm_engine {
   }
   bool layernorm(const float* x, int n_seq, int src_seq_len, int skip, int tokens, int D, const std::string& pre,
                  int remap_B, bf16* ob, long long ob_pitch, long long ob_col, float* of = nullptr, long long of_pitch = 0,
-                 long long of_col = 0) {
+                 long long of_col = 0, bool no_norm = false) {
     LNParams p;
     p.x = x; p.D = D; p.eps = 1e-6f;
-    // an absent norm (CrossAttentionBlock.norm_y = nn.Identity() when norm_cross_tokens=False, transformer_blocks.py:458)
-    // runs the same kernel as a plain fp32 -> bf16 conversion
-    const bool identity = pre.size() > 4 && pre.compare(pre.size() - 4, 4, ".lny") == 0 && !has(pre + ".w");
+    // an absent norm (CrossAttentionBlock.norm_y = nn.Identity() when norm_cross_tokens=False, transformer_blocks.py:458;
+    // norm_intermediate=False, dinov2.py:259-261 / global_attention_transformer.py:549) runs the same kernel as a plain
+    // fp32 -> bf16 conversion
+    const bool identity = no_norm || (pre.size() > 4 && pre.compare(pre.size() - 4, 4, ".lny") == 0 && !has(pre + ".w"));
     p.w = identity ? nullptr : Wf(pre + ".w"); p.b = identity ? nullptr : Wf(pre + ".b");
     if (!identity && (!p.w || !p.b)) return false;
     p.n_seq = n_seq; p.src_seq_len = src_seq_len; p.src_skip = skip; p.tokens = tokens; p.remap_B = remap_B;
@@ -726,8 +770,7 @@ bool ufm_engine::unet_branch(const void* src, const void* tgt, int in_dtype, int
     UnetStemParams sp;
     sp.src = src; sp.tgt = tgt; sp.B = Bp; sp.H = c.img_h; sp.W = c.img_w;
     sp.is_u8 = in_dtype == UFM_U8; sp.is_nhwc = in_layout == UFM_NHWC;
-    const float mean[3] = {0.485f, 0.456f, 0.406f}, stdv[3] = {0.229f, 0.224f, 0.225f};
-    for (int i = 0; i < 3; ++i) { sp.mean[i] = mean[i]; sp.inv_std[i] = 1.0f / stdv[i]; }
+    for (int i = 0; i < 3; ++i) { sp.mean[i] = img_mean(i); sp.inv_std[i] = 1.0f / img_std(i); }
     sp.w = Wf("unet.stem.w"); sp.b = Wf("unet.stem.b"); sp.out = T;
     if (!sp.w || !sp.b) return false;
     const double px = (double)N2 * c.img_h * c.img_w;
@@ -789,6 +832,14 @@ bool ufm_engine::unet_branch(const void* src, const void* tgt, int in_dtype, int
 
 int ufm_engine::forward(const void* src, const void* tgt, int pairs, int in_dtype, int in_layout, float* flow_out,
                         float* covis_out, cudaStream_t stream) {
+  if (!order_after_previous(stream)) return 1;
+  const int rc = forward_impl(src, tgt, pairs, in_dtype, in_layout, flow_out, covis_out, stream);
+  if (!mark_done(stream)) return 1;
+  return rc;
+}
+
+int ufm_engine::forward_impl(const void* src, const void* tgt, int pairs, int in_dtype, int in_layout, float* flow_out,
+                             float* covis_out, cudaStream_t stream) {
   if (!prepared) return fail("ufm_prepare was not called");
   if (pairs < 1 || pairs > max_pairs) return fail("pairs=%d outside [1, %d]", pairs, max_pairs);
   if (in_dtype != UFM_U8 && in_dtype != UFM_F32) return fail("input dtype must be u8 or f32");
@@ -809,10 +860,9 @@ int ufm_engine::forward(const void* src, const void* tgt, int pairs, int in_dtyp
     PatchParams pp;
     pp.src = src; pp.tgt = tgt; pp.B = Bp; pp.H = c.img_h; pp.W = c.img_w; pp.P = c.patch; pp.Kpad = Kpad;
     pp.is_u8 = in_dtype == UFM_U8; pp.is_nhwc = in_layout == UFM_NHWC;
-    const float mean[3] = {0.485f, 0.456f, 0.406f}, stdv[3] = {0.229f, 0.224f, 0.225f};
     for (int i = 0; i < 3; ++i) {
-      pp.mean[i] = mean[i];
-      pp.inv_std[i] = 1.0f / stdv[i];
+      pp.mean[i] = img_mean(i);
+      pp.inv_std[i] = 1.0f / img_std(i);
     }
     pp.out = B<bf16>("Apatch");
     const double px = 2.0 * Bp * c.img_h * c.img_w * 3;
@@ -836,15 +886,16 @@ int ufm_engine::forward(const void* src, const void* tgt, int pairs, int in_dtyp
       return 1;
   }
   bf16* enc_last = B<bf16>("enc_last");
+  const bool enc_raw = c.enc_norm_intermediate == 0, info_raw = c.info_norm_intermediate == 0;
   for (int i = 0; i < c.enc_depth; ++i) {
     if (!block("enc." + std::to_string(i), x, 2 * Bp, S, D, c.enc_heads, 4 * D, false)) return 1;
     if (c.refine && i == c.enc_take_first) {
       // final norm, drop cls, (view,b) -> (b,view) order, into the left D columns of the classification-head input
-      if (!layernorm(x, 2 * Bp, S, 1, n, D, "enc.norm", Bp, B<bf16>("Xcls"), c.cls_in, 0)) return 1;
+      if (!layernorm(x, 2 * Bp, S, 1, n, D, "enc.norm", Bp, B<bf16>("Xcls"), c.cls_in, 0, nullptr, 0, 0, enc_raw)) return 1;
       set_stage("enc_first", B<bf16>("Xcls"), UFM_BF16, {Bp, 2, n, c.cls_in});
     }
     if (i == c.enc_take_last) {
-      if (!layernorm(x, 2 * Bp, S, 1, n, D, "enc.norm", Bp, enc_last, D, 0)) return 1;
+      if (!layernorm(x, 2 * Bp, S, 1, n, D, "enc.norm", Bp, enc_last, D, 0, nullptr, 0, 0, enc_raw)) return 1;
       set_stage("enc_last", enc_last, UFM_BF16, {Bp, 2, n, D});
     }
   }
@@ -869,9 +920,9 @@ int ufm_engine::forward(const void* src, const void* tgt, int pairs, int in_dtyp
     if (!gemm(a, "info.proj.w", 1, e)) return 1;
   }
   // final LayerNorm of the stream -> a pair-major [B,2,n,*] feature buffer (the layout the heads read)
-  auto info_norm = [&](bf16* dst, long long pitch, long long col) {
-    return cross ? layernorm(y, 2 * Bp, n, 0, n, d, "info.norm", Bp, dst, pitch, col)
-                 : layernorm(y, 1, (int)Mi, 0, (int)Mi, d, "info.norm", 0, dst, pitch, col);
+  auto info_norm = [&](bf16* dst, long long pitch, long long col, bool raw = false) {
+    return cross ? layernorm(y, 2 * Bp, n, 0, n, d, "info.norm", Bp, dst, pitch, col, nullptr, 0, 0, raw)
+                 : layernorm(y, 1, (int)Mi, 0, (int)Mi, d, "info.norm", 0, dst, pitch, col, nullptr, 0, 0, raw);
   };
   for (int i = 0; i < c.info_depth; ++i) {
     if (cross) {
@@ -883,11 +934,11 @@ int ufm_engine::forward(const void* src, const void* tgt, int pairs, int in_dtyp
         return 1;
     }
     if (i == c.info_take0) {
-      if (!info_norm(B<bf16>("inter0"), d, 0)) return 1;
+      if (!info_norm(B<bf16>("inter0"), d, 0, info_raw)) return 1;
       set_stage("info_inter0", B<bf16>("inter0"), UFM_BF16, {Bp, 2, n, d});
     }
     if (i == c.info_take1) {
-      if (!info_norm(B<bf16>("inter1"), d, 0)) return 1;
+      if (!info_norm(B<bf16>("inter1"), d, 0, info_raw)) return 1;
       set_stage("info_inter1", B<bf16>("inter1"), UFM_BF16, {Bp, 2, n, d});
     }
   }
@@ -1022,7 +1073,7 @@ int ufm_create(const ufm_config* cfg, int device, ufm_engine** out) {
   e->cfg = *cfg;
   e->device = device;
   e->num_sms = prop.multiProcessorCount;
-  cudaSetDevice(device);
+  DevGuard dev_guard(device);
   const ufm_config& c = e->cfg;
   if (c.img_h % c.patch || c.img_w % c.patch) {
     delete e;
@@ -1075,10 +1126,11 @@ int ufm_create(const ufm_config* cfg, int device, ufm_engine** out) {
 
 void ufm_destroy(ufm_engine* e) {
   if (!e) return;
-  cudaSetDevice(e->device);
+  DevGuard dev_guard(e->device);
   for (auto ev : e->ev_pool) cudaEventDestroy(ev);
   for (auto& kv : e->graphs) cudaGraphExecDestroy(kv.second.exec);
   if (e->graph_st) cudaStreamDestroy(e->graph_st);
+  if (e->ev_done) cudaEventDestroy(e->ev_done);
   if (e->copy_st) {
     cudaStreamDestroy(e->copy_st);
     cudaEventDestroy(e->ev_flow);
@@ -1093,7 +1145,7 @@ const char* ufm_last_error(ufm_engine* e) { return e ? e->err.c_str() : "null en
 
 int ufm_set_weight(ufm_engine* e, const char* name, const void* ptr, int dtype, const int64_t* shape, int ndim) {
   if (!e) return 1;
-  cudaSetDevice(e->device);
+  DevGuard dev_guard(e->device);
   Tensor t;
   t.dtype = dtype;
   t.shape.assign(shape, shape + ndim);
@@ -1114,7 +1166,7 @@ int ufm_set_weight(ufm_engine* e, const char* name, const void* ptr, int dtype, 
 
 int ufm_prepare(ufm_engine* e, int max_pairs) {
   if (!e) return 1;
-  cudaSetDevice(e->device);
+  DevGuard dev_guard(e->device);
   for (auto& kv : e->buf) cudaFree(kv.second.ptr);
   e->buf.clear();
   e->prepared = false;
@@ -1215,7 +1267,7 @@ int ufm_prepare(ufm_engine* e, int max_pairs) {
 int ufm_forward(ufm_engine* e, const void* src, const void* tgt, int pairs, int in_dtype, int in_layout,
                 float* flow_out, float* covis_out, void* stream) {
   if (!e) return 1;
-  cudaSetDevice(e->device);
+  DevGuard dev_guard(e->device);
   if (!flow_out) return e->fail("flow_out is NULL");
   return e->forward(src, tgt, pairs, in_dtype, in_layout, flow_out, covis_out, reinterpret_cast<cudaStream_t>(stream));
 }
@@ -1223,7 +1275,7 @@ int ufm_forward(ufm_engine* e, const void* src, const void* tgt, int pairs, int 
 int ufm_forward_host(ufm_engine* e, const void* src, const void* tgt, int pairs, int in_dtype, int in_layout,
                      float* flow_out, float* covis_out) {
   if (!e) return 1;
-  cudaSetDevice(e->device);
+  DevGuard dev_guard(e->device);
   if (!e->prepared) return e->fail("ufm_prepare was not called");
   if (pairs < 1 || pairs > e->max_pairs) return e->fail("pairs=%d outside [1, %d]", pairs, e->max_pairs);
   const ufm_config& c = e->cfg;
@@ -1239,6 +1291,7 @@ int ufm_forward_host(ufm_engine* e, const void* src, const void* tgt, int pairs,
     // ---- launch-bound regime: replay a captured pass ----
     if (!e->graph_st && !e->ck(cudaStreamCreateWithFlags(&e->graph_st, cudaStreamNonBlocking), "graph stream")) return 1;
     cudaStream_t gs = e->graph_st;
+    if (!e->order_after_previous(gs)) return 1;  // the staging buffers and the workspace may still be in use elsewhere
     if (!e->ck(cudaMemcpyAsync(dsrc, src, in_bytes, cudaMemcpyHostToDevice, gs), "H2D src")) return 1;
     if (!e->ck(cudaMemcpyAsync(dtgt, tgt, in_bytes, cudaMemcpyHostToDevice, gs), "H2D tgt")) return 1;
     const std::vector<int> key = {pairs, in_dtype, in_layout, e->keep_aux ? 1 : 0};
@@ -1250,9 +1303,14 @@ int ufm_forward_host(ufm_engine* e, const void* src, const void* tgt, int pairs,
       ufm_engine::GraphEntry ge;
       cudaGraph_t graph = nullptr;
       if (!e->ck(cudaStreamBeginCapture(gs, cudaStreamCaptureModeThreadLocal), "begin capture")) return 1;
+      e->capturing = true;
       const int rc = e->forward(dsrc, dtgt, pairs, in_dtype, in_layout, dflow, dcov, gs);
+      e->capturing = false;
       const cudaError_t ce = cudaStreamEndCapture(gs, &graph);
-      if (rc) return 1;
+      if (rc || ce != cudaSuccess) {
+        if (graph) cudaGraphDestroy(graph);
+        if (rc) return 1;
+      }
       if (!e->ck(ce, "end capture")) return 1;
       const cudaError_t ie = cudaGraphInstantiate(&ge.exec, graph, 0);
       cudaGraphDestroy(graph);
@@ -1267,12 +1325,14 @@ int ufm_forward_host(ufm_engine* e, const void* src, const void* tgt, int pairs,
       e->launches = it->second.launches;
       e->last_pairs = pairs;
       e->st = gs;
+      if (!e->mark_done(gs)) return 1;
     }
     if (!e->ck(cudaMemcpyAsync(flow_out, dflow, pairs * 2 * plane0 * 4, cudaMemcpyDeviceToHost, gs), "D2H flow")) return 1;
     if (covis_out && dcov)
       if (!e->ck(cudaMemcpyAsync(covis_out, dcov, pairs * plane0 * 4, cudaMemcpyDeviceToHost, gs), "D2H covis")) return 1;
     return e->ck(cudaStreamSynchronize(gs), "sync") ? 0 : 1;
   }
+  if (!e->order_after_previous(st)) return 1;
   if (!e->ck(cudaMemcpyAsync(dsrc, src, in_bytes, cudaMemcpyHostToDevice, st), "H2D src")) return 1;
   if (!e->ck(cudaMemcpyAsync(dtgt, tgt, in_bytes, cudaMemcpyHostToDevice, st), "H2D tgt")) return 1;
   if (!e->copy_st) {
@@ -1320,7 +1380,7 @@ int ufm_stage_desc(ufm_engine* e, const char* name, int* dtype, int64_t* shape, 
 
 int ufm_stage_copy(ufm_engine* e, const char* name, void* dst, int64_t bytes) {
   if (!e) return 1;
-  cudaSetDevice(e->device);
+  DevGuard dev_guard(e->device);
   auto it = e->stage.find(name);
   if (it == e->stage.end()) return e->fail("no stage '%s' in the last forward", name);
   if (bytes != it->second.bytes()) return e->fail("stage '%s' is %lld bytes, caller gave %lld", name,
@@ -1342,7 +1402,7 @@ int ufm_set_profile(ufm_engine* e, int on) {
 
 int ufm_profile_read(ufm_engine* e, double* ms, double* flops, double* bytes, int64_t* launches) {
   if (!e) return 1;
-  cudaSetDevice(e->device);
+  DevGuard dev_guard(e->device);
   if (!e->ck(cudaStreamSynchronize(e->st), "sync")) return 1;
   for (int i = 0; i < UFM_NUM_CATS; ++i) {
     ms[i] = flops[i] = bytes[i] = 0.0;

@@ -430,10 +430,15 @@ __device__ __forceinline__ void cubic_w(float t, float (&w)[4]) {
   w[3] = ((A * x3 - 5.f * A) * x3 + 8.f * A) * x3 - 4.f * A;
 }
 
-// Descriptor maps are stored channel-group planar, [image][C/8][H][W][8] bf16 (the classification head runs under
-// autocast in the reference, ufm.py:949, so its output IS bf16): the 32 pixels of a warp then read 32 consecutive 16-byte
-// chunks per load instruction (4 L1 wavefronts) instead of 32 chunks 64 bytes apart (16 wavefronts) -- the gather of
-// 64 taps x 16 channels per pixel is bound by L1 wavefronts, not by HBM.
+// Descriptor maps are stored channel-group planar, [image][C/8][H][W][8] bf16: the 32 pixels of a warp then read 32
+// consecutive 16-byte chunks per load instruction (4 L1 wavefronts) instead of 32 chunks 64 bytes apart (16 wavefronts)
+// -- the gather of 64 taps x 16 channels per pixel is bound by L1 wavefronts, not by HBM.
+// PRECISION NOTE: bf16 descriptors are NARROWER than the reference.  The classification head, the UNet combine and the
+// refinement sit inside `with torch.autocast("cuda", torch.float32)` (ufm.py:921; :635 for the Base heads), which
+// DISABLES autocast: the reference computes them in fp32 (TF32 matmuls / cuDNN convs on a GPU).  The measured cost
+// (tests/test_gpu_vs_reference.py): on ufm_refine_assumed the engine is 2.0e-2 rel-L2 from the
+// reference's fp32 run where the reference's own GPU recipe is 1.4e-2 (both have ~4 px max-abs outliers where the
+// 25-way softmax flips); the refinement arithmetic itself is within 5e-4 px of the oracle on the same descriptors.
 #ifndef REFINE_MIN_BLOCKS
 #define REFINE_MIN_BLOCKS 6
 #endif

@@ -28,7 +28,7 @@ class Engine:
             raise UfmEngineError(f"engine device must be CUDA, got {self.device}")
         self.index = self.device.index if self.device.index is not None else torch.cuda.current_device()
         self.cfg = cfg
-        self.ec = engine_config(cfg)
+        self.ec = engine_config(cfg, state_dict)
         self.H, self.W = self.ec.img_h, self.ec.img_w
         kinds = [self.ec.unc_kind[i] for i in range(self.ec.unc_n_adaptors)]
         self.has_mask = self.ec.unc_out_ch > 0 and (not kinds or _lib.ADAPT_MASK in kinds)

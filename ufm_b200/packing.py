@@ -56,7 +56,9 @@ def unc_adaptor_kinds(ua):
     return out
 
 
-def flow_affine(cfg, H, W):
+def flow_affine(cfg, H, W, state_dict=None):
+    """(scale, shift) of the FlowAdaptor.  flow_mean / flow_std are registered BUFFERS of the reference adaptor
+    (adaptors.py:70-71, used at :104-112), so a checkpoint's values win over the constructor kwargs."""
     a = cfg["adaptors_kwargs"]
     if list(a.keys()) != ["flow"] or a["flow"]["class"] != "FlowAdaptor":
         raise NotImplementedError("engine flow head supports a single FlowAdaptor named 'flow' (ufm.py:645)")
@@ -69,10 +71,16 @@ def flow_affine(cfg, H, W):
     sx, sy = {"none": (1.0, 1.0), "scale_width": (W / bw, W / bw), "scale_height": (H / bh, H / bh),
               "scale_both": (W / bw, H / bh)}[kw.get("scale_strategy", "none")]
     std, mean = kw["flow_std"], kw["flow_mean"]
+    if state_dict is not None:
+        bm, bs = (state_dict.get(f"head1.1.adaptors.flow.{k}") for k in ("flow_mean", "flow_std"))
+        if bm is not None:
+            mean = [float(v) for v in bm.detach().float().flatten().cpu()]
+        if bs is not None:
+            std = [float(v) for v in bs.detach().float().flatten().cpu()]
     return (std[0] * sx, std[1] * sy), (mean[0] * sx, mean[1] * sy)
 
 
-def engine_config(cfg: Dict[str, Any]) -> "_lib.UfmConfig":
+def engine_config(cfg: Dict[str, Any], state_dict=None) -> "_lib.UfmConfig":
     H, W = inference_hw(cfg)
     ek, ik = cfg["encoder_kwargs"], cfg["info_sharing_kwargs"]
     if cfg.get("encoder_str", "dinov2") != "dinov2" or ek.get("with_registers"):
@@ -116,6 +124,16 @@ def engine_config(cfg: Dict[str, Any]) -> "_lib.UfmConfig":
     c.info_rope = int(cpe == "rope")
     c.info_layerscale = int(bool(ik.get("init_values")))
     c.info_has_proj = 1
+    c.enc_norm_intermediate = int(bool(ek.get("norm_intermediate", True)))    # dinov2.py:259-261
+    c.info_norm_intermediate = int(bool(ik.get("norm_intermediate", True)))   # global_attention_transformer.py:549
+    from .prepost import IMAGE_NORMALIZATION
+
+    norm_name = ek.get("data_norm_type", "dinov2")
+    if norm_name not in IMAGE_NORMALIZATION:
+        raise ValueError(f"encoder data_norm_type {norm_name!r} is not in IMAGE_NORMALIZATION_DICT")
+    mean, std = IMAGE_NORMALIZATION[norm_name]
+    for i in range(3):
+        c.img_mean[i], c.img_std[i] = float(mean[i]), float(std[i])
     f = cfg["feature_head_kwargs"]["dpt_feature"]
     pr = cfg["feature_head_kwargs"]["dpt_processor"]
     if list(f.get("hooks", [0, 1, 2, 3])) != [0, 1, 2, 3]:
@@ -123,12 +141,18 @@ def engine_config(cfg: Dict[str, Any]) -> "_lib.UfmConfig":
     for i in range(4):
         c.dpt_layer_dims[i] = f["layer_dims"][i]
     c.dpt_feature_dim = f["feature_dim"]
+    for hk in ("feature_head_kwargs", "uncertainty_head_kwargs"):
+        for part in ("dpt_feature", "dpt_processor"):
+            nl = (cfg.get(hk) or {}).get(part, {}).get("nonlinearity", "relu")
+            if nl != "relu":
+                raise NotImplementedError(f"{hk}.{part}.nonlinearity={nl!r}: the engine's DPT epilogues implement ReLU "
+                                          "(dpt.py:55,246; dpt_block.py make_nonlinearity)")
     hd = pr.get("hidden_dims") or [pr["input_feature_dim"] // 2] * 2
     if hd[0] != hd[1]:
         raise NotImplementedError("DPT processor hidden dims must match")
     c.dpt_hidden = hd[0]
     c.flow_out_ch = pr["output_dim"]
-    (s0, s1), (b0, b1) = flow_affine(cfg, H, W)
+    (s0, s1), (b0, b1) = flow_affine(cfg, H, W, state_dict)
     c.flow_scale[0], c.flow_scale[1], c.flow_shift[0], c.flow_shift[1] = s0, s1, b0, b1
     c.flow_coord = int(bool(cfg["adaptors_kwargs"]["flow"]["kwargs"].get("output_normalized_coordinate", False)))
     c.unc_out_ch = 0
