@@ -43,7 +43,8 @@ constexpr int OFF_BAR = OFF_V + V_STAGES * TILE_BYTES;
 constexpr int SMEM_BYTES = OFF_BAR + 256;  // 114944 B: two CTAs per SM
 constexpr int TMEM_COLS = 256;
 constexpr uint32_t TM_S = 0, TM_P = 128, TM_O = 192;
-int g_attn_poly = 4;  // every n-th pair of exponentials of a full tile runs on the FMA pipe (0 = never); ufm_debug_flag 2
+int g_attn_poly = 132;  // low 4 bits: every n-th pair of exponentials of a full tile runs on the FMA pipe (0 = never);
+                         // bit 7: streamed softmax steps with a speculative reference maximum; ufm_debug_flag 2
 
 __device__ __forceinline__ float ex2(float x) {
   float y;
@@ -269,6 +270,91 @@ __device__ __forceinline__ void softmax_step(Bars* b, uint32_t s_addr, uint32_t 
   if (lane == 0) mbar_arrive(&b->p_full);
 }
 
+// Exponentials of one 32-column chunk of a score row (in place in s[0..32)): p = exp2(s * sl2 + mb), every POLY-th pair on
+// the FMA pipe; returns the chunk's row sum in (sum_a, sum_b) and the bf16 pairs in pk[0..16).
+template <int POLY>
+__device__ __forceinline__ void exp_chunk32(uint32_t* s, uint32_t* pk, uint64_t sl2_2, uint64_t mb_2, uint64_t& sum_a,
+                                            uint64_t& sum_b, int phase) {
+#pragma unroll
+  for (int i = 0; i < 16; ++i) {
+    float x0, x1, p0, p1;
+    const bool poly = POLY > 0 && ((i + phase) % (POLY > 0 ? POLY : 1)) == POLY - 1;
+    unpack2(fma2(pack2(__uint_as_float(s[2 * i]), __uint_as_float(s[2 * i + 1])), sl2_2, mb_2), x0, x1);
+    if (poly) {
+      ex2_poly2(x0, x1, p0, p1);
+    } else {
+      p0 = ex2(x0);
+      p1 = ex2(x1);
+    }
+    if (i & 1) sum_b = add2(sum_b, pack2(p0, p1));
+    else sum_a = add2(sum_a, pack2(p0, p1));
+    pk[i] = pack_bf16(p0, p1);
+  }
+}
+
+// STREAMED softmax step for a full 128-key tile that is not the first of its query tile (j > 0): the row maximum is not
+// waited for.  The running reference maximum m_ref of the previous steps is used speculatively -- the online softmax
+// only needs ANY reference within 2^8 of the true maximum (lazy rescale), and it changes on a few percent of the steps --
+// so the exponentials of chunk 0 start as soon as its 32 columns have arrived from tensor memory, while chunks 1..3 are
+// still in flight and the max tree (FMNMX3, ALU pipe) runs beside the FFMA2 / MUFU stream instead of in front of it.
+// S leaves tensor memory in four 32-column chunks and P goes back in four 16-column chunks; these loads / stores are
+// ordered (volatile), which pins the chunk pipeline in the instruction stream: the FMA-pipe work of chunk k+1 is issued
+// between the MUFU instructions of chunk k instead of all FMA work first and one long MUFU burst at the end (what ptxas
+// makes of the one-shot version: ncu source view of r01, 25 % of a softmax warp's time in an FMA-only phase and 38 % in
+// a MUFU-only phase).  s_free is signalled once chunk 3 is in registers and the speculation is confirmed; if the row
+// maximum did grow by more than 2^8 (any lane of the warp), nothing has been published yet and the step is redone by
+// the one-shot path below (S is still in tensor memory, P is simply overwritten).
+template <int VAR>
+__device__ __forceinline__ bool softmax_step_stream(Bars* b, uint32_t s_addr, uint32_t p_addr, uint32_t g, float sl2,
+                                                    float m_ref, float& l, int lane) {
+  constexpr int POLY = VAR & 15;
+  uint32_t c0[32], c1[32], c2[32], c3[32];
+  uint32_t pk[16];
+  mbar_wait(&b->s_full, g & 1);
+  tc_fence_after();
+  tmem_ld32(s_addr, c0);
+  tmem_ld32(s_addr + 32, c1);
+  tmem_ld_wait();
+  tmem_ld32(s_addr + 64, c2);
+  const float mb = -m_ref * sl2;
+  const uint64_t sl2_2 = pack2(sl2, sl2), mb_2 = pack2(mb, mb);
+  uint64_t sum_a = pack2(0.f, 0.f), sum_b = sum_a, sum_c = sum_a, sum_d = sum_a;
+  float tmax = fmaxf(tree_max<32>(*reinterpret_cast<const float(*)[32]>(c0)),
+                     tree_max<32>(*reinterpret_cast<const float(*)[32]>(c1)));
+  exp_chunk32<POLY>(c0, pk, sl2_2, mb_2, sum_a, sum_b, 0);
+  tmem_ld_wait();  // chunk 2 has arrived
+  tmem_ld32(s_addr + 96, c3);
+  mbar_wait(&b->o_done, (g - 1) & 1);  // PV_{g-1} has consumed the previous P (j > 0 on this path)
+  tc_fence_after();
+  tmem_st16(p_addr, pk);
+  tmax = fmaxf(tmax, tree_max<32>(*reinterpret_cast<const float(*)[32]>(c2)));
+  exp_chunk32<POLY>(c1, pk, sl2_2, mb_2, sum_c, sum_d, 1);
+  tmem_ld_wait();  // chunk 3 has arrived: the whole row is in registers
+  tmax = fmaxf(tmax, tree_max<32>(*reinterpret_cast<const float(*)[32]>(c3)));
+  if (__any_sync(0xffffffffu, (tmax - m_ref) * sl2 > 8.0f)) {  // rare: redo with a rescale (one-shot path)
+    tmem_st_wait();  // the P chunk already written is overwritten there: keep the two stores ordered
+    return false;
+  }
+  tc_fence_before();
+  __syncwarp();
+  if (lane == 0) mbar_arrive(&b->s_free);
+  tmem_st16(p_addr + 16, pk);
+  exp_chunk32<POLY>(c2, pk, sl2_2, mb_2, sum_a, sum_b, 2);
+  tmem_st16(p_addr + 32, pk);
+  exp_chunk32<POLY>(c3, pk, sl2_2, mb_2, sum_c, sum_d, 3);
+  tmem_st16(p_addr + 48, pk);
+  {
+    float a0, a1;
+    unpack2(add2(add2(sum_a, sum_b), add2(sum_c, sum_d)), a0, a1);
+    l += a0 + a1;
+  }
+  tmem_st_wait();
+  tc_fence_before();
+  __syncwarp();
+  if (lane == 0) mbar_arrive(&b->p_full);
+  return true;
+}
+
 template <int VAR>
 __global__ void __launch_bounds__(kThreads, 2) attn_kernel(const __grid_constant__ AttnParams p) {
   extern __shared__ __align__(1024) uint8_t smem[];
@@ -446,7 +532,12 @@ __global__ void __launch_bounds__(kThreads, 2) attn_kernel(const __grid_constant
       const int qblk = w % p.n_qblk, hs = w / p.n_qblk;
       const int head = hs % p.heads, seq = hs / p.heads;
       float m_ref = -INFINITY, l = 0.f;
-      for (int j = 0; j < n_kv - 1; ++j, ++g) softmax_step<128, VAR>(b, s_addr, p_addr, o_addr, g, j, 128, sl2, m_ref, l, lane);
+      for (int j = 0; j < n_kv - 1; ++j, ++g) {
+        if constexpr ((VAR & 128) != 0) {
+          if (j > 0 && softmax_step_stream<VAR>(b, s_addr, p_addr, g, sl2, m_ref, l, lane)) continue;
+        }
+        softmax_step<128, VAR>(b, s_addr, p_addr, o_addr, g, j, 128, sl2, m_ref, l, lane);
+      }
       if (tail64) softmax_step<64, 0>(b, s_addr, p_addr, o_addr, g, n_kv - 1, kv_tail, sl2, m_ref, l, lane);
       else softmax_step<128, 0>(b, s_addr, p_addr, o_addr, g, n_kv - 1, kv_tail, sl2, m_ref, l, lane);
       // epilogue: O / l -> bf16 (PV_0 of the next tile cannot start before all four warps passed this point: it needs
@@ -488,7 +579,7 @@ cudaError_t launch_attention(const AttnParams& p_in, cudaStream_t stream) {
   static int n_sm = 0;
   if (!n_sm) {
     cudaError_t e = cudaSuccess;
-#define UFM_ATTN_VARIANTS(X) X(0) X(4)
+#define UFM_ATTN_VARIANTS(X) X(0) X(4) X(128) X(132) X(131) X(130)
 #define X(v) if ((e = cudaFuncSetAttribute(attn_kernel<v>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES)) != cudaSuccess) return e;
     UFM_ATTN_VARIANTS(X)
 #undef X
