@@ -138,8 +138,11 @@ int ufm_profile_read(ufm_engine* e, double* ms, double* flops, double* bytes, in
  * | 4 = in-place residuals through a TMA-loaded residual slab instead of the reduce-add store); which = 1: CTA-pair (cta_group::2) GEMM
  * tiles on/off; which = 2: attention, every n-th exp2 pair on the FMA pipe; which = 3: 1 = halo-resident A operand
  * for the 3x3 convolutions (default), 0 = nine shifted boxes; which = 4: 1 = programmatic dependent launches (default); which = 5: 1 = column slices for
- * the tiles of a GEMM's partly filled last wave (default).  Returns non-zero for an
- * unknown switch. */
+ * the tiles of a GEMM's partly filled last wave (default); which = 6: bit 0 = 512 x 256 pair tiles (two row blocks per
+ * CTA, one accumulator set) for the whole waves of the large row-matrix GEMMs, bit 1 = the next item's first row block
+ * runs ahead while the second accumulator is drained, bit 2 = also for GELU epilogues (default 3); which = 7: warp-role
+ * shift of the GEMM kernel (0 default; 4 = TMA / MMA warps above the epilogue warps).  Returns non-zero for an unknown
+ * switch. */
 int ufm_debug_flag(int which, int value);
 
 /* ---- kernel-level entry points (unit parity tests; device pointers, asynchronous on `stream`) ---- */

@@ -16,7 +16,8 @@ sys.path.insert(0, os.path.join(ROOT, "tests"))
 
 def main():
     ap = argparse.ArgumentParser()
-    ap.add_argument("--variants", default="0:1,1:1", help="comma list of epilogue:pair[:split]  (split: last-wave column slices, default 1)")
+    ap.add_argument("--variants", default="0:1,1:1", help="comma list of epilogue:pair[:split[:rows2[:warp_shift]]]  (split: last-wave column "
+                    "slices, default 1; rows2: 512 x 256 pair tiles, ufm_debug_flag 6, default 3; warp_shift: ufm_debug_flag 7)")
     ap.add_argument("--reps", type=int, default=20)
     ap.add_argument("--only", default="")
     a = ap.parse_args()
@@ -43,6 +44,8 @@ def main():
             ("proc.c1@240x320", 4, 240, 320, 256, 128, "convbf16"), ("proc.c2@420x560", 4, 420, 560, 128, 128, "convbf16")]
     variants = [tuple(int(x) for x in v.split(":")) for v in a.variants.split(",")]
     variants = [v if len(v) > 2 else v + (1,) for v in variants]
+    variants = [v if len(v) > 3 else v + (3,) for v in variants]
+    variants = [v if len(v) > 4 else v + (0,) for v in variants]
     gen = torch.Generator(device=dev).manual_seed(0)
 
     def timeit(fn):
@@ -57,7 +60,7 @@ def main():
         torch.cuda.synchronize()
         return e0.elapsed_time(e1) / a.reps
 
-    print(f"{'shape':18s} {'M':>7s} {'K':>5s} {'N':>5s} " + "   ".join(f"e{v[0]}p{v[1]}s{v[2]}: ms TFLOP/s" for v in variants))
+    print(f"{'shape':18s} {'M':>7s} {'K':>5s} {'N':>5s} " + "   ".join(f"e{v[0]}p{v[1]}s{v[2]}r{v[3]}w{v[4]}: ms TFLOP/s" for v in variants))
     for name, M, K, N, kind in lin:
         if a.only and a.only not in name:
             continue
@@ -71,6 +74,8 @@ def main():
             lib.ufm_debug_flag(0, v[0])
             lib.ufm_debug_flag(1, v[1])
             lib.ufm_debug_flag(5, v[2])
+            lib.ufm_debug_flag(6, v[3])
+            lib.ufm_debug_flag(7, v[4])
             if kind == "res":
                 fn = lambda: ops.linear(A, Wt, bias=bias, res1=x, out_f32=x)
             elif kind == "gelu":
@@ -95,6 +100,7 @@ def main():
         for v in variants:
             lib.ufm_debug_flag(0, v[0])
             lib.ufm_debug_flag(1, v[1])
+            lib.ufm_debug_flag(7, v[4])
             if kind == "convres2":  # fusion block: path + skip + conv, fp32 sum + ReLU'd bf16 copy
                 fn = lambda: ops.conv3x3(X, Wp, bias=bias, res1=r, res2=r2, r2=(H * W * Co, W * Co, Co), out_f32=of,
                                          out_bf16=ob, flags=_lib.GEMM_RELU_BF16)
@@ -110,6 +116,8 @@ def main():
     lib.ufm_debug_flag(0, 1)
     lib.ufm_debug_flag(1, 1)
     lib.ufm_debug_flag(5, 1)
+    lib.ufm_debug_flag(6, 3)
+    lib.ufm_debug_flag(7, 0)
 
 
 if __name__ == "__main__":

@@ -70,6 +70,45 @@ def test_gemm_gelu_scale_residual_inplace():
     assert rel(x, ref) < 1e-5
 
 
+# 512 x 256 pair tiles (gemm.cu R2; engine.cu rows2_rows): on a 148-SM part the whole waves of a row-matrix GEMM with N % 256
+# == 0 run with two 128-row blocks per CTA and one accumulator set, the remaining rows on the double-buffered kernel.
+# (M, K, N): the UFM-Base encoder shapes (74 x 512 rows + 544), an exact multiple (37 x 512 rows x 2 column tiles: one
+# wave), and a case too small for any 512-row wave (falls back entirely).
+@pytest.mark.parametrize("M,K,N", [(32 * 1201, 256, 1024), (32 * 1201, 128, 3072), (37 * 512, 192, 512), (37 * 512 + 77, 64, 512),
+                                   (3000, 128, 512)])
+@pytest.mark.parametrize("mode,shift", [(3, 0), (1, 0), (3, 4)])
+def test_gemm_rows2_pair_tiles(M, K, N, mode, shift):
+    """bf16 output with bias and the in-place fp32 residual (TMA reduce-add) through the 512-row tiles: against fp32 torch
+    and bit-identical to the 256-row path (same MMA instruction shapes and K order, so the accumulators are the same)."""
+    import gpu_ops as ops
+
+    lib = _lib.load()
+    a = _rand(M, K, seed=1).bfloat16()
+    w = _rand(N, K, scale=K ** -0.5, seed=2).bfloat16()
+    bias = _rand(N, seed=3)
+    gamma = _rand(N, seed=4)
+    x0 = _rand(M, N, seed=5)
+    outs = {}
+    try:
+        for m in (0, mode):
+            lib.ufm_debug_flag(6, m)
+            lib.ufm_debug_flag(7, shift if m else 0)
+            ob = torch.zeros(M, N, dtype=torch.bfloat16, device="cuda")
+            ops.linear(a, w, bias=bias, out_bf16=ob)
+            x = x0.clone()
+            ops.linear(a, w, bias=bias, scale=gamma, res1=x, out_f32=x)
+            torch.cuda.synchronize()
+            outs[m] = (ob, x)
+    finally:
+        lib.ufm_debug_flag(6, 3)
+        lib.ufm_debug_flag(7, 0)
+    ref = a.float() @ w.float().t() + bias
+    assert rel(outs[mode][0].float(), ref) < 4e-3
+    assert rel(outs[mode][1], x0 + gamma * ref) < 1e-5
+    assert torch.equal(outs[mode][0], outs[0][0])
+    assert torch.equal(outs[mode][1], outs[0][1])
+
+
 # Last-wave column slices (gemm.cu tile_ref / engine.cu build_gemm) on a 148-SM part: pair tiles 256 x 256 on 74 units,
 # single-CTA tiles 128 x 128 on 148.  (M, K, N): 86 row tiles x 1 -> R = 12 -> quarter slices; 104 -> R = 30 -> halves;
 # 151 x 4 = 604 -> R = 12 (the UFM-Base encoder proj shape, ragged last row tile); N = 384: BN = 128, 60 x 3 = 180 ->

@@ -298,9 +298,17 @@ def test_uncertainty_adaptors(conf_type):
     # element-wise error relative to |ref| + a floor (the off-diagonal terms cross zero)
     rel = lambda a, b: ((a - b).abs() / (b.abs() + 1e-2 * b.abs().mean())).max().item()
     assert rel(res.flow.flow_covariance[-n:].cpu(), cov) < 1e-4
-    # 1 / (1 - tanh^2 + 1e-8) is ill-conditioned near |tanh| = 1: an ulp of tanhf is amplified by 2 tanh / (1 - tanh^2)
-    assert rel(res.flow.flow_covariance_inv[-n:].cpu(), inv) < 2e-2
-    assert max_abs(res.flow.flow_covariance_log_det[-n:].cpu(), log_det) < 2e-2  # log of the same 1 - tanh^2 term
+    # 1 / (1 - tanh^2 + 1e-8) is ill-conditioned near |tanh| = 1: an error of a few ulp of tanhf (device tanhf vs the
+    # host's) is amplified by 2 |tanh| / (1 - tanh^2).  The bound is therefore per element: well-conditioned pixels must
+    # agree to 2e-3, the others to 8 ulp of tanh times their own amplification.
+    t = raw[:, 2:3].double().tanh()
+    amp = (2 * t.abs() / (1 - t * t + 1e-8)).float()
+    bound = 2e-3 + 8 * 6e-8 * amp
+    got_inv = res.flow.flow_covariance_inv[-n:].cpu()
+    err_inv = (got_inv - inv).abs() / (inv.abs() + 1e-2 * inv.abs().mean())
+    assert (err_inv <= bound).all(), (err_inv / bound).max().item()
+    err_ld = (res.flow.flow_covariance_log_det[-n:].cpu() - log_det).abs()
+    assert (err_ld <= bound).all(), (err_ld / bound).max().item()  # log of the same 1 - tanh^2 term
     assert rel(res.keypoint_confidence[-n:].cpu(), au["keypoint_confidence"].squeeze(1)) < 2e-4
     assert max_abs(res.covisibility.mask[-n:].cpu(), au["non_occluded_mask"]["mask"]) < 1e-6
     # end to end against the fp32 oracle, native and non-native size (covariance is nearest-resampled and rescaled)

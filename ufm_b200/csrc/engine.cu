@@ -81,8 +81,9 @@ struct Epi {
 };
 
 bool build_gemm(GemmParams* gp, int* BN, const AView& a_in, const void* wt, int n_out, int taps, int cin_pad, const Epi& e,
-                char* err, int errlen, int num_sms = 0) {
+                char* err, int errlen, int num_sms = 0, int rows2 = 0) {
   memset(gp, 0, sizeof(*gp));
+  gp->warp_shift = gemm_warp_shift();
   AView a = a_in;
   const bool halo = taps == 9 && (gemm_halo_mode() & 1);
   if (halo) {  // gemm.cu HALO: 8 x 16-pixel tiles, one (8+2) x (16+2) halo box per channel chunk
@@ -128,7 +129,7 @@ bool build_gemm(GemmParams* gp, int* BN, const AView& a_in, const void* wt, int 
   // ---- last-wave column slices (gemm.cu tile_ref): the static schedule runs ceil(T / U) waves of T tiles on U units; when
   // the last wave holds R <= U/4 (U/2) tiles, each is cut into 4 (2) column slices of >= 64 columns so that the wave
   // costs a fraction of a tile time (UFM-Base encoder proj / fc2: 604 tiles on 74 pairs, R = 12 -> 48 quarter tiles) ----
-  if (!halo && !tail && taps == 1 && num_sms > 0 && gemm_split_mode()) {
+  if (!halo && !tail && taps == 1 && num_sms > 0 && gemm_split_mode() && !rows2) {
     const int tiles_m1 = a.N * gp->tiles_y * gp->tiles_x;
     const int T = ((tiles_m1 + gp->ctas - 1) / gp->ctas) * gp->tiles_n;
     const int U = num_sms / gp->ctas;
@@ -207,6 +208,15 @@ bool build_gemm(GemmParams* gp, int* BN, const AView& a_in, const void* wt, int 
       gp->epi_mode = EPI_TMA_MIX;
     }
   }
+  if (rows2) {
+    // 512 x 256 pair tiles (gemm.cu R2): whole items only, TMA epilogue without a residual slab load
+    const bool epi_ok = gp->epi_mode == EPI_TMA_BF16 || (gp->epi_mode == EPI_TMA_F32 && (!e.res1 || red_inplace));
+    if (halo || tail || taps != 1 || *BN != 256 || gp->ctas != 2 || !epi_ok || (a.N * gp->tiles_y * gp->tiles_x) % 4) {
+      snprintf(err, errlen, "rows2 tiles need a plain CTA-pair BN=256 GEMM over whole 512-row items with a TMA epilogue");
+      return false;
+    }
+    gp->rows2 = rows2;
+  }
   gp->flags = e.flags | (red_inplace ? GEMM_RED_INPLACE : 0u);
   gp->bias = e.bias; gp->scale = e.scale; gp->res1 = e.res1; gp->res2 = e.res2;
   gp->out_f32 = e.out_f32; gp->out_bf16 = e.out_bf16;
@@ -219,6 +229,25 @@ bool build_gemm(GemmParams* gp, int* BN, const AView& a_in, const void* wt, int 
     gp->tail_shift[i] = e.tshift[i];
   }
   return true;
+}
+
+// Rows of a plain row-matrix GEMM that run as 512 x 256 pair tiles (gemm.cu R2): the largest count of whole 512-row items
+// whose (items x column tiles) fill the pair units an integral number of times; the remaining rows go to the
+// double-buffered 256 x 256 kernel in a second launch.  0 = not eligible.
+long long rows2_rows(const AView& a, int n_out, int taps, const Epi& e, int num_sms) {
+  if (!(gemm_rows2_mode() & 1) || !(gemm_pair_mode() & 1) || !gemm_epilogue_variant()) return 0;
+  if (taps != 1 || a.Y != 1 || a.N != 1 || a.tw != 128 || a.th != 1 || n_out % 256 || a.C % 64) return 0;
+  if ((e.flags & GEMM_TAIL) || e.res2 || (e.out_f32 != nullptr) == (e.out_bf16 != nullptr)) return 0;
+  if (e.out_bf16 && e.res1) return 0;
+  if (e.out_f32 && e.res1 && (e.res1 != e.out_f32 || (gemm_epilogue_variant() & 4))) return 0;  // reduce-add in place only
+  // heavy per-element epilogues (GELU) need the overlap of the double-buffered kernel
+  if ((e.flags & GEMM_GELU) && !(gemm_rows2_mode() & 4)) return 0;
+  const int units = num_sms / 2, tiles_n = n_out / 256;
+  const long long items_m = a.X / 512;
+  int g = units, t = tiles_n;  // step = units / gcd(units, tiles_n)
+  while (t) { const int r = g % t; g = t; t = r; }
+  const long long step = units / g;
+  return items_m / step * step * 512;
 }
 
 bool build_attn(AttnParams* ap, const void* qkv, int n_seq, int seq_len, int heads, float scale, void* out, char* err,
@@ -395,16 +424,37 @@ struct ufm_engine {
     if (!wt) return false;
     const int n_out = (int)wt->shape[0];
     const int ktot = (int)wt->shape[1];
-    GemmParams gp;
-    int BN;
     char eb[512];
-    if (!build_gemm(&gp, &BN, a, wt->ptr, n_out, taps, ktot / taps, e, eb, sizeof(eb), num_sms)) {
-      fail("gemm %s: %s", wname.c_str(), eb);
-      return false;
-    }
     double fl = 2.0 * a.N * a.X * a.Y * (double)n_out * taps * a.C;
     if (flops_override >= 0) fl = flops_override;
     flops_override = -1.0;
+    AView ar = a;
+    Epi er = e;
+    const long long r2 = rows2_rows(a, n_out, taps, e, num_sms);
+    if (r2 > 0) {
+      AView a2 = a;
+      a2.X = (int)r2;
+      GemmParams g2;
+      int BN2;
+      if (!build_gemm(&g2, &BN2, a2, wt->ptr, n_out, taps, ktot / taps, e, eb, sizeof(eb), num_sms, gemm_rows2_mode())) {
+        fail("gemm %s (rows2): %s", wname.c_str(), eb);
+        return false;
+      }
+      if (!run(UFM_CAT_GEMM, fl * (double)r2 / a.X, 0.0, ("launch gemm " + wname + " [512-row tiles]").c_str(),
+               [&] { return launch_gemm(g2, BN2, num_sms, st); }))
+        return false;
+      if (r2 == a.X) return true;
+      fl *= (double)(a.X - r2) / a.X;
+      ar.p = reinterpret_cast<const bf16*>(a.p) + r2 * a.sx;
+      ar.X = (int)(a.X - r2);
+      er.out_off = e.out_off + r2 * e.sx;
+    }
+    GemmParams gp;
+    int BN;
+    if (!build_gemm(&gp, &BN, ar, wt->ptr, n_out, taps, ktot / taps, er, eb, sizeof(eb), num_sms)) {
+      fail("gemm %s: %s", wname.c_str(), eb);
+      return false;
+    }
     return run(taps == 9 ? UFM_CAT_CONV : UFM_CAT_GEMM, fl, 0.0, ("launch gemm " + wname).c_str(),
                [&] { return launch_gemm(gp, BN, num_sms, st); });
   }
@@ -1454,6 +1504,14 @@ int ufm_debug_flag(int which, int value) {
     set_gemm_split_mode(value);
     return 0;
   }
+  if (which == 6) {
+    set_gemm_rows2_mode(value);
+    return 0;
+  }
+  if (which == 7) {
+    set_gemm_warp_shift(value);
+    return 0;
+  }
   return 1;
 }
 
@@ -1490,6 +1548,21 @@ int ufm_op_gemm(const void* a, int C, int X, int Y, int Nimg, int64_t a_sx, int6
   }
   GemmParams gp;
   int BN;
+  const long long r2 = rows2_rows(av, n_out, taps, e, g_num_sms());
+  if (r2 > 0) {  // same split as ufm_engine::gemm: 512-row pair tiles for the whole waves, the rest below
+    AView a2 = av;
+    a2.X = (int)r2;
+    if (!build_gemm(&gp, &BN, a2, wt, n_out, taps, cin_pad, e, err, errlen, g_num_sms(), gemm_rows2_mode())) return 1;
+    cudaError_t c2 = launch_gemm(gp, BN, g_num_sms(), reinterpret_cast<cudaStream_t>(stream));
+    if (c2 != cudaSuccess) {
+      snprintf(err, errlen, "launch_gemm (rows2): %s", cudaGetErrorString(c2));
+      return 1;
+    }
+    if (r2 == X) return 0;
+    av.p = reinterpret_cast<const bf16*>(a) + r2 * a_sx;
+    av.X = (int)(X - r2);
+    e.out_off = out_off + r2 * sx;
+  }
   if (!build_gemm(&gp, &BN, av, wt, n_out, taps, cin_pad, e, err, errlen, g_num_sms())) return 1;
   cudaError_t ce = launch_gemm(gp, BN, g_num_sms(), reinterpret_cast<cudaStream_t>(stream));
   if (ce != cudaSuccess) {

@@ -43,18 +43,28 @@ constexpr int HALO_TW = 8, HALO_TH = 16;
 constexpr int HALO_ROW_BYTES = (HALO_TW + 2) * 128;
 constexpr int HALO_TX_BYTES = (HALO_TH + 2) * HALO_ROW_BYTES;  // 23040
 
-template <int BN, int CTAS, bool HALO>
+// R2 (CTAS = 2, BN = 256, plain GEMM): every CTA owns TWO 128-row blocks, i.e. a pair computes a 512 x 256 tile with ONE
+// accumulator set (row block r -> TMEM columns r * 256).  One B half-tile (128 x 64) per stage feeds both row blocks, so a
+// pair moves 96 KB of operands per 512 x 256 x 64 MACs instead of 2 x 64 KB: -25 % L2 -> SM bytes per FLOP, which is what
+// bounds the 256 x 256 pair tile (it is also the tile cuBLAS picks for these shapes: nvjet 256x256 / 256x224
+// per CTA, 2-CTA, profiles/r02_gemm_probe_ncu.csv).  The price is that the epilogue of an item no longer overlaps the
+// next item's main loop through a second accumulator stage; what is recovered (rows2 bit 1): the next item's MMAs of row
+// block 0 start as soon as accumulator 0 is drained and run ahead by the depth of the smem ring while accumulator 1 is
+// still being drained.
+template <int BN, int CTAS, bool HALO, bool R2 = false>
 struct Cfg {
-  static constexpr int A_BYTES = HALO ? 24576 : BM * BK * 2;    // halo tile padded to the 1024-byte swizzle period
-  static constexpr int A_TX = HALO ? HALO_TX_BYTES : BM * BK * 2;
+  static constexpr int A_BYTES = HALO ? 24576 : (R2 ? 2 : 1) * BM * BK * 2;    // halo tile padded to the 1024-byte swizzle period
+  static constexpr int A_TX = HALO ? HALO_TX_BYTES : (R2 ? 2 : 1) * BM * BK * 2;
   static constexpr int B_ROWS = BN / CTAS;
   static constexpr int B_BYTES = B_ROWS * BK * 2;
   static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
-  static constexpr int STAGES = HALO ? (B_BYTES == 32768 ? 2 : B_BYTES == 8192 ? 9 : 5) : (STAGE_BYTES == 49152) ? 3 : 5;  // B (and A) ring
+  static constexpr int STAGES = HALO ? (B_BYTES == 32768 ? 2 : B_BYTES == 8192 ? 9 : 5) : R2 ? 4 : (STAGE_BYTES == 49152) ? 3 : 5;  // B (and A) ring
   static constexpr int A_STAGES = HALO ? 3 : STAGES;  // a halo lasts 36 MMAs: three in flight cover the TMA latency
   static constexpr int BAR_BYTES = 512;
-  // epilogue slabs: 8 warps x 2 x (32 rows x 128 B); TAIL mode reuses them as [acc][half][row][kTailMax] floats
-  static constexpr int SCRATCH_BYTES = kEpiWarps * 2 * 4096;
+  // epilogue slabs: 8 warps x 2 x (32 rows x 128 B) (R2: one slab per warp, the smem goes to the operand ring); TAIL mode
+  // reuses them as [acc][half][row][kTailMax] floats
+  static constexpr int SLABS = R2 ? 1 : 2;
+  static constexpr int SCRATCH_BYTES = kEpiWarps * SLABS * 4096;
   static constexpr int SMEM_BYTES = 1024 + A_STAGES * A_BYTES + STAGES * B_BYTES + BAR_BYTES + SCRATCH_BYTES;
   static constexpr int TMEM_COLS = 2 * BN;
 };
@@ -95,9 +105,11 @@ __device__ __forceinline__ TileRef tile_ref(const GemmParams& p, int item, int s
   return TileRef{tile / p.tiles_n, tn * BN + sub * ncols, ncols};
 }
 
-template <int BN, int CTAS, bool HALO>
+template <int BN, int CTAS, bool HALO, bool R2 = false>
 __global__ void __launch_bounds__(kThreads, 1) gemm_kernel(const __grid_constant__ GemmParams p) {
-  using C = Cfg<BN, CTAS, HALO>;
+  static_assert(!R2 || (CTAS == 2 && BN == 256 && !HALO), "R2 tiles are CTA-pair, BN = 256, plain GEMM");
+  using C = Cfg<BN, CTAS, HALO, R2>;
+  constexpr int RB = R2 ? 2 : 1;  // 128-row blocks per CTA and work item
   const uint32_t cta_rank = (CTAS == 2) ? cluster_ctarank() : 0u;
   const int unit = blockIdx.x / CTAS;          // scheduling unit: a CTA (CTAS 1) or a CTA pair (CTAS 2)
   const int num_units = gridDim.x / CTAS;
@@ -116,7 +128,9 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_kernel(const __grid_constant
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(aempty + 3);
   float* scratch = reinterpret_cast<float*>(epi_smem);  // TAIL mode: [acc][half][row][4] floats
 
-  const int warp = threadIdx.x >> 5;
+  // logical warp (role) index: physical warp + warp_shift mod 12; a shift of 4 keeps the TMEM lane quadrant (warp & 3)
+  int warp = (threadIdx.x >> 5) + p.warp_shift;
+  warp = warp >= kThreads / 32 ? warp - kThreads / 32 : warp;
   const int lane = threadIdx.x & 31;
 
   if (warp == 0 && lane == 0) {
@@ -157,9 +171,9 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_kernel(const __grid_constant
   // a scheduling unit owns CTAS consecutive 128-row tiles (one per CTA) x one BN-wide column tile; a CTA whose row tile
   // lies past the end loads zero-filled boxes (image index out of range) and stores nothing
   const int tiles_m1 = p.Nimg * p.tiles_y * p.tiles_x;
-  const int tiles_m = (tiles_m1 + CTAS - 1) / CTAS;
+  const int tiles_m = (tiles_m1 + CTAS * RB - 1) / (CTAS * RB);  // R2: an item = two consecutive pair tiles of the same columns
   const int total_tiles = tiles_m * p.tiles_n;
-  const int split_from = p.split_log2 ? p.split_from : total_tiles;
+  const int split_from = (p.split_log2 && !R2) ? p.split_from : total_tiles;
   const int total_items = split_from + ((total_tiles - split_from) << p.split_log2);
   const int k_iters = p.taps * p.cchunks;
 
@@ -211,6 +225,30 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_kernel(const __grid_constant
           }
           continue;
         }
+        if constexpr (R2) {
+          // row block r of this CTA = 128-row tile (2 * mt + r) * 2 + rank; both blocks and the B half-tile of the pair land
+          // on the leader's barrier
+          int bx[2], by[2], bi[2];
+          for (int r = 0; r < 2; ++r) {
+            const int t2 = (tr.mt * 2 + r) * CTAS + (int)cta_rank;
+            bx[r] = (t2 % p.tiles_x) * p.tw;
+            by[r] = ((t2 / p.tiles_x) % p.tiles_y) * p.th;
+            bi[r] = t2 / (p.tiles_x * p.tiles_y);
+          }
+          for (int k = 0; k < k_iters; ++k) {
+            mbar_wait(&empty[stage], phase ^ 1);
+            if (cta_rank == 0) mbar_expect_tx(&full[stage], 2 * (C::A_TX + C::B_BYTES));
+            const uint32_t lbar = smem_u32(&full[stage]) & kPeerBitMask;
+            tma2_load_4d(sA + stage * C::A_BYTES, &p.tmA, lbar, k * BK, bx[0], by[0], bi[0]);
+            tma2_load_4d(sA + stage * C::A_BYTES + BM * BK * 2, &p.tmA, lbar, k * BK, bx[1], by[1], bi[1]);
+            tma2_load_2d(sB + stage * C::B_BYTES, &p.tmB, lbar, k * BK, n0);
+            if (++stage == C::STAGES) {
+              stage = 0;
+              phase ^= 1;
+            }
+          }
+          continue;
+        }
         for (int k = 0; k < k_iters; ++k) {
           const int tap = k / p.cchunks;
           const int cc = k - tap * p.cchunks;
@@ -256,6 +294,58 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_kernel(const __grid_constant
       int acc = 0, astage = 0;
       uint32_t accphase = 0, aphase = 0;
       for (int item = unit; item < total_items; item += num_units) {
+        if constexpr (R2) {
+          // both accumulators belong to this item: row block r -> TMEM columns [r * BN, (r + 1) * BN).  With run-ahead the
+          // first `ahead` k-steps of row block 0 are issued as soon as accumulator 0 is drained, without releasing their
+          // smem stages; row block 1 catches up (and releases them) once accumulator 1 is drained as well.
+          auto mma_block = [&](int st_, int r, uint32_t accum0) {
+            const uint32_t a_lo = a_lo0 + st_ * (C::A_BYTES >> 4) + r * ((BM * BK * 2) >> 4);
+            const uint32_t b_lo = b_lo0 + st_ * (C::B_BYTES >> 4);
+#pragma unroll
+            for (int kk = 0; kk < BK / 16; ++kk)
+              umma2_ss(tmem_base + r * BN, umma_desc_words(a_lo + kk * 2, hi_a), umma_desc_words(b_lo + kk * 2, hi_b), idesc_full,
+                       (accum0 | (uint32_t)kk) != 0 ? 1u : 0u);
+          };
+          const int ahead = (p.rows2 & 2) ? (k_iters < C::STAGES ? k_iters : C::STAGES) : 0;
+          mbar_wait(&tempty[0], accphase ^ 1);
+          tc_fence_after();
+          {
+            int s2 = stage;
+            uint32_t ph2 = phase;
+            for (int k = 0; k < ahead; ++k) {
+              mbar_wait(&full[s2], ph2);
+              tc_fence_after();
+              if (leader) mma_block(s2, 0, (uint32_t)k);
+              if (++s2 == C::STAGES) {
+                s2 = 0;
+                ph2 ^= 1;
+              }
+            }
+          }
+          mbar_wait(&tempty[1], accphase ^ 1);
+          tc_fence_after();
+          for (int k = 0; k < k_iters; ++k) {
+            if (k >= ahead) {
+              mbar_wait(&full[stage], phase);
+              tc_fence_after();
+            }
+            if (leader) {
+              if (k >= ahead) mma_block(stage, 0, (uint32_t)k);
+              mma_block(stage, 1, (uint32_t)k);
+              umma2_commit_mc(&empty[stage]);
+              if (k == k_iters - 1) {
+                umma2_commit_mc(&tfull[0]);
+                umma2_commit_mc(&tfull[1]);
+              }
+            }
+            if (++stage == C::STAGES) {
+              stage = 0;
+              phase ^= 1;
+            }
+          }
+          accphase ^= 1;
+          continue;
+        }
         const uint32_t idesc = (HALO || item < split_from) ? idesc_full : idesc_slice;  // a slice fills the first columns
         mbar_wait(&tempty[acc], accphase ^ 1);
         tc_fence_after();
@@ -349,7 +439,7 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_kernel(const __grid_constant
     // TMA epilogues: two 4 KB slabs per warp = 32 rows x 128 bytes in the 128B-swizzle pattern (16-byte chunk j of row r
     // lives at chunk j ^ (r & 7)), so a thread touches only its own row, conflict free, and the slab is the smem image of
     // a (32 fp32 | 64 bf16) x 32-row TMA box.
-    uint8_t* wbuf = epi_smem + e * 8192;
+    uint8_t* wbuf = epi_smem + e * (C::SLABS * 4096);
     uint64_t* rbar = resbar + e * 2;
     uint32_t rph0 = 0, rph1 = 0;
     const uint32_t sw = lane & 7;
@@ -358,11 +448,14 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_kernel(const __grid_constant
       tempty_remote[0] = mapa_cluster(smem_u32(&tempty[0]), 0);
       tempty_remote[1] = mapa_cluster(smem_u32(&tempty[1]), 0);
     }
-    int acc = 0;
-    uint32_t accphase = 0;
-    for (int item = unit; item < total_items; item += num_units) {
+    int iter = 0;
+    for (int item = unit; item < total_items; item += num_units, ++iter)
+    for (int rb = 0; rb < RB; ++rb) {
+      // accumulator slot and its barrier phase: alternating stages per item, or (R2) one stage per row block of the item
+      const int acc = R2 ? rb : (iter & 1);
+      const uint32_t accphase = R2 ? (uint32_t)(iter & 1) : (uint32_t)((iter >> 1) & 1);
       const TileRef tr = tile_ref(p, item, split_from, BN);
-      const int tm = tr.mt * CTAS + (int)cta_rank;
+      const int tm = (tr.mt * RB + rb) * CTAS + (int)cta_rank;
       const int tx = tm % p.tiles_x;
       const int ty = (tm / p.tiles_x) % p.tiles_y;
       const int img = tm / (p.tiles_x * p.tiles_y);
@@ -414,7 +507,7 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_kernel(const __grid_constant
         tc_fence_after();
 #pragma unroll 1
         for (int c = 0; c < nch; ++c) {
-          uint8_t* buf = wbuf + (c & 1) * 4096;
+          uint8_t* buf = wbuf + (R2 ? 0 : (c & 1)) * 4096;
           uint8_t* rowp = buf + lane * 128;
           // EPI_TMA_MIX: second-pass addressing (8 lanes per slab row, 4 rows per warp instruction); the res2 loads are
           // issued here so that their latency runs under the residual wait, the TMEM read and the first pass
@@ -444,12 +537,16 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_kernel(const __grid_constant
               mbar_wait(&rbar[0], rph0);
               rph0 ^= 1;
             }
-          } else if (c >= 2) {
+          } else if (!R2 && c >= 2) {
             if (lane == 0) bulk_wait_read<1>();
             __syncwarp();
           }
           uint32_t vr[32];
           tmem_ld32(acc_addr + c * 32, vr);
+          if (R2 && c >= 1) {  // single slab: the previous chunk's store must have read it (waits under the TMEM load)
+            if (lane == 0) bulk_wait_read<0>();
+            __syncwarp();
+          }
           tmem_ld_wait();
           const int gcol = c0 + c * 32;
 #pragma unroll
@@ -531,13 +628,17 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_kernel(const __grid_constant
         tc_fence_after();
 #pragma unroll 1
         for (int c = 0; c < nch; ++c) {
-          uint8_t* buf = wbuf + (c & 1) * 4096;
+          uint8_t* buf = wbuf + (R2 ? 0 : (c & 1)) * 4096;
           uint8_t* rowp = buf + lane * 128;
           const int gcol = c0 + c * 64;
 #pragma unroll
           for (int h2 = 0; h2 < 2; ++h2) {
             uint32_t vr[32];
             tmem_ld32(acc_addr + c * 64 + h2 * 32, vr);
+            if (R2 && c >= 1 && h2 == 0) {  // single slab: the previous chunk's store must have read it
+              if (lane == 0) bulk_wait_read<0>();
+              __syncwarp();
+            }
             tmem_ld_wait();
             if (gcol + h2 * 32 < Nl) {
 #pragma unroll
@@ -735,8 +836,6 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_kernel(const __grid_constant
           }
         }
       }
-      acc ^= 1;
-      if (acc == 0) accphase ^= 1;
     }
     if (emode != EPI_DIRECT && lane == 0) bulk_wait<0>();
   }
@@ -757,16 +856,16 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_kernel(const __grid_constant
 int g_gemm_epi = 1;
 int g_gemm_pair = 1;  // ufm_debug_flag 1 (bit 1 measured neutral on the N = 128 convs: 808 vs 795 TFLOP/s): bit 0 = CTA-pair (cta_group::2) tiles for BN = 256, bit 1 = also for BN = 128
 
-template <int BN, int CTAS, bool HALO>
+template <int BN, int CTAS, bool HALO, bool R2 = false>
 static cudaError_t launch_one(const GemmParams& p, int grid, cudaStream_t stream) {
-  using C = Cfg<BN, CTAS, HALO>;
+  using C = Cfg<BN, CTAS, HALO, R2>;
   static bool attr = false;
   if (!attr) {
-    cudaError_t err = cudaFuncSetAttribute(gemm_kernel<BN, CTAS, HALO>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM_BYTES);
+    cudaError_t err = cudaFuncSetAttribute(gemm_kernel<BN, CTAS, HALO, R2>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM_BYTES);
     if (err != cudaSuccess) return err;
     attr = true;
   }
-  return launch_kc(gemm_kernel<BN, CTAS, HALO>, CTAS, dim3(grid), dim3(kThreads), C::SMEM_BYTES, stream, p);
+  return launch_kc(gemm_kernel<BN, CTAS, HALO, R2>, CTAS, dim3(grid), dim3(kThreads), C::SMEM_BYTES, stream, p);
 }
 
 }  // namespace
@@ -783,10 +882,26 @@ int gemm_pair_mode() { return g_gemm_pair; }
 int g_gemm_split = 1;  // ufm_debug_flag 5
 void set_gemm_split_mode(int v) { g_gemm_split = v; }
 int gemm_split_mode() { return g_gemm_split; }
+int g_gemm_rows2 = 3;  // ufm_debug_flag 6
+void set_gemm_rows2_mode(int v) { g_gemm_rows2 = v; }
+int gemm_rows2_mode() { return g_gemm_rows2; }
+int g_gemm_warp_shift = 0;  // ufm_debug_flag 7
+void set_gemm_warp_shift(int v) { g_gemm_warp_shift = v; }
+int gemm_warp_shift() { return g_gemm_warp_shift; }
 
 cudaError_t launch_gemm(const GemmParams& p, int BN, int num_sms, cudaStream_t stream) {
   const int ctas = p.ctas == 2 ? 2 : 1;
   const int tiles_m1 = p.Nimg * p.tiles_y * p.tiles_x;
+  if (p.rows2) {
+    // whole 512-row items only (engine.cu gemm() peels the remaining rows off into a second launch)
+    if (ctas != 2 || BN != 256 || p.halo || p.taps != 1 || tiles_m1 % 4 || p.split_log2 || (p.flags & GEMM_TAIL) ||
+        (p.epi_mode != EPI_TMA_BF16 && !(p.epi_mode == EPI_TMA_F32 && (!p.res1 || (p.flags & GEMM_RED_INPLACE)))))
+      return cudaErrorInvalidValue;
+    const int items = tiles_m1 / 4 * p.tiles_n;
+    if (items <= 0) return cudaSuccess;
+    const int g2 = items * 2 < num_sms ? items * 2 : num_sms / 2 * 2;
+    return launch_one<256, 2, false, true>(p, g2, stream);
+  }
   const int total = ((tiles_m1 + ctas - 1) / ctas) * p.tiles_n;
   if (total <= 0) return cudaSuccess;
   int grid = total * ctas < num_sms ? total * ctas : num_sms / ctas * ctas;

@@ -66,6 +66,10 @@ struct alignas(64) GemmParams {
   int tw_log2;
   int ctas;              // 1, or 2 = CTA-pair tiles (tmB box is then BN/2 rows)
   int halo;              // 1 = 3x3 conv with the halo-resident A operand: tw x th = 8 x 16, tmA box (64, 10, 18, 1)
+  int rows2;             // 1 = every CTA of a pair owns TWO 128-row blocks (pair tile 512 x 256, one accumulator set):
+                         //     the B half-tile in smem feeds both row blocks, -25 % L2 -> SM operand bytes per FLOP.
+                         //     Plain GEMMs only (taps 1, ctas 2, BN 256, whole 512-row items, TMA epilogue without residual load)
+  int warp_shift;        // role of physical warp w = (w + warp_shift) % 12 (tuning: 4 puts TMA / MMA warps above the epilogue warps)
   int X, Y, Nimg;        // logical output extents per image
   int tiles_x, tiles_y;  // ceil(X/tw), ceil(Y/th)
   int N;                 // output channels (multiple of 32, or anything in TAIL mode with N <= 128)
@@ -103,6 +107,10 @@ void set_gemm_halo_mode(int v);         // tuning hook: bit 0 = halo-resident A 
 int gemm_halo_mode();
 void set_gemm_split_mode(int v);        // tuning hook: 1 = column-slice the tiles of a partly filled last wave (default on)
 int gemm_split_mode();
+void set_gemm_rows2_mode(int v);        // tuning hook (ufm_debug_flag 6): bit 0 = 512 x 256 pair tiles for the large row-matrix GEMMs,
+int gemm_rows2_mode();                  //   bit 1 = the next item's first row block starts before the second accumulator is drained
+void set_gemm_warp_shift(int v);        // tuning hook (ufm_debug_flag 7): see GemmParams::warp_shift
+int gemm_warp_shift();
 
 // ------------------------------------------------------------------------------------------------
 // Flash-style attention forward, head_dim 64, non-causal: O = softmax(Q K^T * scale) V per (sequence, head).
