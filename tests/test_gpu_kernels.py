@@ -76,7 +76,7 @@ def test_gemm_gelu_scale_residual_inplace():
 # wave), and a case too small for any 512-row wave (falls back entirely).
 @pytest.mark.parametrize("M,K,N", [(32 * 1201, 256, 1024), (32 * 1201, 128, 3072), (37 * 512, 192, 512), (37 * 512 + 77, 64, 512),
                                    (3000, 128, 512)])
-@pytest.mark.parametrize("mode,shift", [(3, 0), (1, 0), (3, 4)])
+@pytest.mark.parametrize("mode,shift", [(3, 0), (1, 0), (3, 4), (7, 0)])
 def test_gemm_rows2_pair_tiles(M, K, N, mode, shift):
     """bf16 output with bias and the in-place fp32 residual (TMA reduce-add) through the 512-row tiles: against fp32 torch
     and bit-identical to the 256-row path (same MMA instruction shapes and K order, so the accumulators are the same)."""
@@ -97,8 +97,10 @@ def test_gemm_rows2_pair_tiles(M, K, N, mode, shift):
             ops.linear(a, w, bias=bias, out_bf16=ob)
             x = x0.clone()
             ops.linear(a, w, bias=bias, scale=gamma, res1=x, out_f32=x)
+            og = torch.zeros(M, N, dtype=torch.bfloat16, device="cuda")
+            ops.linear(a, w, bias=bias, out_bf16=og, flags=_lib.GEMM_GELU)  # 512-row tiles only with mode bit 2
             torch.cuda.synchronize()
-            outs[m] = (ob, x)
+            outs[m] = (ob, x, og)
     finally:
         lib.ufm_debug_flag(6, 3)
         lib.ufm_debug_flag(7, 0)
@@ -107,6 +109,8 @@ def test_gemm_rows2_pair_tiles(M, K, N, mode, shift):
     assert rel(outs[mode][1], x0 + gamma * ref) < 1e-5
     assert torch.equal(outs[mode][0], outs[0][0])
     assert torch.equal(outs[mode][1], outs[0][1])
+    assert torch.equal(outs[mode][2], outs[0][2])
+    assert rel(outs[mode][2].float(), F.gelu(ref)) < 4e-3
 
 
 # Last-wave column slices (gemm.cu tile_ref / engine.cu build_gemm) on a 148-SM part: pair tiles 256 x 256 on 74 units,

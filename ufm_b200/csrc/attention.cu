@@ -304,13 +304,18 @@ __device__ __forceinline__ void exp_chunk32(uint32_t* s, uint32_t* pk, uint64_t 
 // a MUFU-only phase).  s_free is signalled once chunk 3 is in registers and the speculation is confirmed; if the row
 // maximum did grow by more than 2^8 (any lane of the warp), nothing has been published yet and the step is redone by
 // the one-shot path below (S is still in tensor memory, P is simply overwritten).
+// Shared-memory addresses of the barriers a softmax warp touches, computed once per kernel (see opaque_u32)
+struct SoftmaxBars {
+  uint32_t s_full, s_free, p_full, o_done;
+};
+
 template <int VAR>
-__device__ __forceinline__ bool softmax_step_stream(Bars* b, uint32_t s_addr, uint32_t p_addr, uint32_t g, float sl2,
+__device__ __forceinline__ bool softmax_step_stream(const SoftmaxBars& sb, uint32_t s_addr, uint32_t p_addr, uint32_t g, float sl2,
                                                     float m_ref, float& l, int lane) {
   constexpr int POLY = VAR & 15;
   uint32_t c0[32], c1[32], c2[32], c3[32];
-  uint32_t pk[16];
-  mbar_wait(&b->s_full, g & 1);
+  uint32_t pk0[16], pk1[16];
+  mbar_wait_a(sb.s_full, g & 1);
   tc_fence_after();
   tmem_ld32(s_addr, c0);
   tmem_ld32(s_addr + 32, c1);
@@ -321,28 +326,28 @@ __device__ __forceinline__ bool softmax_step_stream(Bars* b, uint32_t s_addr, ui
   uint64_t sum_a = pack2(0.f, 0.f), sum_b = sum_a, sum_c = sum_a, sum_d = sum_a;
   float tmax = fmaxf(tree_max<32>(*reinterpret_cast<const float(*)[32]>(c0)),
                      tree_max<32>(*reinterpret_cast<const float(*)[32]>(c1)));
-  exp_chunk32<POLY>(c0, pk, sl2_2, mb_2, sum_a, sum_b, 0);
+  exp_chunk32<POLY>(c0, pk0, sl2_2, mb_2, sum_a, sum_b, 0);
   tmem_ld_wait();  // chunk 2 has arrived
   tmem_ld32(s_addr + 96, c3);
-  mbar_wait(&b->o_done, (g - 1) & 1);  // PV_{g-1} has consumed the previous P (j > 0 on this path)
-  tc_fence_after();
-  tmem_st16(p_addr, pk);
   tmax = fmaxf(tmax, tree_max<32>(*reinterpret_cast<const float(*)[32]>(c2)));
-  exp_chunk32<POLY>(c1, pk, sl2_2, mb_2, sum_c, sum_d, 1);
+  exp_chunk32<POLY>(c1, pk1, sl2_2, mb_2, sum_c, sum_d, 1);
   tmem_ld_wait();  // chunk 3 has arrived: the whole row is in registers
   tmax = fmaxf(tmax, tree_max<32>(*reinterpret_cast<const float(*)[32]>(c3)));
-  if (__any_sync(0xffffffffu, (tmax - m_ref) * sl2 > 8.0f)) {  // rare: redo with a rescale (one-shot path)
-    tmem_st_wait();  // the P chunk already written is overwritten there: keep the two stores ordered
-    return false;
-  }
+  if (__any_sync(0xffffffffu, (tmax - m_ref) * sl2 > 8.0f)) return false;  // rare: redo with a rescale (one-shot path)
   tc_fence_before();
   __syncwarp();
-  if (lane == 0) mbar_arrive(&b->s_free);
-  tmem_st16(p_addr + 16, pk);
-  exp_chunk32<POLY>(c2, pk, sl2_2, mb_2, sum_a, sum_b, 2);
-  tmem_st16(p_addr + 32, pk);
-  exp_chunk32<POLY>(c3, pk, sl2_2, mb_2, sum_c, sum_d, 3);
-  tmem_st16(p_addr + 48, pk);
+  if (lane == 0) mbar_arrive_a(sb.s_free);
+  // The first P chunks are held back until here: PV_{g-1} (issued when the LAST softmax warp finished step g-1, 256 clk of
+  // MMA behind whatever the co-resident CTA queued) is usually still running when chunk 0 is done -- storing P right
+  // away put 8.5 % of a softmax warp's samples on this wait (ncu source view, round 2).
+  mbar_wait_a(sb.o_done, (g - 1) & 1);  // PV_{g-1} has consumed the previous P (j > 0 on this path)
+  tc_fence_after();
+  tmem_st16(p_addr, pk0);
+  tmem_st16(p_addr + 16, pk1);
+  exp_chunk32<POLY>(c2, pk0, sl2_2, mb_2, sum_a, sum_b, 2);
+  tmem_st16(p_addr + 32, pk0);
+  exp_chunk32<POLY>(c3, pk1, sl2_2, mb_2, sum_c, sum_d, 3);
+  tmem_st16(p_addr + 48, pk1);
   {
     float a0, a1;
     unpack2(add2(add2(sum_a, sum_b), add2(sum_c, sum_d)), a0, a1);
@@ -351,7 +356,7 @@ __device__ __forceinline__ bool softmax_step_stream(Bars* b, uint32_t s_addr, ui
   tmem_st_wait();
   tc_fence_before();
   __syncwarp();
-  if (lane == 0) mbar_arrive(&b->p_full);
+  if (lane == 0) mbar_arrive_a(sb.p_full);
   return true;
 }
 
@@ -521,10 +526,12 @@ __global__ void __launch_bounds__(kThreads, 2) attn_kernel(const __grid_constant
     setmaxnreg_inc<200>();
     const int q = warp & 3;       // TMEM lane quadrant
     const int r = q * 32 + lane;  // row within the tile
-    const uint32_t lane_addr = tmem_base + (uint32_t(q * 32) << 16);
+    const uint32_t lane_addr = opaque_u32(tmem_base + (uint32_t(q * 32) << 16));
     const uint32_t s_addr = lane_addr + TM_S;
     const uint32_t p_addr = lane_addr + TM_P;
     const uint32_t o_addr = lane_addr + TM_O;
+    const SoftmaxBars sb{opaque_u32(smem_u32(&b->s_full)), opaque_u32(smem_u32(&b->s_free)), opaque_u32(smem_u32(&b->p_full)),
+                         opaque_u32(smem_u32(&b->o_done))};
     const float sl2 = p.scale_log2;
     uint32_t g = 0;
     for (int t = 0; t < n_my; ++t) {
@@ -534,7 +541,7 @@ __global__ void __launch_bounds__(kThreads, 2) attn_kernel(const __grid_constant
       float m_ref = -INFINITY, l = 0.f;
       for (int j = 0; j < n_kv - 1; ++j, ++g) {
         if constexpr ((VAR & 128) != 0) {
-          if (j > 0 && softmax_step_stream<VAR>(b, s_addr, p_addr, g, sl2, m_ref, l, lane)) continue;
+          if (j > 0 && softmax_step_stream<VAR>(sb, s_addr, p_addr, g, sl2, m_ref, l, lane)) continue;
         }
         softmax_step<128, VAR>(b, s_addr, p_addr, o_addr, g, j, 128, sl2, m_ref, l, lane);
       }

@@ -14,6 +14,7 @@
 // Pipelines: smem full/empty (TMA <-> MMA), TMEM full/empty (MMA <-> epilogue), so the epilogue of tile i
 // overlaps the mainloop of tile i+1.
 #include <stdio.h>
+#include <stdlib.h>
 
 #include "kernels.h"
 #include "launch.cuh"
@@ -65,7 +66,11 @@ struct Cfg {
   // reuses them as [acc][half][row][kTailMax] floats
   static constexpr int SLABS = R2 ? 1 : 2;
   static constexpr int SCRATCH_BYTES = kEpiWarps * SLABS * 4096;
-  static constexpr int SMEM_BYTES = 1024 + A_STAGES * A_BYTES + STAGES * B_BYTES + BAR_BYTES + SCRATCH_BYTES;
+  // R2: [bias | scale] of the item's BN columns, staged once per item by the epilogue warps (the per-column epilogue
+  // constants are then LDS broadcasts instead of L2 round trips: with ~226 KB of smem carved out there is no L1 left)
+  static constexpr int COLC_BYTES = R2 ? 2 * BN * 4 : 0;
+  static constexpr int ALIGN_SLACK = R2 ? 0 : 1024;  // R2 relies on the 1024-byte alignment of the dynamic smem window (checked)
+  static constexpr int SMEM_BYTES = ALIGN_SLACK + A_STAGES * A_BYTES + STAGES * B_BYTES + BAR_BYTES + SCRATCH_BYTES + COLC_BYTES;
   static constexpr int TMEM_COLS = 2 * BN;
 };
 
@@ -126,6 +131,7 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_kernel(const __grid_constant
   uint64_t* afull = resbar + 2 * kEpiWarps;  // HALO: the A ring's own barriers (full/empty then belong to the B ring)
   uint64_t* aempty = afull + 3;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(aempty + 3);
+  float* colc = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(full) + C::BAR_BYTES);  // R2: [bias BN | scale BN]
   float* scratch = reinterpret_cast<float*>(epi_smem);  // TAIL mode: [acc][half][row][4] floats
 
   // logical warp (role) index: physical warp + warp_shift mod 12; a shift of 4 keeps the TMEM lane quadrant (warp & 3)
@@ -133,6 +139,10 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_kernel(const __grid_constant
   warp = warp >= kThreads / 32 ? warp - kThreads / 32 : warp;
   const int lane = threadIdx.x & 31;
 
+  if (R2 && threadIdx.x == 0 && (smem_u32(smem_raw) & 1023u)) {
+    printf("ufm: gemm shared memory window is not 1024-byte aligned\n");
+    __trap();
+  }
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&p.tmA);
     tma_prefetch_desc(&p.tmB);
@@ -448,6 +458,116 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_kernel(const __grid_constant
       tempty_remote[0] = mapa_cluster(smem_u32(&tempty[0]), 0);
       tempty_remote[1] = mapa_cluster(smem_u32(&tempty[1]), 0);
     }
+    if constexpr (R2) {
+      // ---- 512 x 256 pair tiles: nothing overlaps the epilogue through a second accumulator set, so the accumulator is
+      // handed back as early as possible: all 128 columns of this warp leave tensor memory in one batch of loads, tempty is
+      // signalled, and only then the bias / GELU / LayerScale math, the slab and the TMA store (or reduce-add) run -- under
+      // the next item's main loop.  Column constants come from smem (staged per item by the eight epilogue warps).
+      const bool f32 = emode == EPI_TMA_F32;
+      const bool red = (p.flags & GEMM_RED_INPLACE) != 0;
+      const int tid8 = e * 32 + lane;  // 0..255 over the eight epilogue warps
+      int it2 = 0;
+      for (int item = unit; item < total_items; item += num_units, ++it2) {
+        const TileRef tr = tile_ref(p, item, split_from, BN);
+        const int n0 = tr.n0;
+        // stage bias / scale of columns [n0, n0 + BN): every warp has finished reading the previous item's values
+        asm volatile("bar.sync 2, 256;" ::: "memory");
+        colc[tid8] = (p.bias && n0 + tid8 < p.N) ? __ldg(p.bias + n0 + tid8) : 0.f;
+        colc[BN + tid8] = (p.scale && n0 + tid8 < p.N) ? __ldg(p.scale + n0 + tid8) : 1.f;
+        asm volatile("bar.sync 2, 256;" ::: "memory");
+        const int col_off = half * (BN / 2);
+        const int c0 = n0 + col_off;
+        const float* bcol = colc + col_off;
+        const float* scol = colc + BN + col_off;
+        for (int rb = 0; rb < 2; ++rb) {
+          const int tm = (tr.mt * 2 + rb) * CTAS + (int)cta_rank;
+          const int tx = tm % p.tiles_x;
+          const int ty = (tm / p.tiles_x) % p.tiles_y;
+          const int img = tm / (p.tiles_x * p.tiles_y);
+          const int wx = tx * p.tw + ((32 * q) & (p.tw - 1));
+          const int wy = ty * p.th + ((32 * q) >> p.tw_log2);
+          const uint32_t acc_addr = tmem_base + (uint32_t(q * 32) << 16) + uint32_t(rb * BN + col_off);
+          mbar_wait(&tfull[rb], (uint32_t)(it2 & 1));
+          tc_fence_after();
+          uint32_t vr[128];
+#pragma unroll
+          for (int c = 0; c < 4; ++c) tmem_ld32(acc_addr + c * 32, *reinterpret_cast<uint32_t(*)[32]>(vr + c * 32));
+          tmem_ld_wait();
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive_cluster_relaxed(tempty_remote[rb]);
+          uint8_t* rowp = wbuf + lane * 128;
+          if (f32) {
+#pragma unroll
+            for (int c = 0; c < 4; ++c) {
+              if (c0 + 32 * c >= p.N) break;
+              if (lane == 0) bulk_wait_read<0>();  // single slab: the previous store has read it
+              __syncwarp();
+#pragma unroll
+              for (int j = 0; j < 8; ++j) {
+                const float4 b4 = *reinterpret_cast<const float4*>(bcol + 32 * c + 4 * j);
+                const float4 s4 = *reinterpret_cast<const float4*>(scol + 32 * c + 4 * j);
+                float4 v = make_float4(__uint_as_float(vr[32 * c + 4 * j]) + b4.x, __uint_as_float(vr[32 * c + 4 * j + 1]) + b4.y,
+                                       __uint_as_float(vr[32 * c + 4 * j + 2]) + b4.z, __uint_as_float(vr[32 * c + 4 * j + 3]) + b4.w);
+                if (p.flags & GEMM_GELU) {
+                  v.x = gelu_erf(v.x); v.y = gelu_erf(v.y); v.z = gelu_erf(v.z); v.w = gelu_erf(v.w);
+                }
+                if (p.scale) {
+                  v.x *= s4.x; v.y *= s4.y; v.z *= s4.z; v.w *= s4.w;
+                }
+                *reinterpret_cast<float4*>(rowp + ((uint32_t(j) ^ sw) << 4)) = v;
+              }
+              fence_proxy_async_smem();
+              __syncwarp();
+              if (lane == 0) {
+                if (red) tma_reduce_add_4d(&p.tmOut, wbuf, c0 + 32 * c, wx, wy, img);
+                else tma_store_4d(&p.tmOut, wbuf, c0 + 32 * c, wx, wy, img);
+                bulk_commit_group();
+              }
+            }
+          } else {
+#pragma unroll
+            for (int c = 0; c < 2; ++c) {
+              if (c0 + 64 * c >= p.N) break;
+              if (lane == 0) bulk_wait_read<0>();
+              __syncwarp();
+#pragma unroll
+              for (int j = 0; j < 8; ++j) {
+                float v[8];
+                const float4 b0 = *reinterpret_cast<const float4*>(bcol + 64 * c + 8 * j);
+                const float4 b1 = *reinterpret_cast<const float4*>(bcol + 64 * c + 8 * j + 4);
+                const float bb[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
+#pragma unroll
+                for (int i = 0; i < 8; ++i) v[i] = __uint_as_float(vr[64 * c + 8 * j + i]) + bb[i];
+                if (p.flags & GEMM_GELU) {
+#pragma unroll
+                  for (int i = 0; i < 8; ++i) v[i] = gelu_erf(v[i]);
+                }
+                if (p.scale) {
+                  const float4 s0 = *reinterpret_cast<const float4*>(scol + 64 * c + 8 * j);
+                  const float4 s1 = *reinterpret_cast<const float4*>(scol + 64 * c + 8 * j + 4);
+                  v[0] *= s0.x; v[1] *= s0.y; v[2] *= s0.z; v[3] *= s0.w;
+                  v[4] *= s1.x; v[5] *= s1.y; v[6] *= s1.z; v[7] *= s1.w;
+                }
+                if (p.flags & GEMM_RELU_BF16) {
+#pragma unroll
+                  for (int i = 0; i < 8; ++i) v[i] = fmaxf(v[i], 0.f);
+                }
+                *reinterpret_cast<uint4*>(rowp + ((uint32_t(j) ^ sw) << 4)) =
+                    make_uint4(pack_bf16(v[0], v[1]), pack_bf16(v[2], v[3]), pack_bf16(v[4], v[5]), pack_bf16(v[6], v[7]));
+              }
+              fence_proxy_async_smem();
+              __syncwarp();
+              if (lane == 0) {
+                tma_store_4d(&p.tmOut, wbuf, c0 + 64 * c, wx, wy, img);
+                bulk_commit_group();
+              }
+            }
+          }
+        }
+      }
+      if (lane == 0) bulk_wait<0>();
+    } else {
     int iter = 0;
     for (int item = unit; item < total_items; item += num_units, ++iter)
     for (int rb = 0; rb < RB; ++rb) {
@@ -613,7 +733,7 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_kernel(const __grid_constant
         tc_fence_before();
         __syncwarp();
         if (lane == 0) {
-          if constexpr (CTAS == 2) mbar_arrive_cluster(tempty_remote[acc]);
+          if constexpr (CTAS == 2) mbar_arrive_cluster_relaxed(tempty_remote[acc]);
           else mbar_arrive(&tempty[acc]);
         }
       } else if (emode == EPI_TMA_BF16) {
@@ -682,7 +802,7 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_kernel(const __grid_constant
         tc_fence_before();
         __syncwarp();
         if (lane == 0) {
-          if constexpr (CTAS == 2) mbar_arrive_cluster(tempty_remote[acc]);
+          if constexpr (CTAS == 2) mbar_arrive_cluster_relaxed(tempty_remote[acc]);
           else mbar_arrive(&tempty[acc]);
         }
       } else {
@@ -804,7 +924,7 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_kernel(const __grid_constant
         tc_fence_before();
         __syncwarp();
         if (lane == 0) {
-          if constexpr (CTAS == 2) mbar_arrive_cluster(tempty_remote[acc]);
+          if constexpr (CTAS == 2) mbar_arrive_cluster_relaxed(tempty_remote[acc]);
           else mbar_arrive(&tempty[acc]);
         }
 
@@ -838,6 +958,7 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_kernel(const __grid_constant
       }
     }
     if (emode != EPI_DIRECT && lane == 0) bulk_wait<0>();
+    }  // !R2
   }
 
   tc_fence_before();
@@ -882,9 +1003,12 @@ int gemm_pair_mode() { return g_gemm_pair; }
 int g_gemm_split = 1;  // ufm_debug_flag 5
 void set_gemm_split_mode(int v) { g_gemm_split = v; }
 int gemm_split_mode() { return g_gemm_split; }
-int g_gemm_rows2 = 3;  // ufm_debug_flag 6
+int g_gemm_rows2 = -1;  // ufm_debug_flag 6 / UFM_ROWS2 (tuning)
 void set_gemm_rows2_mode(int v) { g_gemm_rows2 = v; }
-int gemm_rows2_mode() { return g_gemm_rows2; }
+int gemm_rows2_mode() {
+  if (g_gemm_rows2 < 0) g_gemm_rows2 = getenv("UFM_ROWS2") ? atoi(getenv("UFM_ROWS2")) : 3;
+  return g_gemm_rows2;
+}
 int g_gemm_warp_shift = 0;  // ufm_debug_flag 7
 void set_gemm_warp_shift(int v) { g_gemm_warp_shift = v; }
 int gemm_warp_shift() { return g_gemm_warp_shift; }

@@ -50,6 +50,37 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
   }
 }
 
+// The same on a precomputed shared::cta address.  Hot loops keep the address in a register made opaque to the compiler
+// (opaque_u32): ptxas otherwise re-derives it every iteration (S2UR SR_CgaCtaId + ULEA, or S2R SR_TID + IMAD for a TMEM lane
+// address), and the special-register read latency is exposed in front of every barrier wait (ncu source view of
+// attn_kernel, round 2: ~4 % of a softmax warp's samples on those two sequences).
+__device__ __forceinline__ uint32_t opaque_u32(uint32_t v) {
+  asm volatile("mov.b32 %0, %0;" : "+r"(v));
+  return v;
+}
+__device__ __forceinline__ void mbar_arrive_a(uint32_t bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void mbar_wait_a(uint32_t bar, uint32_t parity) {
+  uint32_t spins = 0;
+  for (;;) {
+    uint32_t ok;
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.b32 %0, 1, 0, p;\n\t}"
+        : "=r"(ok)
+        : "r"(bar), "r"(parity)
+        : "memory");
+    if (ok) break;
+    if (++spins > (1u << 24)) {
+      printf("ufm: mbarrier wait timeout block (%d,%d,%d) thread %d bar %u parity %u\n", blockIdx.x, blockIdx.y, blockIdx.z,
+             threadIdx.x, bar, parity);
+      __trap();
+    }
+  }
+}
+
 // ---------------------------------------------------------------- proxies / fences
 __device__ __forceinline__ void fence_proxy_async_smem() {
   asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
@@ -250,6 +281,13 @@ __device__ __forceinline__ uint32_t mapa_cluster(uint32_t local_smem_addr, uint3
 }
 __device__ __forceinline__ void mbar_arrive_cluster(uint32_t cluster_addr) {
   asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
+}
+// Relaxed variant for "accumulator drained" signals: the only accesses the consumer (the MMA issuer) must see ordered are
+// the tcgen05.ld reads, which tcgen05.wait::ld + tcgen05.fence::before_thread_sync already order before the arrive.  The
+// release form compiles to MEMBAR.ALL.CTA + ERRBAR in front of the arrive and waits for every outstanding shared / global
+// store of the epilogue: 24 % of an epilogue warp's busy samples in the round-2 ncu source view of gemm_kernel.
+__device__ __forceinline__ void mbar_arrive_cluster_relaxed(uint32_t cluster_addr) {
+  asm volatile("mbarrier.arrive.relaxed.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
 }
 // In a CTA pair the leader (even rank) owns the "full" barriers: clearing bit 24 of a shared::cluster address
 // addresses the same offset in the leader CTA (cute Sm100MmaPeerBitMask).

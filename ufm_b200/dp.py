@@ -29,13 +29,24 @@ def shard_sizes(n_pairs: int, world: int) -> List[int]:
 
 
 def _gather_ragged(local: torch.Tensor, sizes: List[int], group) -> torch.Tensor:
-    """All-gather tensors whose leading dimension differs per rank (pads to the largest shard for the collective)."""
+    """All-gather tensors whose leading dimension differs per rank into ONE [sum(sizes), ...] tensor.
+
+    Equal shards (B divisible by the world size: the normal case) are gathered by ``all_gather_into_tensor`` straight
+    into the final buffer -- no padding, no per-rank staging buffers, no concatenation.  Ragged shards pad the local
+    shard to the largest one for the collective and compact the result once."""
     per = max(sizes)
-    pad = torch.zeros((per,) + tuple(local.shape[1:]), dtype=local.dtype, device=local.device)
-    pad[: local.shape[0]] = local
-    bufs = [torch.empty_like(pad) for _ in sizes]
-    dist.all_gather(bufs, pad, group=group)
-    return torch.cat([b[:s] for b, s in zip(bufs, sizes)], dim=0)
+    world = len(sizes)
+    tail = tuple(local.shape[1:])
+    local = local.contiguous()
+    if local.shape[0] != per:
+        pad = torch.zeros((per,) + tail, dtype=local.dtype, device=local.device)
+        pad[: local.shape[0]] = local
+        local = pad
+    out = torch.empty((world * per,) + tail, dtype=local.dtype, device=local.device)
+    dist.all_gather_into_tensor(out, local, group=group)
+    if all(s == per for s in sizes):
+        return out
+    return torch.cat([out[r * per: r * per + s] for r, s in enumerate(sizes)], dim=0)
 
 
 def predict_sharded(predict: Callable[[torch.Tensor, torch.Tensor], Tuple[torch.Tensor, Optional[torch.Tensor]]],
