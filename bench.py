@@ -42,7 +42,10 @@ WORKLOADS = {
     "refine16": ("ufm_refine_assumed", (560, 420), 16, "UFM-Refine batch 16 pairs 560x420 (configs[2])"),
     "hires4": ("ufm_base_assumed", (1120, 840), 4, "UFM-Base 1120x840 batch 4 (configs[3])"),
     "refine16_unet": ("ufm_refine_unet", (560, 420), 16, "UFM-Refine + UNet fine-feature branch, batch 16 pairs 560x420 (SURVEY 8f N3)"),
+    # inputs at a FOREIGN size: normalise + anti-alias resize in (prep_resize_kernel), nearest / bilinear un-map out (unmap_kernel)
+    "foreign16": ("ufm_base_assumed", (560, 420), 16, "UFM-Base batch 16 pairs, 640x480 inputs resized to 560x420 and un-mapped back (SURVEY 8f N1)"),
 }
+INPUT_HW = {"foreign16": (480, 640)}  # (H0, W0) of the images handed to the API when they differ from the inference resolution
 
 
 def algorithmic_tflop_per_pair(cfg, refine: bool) -> dict:
@@ -381,9 +384,21 @@ def run_engine(args):
     model = cls(max_pairs_per_call=pairs, **cfg)
     model.load_state_dict(make_state_dict(cfg, seed=0))
     model = model.to(dev)
-    src, tgt = make_inputs(pairs, H, W, seed=1 + rank)
+    H0, W0 = INPUT_HW.get(args.workload, (H, W))
+    foreign = (H0, W0) != (H, W)
+    src, tgt = make_inputs(pairs, H0, W0, seed=1 + rank)
     dsrc, dtgt = src.to(dev), tgt.to(dev)
     eng = model._engine(dev)
+
+    class _Api:  # foreign input size: the timed call is the public API on device tensors (resize in, forward, un-map out)
+        def forward(self, a, b, layout):
+            o = model.predict_correspondences_batched(a, b)
+            return o.flow.flow_output, o.covisibility.mask
+
+        def launch_count(self):
+            return eng.launch_count() + 3  # + 2 prep_resize + 1 unmap launches around the engine's pass
+
+    run = _Api() if foreign else eng
 
     def barrier():
         if world > 1:
@@ -399,7 +414,7 @@ def run_engine(args):
 
     # ---- value: device-timed, inputs resident in HBM -----------------------------------------------------------------
     for _ in range(args.warmup):
-        eng.forward(dsrc, dtgt, _lib.UFM_NHWC)
+        run.forward(dsrc, dtgt, _lib.UFM_NHWC)
     sampler = ClockSampler(local)
     barrier()
     sampler.start()
@@ -407,13 +422,13 @@ def run_engine(args):
     marks = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps)]
     e0.record()
     for i in range(args.steps):
-        flow, cov = eng.forward(dsrc, dtgt, _lib.UFM_NHWC)
+        flow, cov = run.forward(dsrc, dtgt, _lib.UFM_NHWC)
         marks[i].record()
     e1.record()
     barrier()
     clocks = sampler.stop()
     step_ms = [round((e0 if i == 0 else marks[i - 1]).elapsed_time(marks[i]), 3) for i in range(args.steps)]
-    launches = eng.launch_count() * args.steps
+    launches = run.launch_count() * args.steps
     ms = maxreduce(e0.elapsed_time(e1))
     ms_per_step = ms / args.steps
     value = world * pairs * args.steps / (ms / 1e3)
@@ -433,8 +448,8 @@ def run_engine(args):
     barrier()
     e2e_ms = maxreduce(max(e0.elapsed_time(e1), (time.perf_counter() - t0) * 1e3))
     assert out.flow.flow_output.device.type == "cpu"
-    h2d = 2 * pairs * H * W * 3
-    d2h = pairs * H * W * 4 * (2 + (1 if out.covisibility is not None else 0))
+    h2d = 2 * pairs * H0 * W0 * 3
+    d2h = pairs * H0 * W0 * 4 * (2 + (1 if out.covisibility is not None else 0))
     e2e = {"value": world * pairs * args.steps / (e2e_ms / 1e3), "unit": UNIT, "h2d_bytes_per_step": h2d,
            "d2h_bytes_per_step": d2h, "api": "predict_correspondences_batched(pinned host uint8 BHWC) -> host tensors"}
 
@@ -442,9 +457,39 @@ def run_engine(args):
     eng.set_profile(True)
     psteps = max(1, min(args.steps, 3))
     for _ in range(psteps):
-        eng.forward(dsrc, dtgt, _lib.UFM_NHWC)
+        run.forward(dsrc, dtgt, _lib.UFM_NHWC)
     prof = eng.profile_read()
     eng.set_profile(False)
+    prepost_fam = {}
+    if foreign:
+        # the two kernels around the engine's pass run outside its launch wrapper: timed here, back to back, on the
+        # current stream; algorithmic bytes = input read once + output written once
+        from ufm_b200 import prepost
+
+        def timed(fn, reps=10):
+            for _ in range(2):
+                fn()
+            a_, b_ = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a_.record()
+            for _ in range(reps):
+                fn()
+            b_.record()
+            torch.cuda.synchronize()
+            return a_.elapsed_time(b_) / reps
+
+        t_prep = timed(lambda: prepost.prep_resize(dsrc, True, H, W, "dinov2"))
+        rep0 = prepost.scaled_region(H, W, H0, W0)
+        full = [0, H0, 0, W0]
+        f_in = torch.randn(pairs, 2, H, W, device=dev)
+        c_in = torch.rand(pairs, H, W, device=dev)
+        t_unmap = timed(lambda: prepost.unmap(f_in, c_in, rep0, full, full, (H0, W0)))
+        b_prep = pairs * (H0 * W0 * 3 + H * W * 3 * 4)
+        b_unmap = pairs * 3 * 4 * (H * W + H0 * W0)
+        peaks_ = _peaks()
+        for nm, t_, by_, n_ in (("prep_resize", t_prep, b_prep, 2), ("unmap", t_unmap, b_unmap, 1)):
+            prepost_fam[nm] = {"ms_per_step": t_ * n_, "launches_per_step": n_, "bound": "hbm", "achieved": by_ / (t_ * 1e-3) / 1e9,
+                               "peak": peaks_["hbm"], "unit": "GB/s", "frac": by_ / (t_ * 1e-3) / 1e9 / peaks_["hbm"],
+                               "note": "timed alone (kernel-level C-ABI call), algorithmic bytes = input once + output once"}
     peaks = _peaks()
     fl = algorithmic_tflop_per_pair(cfg, refine)
     fam = {}
@@ -459,6 +504,7 @@ def run_engine(args):
             d.update(bound="hbm", achieved=v["bytes"] / (v["ms"] * 1e-3) / 1e9, peak=peaks["hbm"], unit="GB/s")
         d["frac"] = d["achieved"] / d["peak"]
         fam[k] = d
+    fam.update(prepost_fam)
     gm = {k: prof[k] for k in ("gemm", "conv3x3")}
     g_ms = sum(v["ms"] for v in gm.values())
     g_fl = sum(v["flops"] for v in gm.values())

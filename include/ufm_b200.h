@@ -107,6 +107,13 @@ int ufm_forward_host(ufm_engine* e, const void* src, const void* tgt, int pairs,
 /* Ask the next forward calls to also keep optional Refine outputs (residual [B,2,H,W], log_softmax [B,H,W,P*P]). */
 int ufm_set_keep_aux(ufm_engine* e, int keep);
 
+/* Row of info_sharing.view_pos_table that the NON-reference view adds in the following passes (the reference view always
+ * adds row 0).  Default 1.  With use_rand_idx_pe_for_non_reference_views the reference draws the row per forward with
+ * torch.randint(1, max_num_views) (global_attention_transformer.py:520-524; alternating: :281-286); the host mirror draws
+ * the same number from the same generator and hands it over here.  row == number of table rows selects the all-zero row
+ * the engine appends (alternating attention without use_pe_for_non_reference_views). */
+int ufm_set_view_index(ufm_engine* e, int row);
+
 /* Parity hooks: describe / copy an internal stage buffer of the LAST forward (device-to-device or device-to-host).
  * Names: enc_first, enc_last, info_inter0, info_inter1, info_final, dpt1, dptu, head1_raw, headu_raw, flow_reg,
  * desc, residual, log_softmax.  Layouts are the engine's own (documented in DESIGN.md). */

@@ -28,6 +28,8 @@ GOLDEN_CASES = {
     "tiny_coord": dict(cfg="tiny_coord", batch=2, out_gain=0.05),
     # norm_intermediate=False on encoder and info sharing, encoder data_norm_type "dust3r" (Refine model)
     "tiny_nonorm": dict(cfg="tiny_nonorm", batch=2, out_gain=8.0),
+    # random view index for the non-reference view's positional row: torch.manual_seed(rng_seed) right before the call
+    "tiny_randidx": dict(cfg="tiny_randidx", batch=2, out_gain=8.0, rng_seed=1234),
     # UNet fine-feature branch of UFM-Refine, both combine methods
     "tiny_unet": dict(cfg="tiny_unet", batch=2, out_gain=8.0),
     "tiny_unet_mod": dict(cfg="tiny_unet_mod", batch=1, out_gain=8.0),

@@ -90,6 +90,7 @@ def run_reference(name: str):
 
         model.classification_refinement = wrapped
     t0 = time.time()
+    torch.manual_seed(case.get("rng_seed", 0))  # use_rand_idx_pe_for_non_reference_views draws from the global generator
     with torch.no_grad():
         out = model.predict_correspondences_batched(src, tgt)
     dt = time.time() - t0

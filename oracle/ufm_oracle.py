@@ -228,7 +228,12 @@ def info_sharing(f1: torch.Tensor, f2: torch.Tensor, sd, cfg):
     pe = torch.zeros(2, dim)
     pe[0] = tab[0]
     if not alternating or ik.get("use_pe_for_non_reference_views", False):
-        pe[1] = tab[1]  # use_rand_idx_pe_for_non_reference_views must be False
+        # use_rand_idx_pe_for_non_reference_views: one draw from the global generator per forward, as the reference
+        # (global_attention_transformer.py:520-524; alternating_attention_transformer.py:281-286, default True there)
+        rand = ik.get("use_rand_idx_pe_for_non_reference_views", alternating)
+        high = ik.get("max_num_views_for_pe", 1000) if alternating else ik.get("max_num_views")
+        row = int(torch.randint(low=1, high=high, size=(1,)).item()) if rand else 1
+        pe[1] = tab[row]
     x = x + pe.repeat_interleave(n, dim=0)[None]
     idx = ik["indices"]
     take = list(range(depth - idx, depth)) if isinstance(idx, int) else [depth + i if i < 0 else i for i in idx]

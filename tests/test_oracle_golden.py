@@ -22,7 +22,9 @@ def _run_oracle(name):
     src, tgt = make_inputs(case["batch"], H, W)
     with torch.no_grad():
         s0, s1 = O.canonicalize_inputs(src, tgt, cfg["encoder_kwargs"]["data_norm_type"], None)
+        torch.manual_seed(case.get("rng_seed", 0))
         st = O.forward_stages(s0, s1, sd, cfg)
+        torch.manual_seed(case.get("rng_seed", 0))
         api = O.predict_correspondences_batched(src, tgt, sd, cfg) if name.startswith("tiny") else None
     if "log_softmax" in st:
         st["log_softmax"] = st["log_softmax"].permute(0, 3, 4, 1, 2)

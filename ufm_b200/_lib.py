@@ -56,6 +56,7 @@ SYMBOLS = {
     "ufm_forward": (_I, [_P, _P, _P, _I, _I, _I, _P, _P, _P]),
     "ufm_forward_host": (_I, [_P, _P, _P, _I, _I, _I, _P, _P]),
     "ufm_set_keep_aux": (_I, [_P, _I]),
+    "ufm_set_view_index": (_I, [_P, _I]),
     "ufm_stage_desc": (_I, [_P, C.c_char_p, C.POINTER(_I), C.POINTER(_L), C.POINTER(_I)]),
     "ufm_stage_copy": (_I, [_P, C.c_char_p, _P, _L]),
     "ufm_last_launch_count": (_I, [_P]),

@@ -149,6 +149,13 @@ def _nonorm(cfg):
     return cfg
 
 
+def _randidx(cfg):
+    """use_rand_idx_pe_for_non_reference_views (global_attention_transformer.py:520-524): the second view's row of the
+    view_pos_table is drawn per forward with torch.randint(1, max_num_views)."""
+    cfg["info_sharing_kwargs"].update({"max_num_views": 6, "use_rand_idx_pe_for_non_reference_views": True})
+    return cfg
+
+
 def _coord(cfg):
     """FlowAdaptor predicting the landing position (output_normalized_coordinate, adaptors.py:110-118)."""
     cfg["adaptors_kwargs"]["flow"]["kwargs"]["output_normalized_coordinate"] = True
@@ -168,6 +175,7 @@ CONFIGS = {
     "tiny_bn": lambda: _use_bn(tiny(False)),
     "tiny_coord": lambda: _coord(tiny(True)),
     "tiny_nonorm": lambda: _nonorm(tiny(True)),
+    "tiny_randidx": lambda: _randidx(tiny(False)),
     "tiny_unet": lambda: tiny(True, unet="conv"),
     "tiny_unet_mod": lambda: tiny(True, unet="modulate"),
     "ufm_refine_unet": lambda: dict(ufm_refine_assumed(), use_unet_feature=True, feature_combine_method="conv"),

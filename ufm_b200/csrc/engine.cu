@@ -15,6 +15,8 @@
 #include <string>
 #include <vector>
 
+#include <nvtx3/nvToolsExt.h>
+
 #include "../../include/ufm_b200.h"
 #include "kernels.h"
 #include "launch.cuh"
@@ -100,6 +102,11 @@ bool build_gemm(GemmParams* gp, int* BN, const AView& a_in, const void* wt, int 
   const uint32_t abox[4] = {64, (uint32_t)a.tw + (halo ? 2u : 0u), (uint32_t)a.th + (halo ? 2u : 0u), 1};
   if (!make_tmap_bf16(&gp->tmA, a.p, 4, adims, astr, abox, err, errlen)) return false;
   const bool tail = (e.flags & GEMM_TAIL) != 0;
+  // TAIL launches (the 420 x 560 processor conv with ReLU + 1x1 + adaptor in the epilogue) are epilogue-heavy: with the
+  // epilogue on the LOW physical warps the TMA / MMA warps win the issue arbitration (highest warp id first) and are not
+  // delayed behind eight busy epilogue warps: proc.c2 0.301 -> 0.265 ms (profiles/r02_gemm_bench_rows2.txt, w4 column);
+  // neutral to slightly negative elsewhere, so only here
+  if (tail && gp->warp_shift == 0) gp->warp_shift = 4;
   *BN = (!tail && n_out % 256 == 0) ? 256 : (halo && !tail && n_out <= 64) ? 64 : 128;
   const uint64_t bdims[2] = {(uint64_t)taps * cin_pad, (uint64_t)n_out};
   const uint64_t bstr[2] = {2, (uint64_t)taps * cin_pad * 2};
@@ -287,6 +294,7 @@ struct ufm_engine {
   int max_pairs = 0;
   bool prepared = false;
   bool keep_aux = false;
+  int view_index = 1;  // row of info.viewpos the non-reference view adds (ufm_set_view_index)
   int launches = 0;
   int last_pairs = 0;
   std::string err;
@@ -315,6 +323,23 @@ struct ufm_engine {
   }
   int forward_impl(const void* src, const void* tgt, int pairs, int in_dtype, int in_layout, float* flow_out,
                    float* covis_out, cudaStream_t stream);
+  // NVTX ranges per stage of the pass (UFM_NVTX=1): "ufm_forward" > encoder / info_sharing / flow_head / uncertainty_head /
+  // classification_head / unet_branch / local_refinement.  The tracing aid the reference has for this path is the
+  // CUDA-event decorator of UC/models/encoders/utils.py:11-86; ufm_set_profile gives its per-kernel-family equivalent and
+  // these ranges name the stages in an ncu / Nsight timeline.
+  bool nvtx = getenv("UFM_NVTX") != nullptr;
+  int nvtx_depth = 0;
+  void nvtx_stage(const char* name) {  // closes the previous stage range and opens `name` (nullptr: only close)
+    if (!nvtx) return;
+    if (nvtx_depth > 1) {
+      nvtxRangePop();
+      --nvtx_depth;
+    }
+    if (name) {
+      nvtxRangePushA(name);
+      ++nvtx_depth;
+    }
+  }
   // ufm_forward_host: result copies run on their own stream as soon as each output is final (flow after the flow head
   // or the refinement, covisibility after the uncertainty head), under the rest of the pass
   cudaStream_t copy_st = nullptr;
@@ -335,6 +360,55 @@ struct ufm_engine {
   struct GraphEntry { cudaGraphExec_t exec = nullptr; std::map<std::string, Tensor> stage; int launches = 0; };
   std::map<std::vector<int>, GraphEntry> graphs;
   cudaStream_t graph_st = nullptr;
+
+  // Launch-bound regime (small batches: ~330 launches and as many tensor-map encodes per pass): the pass over the
+  // engine-owned staging buffers (in_src / in_tgt -> out_flow / covis) as a CUDA graph, captured once per (pairs, dtype,
+  // layout, keep_aux) on the private graph stream and replayed on `s` (ufm_forward: the caller's stream, around two
+  // device-to-device copies; ufm_forward_host: the graph stream, around the H2D / D2H copies).  The caller has ordered `s`
+  // after the previous pass and filled the staging inputs on `s`.
+  bool graph_pass(int pairs, int in_dtype, int in_layout, cudaStream_t s) {
+    void* dsrc = buf["in_src"].ptr;
+    void* dtgt = buf["in_tgt"].ptr;
+    float* dflow = reinterpret_cast<float*>(buf["out_flow"].ptr);
+    float* dcov = cfg.unc_out_ch > 0 ? reinterpret_cast<float*>(buf["covis"].ptr) : nullptr;
+    const std::vector<int> key = {pairs, in_dtype, in_layout, keep_aux ? 1 : 0, view_index};
+    auto it = graphs.find(key);
+    if (it == graphs.end()) {
+      // first call with this shape: a plain pass (it also sets the lazily initialised kernel attributes and produces this
+      // call's results), then the capture on the graph stream
+      if (forward(dsrc, dtgt, pairs, in_dtype, in_layout, dflow, dcov, s)) return false;
+      if (!ck(cudaStreamSynchronize(s), "sync before capture")) return false;
+      if (!graph_st && !ck(cudaStreamCreateWithFlags(&graph_st, cudaStreamNonBlocking), "graph stream")) return false;
+      GraphEntry ge;
+      cudaGraph_t graph = nullptr;
+      const std::map<std::string, Tensor> stage_keep = stage;
+      const int launches_keep = launches;
+      if (!ck(cudaStreamBeginCapture(graph_st, cudaStreamCaptureModeThreadLocal), "begin capture")) return false;
+      capturing = true;
+      const int rc = forward(dsrc, dtgt, pairs, in_dtype, in_layout, dflow, dcov, graph_st);
+      capturing = false;
+      const cudaError_t ce = cudaStreamEndCapture(graph_st, &graph);
+      st = s;
+      if (rc || ce != cudaSuccess) {
+        if (graph) cudaGraphDestroy(graph);
+        if (rc) return false;
+      }
+      if (!ck(ce, "end capture")) return false;
+      const cudaError_t ie = cudaGraphInstantiate(&ge.exec, graph, 0);
+      cudaGraphDestroy(graph);
+      if (!ck(ie, "graph instantiate")) return false;
+      ge.stage = stage_keep;
+      ge.launches = launches_keep;
+      graphs[key] = ge;
+      return true;
+    }
+    if (!ck(cudaGraphLaunch(it->second.exec, s), "graph launch")) return false;
+    stage = it->second.stage;
+    launches = it->second.launches;
+    last_pairs = pairs;
+    st = s;
+    return mark_done(s);
+  }
 
   // ---- per-kernel-family timing (CUDA events on the launching stream; read by bench.py for the roofline) ----
   bool profile = false;
@@ -883,7 +957,12 @@ bool ufm_engine::unet_branch(const void* src, const void* tgt, int in_dtype, int
 int ufm_engine::forward(const void* src, const void* tgt, int pairs, int in_dtype, int in_layout, float* flow_out,
                         float* covis_out, cudaStream_t stream) {
   if (!order_after_previous(stream)) return 1;
+  if (nvtx) {
+    nvtxRangePushA("ufm_forward");
+    nvtx_depth = 1;
+  }
   const int rc = forward_impl(src, tgt, pairs, in_dtype, in_layout, flow_out, covis_out, stream);
+  for (; nvtx && nvtx_depth > 0; --nvtx_depth) nvtxRangePop();
   if (!mark_done(stream)) return 1;
   return rc;
 }
@@ -906,6 +985,7 @@ int ufm_engine::forward_impl(const void* src, const void* tgt, int pairs, int in
   const long long Me = 2LL * Bp * S, Mi = 2LL * Bp * n;
 
   // ---- encoder (hub DINOv2 forward) ----
+  nvtx_stage("encoder");
   {
     PatchParams pp;
     pp.src = src; pp.tgt = tgt; pp.B = Bp; pp.H = c.img_h; pp.W = c.img_w; pp.P = c.patch; pp.Kpad = Kpad;
@@ -950,6 +1030,7 @@ int ufm_engine::forward_impl(const void* src, const void* tgt, int pairs, int in
     }
   }
   // ---- info sharing ----
+  nvtx_stage("info_sharing");
   float* y = B<float>("y");
   const bool cross = c.info_alternating == 2;
   {
@@ -957,9 +1038,11 @@ int ufm_engine::forward_impl(const void* src, const void* tgt, int pairs, int in
     e.bias = Wf("info.proj.b");
     if (!e.bias) return 1;
     if (!cross) {
-      e.res2 = Wf("info.viewpos");
-      if (!e.res2) return 1;
-      e.r2y = d; e.r2x = 0; e.r2n = 0;
+      const Tensor* vt = W("info.viewpos");
+      if (!vt) return 1;
+      if (view_index < 0 || view_index >= (int)vt->shape[0]) return fail("view index %d outside the view_pos_table", view_index);
+      e.res2 = reinterpret_cast<const float*>(vt->ptr);
+      e.r2y = (long long)view_index * d; e.r2x = 0; e.r2n = 0;  // view 0 -> row 0, view 1 -> row view_index
     }
     // residual stream layout: pair-major [B][2][n][d] (one attention sequence = one pair's 2n tokens), or VIEW-major
     // [2][B][n][d] for the per-view branches of cross-attention info sharing
@@ -998,6 +1081,7 @@ int ufm_engine::forward_impl(const void* src, const void* tgt, int pairs, int in
     if (!info_norm(B<bf16>("Xcls"), c.cls_in, D)) return 1;
   }
   // ---- heads (view 1 only: "dual+single", ufm.py:180,700) ----
+  nvtx_stage("dpt_heads");
   float* flow_reg = c.refine ? B<float>("flow_reg") : flow_out;
   if (!dpt_head("h1", Bp, c.flow_out_ch, false, c.flow_scale, c.flow_shift, B<bf16>("dpt1"), flow_reg,
                 B<float>("head1_raw")))
@@ -1050,6 +1134,7 @@ int ufm_engine::forward_impl(const void* src, const void* tgt, int pairs, int in
   }
   // ---- Refine: classification head + local refinement (ufm.py:954-991) ----
   if (c.refine) {
+    nvtx_stage("classification_head_and_refinement");
     const long long Mc = Mi;
     {
       Epi e;
@@ -1319,7 +1404,29 @@ int ufm_forward(ufm_engine* e, const void* src, const void* tgt, int pairs, int 
   if (!e) return 1;
   DevGuard dev_guard(e->device);
   if (!flow_out) return e->fail("flow_out is NULL");
-  return e->forward(src, tgt, pairs, in_dtype, in_layout, flow_out, covis_out, reinterpret_cast<cudaStream_t>(stream));
+  cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+  cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
+  if (e->prepared && pairs >= 1 && pairs <= kGraphMaxPairs && !e->profile && !getenv("UFM_NO_GRAPH") &&
+      (in_dtype == UFM_U8 || in_dtype == UFM_F32) && cudaStreamIsCapturing(s, &cap) == cudaSuccess &&
+      cap == cudaStreamCaptureStatusNone) {
+    // small batches are launch-bound: device-to-device copies into / out of the engine's staging buffers around a replay
+    // of the captured pass (2 x 0.7 MB in, 2.8 MB out per pair: microseconds, against ~330 launches and tensor-map encodes)
+    const ufm_config& c = e->cfg;
+    const size_t in_bytes = (size_t)pairs * 3 * c.img_h * c.img_w * (in_dtype == UFM_U8 ? 1 : 4);
+    const size_t plane = (size_t)c.img_h * c.img_w;
+    float* dcov = c.unc_out_ch > 0 ? reinterpret_cast<float*>(e->buf["covis"].ptr) : nullptr;
+    if (!e->order_after_previous(s)) return 1;
+    if (!e->ck(cudaMemcpyAsync(e->buf["in_src"].ptr, src, in_bytes, cudaMemcpyDeviceToDevice, s), "D2D src")) return 1;
+    if (!e->ck(cudaMemcpyAsync(e->buf["in_tgt"].ptr, tgt, in_bytes, cudaMemcpyDeviceToDevice, s), "D2D tgt")) return 1;
+    if (!e->graph_pass(pairs, in_dtype, in_layout, s)) return 1;
+    if (!e->ck(cudaMemcpyAsync(flow_out, e->buf["out_flow"].ptr, pairs * 2 * plane * 4, cudaMemcpyDeviceToDevice, s), "D2D flow"))
+      return 1;
+    if (covis_out && dcov &&
+        !e->ck(cudaMemcpyAsync(covis_out, dcov, pairs * plane * 4, cudaMemcpyDeviceToDevice, s), "D2D covis"))
+      return 1;
+    return e->mark_done(s) ? 0 : 1;
+  }
+  return e->forward(src, tgt, pairs, in_dtype, in_layout, flow_out, covis_out, s);
 }
 
 int ufm_forward_host(ufm_engine* e, const void* src, const void* tgt, int pairs, int in_dtype, int in_layout,
@@ -1344,39 +1451,7 @@ int ufm_forward_host(ufm_engine* e, const void* src, const void* tgt, int pairs,
     if (!e->order_after_previous(gs)) return 1;  // the staging buffers and the workspace may still be in use elsewhere
     if (!e->ck(cudaMemcpyAsync(dsrc, src, in_bytes, cudaMemcpyHostToDevice, gs), "H2D src")) return 1;
     if (!e->ck(cudaMemcpyAsync(dtgt, tgt, in_bytes, cudaMemcpyHostToDevice, gs), "H2D tgt")) return 1;
-    const std::vector<int> key = {pairs, in_dtype, in_layout, e->keep_aux ? 1 : 0};
-    auto it = e->graphs.find(key);
-    if (it == e->graphs.end()) {
-      // first call with this shape: a plain pass (it also sets the lazily initialised kernel attributes), then the capture
-      if (e->forward(dsrc, dtgt, pairs, in_dtype, in_layout, dflow, dcov, gs)) return 1;
-      if (!e->ck(cudaStreamSynchronize(gs), "sync before capture")) return 1;
-      ufm_engine::GraphEntry ge;
-      cudaGraph_t graph = nullptr;
-      if (!e->ck(cudaStreamBeginCapture(gs, cudaStreamCaptureModeThreadLocal), "begin capture")) return 1;
-      e->capturing = true;
-      const int rc = e->forward(dsrc, dtgt, pairs, in_dtype, in_layout, dflow, dcov, gs);
-      e->capturing = false;
-      const cudaError_t ce = cudaStreamEndCapture(gs, &graph);
-      if (rc || ce != cudaSuccess) {
-        if (graph) cudaGraphDestroy(graph);
-        if (rc) return 1;
-      }
-      if (!e->ck(ce, "end capture")) return 1;
-      const cudaError_t ie = cudaGraphInstantiate(&ge.exec, graph, 0);
-      cudaGraphDestroy(graph);
-      if (!e->ck(ie, "graph instantiate")) return 1;
-      ge.stage = e->stage;
-      ge.launches = e->launches;
-      e->graphs[key] = ge;
-      // the plain pass above already produced this call's results
-    } else {
-      if (!e->ck(cudaGraphLaunch(it->second.exec, gs), "graph launch")) return 1;
-      e->stage = it->second.stage;
-      e->launches = it->second.launches;
-      e->last_pairs = pairs;
-      e->st = gs;
-      if (!e->mark_done(gs)) return 1;
-    }
+    if (!e->graph_pass(pairs, in_dtype, in_layout, gs)) return 1;
     if (!e->ck(cudaMemcpyAsync(flow_out, dflow, pairs * 2 * plane0 * 4, cudaMemcpyDeviceToHost, gs), "D2H flow")) return 1;
     if (covis_out && dcov)
       if (!e->ck(cudaMemcpyAsync(covis_out, dcov, pairs * plane0 * 4, cudaMemcpyDeviceToHost, gs), "D2H covis")) return 1;
@@ -1415,6 +1490,13 @@ int ufm_forward_host(ufm_engine* e, const void* src, const void* tgt, int pairs,
 int ufm_set_keep_aux(ufm_engine* e, int keep) {
   if (!e) return 1;
   e->keep_aux = keep != 0;
+  return 0;
+}
+
+int ufm_set_view_index(ufm_engine* e, int row) {
+  if (!e) return 1;
+  if (row < 0) return e->fail("view index %d < 0", row);
+  e->view_index = row;
   return 0;
 }
 

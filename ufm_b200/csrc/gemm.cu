@@ -627,7 +627,7 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_kernel(const __grid_constant
         tc_fence_after();
 #pragma unroll 1
         for (int c = 0; c < nch; ++c) {
-          uint8_t* buf = wbuf + (R2 ? 0 : (c & 1)) * 4096;
+          uint8_t* buf = wbuf + (c & 1) * 4096;
           uint8_t* rowp = buf + lane * 128;
           // EPI_TMA_MIX: second-pass addressing (8 lanes per slab row, 4 rows per warp instruction); the res2 loads are
           // issued here so that their latency runs under the residual wait, the TMEM read and the first pass
@@ -657,18 +657,14 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_kernel(const __grid_constant
               mbar_wait(&rbar[0], rph0);
               rph0 ^= 1;
             }
-          } else if (!R2 && c >= 2) {
+          } else if (c >= 2) {
             if (lane == 0) bulk_wait_read<1>();
             __syncwarp();
           }
+          const int gcol = c0 + c * 32;
           uint32_t vr[32];
           tmem_ld32(acc_addr + c * 32, vr);
-          if (R2 && c >= 1) {  // single slab: the previous chunk's store must have read it (waits under the TMEM load)
-            if (lane == 0) bulk_wait_read<0>();
-            __syncwarp();
-          }
           tmem_ld_wait();
-          const int gcol = c0 + c * 32;
 #pragma unroll
           for (int j = 0; j < 8; ++j) {
             float4 v = make_float4(__uint_as_float(vr[4 * j]), __uint_as_float(vr[4 * j + 1]),
@@ -748,19 +744,22 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_kernel(const __grid_constant
         tc_fence_after();
 #pragma unroll 1
         for (int c = 0; c < nch; ++c) {
-          uint8_t* buf = wbuf + (R2 ? 0 : (c & 1)) * 4096;
+          uint8_t* buf = wbuf + (c & 1) * 4096;
           uint8_t* rowp = buf + lane * 128;
           const int gcol = c0 + c * 64;
 #pragma unroll
           for (int h2 = 0; h2 < 2; ++h2) {
+            // bias of these 32 columns before the tensor-memory load (see the fp32 path)
+            float4 bq[8];
+            const bool colok = gcol + h2 * 32 < Nl;
+#pragma unroll
+            for (int j = 0; j < 8; ++j)
+              bq[j] = (p.bias && colok) ? __ldg(reinterpret_cast<const float4*>(p.bias + gcol + h2 * 32 + 4 * j))
+                                        : make_float4(0.f, 0.f, 0.f, 0.f);
             uint32_t vr[32];
             tmem_ld32(acc_addr + c * 64 + h2 * 32, vr);
-            if (R2 && c >= 1 && h2 == 0) {  // single slab: the previous chunk's store must have read it
-              if (lane == 0) bulk_wait_read<0>();
-              __syncwarp();
-            }
             tmem_ld_wait();
-            if (gcol + h2 * 32 < Nl) {
+            if (colok) {
 #pragma unroll
               for (int j = 0; j < 4; ++j) {
                 float v[8];
@@ -768,8 +767,7 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_kernel(const __grid_constant
                 for (int i = 0; i < 8; ++i) v[i] = __uint_as_float(vr[8 * j + i]);
                 const int col = gcol + h2 * 32 + 8 * j;
                 if (p.bias) {
-                  const float4 b0 = __ldg(reinterpret_cast<const float4*>(p.bias + col));
-                  const float4 b1 = __ldg(reinterpret_cast<const float4*>(p.bias + col + 4));
+                  const float4 b0 = bq[2 * j], b1 = bq[2 * j + 1];
                   v[0] += b0.x; v[1] += b0.y; v[2] += b0.z; v[3] += b0.w;
                   v[4] += b1.x; v[5] += b1.y; v[6] += b1.z; v[7] += b1.w;
                 }
@@ -1006,7 +1004,7 @@ int gemm_split_mode() { return g_gemm_split; }
 int g_gemm_rows2 = -1;  // ufm_debug_flag 6 / UFM_ROWS2 (tuning)
 void set_gemm_rows2_mode(int v) { g_gemm_rows2 = v; }
 int gemm_rows2_mode() {
-  if (g_gemm_rows2 < 0) g_gemm_rows2 = getenv("UFM_ROWS2") ? atoi(getenv("UFM_ROWS2")) : 3;
+  if (g_gemm_rows2 < 0) g_gemm_rows2 = getenv("UFM_ROWS2") ? atoi(getenv("UFM_ROWS2")) : 0;
   return g_gemm_rows2;
 }
 int g_gemm_warp_shift = 0;  // ufm_debug_flag 7

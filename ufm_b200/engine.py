@@ -8,7 +8,7 @@ from typing import Any, Dict, Optional, Tuple
 import torch
 
 from . import _lib
-from .packing import engine_config, pack_weights
+from .packing import engine_config, pack_weights, view_index_range
 
 _DT = {torch.float32: _lib.UFM_F32, torch.bfloat16: _lib.UFM_BF16, torch.uint8: _lib.UFM_U8}
 _TD = {_lib.UFM_F32: torch.float32, _lib.UFM_BF16: torch.bfloat16}
@@ -44,6 +44,18 @@ class Engine:
             shape = (C.c_int64 * t.dim())(*t.shape)
             self._ck(self.lib.ufm_set_weight(self.h, name.encode(), t.data_ptr(), _DT[t.dtype], shape, t.dim()))
         self._ck(self.lib.ufm_prepare(self.h, max_pairs))
+        self.view_mode, self.view_high = view_index_range(cfg)
+        if self.view_mode == "none" and cfg["info_sharing_str"] != "cross_attention":
+            n_rows = state_dict["info_sharing.view_pos_table"].shape[0]
+            self._ck(self.lib.ufm_set_view_index(self.h, n_rows))  # the appended zero row
+
+    def draw_view_index(self):
+        """use_rand_idx_pe_for_non_reference_views: one draw from torch's global CPU generator per model forward (the model
+        classes call this once per batch, before the per-chunk engine calls), exactly how the reference draws it
+        (global_attention_transformer.py:521-522), so a seeded run reproduces the reference."""
+        if self.view_mode == "rand":
+            row = int(torch.randint(low=1, high=self.view_high, size=(1,)).item())
+            self._ck(self.lib.ufm_set_view_index(self.h, row))
 
     def _ck(self, rc):
         if rc != 0:

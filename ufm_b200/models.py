@@ -244,6 +244,7 @@ class UniFlowMatchModelsBase(nn.Module):
         hw = tuple(img0.shape[1:3] if layout == _lib.UFM_NHWC else img0.shape[2:4])
         eng = self._engine(img0.device, hw)
         eng.set_keep_aux(keep_aux)
+        eng.draw_view_index()
         flows, covs, aux, unc = [], [], [], []
         B = img0.shape[0]
         for s in range(0, B, self.max_pairs_per_call):
@@ -271,6 +272,7 @@ class UniFlowMatchModelsBase(nn.Module):
         hw = tuple(img0.shape[1:3] if layout == _lib.UFM_NHWC else img0.shape[2:4])
         eng = self._engine(self._device(), hw)
         eng.set_keep_aux(False)
+        eng.draw_view_index()
         B = img0.shape[0]
         flow = torch.empty(B, 2, eng.H, eng.W, dtype=torch.float32, pin_memory=True)
         cov = torch.empty(B, eng.H, eng.W, dtype=torch.float32, pin_memory=True) if eng.has_mask else None

@@ -80,6 +80,25 @@ def flow_affine(cfg, H, W, state_dict=None):
     return (std[0] * sx, std[1] * sy), (mean[0] * sx, mean[1] * sy)
 
 
+def view_index_range(cfg: Dict[str, Any]):
+    """How the non-reference view picks its row of ``view_pos_table``: ("fixed", row) or ("rand", high) where the reference
+    draws ``torch.randint(low=1, high=high, size=(1,))`` on every forward (global_attention_transformer.py:520-524,
+    alternating_attention_transformer.py:281-286); ("none", 0) = no positional encoding on the non-reference view."""
+    ik = cfg["info_sharing_kwargs"]
+    kind = cfg["info_sharing_str"]
+    if kind == "global_attention":
+        if ik.get("use_rand_idx_pe_for_non_reference_views", False):
+            return "rand", int(ik["max_num_views"])
+        return "fixed", 1
+    if kind == "alternating_attention":
+        if not ik.get("use_pe_for_non_reference_views", False):
+            return "none", 0
+        if ik.get("use_rand_idx_pe_for_non_reference_views", True):
+            return "rand", int(ik.get("max_num_views_for_pe", 1000))
+        return "fixed", 1
+    return "none", 0  # cross attention: no view table
+
+
 def engine_config(cfg: Dict[str, Any], state_dict=None) -> "_lib.UfmConfig":
     H, W = inference_hw(cfg)
     ek, ik = cfg["encoder_kwargs"], cfg["info_sharing_kwargs"]
@@ -98,8 +117,6 @@ def engine_config(cfg: Dict[str, Any], state_dict=None) -> "_lib.UfmConfig":
             raise NotImplementedError("custom_positional_encoding must be the string 'rope' with global_attention")
         if cpe != "rope":
             raise ValueError(f"Unknown custom positional encoding: {cpe}")  # global_attention_transformer.py:115
-    if ik.get("use_rand_idx_pe_for_non_reference_views") and cfg["info_sharing_str"] == "global_attention":
-        raise NotImplementedError("use_rand_idx_pe_for_non_reference_views draws from the global RNG (SURVEY.md H7)")
     if cfg.get("head_type", "dpt") != "dpt":
         raise NotImplementedError("head_type must be 'dpt'")
     if cfg.get("use_unet_feature") and "classification_head_kwargs" not in cfg:
@@ -300,14 +317,11 @@ def pack_weights(cfg: Dict[str, Any], sd: Dict[str, torch.Tensor]) -> Dict[str, 
                 if ls:
                     out[dst + ".ls1"], out[dst + ".ls2"], out[dst + ".ls3"] = g("ls1.gamma"), g("ls2.gamma"), g("ls3.gamma")
     else:
-        tab = sd[p + "view_pos_table"]
-        vp = torch.zeros(2, d)
-        vp[0] = tab[0]
-        if not ec.info_alternating or ik.get("use_pe_for_non_reference_views", False):
-            if ec.info_alternating and ik.get("use_rand_idx_pe_for_non_reference_views", True):
-                raise NotImplementedError("random view indices (SURVEY.md H7)")
-            vp[1] = tab[1]
-        out["info.viewpos"] = vp
+        # row 0 = the reference view; the other view adds table row `view_index` (1 by default; drawn per forward by the
+        # host when use_rand_idx_pe_for_non_reference_views, see view_index_range / ufm_set_view_index), or nothing at all
+        # (alternating attention without use_pe_for_non_reference_views): the engine then reads the appended zero row
+        tab = sd[p + "view_pos_table"].float()
+        out["info.viewpos"] = torch.cat([tab, torch.zeros(1, d)], dim=0).contiguous()
         for i in range(ec.info_depth):
             block(f"info.{i}", f"{p}self_attention_blocks.{i}.", bool(ec.info_layerscale), bool(ec.info_qk_norm))
     out["info.norm.w"], out["info.norm.b"] = sd[p + "norm.weight"], sd[p + "norm.bias"]
