@@ -69,6 +69,13 @@ typedef struct ufm_config {
   /* (mean, std) of the encoder's data_norm_type (UC/models/encoders/image_normalizations.py:17-35) applied to uint8
    * inputs as (v / 255 - mean) / std (base.py:215-229).  All zero = the "dinov2" constants. */
   float img_mean[3], img_std[3];
+  /* DPTFeature.hooks of the flow head and of the uncertainty head (dpt.py:47,198-219): input stage k of the head reads
+   * entry hooks[k] of [encoder last, info intermediate 0, info intermediate 1, info final].  hooks_set = 0: [0,1,2,3]. */
+  int hooks_set;
+  int dpt_hooks[4], unc_hooks[4];
+  /* register tokens of the hub dinov2_vit*14_reg models (with_registers=True, dinov2.py:24,49): 0 or 4 rows between the cls
+   * row and the patch rows of every image, dropped with cls from the returned features. */
+  int enc_registers;
 } ufm_config;
 
 /* adaptor kinds and their channel counts: mask 1 ('non_occluded_mask'), covariance 3 ('flow_cov'), confidence 1

@@ -30,6 +30,10 @@ GOLDEN_CASES = {
     "tiny_nonorm": dict(cfg="tiny_nonorm", batch=2, out_gain=8.0),
     # random view index for the non-reference view's positional row: torch.manual_seed(rng_seed) right before the call
     "tiny_randidx": dict(cfg="tiny_randidx", batch=2, out_gain=8.0, rng_seed=1234),
+    # DPT heads hooked onto permuted layers (hooks != [0,1,2,3])
+    "tiny_hooks": dict(cfg="tiny_hooks", batch=2, out_gain=8.0),
+    # DINOv2 with 4 register tokens (with_registers=True), Refine model
+    "tiny_reg": dict(cfg="tiny_reg", batch=2, out_gain=8.0),
     # UNet fine-feature branch of UFM-Refine, both combine methods
     "tiny_unet": dict(cfg="tiny_unet", batch=2, out_gain=8.0),
     "tiny_unet_mod": dict(cfg="tiny_unet_mod", batch=1, out_gain=8.0),

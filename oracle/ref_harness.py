@@ -110,13 +110,16 @@ class HubDinoVisionTransformer(nn.Module):
     """``dinov2_vit{s,b,l}14``: img_size 518, patch 14, LayerScale init 1.0, interpolate_offset 0.1,
     interpolate_antialias False, no register tokens."""
 
-    def __init__(self, dim, depth, heads, patch=14, img=518):
+    def __init__(self, dim, depth, heads, patch=14, img=518, num_register_tokens=0):
         super().__init__()
         self.patch_size = patch
         self.embed_dim = dim
-        self.num_register_tokens = 0
-        self.interpolate_offset = 0.1
-        self.interpolate_antialias = False
+        # the *_reg hub entries: 4 register tokens, interpolate_antialias=True, interpolate_offset=0.0 (hub/backbones.py)
+        self.num_register_tokens = num_register_tokens
+        self.interpolate_offset = 0.0 if num_register_tokens else 0.1
+        self.interpolate_antialias = bool(num_register_tokens)
+        if num_register_tokens:
+            self.register_tokens = nn.Parameter(torch.zeros(1, num_register_tokens, dim))
         self.patch_embed = _PatchEmbed(dim, patch)
         n = (img // patch) ** 2
         self.cls_token = nn.Parameter(torch.zeros(1, 1, dim))
@@ -151,14 +154,19 @@ class HubDinoVisionTransformer(nn.Module):
         B, nc, w, h = x.shape
         x = self.patch_embed(x)
         x = torch.cat((self.cls_token.expand(x.shape[0], -1, -1), x), dim=1)
-        return x + self.interpolate_pos_encoding(x, w, h)
+        x = x + self.interpolate_pos_encoding(x, w, h)
+        if self.num_register_tokens:  # registers sit between cls and the patch tokens and carry no positional embedding
+            x = torch.cat((x[:, :1], self.register_tokens.expand(x.shape[0], -1, -1), x[:, 1:]), dim=1)
+        return x
 
     def forward_features(self, x, masks=None):
         x = self.prepare_tokens_with_masks(x)
         for blk in self.blocks:
             x = blk(x)
         x_norm = self.norm(x)
-        return {"x_norm_clstoken": x_norm[:, 0], "x_norm_patchtokens": x_norm[:, 1:], "x_prenorm": x}
+        R = self.num_register_tokens
+        return {"x_norm_clstoken": x_norm[:, 0], "x_norm_regtokens": x_norm[:, 1:R + 1], "x_norm_patchtokens": x_norm[:, R + 1:],
+                "x_prenorm": x}
 
     def get_intermediate_layers(self, x, n=1, reshape=False, return_class_token=False, norm=True):
         xin = x
@@ -173,7 +181,7 @@ class HubDinoVisionTransformer(nn.Module):
         assert len(outs) == len(take)
         if norm:
             outs = [self.norm(o) for o in outs]
-        outs = [o[:, 1:] for o in outs]
+        outs = [o[:, 1 + self.num_register_tokens:] for o in outs]
         if reshape:
             B, _, w, h = xin.shape
             outs = [o.reshape(B, w // self.patch_size, h // self.patch_size, -1).permute(0, 3, 1, 2).contiguous()
@@ -186,6 +194,8 @@ _HUB = {"dinov2_vits14": (384, 12, 6), "dinov2_vitb14": (768, 12, 12), "dinov2_v
 
 def _hub_load(repo, name, **kw):
     assert repo == "facebookresearch/dinov2", repo
+    if name.endswith("_reg"):
+        return HubDinoVisionTransformer(*_HUB[name[:-4]], num_register_tokens=4)
     return HubDinoVisionTransformer(*_HUB[name])
 
 

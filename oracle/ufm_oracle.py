@@ -106,7 +106,7 @@ def block(x, sd, prefix, heads, qk_norm=False, pos=None):
     return x + h
 
 
-def interpolate_pos_embed(pos_embed: torch.Tensor, h0: int, w0: int, offset: float = 0.1) -> torch.Tensor:
+def interpolate_pos_embed(pos_embed: torch.Tensor, h0: int, w0: int, offset: float = 0.1, antialias: bool = False) -> torch.Tensor:
     """Hub DINOv2 ``interpolate_pos_encoding`` (third-party): bicubic,
     ``scale_factor=((n+0.1)/M)``, no antialias.  ``h0, w0`` = patch-grid rows, cols.  Returns (1, 1+h0*w0, D).
     Note the upstream argument naming: its "w" is the image height."""
@@ -117,7 +117,7 @@ def interpolate_pos_embed(pos_embed: torch.Tensor, h0: int, w0: int, offset: flo
         return pos_embed.float()
     pe = pos_embed.float()
     patch = pe[:, 1:].reshape(1, M, M, D).permute(0, 3, 1, 2)
-    patch = F.interpolate(patch, mode="bicubic", antialias=False,
+    patch = F.interpolate(patch, mode="bicubic", antialias=antialias,
                           scale_factor=(float(h0 + offset) / M, float(w0 + offset) / M))
     assert patch.shape[-2:] == (h0, w0)
     patch = patch.permute(0, 2, 3, 1).reshape(1, -1, D)
@@ -140,7 +140,13 @@ def encoder(img: torch.Tensor, sd, cfg) -> List[torch.Tensor]:
     x = F.conv2d(img, sd[p + "patch_embed.proj.weight"], sd[p + "patch_embed.proj.bias"], stride=patch)
     x = x.flatten(2).transpose(1, 2)
     x = torch.cat([sd[p + "cls_token"].expand(B, -1, -1), x], dim=1)
-    x = x + interpolate_pos_embed(sd[p + "pos_embed"], h0, w0)
+    reg = bool(ek.get("with_registers"))  # hub *_reg models: 4 register tokens, antialiased interpolation, offset 0
+    x = x + interpolate_pos_embed(sd[p + "pos_embed"], h0, w0, 0.0 if reg else 0.1, reg)
+    R = 0
+    if reg:
+        rt = sd[p + "register_tokens"]
+        R = rt.shape[1]
+        x = torch.cat([x[:, :1], rt.expand(B, -1, -1), x[:, 1:]], dim=1)
     indices = ek["indices"]
     if isinstance(indices, int):
         take = list(range(depth - indices, depth))
@@ -151,7 +157,7 @@ def encoder(img: torch.Tensor, sd, cfg) -> List[torch.Tensor]:
         x = block(x, sd, f"{p}blocks.{i}.", heads)
         if i in take:
             o = _ln(x, sd, p + "norm.") if ek.get("norm_intermediate", True) else x
-            outs.append(o[:, 1:].reshape(B, h0, w0, dim).permute(0, 3, 1, 2).contiguous())
+            outs.append(o[:, 1 + R:].reshape(B, h0, w0, dim).permute(0, 3, 1, 2).contiguous())
     return outs
 
 
@@ -283,8 +289,10 @@ def _fusion(sd, prefix, path, skip=None):
     return F.conv2d(out, sd[prefix + "out_conv.weight"], sd[prefix + "out_conv.bias"])
 
 
-def dpt_feature(feats: List[torch.Tensor], sd, prefix) -> torch.Tensor:
-    """``DPTFeature.forward`` (UC/models/prediction_heads/dpt.py:180-232) with ``init`` layers (:94-178)."""
+def dpt_feature(feats: List[torch.Tensor], sd, prefix, hooks=(0, 1, 2, 3)) -> torch.Tensor:
+    """``DPTFeature.forward`` (UC/models/prediction_heads/dpt.py:180-232) with ``init`` layers (:94-178); input stage k
+    reads ``list_features[hooks[k]]`` (:198-205)."""
+    feats = [feats[h] for h in hooks]
     ip = prefix + "input_process."
     l0 = F.conv2d(feats[0], sd[ip + "0.0.0.weight"], sd[ip + "0.0.0.bias"])
     l0 = F.conv_transpose2d(l0, sd[ip + "0.0.1.weight"], sd[ip + "0.0.1.bias"], stride=4)
@@ -520,12 +528,13 @@ def forward_stages(img1: torch.Tensor, img2: torch.Tensor, sd, cfg, stop_after: 
     if stop_after == "info":
         return st
     head_in = [f1, inter[0][0], inter[1][0], final[0]]  # ufm.py:602-608, view 1 only
-    st["dpt1"] = dpt_feature(head_in, sd, "head1.0.0.")
+    hooks = lambda k: tuple((cfg.get(k) or {}).get("dpt_feature", {}).get("hooks", (0, 1, 2, 3)))
+    st["dpt1"] = dpt_feature(head_in, sd, "head1.0.0.", hooks("feature_head_kwargs"))
     st["head1_raw"] = dpt_processor(st["dpt1"], sd, "head1.0.1.", (H, W))
     a1 = run_adaptors(st["head1_raw"], cfg["adaptors_kwargs"], (H, W), sd)
     st["flow_reg"] = a1["flow"]
     if cfg.get("uncertainty_head_kwargs"):
-        st["dptu"] = dpt_feature(head_in, sd, "uncertainty_head.0.0.")
+        st["dptu"] = dpt_feature(head_in, sd, "uncertainty_head.0.0.", hooks("uncertainty_head_kwargs"))
         st["headu_raw"] = dpt_processor(st["dptu"], sd, "uncertainty_head.0.1.", (H, W))
         au = run_adaptors(st["headu_raw"], cfg["uncertainty_adaptors_kwargs"], (H, W))
         if "non_occluded_mask" in au:

@@ -110,7 +110,7 @@ def _report(tag, rows):
         print(f"  {k:14s} rel-L2 {r:.3e}  max-abs {m:.3e}  (ref max {s:.3e})")
 
 
-@pytest.mark.parametrize("name", ["tiny_base", "tiny_refine", "tiny_alt_qknorm", "tiny_cross", "tiny_unet", "tiny_unet_mod", "tiny_rope", "tiny_coord", "tiny_cross_raw", "tiny_bn", "tiny_nonorm", "tiny_randidx"])
+@pytest.mark.parametrize("name", ["tiny_base", "tiny_refine", "tiny_alt_qknorm", "tiny_cross", "tiny_unet", "tiny_unet_mod", "tiny_rope", "tiny_coord", "tiny_cross_raw", "tiny_bn", "tiny_nonorm", "tiny_randidx", "tiny_hooks", "tiny_reg"])
 def test_tiny_stagewise_vs_oracle(name):
     model, cfg, sd = _model(name)
     W, H = cfg["inference_resolution"]

@@ -42,6 +42,8 @@ class UfmConfig(C.Structure):
         ("flow_coord", C.c_int),
         ("enc_norm_intermediate", C.c_int), ("info_norm_intermediate", C.c_int),
         ("img_mean", C.c_float * 3), ("img_std", C.c_float * 3),
+        ("hooks_set", C.c_int), ("dpt_hooks", C.c_int * 4), ("unc_hooks", C.c_int * 4),
+        ("enc_registers", C.c_int),
     ]
 
 

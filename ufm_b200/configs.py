@@ -156,6 +156,23 @@ def _randidx(cfg):
     return cfg
 
 
+def _hooks(cfg):
+    """DPT heads hooked onto permuted layers (dpt.py:47,198-219): the flow head reads [inter0, enc_last, final, inter1], the
+    uncertainty head [final, inter1, inter0, enc_last]; input_feature_dims follow the selected features."""
+    for key, hooks in (("feature_head_kwargs", [1, 0, 3, 2]), ("uncertainty_head_kwargs", [3, 2, 1, 0])):
+        f = cfg[key]["dpt_feature"]
+        dims = [f["input_feature_dims"][0]] + [f["input_feature_dims"][1]] * 3  # dims of [enc_last, inter0, inter1, final]
+        f["hooks"] = hooks
+        f["input_feature_dims"] = [dims[h] for h in hooks]
+    return cfg
+
+
+def _registers(cfg):
+    """DINOv2 with register tokens (with_registers=True -> hub dinov2_vit*14_reg, dinov2.py:24,49,74-79)."""
+    cfg["encoder_kwargs"].update({"with_registers": True, "name": "dinov2_small_reg"})
+    return cfg
+
+
 def _coord(cfg):
     """FlowAdaptor predicting the landing position (output_normalized_coordinate, adaptors.py:110-118)."""
     cfg["adaptors_kwargs"]["flow"]["kwargs"]["output_normalized_coordinate"] = True
@@ -176,6 +193,8 @@ CONFIGS = {
     "tiny_coord": lambda: _coord(tiny(True)),
     "tiny_nonorm": lambda: _nonorm(tiny(True)),
     "tiny_randidx": lambda: _randidx(tiny(False)),
+    "tiny_hooks": lambda: _hooks(tiny(False)),
+    "tiny_reg": lambda: _registers(tiny(True)),
     "tiny_unet": lambda: tiny(True, unet="conv"),
     "tiny_unet_mod": lambda: tiny(True, unet="modulate"),
     "ufm_refine_unet": lambda: dict(ufm_refine_assumed(), use_unet_feature=True, feature_combine_method="conv"),

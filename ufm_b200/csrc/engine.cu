@@ -731,10 +731,15 @@ bool ufm_engine::dpt_head(const std::string& hp, int Bp, int out_ch, bool sigmoi
   const int D = c.enc_dim, d = c.info_dim, fd = c.dpt_feature_dim, hid = c.dpt_hidden;
   const int* ld = c.dpt_layer_dims;
   const int h3 = (hpn - 1) / 2 + 1, w3 = (wpn - 1) / 2 + 1;
-  const bf16* F0 = B<bf16>("enc_last");
-  const bf16* F1 = B<bf16>("inter0");
-  const bf16* F2 = B<bf16>("inter1");
-  const bf16* F3 = B<bf16>("final");
+  // DPTFeature.hooks (dpt.py:198-205): input stage k reads entry hooks[k] of [enc_last, inter0, inter1, final]
+  const bf16* feats[4] = {B<bf16>("enc_last"), B<bf16>("inter0"), B<bf16>("inter1"), B<bf16>("final")};
+  const int fdim[4] = {D, d, d, d};
+  const int* hooks = hp == "hu" ? c.unc_hooks : c.dpt_hooks;
+  int hk[4] = {0, 1, 2, 3};
+  if (c.hooks_set)
+    for (int k = 0; k < 4; ++k) hk[k] = hooks[k];
+  const bf16 *F0 = feats[hk[0]], *F1 = feats[hk[1]], *F2 = feats[hk[2]], *F3 = feats[hk[3]];
+  const int C0 = fdim[hk[0]], C1 = fdim[hk[1]], C2 = fdim[hk[2]], C3 = fdim[hk[3]];
   auto tok_view = [&](const bf16* p, int C) { return AView{p, C, n, 1, Bp, C, (long long)n * C, 2LL * n * C, 128, 1}; };
   bf16* G = B<bf16>("G");
   bf16 *T0 = B<bf16>("T0"), *T1 = B<bf16>("T1"), *T2 = B<bf16>("T2"), *T3 = B<bf16>("T3"), *T3c = B<bf16>("T3col"),
@@ -747,8 +752,8 @@ bool ufm_engine::dpt_head(const std::string& hp, int Bp, int out_ch, bool sigmoi
   {
     Epi e;
     e.bias = Wf(hp + ".in0.b"); e.out_bf16 = G; e.sx = 16LL * ld[0]; e.sn = (long long)n * e.sx;
-    flops_override = 2.0 * Bp * n * ((double)D * ld[0] + 16.0 * ld[0] * ld[0]);  // reference: 1x1 then ConvT 4x4/s4
-    if (!gemm(tok_view(F0, D), hp + ".in0.w", 1, e)) return false;
+    flops_override = 2.0 * Bp * n * ((double)C0 * ld[0] + 16.0 * ld[0] * ld[0]);  // reference: 1x1 then ConvT 4x4/s4
+    if (!gemm(tok_view(F0, C0), hp + ".in0.w", 1, e)) return false;
     if (!run(UFM_CAT_MOVE, 0.0, 4.0 * Bp * n * 16 * ld[0], "shuffle0",
              [&] { return launch_shuffle_bf16(G, T0, Bp, hpn, wpn, 4, ld[0], st); }))
       return false;
@@ -758,8 +763,8 @@ bool ufm_engine::dpt_head(const std::string& hp, int Bp, int out_ch, bool sigmoi
   {
     Epi e;
     e.bias = Wf(hp + ".in1.b"); e.out_bf16 = G; e.sx = 4LL * ld[1]; e.sn = (long long)n * e.sx;
-    flops_override = 2.0 * Bp * n * ((double)d * ld[1] + 4.0 * ld[1] * ld[1]);  // reference: 1x1 then ConvT 2x2/s2
-    if (!gemm(tok_view(F1, d), hp + ".in1.w", 1, e)) return false;
+    flops_override = 2.0 * Bp * n * ((double)C1 * ld[1] + 4.0 * ld[1] * ld[1]);  // reference: 1x1 then ConvT 2x2/s2
+    if (!gemm(tok_view(F1, C1), hp + ".in1.w", 1, e)) return false;
     if (!run(UFM_CAT_MOVE, 0.0, 4.0 * Bp * n * 4 * ld[1], "shuffle1",
              [&] { return launch_shuffle_bf16(G, T1, Bp, hpn, wpn, 2, ld[1], st); }))
       return false;
@@ -769,14 +774,14 @@ bool ufm_engine::dpt_head(const std::string& hp, int Bp, int out_ch, bool sigmoi
   {
     Epi e;
     e.bias = Wf(hp + ".in2.b"); e.out_bf16 = T2; e.sx = ld[2]; e.sn = (long long)n * e.sx;
-    if (!gemm(tok_view(F2, d), hp + ".in2.w", 1, e)) return false;
+    if (!gemm(tok_view(F2, C2), hp + ".in2.w", 1, e)) return false;
     if (!conv3(T2, Bp, LH[2], LW[2], ld[2], hp + ".rn2.w", nullptr, nullptr, nullptr, Lf[2], Lr[2], true)) return false;
   }
   // input_process.3: 1x1, 3x3 stride 2 (as im2col + GEMM) (dpt.py:157-172)
   {
     Epi e;
     e.bias = Wf(hp + ".in3a.b"); e.out_bf16 = T3; e.sx = ld[3]; e.sn = (long long)n * e.sx;
-    if (!gemm(tok_view(F3, d), hp + ".in3a.w", 1, e)) return false;
+    if (!gemm(tok_view(F3, C3), hp + ".in3a.w", 1, e)) return false;
     if (!run(UFM_CAT_MOVE, 0.0, 2.0 * Bp * ld[3] * (n + 9.0 * h3 * w3), "im2col_s2",
              [&] { return launch_im2col_s2(T3, T3c, Bp, hpn, wpn, ld[3], h3, w3, st); }))
       return false;
@@ -979,7 +984,8 @@ int ufm_engine::forward_impl(const void* src, const void* tgt, int pairs, int in
   stage.clear();
   const ufm_config& c = cfg;
   const int Bp = pairs;
-  const int hpn = c.img_h / c.patch, wpn = c.img_w / c.patch, n = hpn * wpn, S = n + 1;
+  const int R1 = 1 + c.enc_registers;  // rows in front of the patch tokens of every image: cls (+ register tokens)
+  const int hpn = c.img_h / c.patch, wpn = c.img_w / c.patch, n = hpn * wpn, S = n + R1;
   const int D = c.enc_dim, d = c.info_dim;
   const int Kpad = (int)w["enc.patch.w"].shape[1];
   const long long Me = 2LL * Bp * S, Mi = 2LL * Bp * n;
@@ -1007,12 +1013,12 @@ int ufm_engine::forward_impl(const void* src, const void* tgt, int pairs, int in
     const float* pos = Wf("enc.pos");
     if (!e.bias || !pos) return 1;
     e.res2 = pos + D; e.r2x = D; e.r2n = 0; e.r2y = 0;
-    e.out_f32 = x; e.sx = D; e.sn = (long long)S * D; e.out_off = D;
+    e.out_f32 = x; e.sx = D; e.sn = (long long)S * D; e.out_off = (long long)R1 * D;
     AView a{B<bf16>("Apatch"), Kpad, n, 1, 2 * Bp, Kpad, (long long)n * Kpad, (long long)n * Kpad, 128, 1};
     flops_override = 2.0 * 2 * Bp * n * (double)D * 3 * c.patch * c.patch;  // K = 588, not the padded 640
     if (!gemm(a, "enc.patch.w", 1, e)) return 1;
-    if (!run(UFM_CAT_MOVE, 0.0, 2.0 * Bp * D * 4, "cls_rows",
-             [&] { return launch_cls_rows(x, Wf("enc.cls"), pos, 2 * Bp, S, D, st); }))
+    if (!run(UFM_CAT_MOVE, 0.0, 2.0 * Bp * R1 * D * 4, "cls_rows",
+             [&] { return launch_cls_rows(x, Wf("enc.cls"), R1, 2 * Bp, S, D, st); }))
       return 1;
   }
   bf16* enc_last = B<bf16>("enc_last");
@@ -1021,11 +1027,11 @@ int ufm_engine::forward_impl(const void* src, const void* tgt, int pairs, int in
     if (!block("enc." + std::to_string(i), x, 2 * Bp, S, D, c.enc_heads, 4 * D, false)) return 1;
     if (c.refine && i == c.enc_take_first) {
       // final norm, drop cls, (view,b) -> (b,view) order, into the left D columns of the classification-head input
-      if (!layernorm(x, 2 * Bp, S, 1, n, D, "enc.norm", Bp, B<bf16>("Xcls"), c.cls_in, 0, nullptr, 0, 0, enc_raw)) return 1;
+      if (!layernorm(x, 2 * Bp, S, R1, n, D, "enc.norm", Bp, B<bf16>("Xcls"), c.cls_in, 0, nullptr, 0, 0, enc_raw)) return 1;
       set_stage("enc_first", B<bf16>("Xcls"), UFM_BF16, {Bp, 2, n, c.cls_in});
     }
     if (i == c.enc_take_last) {
-      if (!layernorm(x, 2 * Bp, S, 1, n, D, "enc.norm", Bp, enc_last, D, 0, nullptr, 0, 0, enc_raw)) return 1;
+      if (!layernorm(x, 2 * Bp, S, R1, n, D, "enc.norm", Bp, enc_last, D, 0, nullptr, 0, 0, enc_raw)) return 1;
       set_stage("enc_last", enc_last, UFM_BF16, {Bp, 2, n, D});
     }
   }
@@ -1307,7 +1313,7 @@ int ufm_prepare(ufm_engine* e, int max_pairs) {
   e->prepared = false;
   const ufm_config& c = e->cfg;
   const long long Bp = max_pairs;
-  const long long hpn = c.img_h / c.patch, wpn = c.img_w / c.patch, n = hpn * wpn, S = n + 1;
+  const long long hpn = c.img_h / c.patch, wpn = c.img_w / c.patch, n = hpn * wpn, S = n + 1 + c.enc_registers;
   const long long D = c.enc_dim, d = c.info_dim, fd = c.dpt_feature_dim, hid = c.dpt_hidden;
   const long long Me = 2 * Bp * S, Mi = 2 * Bp * n;
   if (!e->W("enc.patch.w")) return 1;

@@ -166,7 +166,7 @@ struct PatchParams {
 cudaError_t launch_patch_im2col(const PatchParams& p, cudaStream_t stream);
 
 // x[img, 0, :] = cls + pos[0]   (fp32 residual stream, seq_len = 1 + tokens)
-cudaError_t launch_cls_rows(float* x, const float* cls, const float* pos, int n_img, int seq_len, int D, cudaStream_t s);
+cudaError_t launch_cls_rows(float* x, const float* prefix, int n_prefix, int n_img, int seq_len, int D, cudaStream_t s);
 
 // Pixel shuffle of a GEMM result: in[(n, y, x), (i, j, c)] -> out[n, y*k+i, x*k+j, c]   (ConvTranspose k==s and
 // F.pixel_shuffle; the (i,j,c) column order is produced by host-side weight row permutation)

@@ -203,12 +203,15 @@ __global__ void __launch_bounds__(256) patch_im2col_kernel(const PatchParams p) 
       make_uint4(pack_bf16(f[0], f[1]), pack_bf16(f[2], f[3]), pack_bf16(f[4], f[5]), pack_bf16(f[6], f[7]));
 }
 
-__global__ void cls_rows_kernel(float* x, const float* cls, const float* pos, int n_img, int seq_len, int D) {
+// rows in front of the patch tokens of every image: `prefix` [n_prefix, D] = (cls + its positional row), then the register
+// tokens of the hub *_reg models (no positional embedding), precomputed at pack time
+__global__ void cls_rows_kernel(float* x, const float* prefix, int n_prefix, int n_img, int seq_len, int D) {
   pdl_wait();
   const int idx = blockIdx.x * blockDim.x + threadIdx.x;
-  if (idx >= n_img * D) return;
-  const int img = idx / D, d = idx - img * D;
-  x[(long long)img * seq_len * D + d] = cls[d] + pos[d];
+  const int per = n_prefix * D;
+  if (idx >= n_img * per) return;
+  const int img = idx / per, r = idx - img * per;
+  x[(long long)img * seq_len * D + r] = prefix[r];
 }
 
 // ------------------------------------------------------------------------------------------------ pixel shuffle
@@ -645,8 +648,8 @@ cudaError_t launch_patch_im2col(const PatchParams& p, cudaStream_t stream) {
   return cudaGetLastError();
 }
 
-cudaError_t launch_cls_rows(float* x, const float* cls, const float* pos, int n_img, int seq_len, int D, cudaStream_t s) {
-  launch_k(cls_rows_kernel, blocks_for((long long)n_img * D, 256), 256, 0, s, x, cls, pos, n_img, seq_len, D);
+cudaError_t launch_cls_rows(float* x, const float* prefix, int n_prefix, int n_img, int seq_len, int D, cudaStream_t s) {
+  launch_k(cls_rows_kernel, blocks_for((long long)n_img * n_prefix * D, 256), 256, 0, s, x, prefix, n_prefix, n_img, seq_len, D);
   return cudaGetLastError();
 }
 

@@ -102,8 +102,8 @@ def view_index_range(cfg: Dict[str, Any]):
 def engine_config(cfg: Dict[str, Any], state_dict=None) -> "_lib.UfmConfig":
     H, W = inference_hw(cfg)
     ek, ik = cfg["encoder_kwargs"], cfg["info_sharing_kwargs"]
-    if cfg.get("encoder_str", "dinov2") != "dinov2" or ek.get("with_registers"):
-        raise NotImplementedError("engine encoder is DINOv2 ViT-S/B/L without registers")
+    if cfg.get("encoder_str", "dinov2") != "dinov2":
+        raise NotImplementedError("engine encoder is DINOv2 ViT-S/B/L (with or without registers)")
     if cfg["info_sharing_str"] not in ("global_attention", "alternating_attention", "cross_attention"):
         raise NotImplementedError(f"info_sharing_str={cfg['info_sharing_str']}")
     if cfg["info_sharing_str"] == "cross_attention":
@@ -141,6 +141,7 @@ def engine_config(cfg: Dict[str, Any], state_dict=None) -> "_lib.UfmConfig":
     c.info_rope = int(cpe == "rope")
     c.info_layerscale = int(bool(ik.get("init_values")))
     c.info_has_proj = 1
+    c.enc_registers = 4 if ek.get("with_registers") else 0                    # hub dinov2_vit*14_reg (dinov2.py:24,49,74-79)
     c.enc_norm_intermediate = int(bool(ek.get("norm_intermediate", True)))    # dinov2.py:259-261
     c.info_norm_intermediate = int(bool(ik.get("norm_intermediate", True)))   # global_attention_transformer.py:549
     from .prepost import IMAGE_NORMALIZATION
@@ -153,8 +154,20 @@ def engine_config(cfg: Dict[str, Any], state_dict=None) -> "_lib.UfmConfig":
         c.img_mean[i], c.img_std[i] = float(mean[i]), float(std[i])
     f = cfg["feature_head_kwargs"]["dpt_feature"]
     pr = cfg["feature_head_kwargs"]["dpt_processor"]
-    if list(f.get("hooks", [0, 1, 2, 3])) != [0, 1, 2, 3]:
-        raise NotImplementedError("DPT hooks != [0,1,2,3]")
+    # DPTFeature.hooks (dpt.py:47,198-219): input stage k reads list_features[hooks[k]] of [enc_last, inter0, inter1, final]
+    feat_dims = [dim, ik["dim"], ik["dim"], ik["dim"]]
+    c.hooks_set = 1
+    for name, dst in (("feature_head_kwargs", c.dpt_hooks), ("uncertainty_head_kwargs", c.unc_hooks)):
+        hk = (cfg.get(name) or {}).get("dpt_feature", {})
+        hooks = list(hk.get("hooks", [0, 1, 2, 3]))
+        if len(hooks) != 4 or any(h not in (0, 1, 2, 3) for h in hooks):
+            raise ValueError(f"{name}.dpt_feature.hooks={hooks}: four indices into the 4 layered features (dpt.py:198-205)")
+        want = [feat_dims[h] for h in hooks]
+        if hk and list(hk.get("input_feature_dims", want)) != want:
+            raise AssertionError(f"Input feature dimension mismatch at hook: hooks {hooks} select dims {want}, "
+                                 f"input_feature_dims is {hk.get('input_feature_dims')}")  # dpt.py:199-202
+        for k in range(4):
+            dst[k] = hooks[k]
     for i in range(4):
         c.dpt_layer_dims[i] = f["layer_dims"][i]
     c.dpt_feature_dim = f["feature_dim"]
@@ -202,7 +215,7 @@ def engine_config(cfg: Dict[str, Any], state_dict=None) -> "_lib.UfmConfig":
     return c
 
 
-def interpolate_pos_embed(pos_embed: torch.Tensor, h0: int, w0: int, offset: float = 0.1) -> torch.Tensor:
+def interpolate_pos_embed(pos_embed: torch.Tensor, h0: int, w0: int, offset: float = 0.1, antialias: bool = False) -> torch.Tensor:
     """Hub DINOv2 ``interpolate_pos_encoding``: bicubic, scale_factor=(n+0.1)/M, no antialias -> (1+h0*w0, D)."""
     N = pos_embed.shape[1] - 1
     M = int(math.sqrt(N))
@@ -211,7 +224,7 @@ def interpolate_pos_embed(pos_embed: torch.Tensor, h0: int, w0: int, offset: flo
     if h0 * w0 == N and h0 == w0:
         return pe[0]
     patch = pe[:, 1:].reshape(1, M, M, D).permute(0, 3, 1, 2)
-    patch = F.interpolate(patch, mode="bicubic", antialias=False,
+    patch = F.interpolate(patch, mode="bicubic", antialias=antialias,
                           scale_factor=(float(h0 + offset) / M, float(w0 + offset) / M))
     assert patch.shape[-2:] == (h0, w0)
     return torch.cat([pe[0, :1], patch.permute(0, 2, 3, 1).reshape(-1, D)], dim=0)
@@ -255,8 +268,13 @@ def pack_weights(cfg: Dict[str, Any], sd: Dict[str, torch.Tensor]) -> Dict[str, 
     wpad[:, : wpe.shape[1]] = wpe
     out["enc.patch.w"] = bf(wpad)
     out["enc.patch.b"] = sd[p + "patch_embed.proj.bias"]
-    out["enc.pos"] = interpolate_pos_embed(sd[p + "pos_embed"], hp, wp)
-    out["enc.cls"] = sd[p + "cls_token"].reshape(-1)
+    reg = ec.enc_registers > 0  # hub *_reg models interpolate with antialias and without the 0.1 offset
+    out["enc.pos"] = interpolate_pos_embed(sd[p + "pos_embed"], hp, wp, 0.0 if reg else 0.1, reg)
+    # the rows in front of the patch tokens: cls + its positional row, then the register tokens (no positional embedding)
+    prefix = [sd[p + "cls_token"].reshape(1, -1).float() + out["enc.pos"][:1]]
+    if reg:
+        prefix.append(sd[p + "register_tokens"].reshape(-1, D).float())
+    out["enc.cls"] = torch.cat(prefix, dim=0).contiguous()
 
     def block(dst, src, layerscale, qk_norm):
         out[dst + ".ln1.w"], out[dst + ".ln1.b"] = sd[src + "norm1.weight"], sd[src + "norm1.bias"]

@@ -64,6 +64,8 @@ def encoder_spec(cfg: Dict[str, Any]) -> Spec:
         (p + "patch_embed.proj.weight", (dim, 3, patch, patch), "w"),
         (p + "patch_embed.proj.bias", (dim,), "b"),
     ]
+    if ek.get("with_registers"):
+        s.append((p + "register_tokens", (1, 4, dim), "cls"))
     for i in range(depth):
         s += _block_spec(f"{p}blocks.{i}.", dim, 4 * dim, True, False, dim // heads)
     s += [(p + "norm.weight", (dim,), "ln_w"), (p + "norm.bias", (dim,), "ln_b")]
