@@ -37,7 +37,7 @@ def _worker(rank, world, port, B, q):
             o = m.predict_correspondences_batched(s.to(dev), t.to(dev))
             return o.flow.flow_output, o.covisibility.mask
 
-        flow, cov = predict_sharded(predict, src, tgt, gather=True)
+        flow, cov = predict_sharded(predict, src, tgt, gather=True)  # host tensors in: rank 1's shard is empty for B = 1
         one_f, one_c = predict(src, tgt)  # the whole batch on this GPU alone
         torch.cuda.synchronize()
         q.put((rank, bool(torch.equal(flow, one_f) and torch.equal(cov, one_c) and flow.shape[0] == B)))
@@ -46,7 +46,7 @@ def _worker(rank, world, port, B, q):
 
 
 @pytest.mark.skipif(not torch.cuda.is_available() or torch.cuda.device_count() < 2, reason="needs two GPUs")
-@pytest.mark.parametrize("B", [6, 5])
+@pytest.mark.parametrize("B", [6, 5, 1])
 def test_predict_sharded_two_gpus_bit_identical(B):
     import torch.multiprocessing as mp
 

@@ -72,7 +72,14 @@ def predict_sharded(predict: Callable[[torch.Tensor, torch.Tensor], Tuple[torch.
         meta = [(tuple(flow.shape[1:]), flow.dtype, None if cov is None else tuple(cov.shape[1:]))]
     dist.broadcast_object_list(meta, src=dist.get_global_rank(group, 0) if group is not None else 0, group=group)
     fshape, dtype, cshape = meta[0]
-    dev = source.device if flow is None else flow.device
+    if flow is not None:
+        dev = flow.device
+    elif dist.get_backend(group) == "nccl":
+        # an empty shard (B < world size) still joins the collective: NCCL needs its buffers on this rank's GPU even when
+        # the inputs are host tensors
+        dev = torch.device("cuda", torch.cuda.current_device())
+    else:
+        dev = source.device
     if flow is None:
         flow = torch.zeros((0,) + fshape, dtype=dtype, device=dev)
         cov = None if cshape is None else torch.zeros((0,) + cshape, dtype=dtype, device=dev)
