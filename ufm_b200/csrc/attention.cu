@@ -608,4 +608,6 @@ cudaError_t launch_attention(const AttnParams& p_in, cudaStream_t stream) {
   return cudaGetLastError();
 }
 
+UFM_DEFINE_PDL_EARLY_SETTER(attention)
+
 }  // namespace ufm

@@ -323,6 +323,26 @@ struct ufm_engine {
   }
   int forward_impl(const void* src, const void* tgt, int pairs, int in_dtype, int in_layout, float* flow_out,
                    float* covis_out, cudaStream_t stream);
+  // early programmatic-launch trigger for launch-latency-bound passes only (<= 2 pairs; launch.cuh).  The flag is a
+  // constant per translation unit and per device; it is read when a kernel executes, so it is (re)set in stream order in
+  // front of every pass or graph replay whose batch size asks for the other value.
+  bool set_pdl_early(int pairs, cudaStream_t s) {
+    static int cur[64];
+    static bool init = false;
+    if (!init) {
+      for (int& v : cur) v = -1;
+      init = true;
+    }
+    if (capturing || device >= 64) return true;
+    const int want = (pairs <= 2 && !getenv("UFM_NO_PDL_EARLY")) ? 1 : 0;
+    if (cur[device] == want) return true;
+    if (!ck(ufm_set_pdl_early_gemm(want, s), "pdl flag") || !ck(ufm_set_pdl_early_attention(want, s), "pdl flag") ||
+        !ck(ufm_set_pdl_early_simt(want, s), "pdl flag") || !ck(ufm_set_pdl_early_prepost(want, s), "pdl flag") ||
+        !ck(ufm_set_pdl_early_unet(want, s), "pdl flag"))
+      return false;
+    cur[device] = want;
+    return true;
+  }
   // NVTX ranges per stage of the pass (UFM_NVTX=1): "ufm_forward" > encoder / info_sharing / flow_head / uncertainty_head /
   // classification_head / unet_branch / local_refinement.  The tracing aid the reference has for this path is the
   // CUDA-event decorator of UC/models/encoders/utils.py:11-86; ufm_set_profile gives its per-kernel-family equivalent and
@@ -402,6 +422,7 @@ struct ufm_engine {
       graphs[key] = ge;
       return true;
     }
+    if (!set_pdl_early(pairs, s)) return false;
     if (!ck(cudaGraphLaunch(it->second.exec, s), "graph launch")) return false;
     stage = it->second.stage;
     launches = it->second.launches;
@@ -962,6 +983,7 @@ bool ufm_engine::unet_branch(const void* src, const void* tgt, int in_dtype, int
 int ufm_engine::forward(const void* src, const void* tgt, int pairs, int in_dtype, int in_layout, float* flow_out,
                         float* covis_out, cudaStream_t stream) {
   if (!order_after_previous(stream)) return 1;
+  if (!set_pdl_early(pairs, stream)) return 1;
   if (nvtx) {
     nvtxRangePushA("ufm_forward");
     nvtx_depth = 1;

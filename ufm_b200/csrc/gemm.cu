@@ -1046,4 +1046,6 @@ cudaError_t launch_gemm(const GemmParams& p, int BN, int num_sms, cudaStream_t s
   return cudaErrorInvalidValue;
 }
 
+UFM_DEFINE_PDL_EARLY_SETTER(gemm)
+
 }  // namespace ufm

@@ -258,4 +258,11 @@ cudaError_t launch_unet_combine(const UnetCombineParams& p, cudaStream_t s);
 // NHWC fp32 [n,H,W,C] -> NCHW fp32 (stage dumps / descriptor export)
 cudaError_t launch_nhwc_to_nchw(const float* in, float* out, int n, int H, int W, int C, cudaStream_t s);
 
+// early programmatic-launch trigger (launch.cuh), one constant per translation unit
+cudaError_t ufm_set_pdl_early_gemm(int v, cudaStream_t s);
+cudaError_t ufm_set_pdl_early_attention(int v, cudaStream_t s);
+cudaError_t ufm_set_pdl_early_simt(int v, cudaStream_t s);
+cudaError_t ufm_set_pdl_early_prepost(int v, cudaStream_t s);
+cudaError_t ufm_set_pdl_early_unet(int v, cudaStream_t s);
+
 }  // namespace ufm

@@ -255,4 +255,6 @@ cudaError_t launch_unc_adaptors(const UncAdaptParams& p, cudaStream_t s) {
   return cudaGetLastError();
 }
 
+UFM_DEFINE_PDL_EARLY_SETTER(prepost)
+
 }  // namespace ufm

@@ -721,4 +721,6 @@ cudaError_t launch_nhwc_to_nchw(const float* in, float* out, int n, int H, int W
   return cudaGetLastError();
 }
 
+UFM_DEFINE_PDL_EARLY_SETTER(simt)
+
 }  // namespace ufm

@@ -451,4 +451,6 @@ cudaError_t launch_unet_combine(const UnetCombineParams& p, cudaStream_t s) {
   return cudaGetLastError();
 }
 
+UFM_DEFINE_PDL_EARLY_SETTER(unet)
+
 }  // namespace ufm
