@@ -200,6 +200,26 @@ int ufm_op_unmap(const float* flow, const float* cov, int B, int H, int W, int H
 int ufm_op_refine(const void* desc, int B, int H, int W, const float* flow_in, const float* bias25,
                   float inv_temperature, float* flow_out, float* residual, float* log_softmax, void* stream);
 
+
+/* 3x3 convolution, stride 2, padding 1 (the im2col_s2_kernel + gemm_kernel pair of the DPT head's last input stage) that
+ * ALLOCATES NOTHING: no cudaMalloc / cudaFree and no allocating library routine on any call, so it may be used under CUDA
+ * graph capture, from a serving loop or from a harness that forbids allocation.  It has no counterpart in the reference.
+ * The im2col operand, which ufm_op_im2col_s2 + ufm_op_gemm keep in a
+ * caller-allocated buffer, lives in a file-scope `static __device__` array of UFM_CONV3X3_S2_STATIC_MAX_BYTES that every
+ * GPU loading the library holds until the process exits (with CUDA's lazy module loading the 16 MiB appear at the
+ * first call on a device, which is also when the array's device address is taken; later calls change nothing).
+ *   in      : bf16 [n, h, w, C] (NHWC), C a multiple of 64
+ *   wt      : bf16 [n_out, 9 * C], taps row-major (ky, kx) then channels (the conv weight permuted to [n_out, 3, 3, C])
+ *   bias    : fp32 [n_out] or NULL
+ *   out_f32 : fp32 [n, (h-1)/2+1, (w-1)/2+1, n_out]
+ * Works on the CURRENT device (all pointers must belong to it), asynchronous on `stream`.  Returns 2 with a message in
+ * `err` when n * oh * ow * 9 * C * 2 bytes exceed the maximum, 1 on any other error.  All calls on one GPU share the
+ * array: calls that overlap on the GPU (different streams, no ordering between them) race on it; calls on one stream
+ * are safe.  Every element a call reads was written by that call, so nothing is carried over from the previous one. */
+#define UFM_CONV3X3_S2_STATIC_MAX_BYTES (16u << 20)
+int ufm_op_conv3x3_s2_static(const void* in, int n, int h, int w, int C, const void* wt, int n_out, const float* bias,
+                             float* out_f32, void* stream, char* err, int errlen);
+
 #ifdef __cplusplus
 }
 #endif

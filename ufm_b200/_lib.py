@@ -77,7 +77,9 @@ SYMBOLS = {
     "ufm_op_refine": (_I, [_P, _I, _I, _I, _P, _P, _F, _P, _P, _P, _P]),
     "ufm_op_prep_resize": (_I, [_P, _I, _I, _I, _I, _I, _I, _I, _P, _P, _P, _P, _P, _P]),
     "ufm_op_unmap": (_I, [_P, _P, _I, _I, _I, _I, _I, _P, _P, _P, _P, _P, _P, _P, _P, _I, _P]),
+    "ufm_op_conv3x3_s2_static": (_I, [_P, _I, _I, _I, _I, _P, _I, _P, _P, _P, C.c_char_p, _I]),
 }
+CONV3X3_S2_STATIC_MAX_BYTES = 16 << 20  # UFM_CONV3X3_S2_STATIC_MAX_BYTES of include/ufm_b200.h
 
 _lib = None
 

@@ -12,6 +12,7 @@
 #include <string.h>
 
 #include <map>
+#include <mutex>
 #include <string>
 #include <vector>
 
@@ -1784,3 +1785,76 @@ int ufm_op_refine(const void* desc, int B, int H, int W, const float* flow_in, c
 }
 
 }  // extern "C"
+
+// ---- allocation-free 3x3 stride-2 convolution -------------------------------------------------------------------------
+// The im2col operand of the one stride-2 convolution (im2col_s2_kernel -> gemm_kernel) normally sits in the engine's
+// workspace or in a caller-allocated buffer.  This variant keeps it in a file-scope device array instead, so the entry
+// point below allocates nothing.  Every GPU that loads the library holds the array until the process exits.  In host code
+// `g_s2_scratch` is only the host-side stand-in of the symbol: the device address is taken once per device with
+// cudaGetSymbolAddress (that device current) and that pointer is what the kernels and the tensor map receive.
+static __device__ __align__(256) unsigned char g_s2_scratch[UFM_CONV3X3_S2_STATIC_MAX_BYTES];
+
+namespace {
+constexpr int kMaxDevices = 64;
+void* g_s2_scratch_ptr[kMaxDevices] = {};
+std::mutex g_s2_mutex;
+
+// device address of g_s2_scratch on the CURRENT device (nullptr + message on failure)
+void* s2_scratch_on_current_device(char* err, int errlen) {
+  int dev = -1;
+  cudaError_t ce = cudaGetDevice(&dev);
+  if (ce != cudaSuccess || dev < 0 || dev >= kMaxDevices) {
+    snprintf(err, errlen, "ufm_op_conv3x3_s2_static: cudaGetDevice: %s (device %d)", cudaGetErrorString(ce), dev);
+    return nullptr;
+  }
+  std::lock_guard<std::mutex> lock(g_s2_mutex);
+  if (!g_s2_scratch_ptr[dev]) {
+    void* p = nullptr;
+    ce = cudaGetSymbolAddress(&p, g_s2_scratch);
+    if (ce != cudaSuccess || !p) {
+      snprintf(err, errlen, "ufm_op_conv3x3_s2_static: cudaGetSymbolAddress on device %d: %s", dev, cudaGetErrorString(ce));
+      return nullptr;
+    }
+    g_s2_scratch_ptr[dev] = p;
+  }
+  return g_s2_scratch_ptr[dev];
+}
+}  // namespace
+
+extern "C" int ufm_op_conv3x3_s2_static(const void* in, int n, int h, int w, int C, const void* wt, int n_out,
+                                        const float* bias, float* out_f32, void* stream, char* err, int errlen) {
+  char local[8];
+  if (!err || errlen <= 0) {
+    err = local;
+    errlen = (int)sizeof(local);
+  }
+  err[0] = 0;
+  if (!in || !wt || !out_f32 || n <= 0 || h <= 0 || w <= 0 || n_out <= 0 || C <= 0 || (C & 63)) {
+    snprintf(err, errlen, "ufm_op_conv3x3_s2_static: needs in / wt / out_f32, positive sizes and C a multiple of 64 (C = %d)", C);
+    return 1;
+  }
+  const int oh = (h - 1) / 2 + 1, ow = (w - 1) / 2 + 1;
+  const long long rows = (long long)n * oh * ow;
+  const long long need = rows * 9 * C * (long long)sizeof(bf16);
+  if (need > (long long)UFM_CONV3X3_S2_STATIC_MAX_BYTES) {
+    snprintf(err, errlen,
+             "ufm_op_conv3x3_s2_static: the im2col operand of n=%d h=%d w=%d C=%d needs %lld bytes, the static scratch holds "
+             "%lld (UFM_CONV3X3_S2_STATIC_MAX_BYTES): use ufm_op_im2col_s2 + ufm_op_gemm with a buffer of your own",
+             n, h, w, C, need, (long long)UFM_CONV3X3_S2_STATIC_MAX_BYTES);
+    return 2;
+  }
+  bf16* col = reinterpret_cast<bf16*>(s2_scratch_on_current_device(err, errlen));
+  if (!col) return 1;
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  // every element of col[rows][9 * C] is written (zeros for the padding taps) before the GEMM reads it: nothing of the
+  // previous call's contents survives into this one, so nothing needs clearing
+  cudaError_t ce = launch_im2col_s2(reinterpret_cast<const bf16*>(in), col, n, h, w, C, oh, ow, st);
+  if (ce != cudaSuccess) {
+    snprintf(err, errlen, "ufm_op_conv3x3_s2_static: im2col_s2: %s", cudaGetErrorString(ce));
+    return 1;
+  }
+  const long long K = 9LL * C;
+  return ufm_op_gemm(col, (int)K, (int)rows, 1, 1, K, rows * K, rows * K, 128, 1, wt, n_out, 1, (int)K, bias, nullptr, nullptr,
+                     nullptr, 0, 0, 0, out_f32, nullptr, 0, 0, n_out, 0, 0u, nullptr, nullptr, nullptr, nullptr, 0, nullptr,
+                     stream, err, errlen);
+}
