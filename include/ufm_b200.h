@@ -155,8 +155,10 @@ int ufm_profile_read(ufm_engine* e, double* ms, double* flops, double* bytes, in
  * the tiles of a GEMM's partly filled last wave (default); which = 6: bit 0 = 512 x 256 pair tiles (two row blocks per
  * CTA, one accumulator set) for the whole waves of the large row-matrix GEMMs, bit 1 = the next item's first row block
  * runs ahead while the second accumulator is drained, bit 2 = also for GELU epilogues (default 3); which = 7: warp-role
- * shift of the GEMM kernel (0 default; 4 = TMA / MMA warps above the epilogue warps).  Returns non-zero for an unknown
- * switch. */
+ * shift of the GEMM kernel (0 default; 4 = TMA / MMA warps above the epilogue warps); which = 8: 1 = passes of <= 4 pairs
+ * run their independent branches (uncertainty head, classification head + UNet branch, the four input chains of each DPT
+ * head) on side streams beside the flow head (default; bit-identical results), 0 = one stream.  Returns non-zero for an
+ * unknown switch. */
 int ufm_debug_flag(int which, int value);
 
 /* ---- kernel-level entry points (unit parity tests; device pointers, asynchronous on `stream`) ---- */

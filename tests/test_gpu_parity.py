@@ -25,7 +25,7 @@ pytestmark = pytest.mark.gpu
 
 from oracle import ufm_oracle as O  # noqa: E402
 from oracle.golden_util import GOLDEN_CASES, case_config, make_inputs, max_abs, rel_l2, subsample  # noqa: E402
-from ufm_b200 import UniFlowMatchClassificationRefinement, UniFlowMatchConfidence  # noqa: E402
+from ufm_b200 import UniFlowMatchClassificationRefinement, UniFlowMatchConfidence, _lib  # noqa: E402
 from ufm_b200.weights import make_state_dict  # noqa: E402
 
 GOLDEN = os.path.join(os.path.dirname(__file__), "golden")
@@ -254,6 +254,40 @@ def test_batch_chunking_and_determinism():
         o = model.predict_correspondences_batched(hs, ht)
         assert o.flow.flow_output.device.type == "cpu" and o.covisibility.mask.device.type == "cpu"
         assert torch.equal(o.flow.flow_output, a.cpu())
+
+
+@pytest.mark.parametrize("name", ["tiny_base", "tiny_refine", "tiny_unet", "tiny_cov"])
+def test_branches_bit_identical(name):
+    """Passes of <= 4 pairs run the uncertainty head, the classification head (+ UNet branch) and the input chains of each
+    DPT head on side streams (ufm_debug_flag 8, engine.cu `branches`): the same kernels on the same operands, so device
+    and host paths (plain pass, graph capture, graph replay) must give the bits of the one-stream pass."""
+    lib = _lib.load()
+    cfg = case_config(name)
+    sd = make_state_dict(cfg, seed=0, out_gain=1.0)
+    W, H = cfg["inference_resolution"]
+    src, tgt = make_inputs(3, H, W, seed=13)
+    cls = UniFlowMatchClassificationRefinement if "classification_head_kwargs" in cfg else UniFlowMatchConfidence
+    res = {}
+    try:
+        for mode in (0, 1):
+            assert lib.ufm_debug_flag(8, mode) == 0
+            m = cls(max_pairs_per_call=4, **cfg).to("cuda")
+            m.load_state_dict(sd)
+            outs = []
+            for pairs in (1, 3):
+                for rep in range(3):  # plain pass + capture, then two replays
+                    o = m.predict_correspondences_batched(src[:pairs].cuda(), tgt[:pairs].cuda())
+                    outs.append((o.flow.flow_output.clone(), o.covisibility.mask.clone()))
+                oh = m.predict_correspondences_batched(src[:pairs], tgt[:pairs])  # host path
+                outs.append((oh.flow.flow_output.cuda(), oh.covisibility.mask.cuda()))
+            torch.cuda.synchronize()
+            res[mode] = outs
+            del m
+    finally:
+        lib.ufm_debug_flag(8, 1)
+    for (f0, c0), (f1, c1) in zip(res[0], res[1]):
+        assert torch.isfinite(f1).all()
+        assert torch.equal(f0, f1) and torch.equal(c0, c1)
 
 
 @pytest.mark.parametrize("name", ["tiny_base", "ufm_base_assumed"])

@@ -26,6 +26,15 @@ using namespace ufm;
 typedef __nv_bfloat16 bf16;
 
 namespace {
+constexpr int kGraphMaxPairs = 4;  // ufm_forward / ufm_forward_host replay a CUDA graph up to this batch size
+
+// ufm_debug_flag 8 / UFM_BRANCHES: independent branches of a launch-bound pass (<= kGraphMaxPairs pairs) on side streams
+int g_branch_mode = -1;
+void set_branch_mode(int v) { g_branch_mode = v; }
+int branch_mode() {
+  if (g_branch_mode < 0) g_branch_mode = getenv("UFM_BRANCHES") ? atoi(getenv("UFM_BRANCHES")) : 1;
+  return g_branch_mode;
+}
 
 struct Tensor {
   void* ptr = nullptr;
@@ -382,6 +391,57 @@ struct ufm_engine {
   std::map<std::vector<int>, GraphEntry> graphs;
   cudaStream_t graph_st = nullptr;
 
+  // ---- concurrent branches for launch-bound passes (<= kGraphMaxPairs pairs; ufm_debug_flag 8) ----
+  // With one or two pairs most launches of the DPT heads fill 4 - 40 of the 148 SMs and are pure latency chains (two heads
+  // x ~36 launches x ~28 us at one pair = a third of the pass).  The pass then forks: the uncertainty head, the
+  // classification head (+ UNet branch) of UFM-Refine and the four input_process chains of each head run on side streams
+  // ("lanes") and join where their results are consumed.  Fork / join are event record + wait pairs, which stream capture
+  // turns into graph edges, so the replayed graph carries the same parallelism.  The side-lane head works on its own copy
+  // of the head workspace (buffer names with the suffix "@u", sized for kGraphMaxPairs).  Same kernels on the same
+  // operands: results are bit-identical to the sequential pass (tests/test_gpu_parity.py::test_branches_bit_identical).
+  static constexpr int kLanes = 8;  // 0: classification head; 1-3: flow-head chains; 4: uncertainty head; 5-7: its chains
+  cudaStream_t lane_st[kLanes] = {};
+  std::vector<cudaEvent_t> sync_ev;
+  size_t sync_used = 0;
+  bool branches = false;  // set per pass
+  std::string bsfx;       // workspace suffix of the branch being issued ("" or "@u")
+  cudaEvent_t next_sync() {
+    if (sync_used == sync_ev.size()) {
+      cudaEvent_t e = nullptr;
+      if (!ck(cudaEventCreateWithFlags(&e, cudaEventDisableTiming), "sync event")) return nullptr;
+      sync_ev.push_back(e);
+    }
+    return sync_ev[sync_used++];
+  }
+  // an event on the current stream that lanes started later wait for (nullptr when not branching)
+  cudaEvent_t fork_point() {
+    if (!branches) return nullptr;
+    cudaEvent_t ev = next_sync();
+    if (ev && !ck(cudaEventRecord(ev, st), "fork record")) return nullptr;
+    return ev;
+  }
+  // the launches that follow go to lane i, ordered after `fork`
+  bool lane_begin(int i, cudaEvent_t fork, cudaStream_t* saved) {
+    *saved = st;
+    if (!branches) return true;
+    if (!fork) return false;  // fork_point failed (error already recorded)
+    if (!lane_st[i] && !ck(cudaStreamCreateWithFlags(&lane_st[i], cudaStreamNonBlocking), "lane stream")) return false;
+    if (!ck(cudaStreamWaitEvent(lane_st[i], fork, 0), "fork wait")) return false;
+    st = lane_st[i];
+    return true;
+  }
+  // back to the stream saved by lane_begin; *done marks the end of the lane's work (nullptr when not branching)
+  bool lane_end(cudaStream_t saved, cudaEvent_t* done) {
+    *done = nullptr;
+    if (!branches) return true;
+    cudaEvent_t ev = next_sync();
+    if (!ev || !ck(cudaEventRecord(ev, st), "join record")) return false;
+    *done = ev;
+    st = saved;
+    return true;
+  }
+  bool lane_join(cudaEvent_t done) { return !done || ck(cudaStreamWaitEvent(st, done, 0), "join wait"); }
+
   // Launch-bound regime (small batches: ~330 launches and as many tensor-map encodes per pass): the pass over the
   // engine-owned staging buffers (in_src / in_tgt -> out_flow / covis) as a CUDA graph, captured once per (pairs, dtype,
   // layout, keep_aux) on the private graph stream and replayed on `s` (ufm_forward: the caller's stream, around two
@@ -392,7 +452,7 @@ struct ufm_engine {
     void* dtgt = buf["in_tgt"].ptr;
     float* dflow = reinterpret_cast<float*>(buf["out_flow"].ptr);
     float* dcov = cfg.unc_out_ch > 0 ? reinterpret_cast<float*>(buf["covis"].ptr) : nullptr;
-    const std::vector<int> key = {pairs, in_dtype, in_layout, keep_aux ? 1 : 0, view_index};
+    const std::vector<int> key = {pairs, in_dtype, in_layout, keep_aux ? 1 : 0, view_index, branch_mode()};
     auto it = graphs.find(key);
     if (it == graphs.end()) {
       // first call with this shape: a plain pass (it also sets the lazily initialised kernel attributes and produces this
@@ -504,6 +564,10 @@ struct ufm_engine {
   }
   template <typename T>
   T* B(const char* n) {
+    if (!bsfx.empty()) {
+      auto it = buf.find(std::string(n) + bsfx);
+      if (it != buf.end()) return reinterpret_cast<T*>(it->second.ptr);
+    }
     return reinterpret_cast<T*>(buf[n].ptr);
   }
   void set_stage(const char* name, void* p, int dtype, std::vector<int64_t> shape) {
@@ -739,7 +803,7 @@ struct ufm_engine {
   }
 
   bool dpt_head(const std::string& hp, int Bp, int out_ch, bool sigmoid, const float* tscale, const float* tshift,
-                bf16* dpt_out, float* out_final, float* out_raw);
+                bf16* dpt_out, float* out_final, float* out_raw, int lane_base);
   bool unet_branch(const void* src, const void* tgt, int in_dtype, int in_layout, int Bp);
   int forward(const void* src, const void* tgt, int pairs, int in_dtype, int in_layout, float* flow_out, float* covis_out,
               cudaStream_t stream);
@@ -747,7 +811,7 @@ struct ufm_engine {
 
 // UC/models/prediction_heads/dpt.py:180-232 (DPTFeature.forward) + :285-311 (DPTRegressionProcessor.forward) + adaptor.
 bool ufm_engine::dpt_head(const std::string& hp, int Bp, int out_ch, bool sigmoid, const float* tscale,
-                          const float* tshift, bf16* dpt_out, float* out_final, float* out_raw) {
+                          const float* tshift, bf16* dpt_out, float* out_final, float* out_raw, int lane_base) {
   const ufm_config& c = cfg;
   const int hpn = c.img_h / c.patch, wpn = c.img_w / c.patch, n = hpn * wpn;
   const int D = c.enc_dim, d = c.info_dim, fd = c.dpt_feature_dim, hid = c.dpt_hidden;
@@ -763,13 +827,18 @@ bool ufm_engine::dpt_head(const std::string& hp, int Bp, int out_ch, bool sigmoi
   const bf16 *F0 = feats[hk[0]], *F1 = feats[hk[1]], *F2 = feats[hk[2]], *F3 = feats[hk[3]];
   const int C0 = fdim[hk[0]], C1 = fdim[hk[1]], C2 = fdim[hk[2]], C3 = fdim[hk[3]];
   auto tok_view = [&](const bf16* p, int C) { return AView{p, C, n, 1, Bp, C, (long long)n * C, 2LL * n * C, 128, 1}; };
-  bf16* G = B<bf16>("G");
+  bf16 *G = B<bf16>("G"), *G1 = B<bf16>("G1");
   bf16 *T0 = B<bf16>("T0"), *T1 = B<bf16>("T1"), *T2 = B<bf16>("T2"), *T3 = B<bf16>("T3"), *T3c = B<bf16>("T3col"),
        *T3b = B<bf16>("T3b");
   float* Lf[4] = {B<float>("L0f"), B<float>("L1f"), B<float>("L2f"), B<float>("L3f")};
   bf16* Lr[4] = {B<bf16>("L0r"), B<bf16>("L1r"), B<bf16>("L2r"), B<bf16>("L3r")};
   const int LH[4] = {4 * hpn, 2 * hpn, hpn, h3}, LW[4] = {4 * wpn, 2 * wpn, wpn, w3};
 
+  // The four input_process chains are independent: in a branching pass (launch-bound batches) chains 1-3 run on the
+  // lanes lane_base .. lane_base + 2 and join in front of the fusion blocks.
+  const cudaEvent_t chains_fork = fork_point();
+  cudaStream_t home = st;
+  cudaEvent_t chain_done[3] = {nullptr, nullptr, nullptr};
   // input_process.0: 1x1 (D -> ld0) folded with ConvT 4x4/s4 into one GEMM, pixel shuffle, 3x3 -> fd (dpt.py:107-125)
   {
     Epi e;
@@ -781,26 +850,32 @@ bool ufm_engine::dpt_head(const std::string& hp, int Bp, int out_ch, bool sigmoi
       return false;
     if (!conv3(T0, Bp, LH[0], LW[0], ld[0], hp + ".rn0.w", nullptr, nullptr, nullptr, Lf[0], Lr[0], true)) return false;
   }
-  // input_process.1: 1x1 + ConvT 2x2/s2 (dpt.py:127-145)
+  // input_process.1: 1x1 + ConvT 2x2/s2 (dpt.py:127-145); its GEMM result has a buffer of its own (G1) so that it can
+  // run beside chain 0
   {
+    if (!lane_begin(lane_base, chains_fork, &home)) return false;
     Epi e;
-    e.bias = Wf(hp + ".in1.b"); e.out_bf16 = G; e.sx = 4LL * ld[1]; e.sn = (long long)n * e.sx;
+    e.bias = Wf(hp + ".in1.b"); e.out_bf16 = G1; e.sx = 4LL * ld[1]; e.sn = (long long)n * e.sx;
     flops_override = 2.0 * Bp * n * ((double)C1 * ld[1] + 4.0 * ld[1] * ld[1]);  // reference: 1x1 then ConvT 2x2/s2
     if (!gemm(tok_view(F1, C1), hp + ".in1.w", 1, e)) return false;
     if (!run(UFM_CAT_MOVE, 0.0, 4.0 * Bp * n * 4 * ld[1], "shuffle1",
-             [&] { return launch_shuffle_bf16(G, T1, Bp, hpn, wpn, 2, ld[1], st); }))
+             [&] { return launch_shuffle_bf16(G1, T1, Bp, hpn, wpn, 2, ld[1], st); }))
       return false;
     if (!conv3(T1, Bp, LH[1], LW[1], ld[1], hp + ".rn1.w", nullptr, nullptr, nullptr, Lf[1], Lr[1], true)) return false;
+    if (!lane_end(home, &chain_done[0])) return false;
   }
   // input_process.2: 1x1 (dpt.py:147-155)
   {
+    if (!lane_begin(lane_base + 1, chains_fork, &home)) return false;
     Epi e;
     e.bias = Wf(hp + ".in2.b"); e.out_bf16 = T2; e.sx = ld[2]; e.sn = (long long)n * e.sx;
     if (!gemm(tok_view(F2, C2), hp + ".in2.w", 1, e)) return false;
     if (!conv3(T2, Bp, LH[2], LW[2], ld[2], hp + ".rn2.w", nullptr, nullptr, nullptr, Lf[2], Lr[2], true)) return false;
+    if (!lane_end(home, &chain_done[1])) return false;
   }
   // input_process.3: 1x1, 3x3 stride 2 (as im2col + GEMM) (dpt.py:157-172)
   {
+    if (!lane_begin(lane_base + 2, chains_fork, &home)) return false;
     Epi e;
     e.bias = Wf(hp + ".in3a.b"); e.out_bf16 = T3; e.sx = ld[3]; e.sn = (long long)n * e.sx;
     if (!gemm(tok_view(F3, C3), hp + ".in3a.w", 1, e)) return false;
@@ -811,7 +886,10 @@ bool ufm_engine::dpt_head(const std::string& hp, int Bp, int out_ch, bool sigmoi
     e2.bias = Wf(hp + ".in3b.b"); e2.out_bf16 = T3b; e2.sx = ld[3];
     if (!gemm(rows_view(T3c, (long long)Bp * h3 * w3, 9 * ld[3]), hp + ".in3b.w", 1, e2)) return false;
     if (!conv3(T3b, Bp, LH[3], LW[3], ld[3], hp + ".rn3.w", nullptr, nullptr, nullptr, Lf[3], Lr[3], true)) return false;
+    if (!lane_end(home, &chain_done[2])) return false;
   }
+  for (cudaEvent_t ev : chain_done)
+    if (!lane_join(ev)) return false;
   // fusion blocks (dpt_block.py:225-255): refinenet4 (no resConfUnit1) ... refinenet1
   bf16* bufA = B<bf16>("bufA");
   bf16* bufO = B<bf16>("bufO");
@@ -1002,6 +1080,9 @@ int ufm_engine::forward_impl(const void* src, const void* tgt, int pairs, int in
   if (in_dtype != UFM_U8 && in_dtype != UFM_F32) return fail("input dtype must be u8 or f32");
   st = stream;
   launches = 0;
+  branches = pairs <= kGraphMaxPairs && !profile && branch_mode();
+  sync_used = 0;
+  bsfx.clear();
   if (profile && prof.size() > (1u << 20)) return fail("profile records not drained: call ufm_profile_read");
   last_pairs = pairs;
   stage.clear();
@@ -1110,27 +1191,46 @@ int ufm_engine::forward_impl(const void* src, const void* tgt, int pairs, int in
     if (!info_norm(B<bf16>("Xcls"), c.cls_in, D)) return 1;
   }
   // ---- heads (view 1 only: "dual+single", ufm.py:180,700) ----
+  // The flow head, the uncertainty head and (UFM-Refine) the classification head + UNet branch only read the encoder /
+  // info-sharing features: a branching pass (launch-bound batches, see `branches`) issues the last two on side lanes and
+  // joins them where their results are needed; otherwise they follow each other on the one stream, in this order.
   nvtx_stage("dpt_heads");
-  float* flow_reg = c.refine ? B<float>("flow_reg") : flow_out;
-  if (!dpt_head("h1", Bp, c.flow_out_ch, false, c.flow_scale, c.flow_shift, B<bf16>("dpt1"), flow_reg,
-                B<float>("head1_raw")))
-    return 1;
   const int H8 = 8 * hpn, W8 = 8 * wpn;
-  set_stage("dpt1", B<bf16>("dpt1"), UFM_BF16, {Bp, H8, W8, c.dpt_feature_dim});
-  set_stage("head1_raw", B<float>("head1_raw"), UFM_F32, {Bp, c.flow_out_ch, c.img_h, c.img_w});
-  set_stage("flow_reg", flow_reg, UFM_F32, {Bp, 2, c.img_h, c.img_w});
-  if (mark_outputs && !c.refine) cudaEventRecord(ev_flow, st);
-  if (c.unc_out_ch > 0) {
+  float* flow_reg = c.refine ? B<float>("flow_reg") : flow_out;
+  const cudaEvent_t heads_fork = fork_point();
+  cudaStream_t main_st = st;
+  cudaEvent_t unc_done = nullptr, cls_done = nullptr;
+
+  auto flow_head = [&]() -> bool {
+    if (!dpt_head("h1", Bp, c.flow_out_ch, false, c.flow_scale, c.flow_shift, B<bf16>("dpt1"), flow_reg,
+                  B<float>("head1_raw"), 1))
+      return false;
+    set_stage("dpt1", B<bf16>("dpt1"), UFM_BF16, {Bp, H8, W8, c.dpt_feature_dim});
+    set_stage("head1_raw", B<float>("head1_raw"), UFM_F32, {Bp, c.flow_out_ch, c.img_h, c.img_w});
+    set_stage("flow_reg", flow_reg, UFM_F32, {Bp, 2, c.img_h, c.img_w});
+    if (mark_outputs && !c.refine) cudaEventRecord(ev_flow, st);
+    return true;
+  };
+
+  auto unc_head = [&]() -> bool {
     float* cov = covis_out ? covis_out : B<float>("covis");
+    bf16* dptu = B<bf16>("dptu");
+    float* headu_raw = B<float>("headu_raw");
+    if (!lane_begin(4, heads_fork, &main_st)) return false;
+    if (branches) bsfx = "@u";  // the side-lane head works on its own copy of the head workspace
+    bool ok = true;
     if (c.unc_n_adaptors == 0) {
       // the single non_occluded_mask MaskAdaptor: sigmoid fused into the tail epilogue
-      if (!dpt_head("hu", Bp, c.unc_out_ch, true, nullptr, nullptr, B<bf16>("dptu"), cov, B<float>("headu_raw"))) return 1;
+      ok = dpt_head("hu", Bp, c.unc_out_ch, true, nullptr, nullptr, dptu, cov, headu_raw, 5);
+      bsfx.clear();
+      if (!ok) return false;
     } else {
       // several adaptors: the tail writes the raw channels, one elementwise kernel applies AdaptorMap (adaptors.py)
-      if (!dpt_head("hu", Bp, c.unc_out_ch, false, nullptr, nullptr, B<bf16>("dptu"), B<float>("headu_raw"), nullptr))
-        return 1;
+      ok = dpt_head("hu", Bp, c.unc_out_ch, false, nullptr, nullptr, dptu, headu_raw, nullptr, 5);
+      bsfx.clear();
+      if (!ok) return false;
       UncAdaptParams up;
-      up.raw = B<float>("headu_raw"); up.B = Bp; up.C = c.unc_out_ch; up.H = c.img_h; up.W = c.img_w;
+      up.raw = headu_raw; up.B = Bp; up.C = c.unc_out_ch; up.H = c.img_h; up.W = c.img_w;
       up.n = c.unc_n_adaptors;
       int ch = 0;
       bool has_cov = false, has_conf = false;
@@ -1149,7 +1249,7 @@ int ufm_engine::forward_impl(const void* src, const void* tgt, int pairs, int in
       const double plane = (double)c.img_h * c.img_w;
       if (!run(UFM_CAT_MOVE, 0.0, Bp * plane * 4.0 * (c.unc_out_ch + 1 + (has_cov ? 7 : 0) + (has_conf ? 1 : 0)),
                "unc adaptors", [&] { return launch_unc_adaptors(up, st); }))
-        return 1;
+        return false;
       if (has_cov) {
         set_stage("flow_cov", up.cov, UFM_F32, {Bp, 3, c.img_h, c.img_w});
         set_stage("flow_cov_inv", up.cov_inv, UFM_F32, {Bp, 3, c.img_h, c.img_w});
@@ -1157,40 +1257,63 @@ int ufm_engine::forward_impl(const void* src, const void* tgt, int pairs, int in
       }
       if (has_conf) set_stage("keypoint_confidence", up.conf, UFM_F32, {Bp, c.img_h, c.img_w});
     }
-    set_stage("dptu", B<bf16>("dptu"), UFM_BF16, {Bp, H8, W8, c.dpt_feature_dim});
-    set_stage("headu_raw", B<float>("headu_raw"), UFM_F32, {Bp, c.unc_out_ch, c.img_h, c.img_w});
+    set_stage("dptu", dptu, UFM_BF16, {Bp, H8, W8, c.dpt_feature_dim});
+    set_stage("headu_raw", headu_raw, UFM_F32, {Bp, c.unc_out_ch, c.img_h, c.img_w});
     if (mark_outputs) cudaEventRecord(ev_cov, st);
-  }
-  // ---- Refine: classification head + local refinement (ufm.py:954-991) ----
-  if (c.refine) {
-    nvtx_stage("classification_head_and_refinement");
+    return lane_end(main_st, &unc_done);
+  };
+
+  // Refine: classification head (ufm.py:954-966) and UNet branch (:916-918, :967-982) -> descriptors
+  auto cls_head = [&]() -> bool {
+    if (!lane_begin(0, heads_fork, &main_st)) return false;
     const long long Mc = Mi;
     {
       Epi e;
       e.bias = Wf("cls.fc1.b"); e.flags = GEMM_GELU; e.out_bf16 = B<bf16>("Hcls"); e.sx = c.cls_hidden;
-      if (!gemm(rows_view(B<bf16>("Xcls"), Mc, c.cls_in), "cls.fc1.w", 1, e)) return 1;
+      if (!gemm(rows_view(B<bf16>("Xcls"), Mc, c.cls_in), "cls.fc1.w", 1, e)) return false;
     }
     {
       Epi e;
       e.bias = Wf("cls.fc2.b"); e.out_bf16 = B<bf16>("Ycls"); e.sx = c.cls_in;
-      if (!gemm(rows_view(B<bf16>("Hcls"), Mc, c.cls_hidden), "cls.fc2.w", 1, e)) return 1;
+      if (!gemm(rows_view(B<bf16>("Hcls"), Mc, c.cls_hidden), "cls.fc2.w", 1, e)) return false;
     }
     const int zc = c.cls_patch * c.cls_patch * c.cls_out;
     {
       Epi e;
       e.bias = Wf("cls.lin.b"); e.out_bf16 = B<bf16>("Z"); e.sx = zc;
-      if (!gemm(rows_view(B<bf16>("Ycls"), Mc, c.cls_in), "cls.lin.w", 1, e)) return 1;
+      if (!gemm(rows_view(B<bf16>("Ycls"), Mc, c.cls_in), "cls.lin.w", 1, e)) return false;
     }
     bf16* desc_dst = c.unet ? B<bf16>("desc_cls") : B<bf16>("desc");
     if (!run(UFM_CAT_MOVE, 0.0, 4.0 * Mi * zc, "shuffle desc", [&] {
           return launch_desc_shuffle(B<bf16>("Z"), desc_dst, 2 * Bp, hpn, wpn, c.cls_patch, c.cls_out, st);
         }))
-      return 1;
+      return false;
     if (c.unet) {
-      if (!unet_branch(src, tgt, in_dtype, in_layout, Bp)) return 1;
+      if (!unet_branch(src, tgt, in_dtype, in_layout, Bp)) return false;
       set_stage("desc_cls", desc_dst, UFM_BF16, {Bp, 2, c.cls_out / 8, c.img_h, c.img_w, 8});
     }
     set_stage("desc", B<bf16>("desc"), UFM_BF16, {Bp, 2, c.cls_out / 8, c.img_h, c.img_w, 8});
+    return lane_end(main_st, &cls_done);
+  };
+
+  if (branches) {  // side lanes first, so that their first launches are queued while the flow head is being issued
+    if (c.unc_out_ch > 0 && !unc_head()) return 1;
+    if (c.refine) {
+      nvtx_stage("classification_head");
+      if (!cls_head()) return 1;
+    }
+    if (!flow_head()) return 1;
+  } else {
+    if (!flow_head()) return 1;
+    if (c.unc_out_ch > 0 && !unc_head()) return 1;
+    if (c.refine) {
+      nvtx_stage("classification_head_and_refinement");
+      if (!cls_head()) return 1;
+    }
+  }
+  // ---- Refine: local refinement (ufm.py:983-991, 1041-1178) ----
+  if (c.refine) {
+    if (!lane_join(cls_done)) return 1;
     RefineParams rp;
     rp.desc = B<bf16>("desc"); rp.B = Bp; rp.H = c.img_h; rp.W = c.img_w;
     rp.flow_in = flow_reg;
@@ -1212,10 +1335,10 @@ int ufm_engine::forward_impl(const void* src, const void* tgt, int pairs, int in
     }
     if (mark_outputs) cudaEventRecord(ev_flow, st);
   }
+  if (!lane_join(unc_done)) return 1;
   return 0;
 }
 
-constexpr int kGraphMaxPairs = 4;  // ufm_forward_host replays a CUDA graph up to this batch size
 
 // ================================================================================================ C ABI
 extern "C" {
@@ -1295,6 +1418,9 @@ void ufm_destroy(ufm_engine* e) {
   for (auto& kv : e->graphs) cudaGraphExecDestroy(kv.second.exec);
   if (e->graph_st) cudaStreamDestroy(e->graph_st);
   if (e->ev_done) cudaEventDestroy(e->ev_done);
+  for (auto ev : e->sync_ev) cudaEventDestroy(ev);
+  for (auto ls : e->lane_st)
+    if (ls) cudaStreamDestroy(ls);
   if (e->copy_st) {
     cudaStreamDestroy(e->copy_st);
     cudaEventDestroy(e->ev_flow);
@@ -1358,6 +1484,7 @@ int ufm_prepare(ufm_engine* e, int max_pairs) {
   const int* ld = c.dpt_layer_dims;
   const long long h3 = (hpn - 1) / 2 + 1, w3 = (wpn - 1) / 2 + 1;
   ok = ok && e->alloc("G", UFM_BF16, Bp * n * mx(16 * ld[0], 4 * ld[1]));
+  ok = ok && e->alloc("G1", UFM_BF16, Bp * n * 4 * ld[1]);
   ok = ok && e->alloc("T0", UFM_BF16, Bp * 16 * n * ld[0]);
   ok = ok && e->alloc("T1", UFM_BF16, Bp * 4 * n * ld[1]);
   ok = ok && e->alloc("T2", UFM_BF16, Bp * n * ld[2]);
@@ -1382,6 +1509,24 @@ int ufm_prepare(ufm_engine* e, int max_pairs) {
   ok = ok && e->alloc("rs", UFM_BF16, Bp * c.img_h * c.img_w * hid);
   ok = ok && e->alloc("head1_raw", UFM_F32, Bp * c.flow_out_ch * c.img_h * c.img_w);
   if (c.unc_out_ch > 0) {
+    // second copy of the head workspace for the uncertainty head of a branching pass (it runs beside the flow head)
+    const long long Bs = Bp < kGraphMaxPairs ? Bp : kGraphMaxPairs;
+    ok = ok && e->alloc("G@u", UFM_BF16, Bs * n * mx(16 * ld[0], 4 * ld[1]));
+    ok = ok && e->alloc("G1@u", UFM_BF16, Bs * n * 4 * ld[1]);
+    ok = ok && e->alloc("T0@u", UFM_BF16, Bs * 16 * n * ld[0]);
+    ok = ok && e->alloc("T1@u", UFM_BF16, Bs * 4 * n * ld[1]);
+    ok = ok && e->alloc("T2@u", UFM_BF16, Bs * n * ld[2]);
+    ok = ok && e->alloc("T3@u", UFM_BF16, Bs * n * ld[3]);
+    ok = ok && e->alloc("T3col@u", UFM_BF16, Bs * h3 * w3 * 9 * ld[3]);
+    ok = ok && e->alloc("T3b@u", UFM_BF16, Bs * h3 * w3 * ld[3]);
+    for (int k = 0; k < 4; ++k) {
+      ok = ok && e->alloc(std::string(lfn[k]) + "@u", UFM_F32, Bs * lv[k] * fd);
+      ok = ok && e->alloc(std::string(lrn[k]) + "@u", UFM_BF16, Bs * lv[k] * fd);
+    }
+    for (const char* nm : {"bufA@u", "bufO@u", "sR@u"}) ok = ok && e->alloc(nm, UFM_BF16, Bs * 16 * n * fd);
+    for (const char* nm : {"sF@u", "low@u", "path@u"}) ok = ok && e->alloc(nm, UFM_F32, Bs * 16 * n * fd);
+    ok = ok && e->alloc("c1@u", UFM_BF16, Bs * 64 * n * hid);
+    ok = ok && e->alloc("rs@u", UFM_BF16, Bs * c.img_h * c.img_w * hid);
     ok = ok && e->alloc("dptu", UFM_BF16, Bp * 64 * n * fd);
     ok = ok && e->alloc("headu_raw", UFM_F32, Bp * c.unc_out_ch * c.img_h * c.img_w);
     ok = ok && e->alloc("covis", UFM_F32, Bp * c.img_h * c.img_w);
@@ -1621,6 +1766,10 @@ int ufm_debug_flag(int which, int value) {
   }
   if (which == 7) {
     set_gemm_warp_shift(value);
+    return 0;
+  }
+  if (which == 8) {
+    set_branch_mode(value);
     return 0;
   }
   return 1;
