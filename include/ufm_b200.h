@@ -154,11 +154,14 @@ int ufm_profile_read(ufm_engine* e, double* ms, double* flops, double* bytes, in
  * for the 3x3 convolutions (default), 0 = nine shifted boxes; which = 4: 1 = programmatic dependent launches (default); which = 5: 1 = column slices for
  * the tiles of a GEMM's partly filled last wave (default); which = 6: bit 0 = 512 x 256 pair tiles (two row blocks per
  * CTA, one accumulator set) for the whole waves of the large row-matrix GEMMs, bit 1 = the next item's first row block
- * runs ahead while the second accumulator is drained, bit 2 = also for GELU epilogues (default 3); which = 7: warp-role
+ * runs ahead while the second accumulator is drained, bit 2 = also for GELU epilogues, bit 3 = only K >= 2048 or (K >= 1024
+ * and N >= 2048), bit 4 = only K >= 2048 (default 27; -1 = back to the default / UFM_ROWS2; the rows behind the last whole
+ * wave of 512-row items run as column-sliced 256-row half items of the same launch); which = 7: warp-role
  * shift of the GEMM kernel (0 default; 4 = TMA / MMA warps above the epilogue warps); which = 8: 1 = passes of <= 4 pairs
  * run their independent branches (uncertainty head, classification head + UNet branch, the four input chains of each DPT
- * head) on side streams beside the flow head (default; bit-identical results), 0 = one stream.  Returns non-zero for an
- * unknown switch. */
+ * head) on side streams beside the flow head (default; bit-identical results), 0 = one stream; which = 9: 1 = GELU of the
+ * bf16 TMA epilogue on packed f32x2 arithmetic (default; same bits as the scalar form), -1 = default / UFM_GELU_PACKED.
+ * Returns non-zero for an unknown switch. */
 int ufm_debug_flag(int which, int value);
 
 /* ---- kernel-level entry points (unit parity tests; device pointers, asynchronous on `stream`) ---- */

@@ -16,10 +16,12 @@ sys.path.insert(0, os.path.join(ROOT, "tests"))
 
 def main():
     ap = argparse.ArgumentParser()
-    ap.add_argument("--variants", default="0:1,1:1", help="comma list of epilogue:pair[:split[:rows2[:warp_shift]]]  (split: last-wave column "
-                    "slices, default 1; rows2: 512 x 256 pair tiles, ufm_debug_flag 6, default 3; warp_shift: ufm_debug_flag 7)")
+    ap.add_argument("--variants", default="0:1,1:1", help="comma list of epilogue:pair[:split[:rows2[:warp_shift[:gelu_packed]]]]  (split: last-wave column "
+                    "slices, default 1; rows2: 512 x 256 pair tiles, ufm_debug_flag 6, default 0; warp_shift: ufm_debug_flag 7; "
+                    "gelu_packed: ufm_debug_flag 9)")
     ap.add_argument("--reps", type=int, default=20)
     ap.add_argument("--only", default="")
+    ap.add_argument("--no-conv", action="store_true", help="row-matrix GEMM shapes only")
     a = ap.parse_args()
     import torch
 
@@ -44,8 +46,9 @@ def main():
             ("proc.c1@240x320", 4, 240, 320, 256, 128, "convbf16"), ("proc.c2@420x560", 4, 420, 560, 128, 128, "convbf16")]
     variants = [tuple(int(x) for x in v.split(":")) for v in a.variants.split(",")]
     variants = [v if len(v) > 2 else v + (1,) for v in variants]
-    variants = [v if len(v) > 3 else v + (3,) for v in variants]
+    variants = [v if len(v) > 3 else v + (0,) for v in variants]
     variants = [v if len(v) > 4 else v + (0,) for v in variants]
+    variants = [v if len(v) > 5 else v + (0,) for v in variants]
     gen = torch.Generator(device=dev).manual_seed(0)
 
     def timeit(fn):
@@ -60,7 +63,7 @@ def main():
         torch.cuda.synchronize()
         return e0.elapsed_time(e1) / a.reps
 
-    print(f"{'shape':18s} {'M':>7s} {'K':>5s} {'N':>5s} " + "   ".join(f"e{v[0]}p{v[1]}s{v[2]}r{v[3]}w{v[4]}: ms TFLOP/s" for v in variants))
+    print(f"{'shape':18s} {'M':>7s} {'K':>5s} {'N':>5s} " + "   ".join(f"e{v[0]}p{v[1]}s{v[2]}r{v[3]}w{v[4]}g{v[5]}: ms TFLOP/s" for v in variants))
     for name, M, K, N, kind in lin:
         if a.only and a.only not in name:
             continue
@@ -76,6 +79,7 @@ def main():
             lib.ufm_debug_flag(5, v[2])
             lib.ufm_debug_flag(6, v[3])
             lib.ufm_debug_flag(7, v[4])
+            lib.ufm_debug_flag(9, v[5])
             if kind == "res":
                 fn = lambda: ops.linear(A, Wt, bias=bias, res1=x, out_f32=x)
             elif kind == "gelu":
@@ -86,7 +90,7 @@ def main():
             res.append(f"{ms:7.3f} {2.0 * M * K * N / ms / 1e9:7.1f}")
         print(f"{name:18s} {M:7d} {K:5d} {N:5d} " + "   ".join(res))
         del A, Wt, x, ob
-    for name, n, H, W, Ci, Co, kind in conv:
+    for name, n, H, W, Ci, Co, kind in ([] if a.no_conv else conv):
         if a.only and a.only not in name:
             continue
         X = (torch.randn(n, H, W, Ci, device=dev, generator=gen) * 0.5).bfloat16()
@@ -116,8 +120,9 @@ def main():
     lib.ufm_debug_flag(0, 1)
     lib.ufm_debug_flag(1, 1)
     lib.ufm_debug_flag(5, 1)
-    lib.ufm_debug_flag(6, 3)
+    lib.ufm_debug_flag(6, -1)
     lib.ufm_debug_flag(7, 0)
+    lib.ufm_debug_flag(9, -1)
 
 
 if __name__ == "__main__":

@@ -71,12 +71,15 @@ def test_gemm_gelu_scale_residual_inplace():
 
 
 # 512 x 256 pair tiles (gemm.cu R2; engine.cu rows2_rows): on a 148-SM part the whole waves of a row-matrix GEMM with N % 256
-# == 0 run with two 128-row blocks per CTA and one accumulator set, the remaining rows on the double-buffered kernel.
-# (M, K, N): the UFM-Base encoder shapes (74 x 512 rows + 544), an exact multiple (37 x 512 rows x 2 column tiles: one
-# wave), and a case too small for any 512-row wave (falls back entirely).
+# == 0 run with two 128-row blocks per CTA and one accumulator set, the remaining rows as 256-row half items (column-sliced
+# when they fill less than half a wave) in the SAME launch.
+# (M, K, N): the UFM-Base encoder shapes (74 x 512 rows + 544 -> 12 half tiles in quarter slices, 36 in half slices), an
+# exact multiple (37 x 512 rows x 2 column tiles: one wave, no half items), 77 rows behind a whole wave (2 half tiles in
+# 64-column quarter slices taken by one warp half), a case too small for any 512-row wave (falls back entirely), and a
+# long-K shape that the shape rule of mode bit 3 admits (the short-K ones then run on the 256-row kernel).
 @pytest.mark.parametrize("M,K,N", [(32 * 1201, 256, 1024), (32 * 1201, 128, 3072), (37 * 512, 192, 512), (37 * 512 + 77, 64, 512),
-                                   (3000, 128, 512)])
-@pytest.mark.parametrize("mode,shift", [(3, 0), (1, 0), (3, 4), (7, 0)])
+                                   (3000, 128, 512), (74 * 512 + 300, 2048, 256), (32 * 1201, 128, 4096)])
+@pytest.mark.parametrize("mode,shift", [(3, 0), (1, 0), (3, 4), (7, 0), (11, 0)])
 def test_gemm_rows2_pair_tiles(M, K, N, mode, shift):
     """bf16 output with bias and the in-place fp32 residual (TMA reduce-add) through the 512-row tiles: against fp32 torch
     and bit-identical to the 256-row path (same MMA instruction shapes and K order, so the accumulators are the same)."""
@@ -102,7 +105,7 @@ def test_gemm_rows2_pair_tiles(M, K, N, mode, shift):
             torch.cuda.synchronize()
             outs[m] = (ob, x, og)
     finally:
-        lib.ufm_debug_flag(6, 3)
+        lib.ufm_debug_flag(6, -1)  # back to the library default (UFM_ROWS2 or the built-in one)
         lib.ufm_debug_flag(7, 0)
     ref = a.float() @ w.float().t() + bias
     assert rel(outs[mode][0].float(), ref) < 4e-3
@@ -111,6 +114,29 @@ def test_gemm_rows2_pair_tiles(M, K, N, mode, shift):
     assert torch.equal(outs[mode][1], outs[0][1])
     assert torch.equal(outs[mode][2], outs[0][2])
     assert rel(outs[mode][2].float(), F.gelu(ref)) < 4e-3
+
+
+def test_gemm_gelu_packed_bits():
+    """The packed f32x2 GELU of the bf16 TMA epilogue (ufm_debug_flag 9) gives the bits of the scalar one."""
+    import gpu_ops as ops
+
+    lib = _lib.load()
+    M, K, N = 5000, 192, 1024
+    a = _rand(M, K, seed=1).bfloat16()
+    w = _rand(N, K, scale=4.0 * K ** -0.5, seed=2).bfloat16()
+    bias = _rand(N, seed=3)
+    outs = []
+    try:
+        for m in (0, 1):
+            lib.ufm_debug_flag(9, m)
+            og = torch.zeros(M, N, dtype=torch.bfloat16, device="cuda")
+            ops.linear(a, w, bias=bias, out_bf16=og, flags=_lib.GEMM_GELU)
+            torch.cuda.synchronize()
+            outs.append(og)
+    finally:
+        lib.ufm_debug_flag(9, -1)
+    assert torch.equal(outs[0], outs[1])
+    assert rel(outs[1].float(), F.gelu(a.float() @ w.float().t() + bias)) < 4e-3
 
 
 # Last-wave column slices (gemm.cu tile_ref / engine.cu build_gemm) on a 148-SM part: pair tiles 256 x 256 on 74 units,

@@ -93,7 +93,7 @@ struct Epi {
 };
 
 bool build_gemm(GemmParams* gp, int* BN, const AView& a_in, const void* wt, int n_out, int taps, int cin_pad, const Epi& e,
-                char* err, int errlen, int num_sms = 0, int rows2 = 0) {
+                char* err, int errlen, int num_sms = 0, int rows2 = 0, long long r2_rows = 0) {
   memset(gp, 0, sizeof(*gp));
   gp->warp_shift = gemm_warp_shift();
   AView a = a_in;
@@ -163,6 +163,25 @@ bool build_gemm(GemmParams* gp, int* BN, const AView& a_in, const void* wt, int 
       if (!make_tmap_bf16(&gp->tmBs, wt, 2, bdims, bstr, sbox, err, errlen)) return false;
     }
   }
+  if (rows2 && num_sms > 0) {
+    // rows2 launch (gemm.cu R2): r2_rows rows as 512-row items, the rest as half items (256-row pair tiles) behind them in
+    // the same launch; one partly filled wave of half items is column-sliced like the last wave above
+    const int U = num_sms / 2;
+    gp->r2_items = (int)(r2_rows / 512) * gp->tiles_n;
+    gp->r2_half_mt0 = (int)(r2_rows / 256);
+    const int R = (int)((a.X - r2_rows + 255) / 256) * gp->tiles_n;
+    gp->r2_half_tiles = R;
+    int sl = 0;
+    if (gemm_split_mode() && R > 0) {
+      if (R * 4 <= U) sl = 2;
+      else if (R * 2 <= U) sl = 1;
+    }
+    if (sl) {
+      gp->split_log2 = sl;
+      const uint32_t sbox[2] = {64, (uint32_t)((*BN / gp->ctas) >> sl)};
+      if (!make_tmap_bf16(&gp->tmBs, wt, 2, bdims, bstr, sbox, err, errlen)) return false;
+    }
+  }
   if (gp->cchunks * 64 > cin_pad && taps > 1) {
     snprintf(err, errlen, "conv weight pitch %d too small for C=%d", cin_pad, a.C);
     return false;
@@ -226,15 +245,17 @@ bool build_gemm(GemmParams* gp, int* BN, const AView& a_in, const void* wt, int 
     }
   }
   if (rows2) {
-    // 512 x 256 pair tiles (gemm.cu R2): whole items only, TMA epilogue without a residual slab load
+    // 512 x 256 pair tiles (gemm.cu R2): TMA epilogue without a residual slab load
     const bool epi_ok = gp->epi_mode == EPI_TMA_BF16 || (gp->epi_mode == EPI_TMA_F32 && (!e.res1 || red_inplace));
-    if (halo || tail || taps != 1 || *BN != 256 || gp->ctas != 2 || !epi_ok || (a.N * gp->tiles_y * gp->tiles_x) % 4) {
-      snprintf(err, errlen, "rows2 tiles need a plain CTA-pair BN=256 GEMM over whole 512-row items with a TMA epilogue");
+    if (halo || tail || taps != 1 || *BN != 256 || gp->ctas != 2 || !epi_ok || r2_rows <= 0 || r2_rows % 512 || r2_rows > a.X ||
+        a.Y != 1 || a.N != 1 || a.tw != 128) {
+      snprintf(err, errlen, "rows2 tiles need a plain CTA-pair BN=256 row-matrix GEMM with a TMA epilogue");
       return false;
     }
     gp->rows2 = rows2;
   }
   gp->flags = e.flags | (red_inplace ? GEMM_RED_INPLACE : 0u);
+  if ((e.flags & GEMM_GELU) && gp->epi_mode == EPI_TMA_BF16 && gemm_gelu_packed()) gp->flags |= GEMM_GELU_PACKED;
   gp->bias = e.bias; gp->scale = e.scale; gp->res1 = e.res1; gp->res2 = e.res2;
   gp->out_f32 = e.out_f32; gp->out_bf16 = e.out_bf16;
   gp->sN = e.sn; gp->sY = e.sy; gp->sX = e.sx; gp->out_off = e.out_off;
@@ -249,8 +270,8 @@ bool build_gemm(GemmParams* gp, int* BN, const AView& a_in, const void* wt, int 
 }
 
 // Rows of a plain row-matrix GEMM that run as 512 x 256 pair tiles (gemm.cu R2): the largest count of whole 512-row items
-// whose (items x column tiles) fill the pair units an integral number of times; the remaining rows go to the
-// double-buffered 256 x 256 kernel in a second launch.  0 = not eligible.
+// whose (items x column tiles) fill the pair units an integral number of times; the remaining rows follow as 256-row half
+// items in the same launch.  0 = not eligible.
 long long rows2_rows(const AView& a, int n_out, int taps, const Epi& e, int num_sms) {
   if (!(gemm_rows2_mode() & 1) || !(gemm_pair_mode() & 1) || !gemm_epilogue_variant()) return 0;
   if (taps != 1 || a.Y != 1 || a.N != 1 || a.tw != 128 || a.th != 1 || n_out % 256 || a.C % 64) return 0;
@@ -259,6 +280,11 @@ long long rows2_rows(const AView& a, int n_out, int taps, const Epi& e, int num_
   if (e.out_f32 && e.res1 && (e.res1 != e.out_f32 || (gemm_epilogue_variant() & 4))) return 0;  // reduce-add in place only
   // heavy per-element epilogues (GELU) need the overlap of the double-buffered kernel
   if ((e.flags & GEMM_GELU) && !(gemm_rows2_mode() & 4)) return 0;
+  // bits 3 / 4: shape rules (profiles/r02_gemm_bench_fold.txt).  Short-K items cannot hide the single accumulator set's drain
+  // (the second row block's accumulator is released only after the first one's epilogue math): K = 768 loses up to 25 % on
+  // some boxes, K = 1024 is +5 % .. -2 % depending on the box, K >= 3072 gains 10 - 16 % everywhere
+  if ((gemm_rows2_mode() & 8) && !(a.C >= 2048 || (a.C >= 1024 && n_out >= 2048))) return 0;
+  if ((gemm_rows2_mode() & 16) && a.C < 2048) return 0;
   const int units = num_sms / 2, tiles_n = n_out / 256;
   const long long items_m = a.X / 512;
   int g = units, t = tiles_n;  // step = units / gcd(units, tiles_n)
@@ -588,30 +614,20 @@ struct ufm_engine {
     double fl = 2.0 * a.N * a.X * a.Y * (double)n_out * taps * a.C;
     if (flops_override >= 0) fl = flops_override;
     flops_override = -1.0;
-    AView ar = a;
-    Epi er = e;
     const long long r2 = rows2_rows(a, n_out, taps, e, num_sms);
     if (r2 > 0) {
-      AView a2 = a;
-      a2.X = (int)r2;
       GemmParams g2;
       int BN2;
-      if (!build_gemm(&g2, &BN2, a2, wt->ptr, n_out, taps, ktot / taps, e, eb, sizeof(eb), num_sms, gemm_rows2_mode())) {
+      if (!build_gemm(&g2, &BN2, a, wt->ptr, n_out, taps, ktot / taps, e, eb, sizeof(eb), num_sms, gemm_rows2_mode(), r2)) {
         fail("gemm %s (rows2): %s", wname.c_str(), eb);
         return false;
       }
-      if (!run(UFM_CAT_GEMM, fl * (double)r2 / a.X, 0.0, ("launch gemm " + wname + " [512-row tiles]").c_str(),
-               [&] { return launch_gemm(g2, BN2, num_sms, st); }))
-        return false;
-      if (r2 == a.X) return true;
-      fl *= (double)(a.X - r2) / a.X;
-      ar.p = reinterpret_cast<const bf16*>(a.p) + r2 * a.sx;
-      ar.X = (int)(a.X - r2);
-      er.out_off = e.out_off + r2 * e.sx;
+      return run(UFM_CAT_GEMM, fl, 0.0, ("launch gemm " + wname + " [512-row tiles]").c_str(),
+                 [&] { return launch_gemm(g2, BN2, num_sms, st); });
     }
     GemmParams gp;
     int BN;
-    if (!build_gemm(&gp, &BN, ar, wt->ptr, n_out, taps, ktot / taps, er, eb, sizeof(eb), num_sms)) {
+    if (!build_gemm(&gp, &BN, a, wt->ptr, n_out, taps, ktot / taps, e, eb, sizeof(eb), num_sms)) {
       fail("gemm %s: %s", wname.c_str(), eb);
       return false;
     }
@@ -1772,6 +1788,10 @@ int ufm_debug_flag(int which, int value) {
     set_branch_mode(value);
     return 0;
   }
+  if (which == 9) {
+    set_gemm_gelu_packed(value);
+    return 0;
+  }
   return 1;
 }
 
@@ -1809,19 +1829,14 @@ int ufm_op_gemm(const void* a, int C, int X, int Y, int Nimg, int64_t a_sx, int6
   GemmParams gp;
   int BN;
   const long long r2 = rows2_rows(av, n_out, taps, e, g_num_sms());
-  if (r2 > 0) {  // same split as ufm_engine::gemm: 512-row pair tiles for the whole waves, the rest below
-    AView a2 = av;
-    a2.X = (int)r2;
-    if (!build_gemm(&gp, &BN, a2, wt, n_out, taps, cin_pad, e, err, errlen, g_num_sms(), gemm_rows2_mode())) return 1;
+  if (r2 > 0) {  // same as ufm_engine::gemm: 512-row pair tiles for the whole waves, the rest as half items of the same launch
+    if (!build_gemm(&gp, &BN, av, wt, n_out, taps, cin_pad, e, err, errlen, g_num_sms(), gemm_rows2_mode(), r2)) return 1;
     cudaError_t c2 = launch_gemm(gp, BN, g_num_sms(), reinterpret_cast<cudaStream_t>(stream));
     if (c2 != cudaSuccess) {
       snprintf(err, errlen, "launch_gemm (rows2): %s", cudaGetErrorString(c2));
       return 1;
     }
-    if (r2 == X) return 0;
-    av.p = reinterpret_cast<const bf16*>(a) + r2 * a_sx;
-    av.X = (int)(X - r2);
-    e.out_off = out_off + r2 * sx;
+    return 0;
   }
   if (!build_gemm(&gp, &BN, av, wt, n_out, taps, cin_pad, e, err, errlen, g_num_sms())) return 1;
   cudaError_t ce = launch_gemm(gp, BN, g_num_sms(), reinterpret_cast<cudaStream_t>(stream));

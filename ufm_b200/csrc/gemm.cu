@@ -91,6 +91,49 @@ __device__ __forceinline__ float gelu_erf(float x) {
   return fmaf(-ax * 0.3989422804014327f, pl * e, fmaxf(x, 0.f));
 }
 
+// The same function for two values with packed f32x2 arithmetic (fma.rn.f32x2 / mul.rn.f32x2: one issue slot for two lanes;
+// every operation is the IEEE round-to-nearest counterpart of the scalar one in the same order, so the bits are the same):
+// 19 instead of 26 issue slots per pair in the fc1 epilogue, which paces that GEMM (GEMM_GELU_PACKED).
+__device__ __forceinline__ uint64_t f2pack(float a, float b) {
+  uint64_t r;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(a), "f"(b));
+  return r;
+}
+__device__ __forceinline__ void f2unpack(uint64_t v, float& a, float& b) {
+  asm("mov.b64 {%0, %1}, %2;" : "=f"(a), "=f"(b) : "l"(v));
+}
+__device__ __forceinline__ uint64_t f2fma(uint64_t a, uint64_t b, uint64_t c) {
+  uint64_t d;
+  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c));
+  return d;
+}
+__device__ __forceinline__ uint64_t f2mul(uint64_t a, uint64_t b) {
+  uint64_t d;
+  asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+  return d;
+}
+__device__ __forceinline__ void gelu_erf2(float& x0, float& x1) {
+  const float ax0 = fabsf(x0), ax1 = fabsf(x1);
+  const uint64_t ax = f2pack(ax0, ax1), x = f2pack(x0, x1);
+  float d0, d1, t0, t1;
+  f2unpack(f2fma(f2pack(0.2316419f, 0.2316419f), ax, f2pack(1.0f, 1.0f)), d0, d1);
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(t0) : "f"(d0));
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(t1) : "f"(d1));
+  const uint64_t t = f2pack(t0, t1);
+  uint64_t pl = f2fma(t, f2pack(1.330274429f, 1.330274429f), f2pack(-1.821255978f, -1.821255978f));
+  pl = f2fma(pl, t, f2pack(1.781477937f, 1.781477937f));
+  pl = f2fma(pl, t, f2pack(-0.356563782f, -0.356563782f));
+  pl = f2fma(pl, t, f2pack(0.319381530f, 0.319381530f));
+  pl = f2mul(pl, t);
+  float a0, a1, e0, e1;
+  f2unpack(f2mul(f2mul(x, x), f2pack(-0.72134752044448170f, -0.72134752044448170f)), a0, a1);
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e0) : "f"(a0));
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e1) : "f"(a1));
+  const uint64_t r = f2fma(f2mul(f2pack(-ax0, -ax1), f2pack(0.3989422804014327f, 0.3989422804014327f)), f2mul(pl, f2pack(e0, e1)),
+                           f2pack(fmaxf(x0, 0.f), fmaxf(x1, 0.f)));
+  f2unpack(r, x0, x1);
+}
+
 // Work item -> (row-tile index, first column, width).  Items below split_from are whole BN-wide tiles; the tiles of the
 // last, partly filled wave (item >= split_from) are cut into 2^split_log2 column slices so that they spread over the idle
 // scheduling units: with 604 tiles on 74 CTA pairs the ninth wave holds 12 tiles, as 48 quarter tiles it costs about a
@@ -108,6 +151,19 @@ __device__ __forceinline__ TileRef tile_ref(const GemmParams& p, int item, int s
   }
   const int tn = tile % p.tiles_n;
   return TileRef{tile / p.tiles_n, tn * BN + sub * ncols, ncols};
+}
+
+// R2 launches: items >= r2_items are HALF items -- ordinary 256 x BN pair tiles (row block 0 / accumulator 0 only) over the
+// rows behind the last whole wave of 512-row items, each cut into 2^split_log2 column slices like the last wave of the
+// 256-row kernel, so that the remainder rides in the same launch instead of a second, serialised one.
+struct HalfRef {
+  int mt, n0, ncols;  // pair-tile (256-row) index, first column, width
+};
+__device__ __forceinline__ HalfRef half_ref(const GemmParams& p, int item, int BN) {
+  const int h = item - p.r2_items;
+  const int tile = h >> p.split_log2, sub = h & ((1 << p.split_log2) - 1);
+  const int ncols = BN >> p.split_log2;
+  return HalfRef{p.r2_half_mt0 + tile / p.tiles_n, (tile % p.tiles_n) * BN + sub * ncols, ncols};
 }
 
 template <int BN, int CTAS, bool HALO, bool R2 = false>
@@ -184,7 +240,7 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_kernel(const __grid_constant
   const int tiles_m = (tiles_m1 + CTAS * RB - 1) / (CTAS * RB);  // R2: an item = two consecutive pair tiles of the same columns
   const int total_tiles = tiles_m * p.tiles_n;
   const int split_from = (p.split_log2 && !R2) ? p.split_from : total_tiles;
-  const int total_items = split_from + ((total_tiles - split_from) << p.split_log2);
+  const int total_items = R2 ? p.r2_items + (p.r2_half_tiles << p.split_log2) : split_from + ((total_tiles - split_from) << p.split_log2);
   const int k_iters = p.taps * p.cchunks;
 
   if (warp == 0) {
@@ -236,21 +292,36 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_kernel(const __grid_constant
           continue;
         }
         if constexpr (R2) {
+          if (item >= p.r2_items) {
+            // half item: one 128-row block per CTA, the B half-tile (or its column slice) of the pair
+            const HalfRef hr = half_ref(p, item, BN);
+            const int hx = (hr.mt * CTAS + (int)cta_rank) * BM;
+            const int hn0 = hr.n0 + (int)cta_rank * (hr.ncols / CTAS);
+            const CUtensorMap* tmBh = p.split_log2 ? &p.tmBs : &p.tmB;
+            const uint32_t hb_tx = (uint32_t)(C::B_BYTES >> p.split_log2);
+            for (int k = 0; k < k_iters; ++k) {
+              mbar_wait(&empty[stage], phase ^ 1);
+              if (cta_rank == 0) mbar_expect_tx(&full[stage], 2 * (BM * BK * 2 + hb_tx));
+              const uint32_t lbar = smem_u32(&full[stage]) & kPeerBitMask;
+              tma2_load_4d(sA + stage * C::A_BYTES, &p.tmA, lbar, k * BK, hx, 0, 0);
+              tma2_load_2d(sB + stage * C::B_BYTES, tmBh, lbar, k * BK, hn0);
+              if (++stage == C::STAGES) {
+                stage = 0;
+                phase ^= 1;
+              }
+            }
+            continue;
+          }
           // row block r of this CTA = 128-row tile (2 * mt + r) * 2 + rank; both blocks and the B half-tile of the pair land
           // on the leader's barrier
-          int bx[2], by[2], bi[2];
-          for (int r = 0; r < 2; ++r) {
-            const int t2 = (tr.mt * 2 + r) * CTAS + (int)cta_rank;
-            bx[r] = (t2 % p.tiles_x) * p.tw;
-            by[r] = ((t2 / p.tiles_x) % p.tiles_y) * p.th;
-            bi[r] = t2 / (p.tiles_x * p.tiles_y);
-          }
+          // (plain row matrix: X = rows, Y = Nimg = 1, tw = 128; boxes past the last row are zero-filled by TMA)
+          const int bx0 = ((tr.mt * 2) * CTAS + (int)cta_rank) * BM, bx1 = bx0 + CTAS * BM;
           for (int k = 0; k < k_iters; ++k) {
             mbar_wait(&empty[stage], phase ^ 1);
             if (cta_rank == 0) mbar_expect_tx(&full[stage], 2 * (C::A_TX + C::B_BYTES));
             const uint32_t lbar = smem_u32(&full[stage]) & kPeerBitMask;
-            tma2_load_4d(sA + stage * C::A_BYTES, &p.tmA, lbar, k * BK, bx[0], by[0], bi[0]);
-            tma2_load_4d(sA + stage * C::A_BYTES + BM * BK * 2, &p.tmA, lbar, k * BK, bx[1], by[1], bi[1]);
+            tma2_load_4d(sA + stage * C::A_BYTES, &p.tmA, lbar, k * BK, bx0, 0, 0);
+            tma2_load_4d(sA + stage * C::A_BYTES + BM * BK * 2, &p.tmA, lbar, k * BK, bx1, 0, 0);
             tma2_load_2d(sB + stage * C::B_BYTES, &p.tmB, lbar, k * BK, n0);
             if (++stage == C::STAGES) {
               stage = 0;
@@ -308,14 +379,35 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_kernel(const __grid_constant
           // both accumulators belong to this item: row block r -> TMEM columns [r * BN, (r + 1) * BN).  With run-ahead the
           // first `ahead` k-steps of row block 0 are issued as soon as accumulator 0 is drained, without releasing their
           // smem stages; row block 1 catches up (and releases them) once accumulator 1 is drained as well.
-          auto mma_block = [&](int st_, int r, uint32_t accum0) {
+          auto mma_block = [&](int st_, int r, uint32_t accum0, uint32_t idesc_) {
             const uint32_t a_lo = a_lo0 + st_ * (C::A_BYTES >> 4) + r * ((BM * BK * 2) >> 4);
             const uint32_t b_lo = b_lo0 + st_ * (C::B_BYTES >> 4);
 #pragma unroll
             for (int kk = 0; kk < BK / 16; ++kk)
-              umma2_ss(tmem_base + r * BN, umma_desc_words(a_lo + kk * 2, hi_a), umma_desc_words(b_lo + kk * 2, hi_b), idesc_full,
+              umma2_ss(tmem_base + r * BN, umma_desc_words(a_lo + kk * 2, hi_a), umma_desc_words(b_lo + kk * 2, hi_b), idesc_,
                        (accum0 | (uint32_t)kk) != 0 ? 1u : 0u);
           };
+          if (item >= p.r2_items) {
+            // half item: row block 0 into accumulator 0 (a column slice fills its first columns); accumulator 1 is not
+            // touched any more -- half items come after every 512-row item of this unit
+            mbar_wait(&tempty[0], accphase ^ 1);
+            tc_fence_after();
+            for (int k = 0; k < k_iters; ++k) {
+              mbar_wait(&full[stage], phase);
+              tc_fence_after();
+              if (leader) {
+                mma_block(stage, 0, (uint32_t)k, idesc_slice);
+                umma2_commit_mc(&empty[stage]);
+                if (k == k_iters - 1) umma2_commit_mc(&tfull[0]);
+              }
+              if (++stage == C::STAGES) {
+                stage = 0;
+                phase ^= 1;
+              }
+            }
+            accphase ^= 1;
+            continue;
+          }
           const int ahead = (p.rows2 & 2) ? (k_iters < C::STAGES ? k_iters : C::STAGES) : 0;
           mbar_wait(&tempty[0], accphase ^ 1);
           tc_fence_after();
@@ -325,7 +417,7 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_kernel(const __grid_constant
             for (int k = 0; k < ahead; ++k) {
               mbar_wait(&full[s2], ph2);
               tc_fence_after();
-              if (leader) mma_block(s2, 0, (uint32_t)k);
+              if (leader) mma_block(s2, 0, (uint32_t)k, idesc_full);
               if (++s2 == C::STAGES) {
                 s2 = 0;
                 ph2 ^= 1;
@@ -340,8 +432,8 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_kernel(const __grid_constant
               tc_fence_after();
             }
             if (leader) {
-              if (k >= ahead) mma_block(stage, 0, (uint32_t)k);
-              mma_block(stage, 1, (uint32_t)k);
+              if (k >= ahead) mma_block(stage, 0, (uint32_t)k, idesc_full);
+              mma_block(stage, 1, (uint32_t)k, idesc_full);
               umma2_commit_mc(&empty[stage]);
               if (k == k_iters - 1) {
                 umma2_commit_mc(&tfull[0]);
@@ -467,7 +559,8 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_kernel(const __grid_constant
       const bool red = (p.flags & GEMM_RED_INPLACE) != 0;
       const int tid8 = e * 32 + lane;  // 0..255 over the eight epilogue warps
       int it2 = 0;
-      for (int item = unit; item < total_items; item += num_units, ++it2) {
+      int item = unit;
+      for (; item < p.r2_items; item += num_units, ++it2) {
         const TileRef tr = tile_ref(p, item, split_from, BN);
         const int n0 = tr.n0;
         // stage bias / scale of columns [n0, n0 + BN): every warp has finished reading the previous item's values
@@ -480,12 +573,9 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_kernel(const __grid_constant
         const float* bcol = colc + col_off;
         const float* scol = colc + BN + col_off;
         for (int rb = 0; rb < 2; ++rb) {
-          const int tm = (tr.mt * 2 + rb) * CTAS + (int)cta_rank;
-          const int tx = tm % p.tiles_x;
-          const int ty = (tm / p.tiles_x) % p.tiles_y;
-          const int img = tm / (p.tiles_x * p.tiles_y);
-          const int wx = tx * p.tw + ((32 * q) & (p.tw - 1));
-          const int wy = ty * p.th + ((32 * q) >> p.tw_log2);
+          // plain row matrix (X = rows, Y = Nimg = 1, tw = 128; checked by the host): rows past the end are clipped by TMA
+          const int wx = ((tr.mt * 2 + rb) * CTAS + (int)cta_rank) * BM + 32 * q;
+          constexpr int wy = 0, img = 0;
           const uint32_t acc_addr = tmem_base + (uint32_t(q * 32) << 16) + uint32_t(rb * BN + col_off);
           mbar_wait(&tfull[rb], (uint32_t)(it2 & 1));
           tc_fence_after();
@@ -539,7 +629,10 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_kernel(const __grid_constant
                 const float bb[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
 #pragma unroll
                 for (int i = 0; i < 8; ++i) v[i] = __uint_as_float(vr[64 * c + 8 * j + i]) + bb[i];
-                if (p.flags & GEMM_GELU) {
+                if (p.flags & GEMM_GELU_PACKED) {
+#pragma unroll
+                  for (int i = 0; i < 8; i += 2) gelu_erf2(v[i], v[i + 1]);
+                } else if (p.flags & GEMM_GELU) {
 #pragma unroll
                   for (int i = 0; i < 8; ++i) v[i] = gelu_erf(v[i]);
                 }
@@ -565,6 +658,81 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_kernel(const __grid_constant
             }
           }
         }
+      }
+      // ---- half items (the rows behind the last whole wave of 512-row items): row block 0 / accumulator 0 of a 256-row pair
+      // tile, possibly a column slice; chunk by chunk, the accumulator is released once all chunks are out ----
+      for (; item < total_items; item += num_units, ++it2) {
+        const HalfRef hr = half_ref(p, item, BN);
+        const int n0 = hr.n0;
+        asm volatile("bar.sync 2, 256;" ::: "memory");
+        colc[tid8] = (p.bias && n0 + tid8 < p.N) ? __ldg(p.bias + n0 + tid8) : 0.f;
+        colc[BN + tid8] = (p.scale && n0 + tid8 < p.N) ? __ldg(p.scale + n0 + tid8) : 1.f;
+        asm volatile("bar.sync 2, 256;" ::: "memory");
+        // columns of this warp: 128+ columns are shared by the two warp halves, a 64-column slice is taken by half 0 alone
+        // (half 1 only keeps the barrier protocol)
+        const int per_half = hr.ncols >= 128 ? (hr.ncols >> 1) : hr.ncols;
+        const int col_off = hr.ncols >= 128 ? half * per_half : 0;
+        const int c0 = n0 + col_off;
+        const int cend = (hr.ncols < 128 && half == 1) ? c0 : (c0 + per_half < p.N ? c0 + per_half : p.N);
+        const float* bcol = colc + col_off;
+        const float* scol = colc + BN + col_off;
+        const int wx = (hr.mt * CTAS + (int)cta_rank) * BM + 32 * q;
+        const uint32_t acc_addr = tmem_base + (uint32_t(q * 32) << 16) + uint32_t(col_off);
+        mbar_wait(&tfull[0], (uint32_t)(it2 & 1));
+        tc_fence_after();
+        uint8_t* rowp = wbuf + lane * 128;
+#pragma unroll 1
+        for (int cc = c0; cc < cend; cc += 32) {
+          // 32 accumulator columns: one fp32 slab, or half of a 64-column bf16 slab
+          const int o = cc - c0;
+          uint32_t vr[32];
+          tmem_ld32(acc_addr + o, vr);
+          tmem_ld_wait();
+          const bool first = f32 || (o & 32) == 0, last = f32 || (o & 32) != 0;
+          if (first) {
+            if (lane == 0) bulk_wait_read<0>();  // single slab: the previous store has read it
+            __syncwarp();
+          }
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            const float4 b4 = *reinterpret_cast<const float4*>(bcol + o + 4 * j);
+            float4 v = make_float4(__uint_as_float(vr[4 * j]) + b4.x, __uint_as_float(vr[4 * j + 1]) + b4.y,
+                                   __uint_as_float(vr[4 * j + 2]) + b4.z, __uint_as_float(vr[4 * j + 3]) + b4.w);
+            if (p.flags & GEMM_GELU_PACKED) {
+              gelu_erf2(v.x, v.y);
+              gelu_erf2(v.z, v.w);
+            } else if (p.flags & GEMM_GELU) {
+              v.x = gelu_erf(v.x); v.y = gelu_erf(v.y); v.z = gelu_erf(v.z); v.w = gelu_erf(v.w);
+            }
+            if (p.scale) {
+              const float4 s4 = *reinterpret_cast<const float4*>(scol + o + 4 * j);
+              v.x *= s4.x; v.y *= s4.y; v.z *= s4.z; v.w *= s4.w;
+            }
+            if (f32) {
+              *reinterpret_cast<float4*>(rowp + ((uint32_t(j) ^ sw) << 4)) = v;
+            } else {
+              if (p.flags & GEMM_RELU_BF16) {
+                v.x = fmaxf(v.x, 0.f); v.y = fmaxf(v.y, 0.f); v.z = fmaxf(v.z, 0.f); v.w = fmaxf(v.w, 0.f);
+              }
+              // 8-byte half of 16-byte chunk (o & 32) / 8 + j / 2 of the 64-column bf16 slab row
+              const uint32_t chunk = uint32_t(((o & 32) >> 3) + (j >> 1));
+              *reinterpret_cast<uint2*>(rowp + ((chunk ^ sw) << 4) + ((j & 1) << 3)) =
+                  make_uint2(pack_bf16(v.x, v.y), pack_bf16(v.z, v.w));
+            }
+          }
+          if (last) {
+            fence_proxy_async_smem();
+            __syncwarp();
+            if (lane == 0) {
+              if (f32 && red) tma_reduce_add_4d(&p.tmOut, wbuf, cc, wx, 0, 0);
+              else tma_store_4d(&p.tmOut, wbuf, f32 ? cc : cc - 32, wx, 0, 0);
+              bulk_commit_group();
+            }
+          }
+        }
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive_cluster_relaxed(tempty_remote[0]);
       }
       if (lane == 0) bulk_wait<0>();
     } else {
@@ -771,7 +939,10 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_kernel(const __grid_constant
                   v[0] += b0.x; v[1] += b0.y; v[2] += b0.z; v[3] += b0.w;
                   v[4] += b1.x; v[5] += b1.y; v[6] += b1.z; v[7] += b1.w;
                 }
-                if (p.flags & GEMM_GELU) {
+                if (p.flags & GEMM_GELU_PACKED) {
+#pragma unroll
+                  for (int i = 0; i < 8; i += 2) gelu_erf2(v[i], v[i + 1]);
+                } else if (p.flags & GEMM_GELU) {
 #pragma unroll
                   for (int i = 0; i < 8; ++i) v[i] = gelu_erf(v[i]);
                 }
@@ -1001,11 +1172,20 @@ int gemm_pair_mode() { return g_gemm_pair; }
 int g_gemm_split = 1;  // ufm_debug_flag 5
 void set_gemm_split_mode(int v) { g_gemm_split = v; }
 int gemm_split_mode() { return g_gemm_split; }
-int g_gemm_rows2 = -1;  // ufm_debug_flag 6 / UFM_ROWS2 (tuning)
+// ufm_debug_flag 6 / UFM_ROWS2: bit 0 = 512-row pair tiles, bit 1 = run-ahead, bit 2 = also with GELU, bit 3 = only K >= 2048 or
+// (K >= 1024 and N >= 2048), bit 4 = only K >= 2048.  Default 27: the long-K GEMMs (fc2), +10 - 16 % on every box measured;
+// the K = 1024 qkv GEMM gains 5 % on some boxes and loses 2 % on others, short-K shapes lose (profiles/r02_gemm_bench_fold.txt)
+int g_gemm_rows2 = -1;
 void set_gemm_rows2_mode(int v) { g_gemm_rows2 = v; }
 int gemm_rows2_mode() {
-  if (g_gemm_rows2 < 0) g_gemm_rows2 = getenv("UFM_ROWS2") ? atoi(getenv("UFM_ROWS2")) : 0;
+  if (g_gemm_rows2 < 0) g_gemm_rows2 = getenv("UFM_ROWS2") ? atoi(getenv("UFM_ROWS2")) : 27;
   return g_gemm_rows2;
+}
+int g_gemm_gelu_packed = -1;  // ufm_debug_flag 9 / UFM_GELU_PACKED (tuning); -1 = default
+void set_gemm_gelu_packed(int v) { g_gemm_gelu_packed = v; }
+int gemm_gelu_packed() {
+  if (g_gemm_gelu_packed < 0) g_gemm_gelu_packed = getenv("UFM_GELU_PACKED") ? atoi(getenv("UFM_GELU_PACKED")) : 1;
+  return g_gemm_gelu_packed;
 }
 int g_gemm_warp_shift = 0;  // ufm_debug_flag 7
 void set_gemm_warp_shift(int v) { g_gemm_warp_shift = v; }
@@ -1015,11 +1195,13 @@ cudaError_t launch_gemm(const GemmParams& p, int BN, int num_sms, cudaStream_t s
   const int ctas = p.ctas == 2 ? 2 : 1;
   const int tiles_m1 = p.Nimg * p.tiles_y * p.tiles_x;
   if (p.rows2) {
-    // whole 512-row items only (engine.cu gemm() peels the remaining rows off into a second launch)
-    if (ctas != 2 || BN != 256 || p.halo || p.taps != 1 || tiles_m1 % 4 || p.split_log2 || (p.flags & GEMM_TAIL) ||
+    // r2_items whole 512-row items, then the remaining rows as (column-sliced) 256-row half items in the same launch
+    if (ctas != 2 || BN != 256 || p.halo || p.taps != 1 || (p.flags & GEMM_TAIL) || p.r2_items < 0 || p.r2_half_tiles < 0 ||
+        p.r2_items % p.tiles_n || p.r2_half_tiles % p.tiles_n || p.split_log2 > 2 ||
+        (p.r2_items / p.tiles_n) * 4 + (p.r2_half_tiles / p.tiles_n) * 2 < tiles_m1 || p.r2_half_mt0 != p.r2_items / p.tiles_n * 2 ||
         (p.epi_mode != EPI_TMA_BF16 && !(p.epi_mode == EPI_TMA_F32 && (!p.res1 || (p.flags & GEMM_RED_INPLACE)))))
       return cudaErrorInvalidValue;
-    const int items = tiles_m1 / 4 * p.tiles_n;
+    const int items = p.r2_items + (p.r2_half_tiles << p.split_log2);
     if (items <= 0) return cudaSuccess;
     const int g2 = items * 2 < num_sms ? items * 2 : num_sms / 2 * 2;
     return launch_one<256, 2, false, true>(p, g2, stream);

@@ -37,6 +37,8 @@ enum : uint32_t {
   // set by build_gemm only (EPI_TMA_F32, res1 == out_f32): the in-place residual add is done by the L2 through a TMA
   // reduce-add store (x += v) instead of loading the residual slab into the SM; one fp32 rounding either way
   GEMM_RED_INPLACE = 1u << 8,
+  // set by build_gemm only (GEMM_GELU with the EPI_TMA_BF16 epilogue): GELU on packed f32x2 arithmetic, same bits
+  GEMM_GELU_PACKED = 1u << 9,
 };
 
 // Epilogue paths of the GEMM kernel (chosen per launch by the host, engine.cu build_gemm):
@@ -68,7 +70,11 @@ struct alignas(64) GemmParams {
   int halo;              // 1 = 3x3 conv with the halo-resident A operand: tw x th = 8 x 16, tmA box (64, 10, 18, 1)
   int rows2;             // 1 = every CTA of a pair owns TWO 128-row blocks (pair tile 512 x 256, one accumulator set):
                          //     the B half-tile in smem feeds both row blocks, -25 % L2 -> SM operand bytes per FLOP.
-                         //     Plain GEMMs only (taps 1, ctas 2, BN 256, whole 512-row items, TMA epilogue without residual load)
+                         //     Plain GEMMs only (taps 1, ctas 2, BN 256, TMA epilogue without residual load)
+  // rows2 launches: items [0, r2_items) are 512-row items (r2_items / tiles_n row units x tiles_n column tiles, whole waves of
+  // the pair units); the rows behind them -- pair tiles (256 rows) r2_half_mt0 ... -- run as r2_half_tiles half items (row
+  // block 0 / accumulator 0 only), each cut into 2^split_log2 column slices (tmBs), in the same launch
+  int r2_items, r2_half_mt0, r2_half_tiles;
   int warp_shift;        // role of physical warp w = (w + warp_shift) % 12 (tuning: 4 puts TMA / MMA warps above the epilogue warps)
   int X, Y, Nimg;        // logical output extents per image
   int tiles_x, tiles_y;  // ceil(X/tw), ceil(Y/th)
@@ -109,6 +115,8 @@ void set_gemm_split_mode(int v);        // tuning hook: 1 = column-slice the til
 int gemm_split_mode();
 void set_gemm_rows2_mode(int v);        // tuning hook (ufm_debug_flag 6): bit 0 = 512 x 256 pair tiles for the large row-matrix GEMMs,
 int gemm_rows2_mode();                  //   bit 1 = the next item's first row block starts before the second accumulator is drained
+void set_gemm_gelu_packed(int v);       // tuning hook (ufm_debug_flag 9): 1 = packed f32x2 GELU in the bf16 TMA epilogue
+int gemm_gelu_packed();
 void set_gemm_warp_shift(int v);        // tuning hook (ufm_debug_flag 7): see GemmParams::warp_shift
 int gemm_warp_shift();
 
