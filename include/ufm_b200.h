@@ -160,7 +160,8 @@ int ufm_profile_read(ufm_engine* e, double* ms, double* flops, double* bytes, in
  * shift of the GEMM kernel (0 default; 4 = TMA / MMA warps above the epilogue warps); which = 8: 1 = passes of <= 4 pairs
  * run their independent branches (uncertainty head, classification head + UNet branch, the four input chains of each DPT
  * head) on side streams beside the flow head (default; bit-identical results), 0 = one stream; which = 9: 1 = GELU of the
- * bf16 TMA epilogue on packed f32x2 arithmetic (default; same bits as the scalar form), -1 = default / UFM_GELU_PACKED.
+ * bf16 TMA epilogue on packed f32x2 arithmetic (default; same bits as the scalar form), -1 = default / UFM_GELU_PACKED;
+ * which = 10: 1 = L2 prefetch of the residual slabs of an in-place reduce-add tile (measured slower, default 0).
  * Returns non-zero for an unknown switch. */
 int ufm_debug_flag(int which, int value);
 

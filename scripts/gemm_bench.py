@@ -18,7 +18,7 @@ def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--variants", default="0:1,1:1", help="comma list of epilogue:pair[:split[:rows2[:warp_shift[:gelu_packed]]]]  (split: last-wave column "
                     "slices, default 1; rows2: 512 x 256 pair tiles, ufm_debug_flag 6, default 0; warp_shift: ufm_debug_flag 7; "
-                    "gelu_packed: ufm_debug_flag 9)")
+                    "gelu_packed: bit 0 = ufm_debug_flag 9, bit 1 = ufm_debug_flag 10 (L2 prefetch of in-place residual slabs))")
     ap.add_argument("--reps", type=int, default=20)
     ap.add_argument("--only", default="")
     ap.add_argument("--no-conv", action="store_true", help="row-matrix GEMM shapes only")
@@ -79,7 +79,8 @@ def main():
             lib.ufm_debug_flag(5, v[2])
             lib.ufm_debug_flag(6, v[3])
             lib.ufm_debug_flag(7, v[4])
-            lib.ufm_debug_flag(9, v[5])
+            lib.ufm_debug_flag(9, v[5] & 1)
+            lib.ufm_debug_flag(10, (v[5] >> 1) & 1)
             if kind == "res":
                 fn = lambda: ops.linear(A, Wt, bias=bias, res1=x, out_f32=x)
             elif kind == "gelu":
@@ -123,6 +124,7 @@ def main():
     lib.ufm_debug_flag(6, -1)
     lib.ufm_debug_flag(7, 0)
     lib.ufm_debug_flag(9, -1)
+    lib.ufm_debug_flag(10, -1)
 
 
 if __name__ == "__main__":

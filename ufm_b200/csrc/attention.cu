@@ -24,6 +24,7 @@
 //               packed f32x2 FMA / ADD around the exp2, online softmax with lazy rescale (O is rescaled in TMEM only
 //               when the row max grows by more than 2^8), P -> bf16 -> TMEM; then the tile epilogue O / l -> bf16.
 #include <stdio.h>
+#include <stdlib.h>
 
 #include "kernels.h"
 #include "launch.cuh"
@@ -586,7 +587,8 @@ cudaError_t launch_attention(const AttnParams& p_in, cudaStream_t stream) {
   static int n_sm = 0;
   if (!n_sm) {
     cudaError_t e = cudaSuccess;
-#define UFM_ATTN_VARIANTS(X) X(0) X(4) X(128) X(132) X(131) X(130)
+    if (getenv("UFM_ATTN_POLY")) g_attn_poly = atoi(getenv("UFM_ATTN_POLY"));  // tuning
+#define UFM_ATTN_VARIANTS(X) X(0) X(4) X(128) X(132) X(131) X(130) X(133) X(134) X(136)
 #define X(v) if ((e = cudaFuncSetAttribute(attn_kernel<v>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES)) != cudaSuccess) return e;
     UFM_ATTN_VARIANTS(X)
 #undef X

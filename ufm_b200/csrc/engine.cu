@@ -256,6 +256,7 @@ bool build_gemm(GemmParams* gp, int* BN, const AView& a_in, const void* wt, int 
   }
   gp->flags = e.flags | (red_inplace ? GEMM_RED_INPLACE : 0u);
   if ((e.flags & GEMM_GELU) && gp->epi_mode == EPI_TMA_BF16 && gemm_gelu_packed()) gp->flags |= GEMM_GELU_PACKED;
+  if (red_inplace && gemm_red_prefetch()) gp->flags |= GEMM_RED_PREFETCH;
   gp->bias = e.bias; gp->scale = e.scale; gp->res1 = e.res1; gp->res2 = e.res2;
   gp->out_f32 = e.out_f32; gp->out_bf16 = e.out_bf16;
   gp->sN = e.sn; gp->sY = e.sy; gp->sX = e.sx; gp->out_off = e.out_off;
@@ -1790,6 +1791,10 @@ int ufm_debug_flag(int which, int value) {
   }
   if (which == 9) {
     set_gemm_gelu_packed(value);
+    return 0;
+  }
+  if (which == 10) {
+    set_gemm_red_prefetch(value);
     return 0;
   }
   return 1;

@@ -577,6 +577,15 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_kernel(const __grid_constant
           const int wx = ((tr.mt * 2 + rb) * CTAS + (int)cta_rank) * BM + 32 * q;
           constexpr int wy = 0, img = 0;
           const uint32_t acc_addr = tmem_base + (uint32_t(q * 32) << 16) + uint32_t(rb * BN + col_off);
+          if (f32 && red && rb == 0 && lane == 0 && (p.flags & GEMM_RED_PREFETCH)) {
+            // x slabs of both row blocks into L2 under the main loop (see the 256-row kernel)
+#pragma unroll
+            for (int c = 0; c < 4; ++c) {
+              if (c0 + 32 * c >= p.N) break;
+              tma_prefetch_4d(&p.tmOut, c0 + 32 * c, wx, 0, 0);
+              tma_prefetch_4d(&p.tmOut, c0 + 32 * c, wx + CTAS * BM, 0, 0);
+            }
+          }
           mbar_wait(&tfull[rb], (uint32_t)(it2 & 1));
           tc_fence_after();
           uint32_t vr[128];
@@ -769,6 +778,11 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_kernel(const __grid_constant
         const bool has_res = p.res1 != nullptr && !red;
         if (lane == 0) {
           bulk_wait_read<0>();  // the previous tile's stores have left both slabs
+          if (red && (p.flags & GEMM_RED_PREFETCH)) {
+            // in-place reduce-add: pull the x slabs of this tile into L2 while the MMAs run, so that the L2's read-modify-write
+            // does not wait for DRAM when the stores arrive
+            for (int c = 0; c < nch; ++c) tma_prefetch_4d(&p.tmOut, c0 + 32 * c, wx, wy, img);
+          }
           if (has_res) {
             for (int c = 0; c < nch; ++c) {
               if (c < 2) {
@@ -1186,6 +1200,12 @@ void set_gemm_gelu_packed(int v) { g_gemm_gelu_packed = v; }
 int gemm_gelu_packed() {
   if (g_gemm_gelu_packed < 0) g_gemm_gelu_packed = getenv("UFM_GELU_PACKED") ? atoi(getenv("UFM_GELU_PACKED")) : 1;
   return g_gemm_gelu_packed;
+}
+int g_gemm_red_prefetch = -1;  // ufm_debug_flag 10 / UFM_RED_PREFETCH (tuning)
+void set_gemm_red_prefetch(int v) { g_gemm_red_prefetch = v; }
+int gemm_red_prefetch() {
+  if (g_gemm_red_prefetch < 0) g_gemm_red_prefetch = getenv("UFM_RED_PREFETCH") ? atoi(getenv("UFM_RED_PREFETCH")) : 0;
+  return g_gemm_red_prefetch;
 }
 int g_gemm_warp_shift = 0;  // ufm_debug_flag 7
 void set_gemm_warp_shift(int v) { g_gemm_warp_shift = v; }

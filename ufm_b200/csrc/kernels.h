@@ -39,6 +39,8 @@ enum : uint32_t {
   GEMM_RED_INPLACE = 1u << 8,
   // set by build_gemm only (GEMM_GELU with the EPI_TMA_BF16 epilogue): GELU on packed f32x2 arithmetic, same bits
   GEMM_GELU_PACKED = 1u << 9,
+  // set by build_gemm only (with GEMM_RED_INPLACE): the x slabs of a tile are prefetched into L2 under its main loop
+  GEMM_RED_PREFETCH = 1u << 10,
 };
 
 // Epilogue paths of the GEMM kernel (chosen per launch by the host, engine.cu build_gemm):
@@ -117,6 +119,8 @@ void set_gemm_rows2_mode(int v);        // tuning hook (ufm_debug_flag 6): bit 0
 int gemm_rows2_mode();                  //   bit 1 = the next item's first row block starts before the second accumulator is drained
 void set_gemm_gelu_packed(int v);       // tuning hook (ufm_debug_flag 9): 1 = packed f32x2 GELU in the bf16 TMA epilogue
 int gemm_gelu_packed();
+void set_gemm_red_prefetch(int v);      // tuning hook (ufm_debug_flag 10): 1 = L2 prefetch of the x slabs of an in-place reduce-add
+int gemm_red_prefetch();
 void set_gemm_warp_shift(int v);        // tuning hook (ufm_debug_flag 7): see GemmParams::warp_shift
 int gemm_warp_shift();
 
