@@ -150,7 +150,7 @@ int ufm_profile_read(ufm_engine* e, double* ms, double* flops, double* bytes, in
  * (0 = row-per-thread direct epilogue everywhere; 1 = TMA slab epilogues where the output geometry allows, including the
  * mixed second-residual / dual-output mode and the TMA reduce-add in-place residual (default); 2 = as 1 without the mixed mode;
  * | 4 = in-place residuals through a TMA-loaded residual slab instead of the reduce-add store); which = 1: CTA-pair (cta_group::2) GEMM
- * tiles on/off; which = 2: attention, every n-th exp2 pair on the FMA pipe; which = 3: 1 = halo-resident A operand
+ * tiles, bit 0 = for the 256-column tiles, bit 1 = also for the 128-column tiles (default 3; -1 = default / UFM_PAIR); which = 2: attention, every n-th exp2 pair on the FMA pipe; which = 3: 1 = halo-resident A operand
  * for the 3x3 convolutions (default), 0 = nine shifted boxes; which = 4: 1 = programmatic dependent launches (default); which = 5: 1 = column slices for
  * the tiles of a GEMM's partly filled last wave (default); which = 6: bit 0 = 512 x 256 pair tiles (two row blocks per
  * CTA, one accumulator set) for the whole waves of the large row-matrix GEMMs, bit 1 = the next item's first row block

@@ -119,7 +119,7 @@ def main():
             res.append(f"{ms:7.3f} {2.0 * n * H * W * 9 * Ci * Co / ms / 1e9:7.1f}")
         print(f"{name:18s} {n * H * W:7d} {9 * Ci:5d} {Co:5d} " + "   ".join(res))
     lib.ufm_debug_flag(0, 1)
-    lib.ufm_debug_flag(1, 1)
+    lib.ufm_debug_flag(1, -1)
     lib.ufm_debug_flag(5, 1)
     lib.ufm_debug_flag(6, -1)
     lib.ufm_debug_flag(7, 0)

@@ -1158,7 +1158,10 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_kernel(const __grid_constant
 // residual included (default); 2 = TMA epilogues without EPI_TMA_MIX; | 4 = in-place residuals through a residual slab
 // (TMA load + add in the SM) instead of the TMA reduce-add store
 int g_gemm_epi = 1;
-int g_gemm_pair = 1;  // ufm_debug_flag 1 (bit 1 measured neutral on the N = 128 convs: 808 vs 795 TFLOP/s): bit 0 = CTA-pair (cta_group::2) tiles for BN = 256, bit 1 = also for BN = 128
+// ufm_debug_flag 1 / UFM_PAIR: bit 0 = CTA-pair (cta_group::2) tiles for BN = 256, bit 1 = also for BN = 128 (the N = 128 processor
+// convs of the DPT heads: each CTA then loads half of the weight tile, 39 instead of 69 B/clk/SM of operand traffic against the
+// ~43 B/clk/SM the L2 delivers; neutral in round 1 (808 vs 795 TFLOP/s, the issue loop was the limit then), +12 - 14 % now)
+int g_gemm_pair = -1;
 
 template <int BN, int CTAS, bool HALO, bool R2 = false>
 static cudaError_t launch_one(const GemmParams& p, int grid, cudaStream_t stream) {
@@ -1182,7 +1185,10 @@ void set_gemm_pair_mode(int v) { g_gemm_pair = v; }
 int g_gemm_halo = 1;
 void set_gemm_halo_mode(int v) { g_gemm_halo = v; }
 int gemm_halo_mode() { return g_gemm_halo; }
-int gemm_pair_mode() { return g_gemm_pair; }
+int gemm_pair_mode() {
+  if (g_gemm_pair < 0) g_gemm_pair = getenv("UFM_PAIR") ? atoi(getenv("UFM_PAIR")) : 3;
+  return g_gemm_pair;
+}
 int g_gemm_split = 1;  // ufm_debug_flag 5
 void set_gemm_split_mode(int v) { g_gemm_split = v; }
 int gemm_split_mode() { return g_gemm_split; }
