@@ -256,6 +256,27 @@ def test_batch_chunking_and_determinism():
         assert torch.equal(o.flow.flow_output, a.cpu())
 
 
+@pytest.mark.parametrize("layout", ["bhwc", "bchw"])
+def test_patch_im2col_u8_kernel_matches_generic(layout, monkeypatch):
+    """uint8 images take the table-driven one-warp-per-patch gather (simt.cu patch_im2col_u8_kernel); UFM_PATCH_GENERIC=1
+    routes them through the generic kernel.  Same normalisation arithmetic, so the outputs of a pass are bit-identical."""
+    model, cfg, sd = _model("tiny_base")
+    W, H = cfg["inference_resolution"]
+    src, tgt = make_inputs(3, H, W, seed=5)
+    if layout == "bchw":
+        src, tgt = src.permute(0, 3, 1, 2).contiguous(), tgt.permute(0, 3, 1, 2).contiguous()
+    assert src.dtype == torch.uint8
+    outs = []
+    for generic in (False, True):
+        if generic:
+            monkeypatch.setenv("UFM_PATCH_GENERIC", "1")
+        else:
+            monkeypatch.delenv("UFM_PATCH_GENERIC", raising=False)
+        o = model.predict_correspondences_batched(src.cuda(), tgt.cuda())
+        outs.append((o.flow.flow_output.clone(), o.covisibility.mask.clone()))
+    assert torch.equal(outs[0][0], outs[1][0]) and torch.equal(outs[0][1], outs[1][1])
+
+
 @pytest.mark.parametrize("name", ["tiny_base", "tiny_refine", "tiny_unet", "tiny_cov"])
 def test_branches_bit_identical(name):
     """Passes of <= 4 pairs run the uncertainty head, the classification head (+ UNet branch) and the input chains of each

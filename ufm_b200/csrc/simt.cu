@@ -203,6 +203,57 @@ __global__ void __launch_bounds__(256) patch_im2col_kernel(const PatchParams p) 
       make_uint4(pack_bf16(f[0], f[1]), pack_bf16(f[2], f[3]), pack_bf16(f[4], f[5]), pack_bf16(f[6], f[7]));
 }
 
+// uint8 images, 14 x 14 patches (every UFM configuration): one warp per patch row of the operand, 32-bit index arithmetic
+// with compile-time divisors, the normalisation through a 3 x 256-entry table built per block with the arithmetic of the
+// generic kernel above (same bits), blocks walking PATCH_PER_WARP patches per warp so that the table is amortised.  The
+// generic kernel spent its time in 64-bit divisions and an fp32 division per element (154 us at B = 16 for 22.6 MB in /
+// 49 MB out).
+constexpr int PATCH_PER_WARP = 8;
+template <int P, bool NHWC>
+__global__ void __launch_bounds__(256) patch_im2col_u8_kernel(const PatchParams p) {
+  __shared__ float lut[3][256];
+  for (int i = threadIdx.x; i < 768; i += 256) {
+    const int c = i >> 8;
+    lut[c][i & 255] = ((float)(i & 255) / 255.0f - p.mean[c]) * p.inv_std[c];
+  }
+  __syncthreads();
+  pdl_wait();
+  constexpr int PP = P * P, K = 3 * PP;
+  const int hp = p.H / P, wp = p.W / P;
+  const int n_tok = hp * wp;
+  const int rows = 2 * p.B * n_tok;
+  const int lane = threadIdx.x & 31;
+  const int kgroups = p.Kpad >> 3;
+  int row = (blockIdx.x * 8 + (threadIdx.x >> 5)) * PATCH_PER_WARP;
+  for (int it = 0; it < PATCH_PER_WARP && row < rows; ++it, ++row) {
+    const int img = row / n_tok, t = row - img * n_tok;
+    const int py = t / wp, px = t - py * wp;
+    const int view = img / p.B, b = img - view * p.B;
+    const uint8_t* base = reinterpret_cast<const uint8_t*>(view ? p.tgt : p.src);
+    // first pixel of the patch
+    const uint8_t* b0 = NHWC ? base + (((size_t)b * p.H + py * P) * p.W + px * P) * 3
+                             : base + ((size_t)b * 3 * p.H + py * P) * p.W + px * P;
+    const size_t plane = (size_t)p.H * p.W;
+    for (int kg = lane; kg < kgroups; kg += 32) {
+      float f[8];
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        const int k = kg * 8 + i;
+        float val = 0.f;
+        if (k < K) {
+          const int c = k / PP, rem = k - c * PP;
+          const int ky = rem / P, kx = rem - ky * P;
+          const uint8_t u = NHWC ? b0[((size_t)ky * p.W + kx) * 3 + c] : b0[c * plane + (size_t)ky * p.W + kx];
+          val = lut[c][u];
+        }
+        f[i] = val;
+      }
+      *reinterpret_cast<uint4*>(p.out + (size_t)row * p.Kpad + kg * 8) =
+          make_uint4(pack_bf16(f[0], f[1]), pack_bf16(f[2], f[3]), pack_bf16(f[4], f[5]), pack_bf16(f[6], f[7]));
+    }
+  }
+}
+
 // rows in front of the patch tokens of every image: `prefix` [n_prefix, D] = (cls + its positional row), then the register
 // tokens of the hub *_reg models (no positional embedding), precomputed at pack time
 __global__ void cls_rows_kernel(float* x, const float* prefix, int n_prefix, int n_img, int seq_len, int D) {
@@ -215,45 +266,48 @@ __global__ void cls_rows_kernel(float* x, const float* prefix, int n_prefix, int
 }
 
 // ------------------------------------------------------------------------------------------------ pixel shuffle
-template <typename T, int VEC>
+// I = index type: unsigned 32-bit when every element index fits (the usual case; 64-bit divisions are software routines
+// and made this copy issue-bound at a third of the HBM rate), long long otherwise
+template <typename T, int VEC, typename I = long long>
 __global__ void __launch_bounds__(256) shuffle_kernel(const T* in, T* out, int n, int h, int w, int k, int C) {
   pdl_wait();
   const int cg = C / VEC;
-  const long long total = (long long)n * h * w * k * k * cg;
-  const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  const I total = (I)n * h * w * k * k * cg;
+  const I idx = (I)blockIdx.x * blockDim.x + threadIdx.x;
   if (idx >= total) return;
   // idx enumerates the INPUT contiguously: (row=(n,y,x), i, j, cgroup)
   const int g = (int)(idx % cg);
   const int j = (int)((idx / cg) % k);
-  const int i = (int)((idx / ((long long)cg * k)) % k);
-  const long long row = idx / ((long long)cg * k * k);
+  const int i = (int)((idx / ((I)cg * k)) % k);
+  const I row = idx / ((I)cg * k * k);
   const int x = (int)(row % w);
   const int y = (int)((row / w) % h);
-  const int nn = (int)(row / ((long long)w * h));
+  const int nn = (int)(row / ((I)w * h));
   typedef typename std::conditional<sizeof(T) * VEC == 16, uint4, uint2>::type V;
   const V val = *reinterpret_cast<const V*>(in + idx * VEC);
-  const long long o = ((((long long)nn * h * k + (y * k + i)) * (w * k)) + (x * k + j)) * C + g * VEC;
+  const I o = ((((I)nn * h * k + (y * k + i)) * (w * k)) + (x * k + j)) * C + g * VEC;
   *reinterpret_cast<V*>(out + o) = val;
 }
 
 // ------------------------------------------------------------------------------------------------ 3x3 s2 im2col
+template <typename I>
 __global__ void __launch_bounds__(256) im2col_s2_kernel(const __nv_bfloat16* in, __nv_bfloat16* out, int n, int h, int w,
                                                        int C, int oh, int ow) {
   pdl_wait();
   const int cg = C >> 3;
-  const long long total = (long long)n * oh * ow * 9 * cg;
-  const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  const I total = (I)n * oh * ow * 9 * cg;
+  const I idx = (I)blockIdx.x * blockDim.x + threadIdx.x;
   if (idx >= total) return;
   const int g = (int)(idx % cg);
   const int tap = (int)((idx / cg) % 9);
-  const long long row = idx / ((long long)cg * 9);
+  const I row = idx / ((I)cg * 9);
   const int ox = (int)(row % ow);
   const int oy = (int)((row / ow) % oh);
-  const int nn = (int)(row / ((long long)ow * oh));
+  const int nn = (int)(row / ((I)ow * oh));
   const int y = 2 * oy + tap / 3 - 1, x = 2 * ox + tap % 3 - 1;
   uint4 v = make_uint4(0, 0, 0, 0);
   if (y >= 0 && y < h && x >= 0 && x < w)
-    v = *reinterpret_cast<const uint4*>(in + (((long long)nn * h + y) * w + x) * C + g * 8);
+    v = *reinterpret_cast<const uint4*>(in + (((I)nn * h + y) * w + x) * C + g * 8);
   *reinterpret_cast<uint4*>(out + idx * 8) = v;
 }
 
@@ -643,6 +697,13 @@ cudaError_t launch_qk_norm(__nv_bfloat16* qkv, long long rows, int heads, const 
 }
 
 cudaError_t launch_patch_im2col(const PatchParams& p, cudaStream_t stream) {
+  const long long rows = 2LL * p.B * (p.H / p.P) * (p.W / p.P);
+  if (p.is_u8 && p.P == 14 && rows * p.Kpad < (1LL << 31) && !getenv("UFM_PATCH_GENERIC")) {
+    const unsigned grid = blocks_for(rows, 8 * PATCH_PER_WARP);
+    if (p.is_nhwc) launch_k(patch_im2col_u8_kernel<14, true>, grid, 256, 0, stream, p);
+    else launch_k(patch_im2col_u8_kernel<14, false>, grid, 256, 0, stream, p);
+    return cudaGetLastError();
+  }
   const long long total = 2LL * p.B * (p.H / p.P) * (p.W / p.P) * (p.Kpad / 8);
   launch_k(patch_im2col_kernel, blocks_for(total, 256), 256, 0, stream, p);
   return cudaGetLastError();
@@ -657,13 +718,15 @@ cudaError_t launch_shuffle_bf16(const __nv_bfloat16* in, __nv_bfloat16* out, int
                                 cudaStream_t s) {
   if (C % 8) return cudaErrorInvalidValue;
   const long long total = (long long)n * h * w * k * k * (C / 8);
-  launch_k(shuffle_kernel<__nv_bfloat16, 8>, blocks_for(total, 256), 256, 0, s, in, out, n, h, w, k, C);
+  if (total * 8 < (1LL << 31)) launch_k(shuffle_kernel<__nv_bfloat16, 8, unsigned>, blocks_for(total, 256), 256, 0, s, in, out, n, h, w, k, C);
+  else launch_k(shuffle_kernel<__nv_bfloat16, 8>, blocks_for(total, 256), 256, 0, s, in, out, n, h, w, k, C);
   return cudaGetLastError();
 }
 cudaError_t launch_shuffle_f32(const float* in, float* out, int n, int h, int w, int k, int C, cudaStream_t s) {
   if (C % 4) return cudaErrorInvalidValue;
   const long long total = (long long)n * h * w * k * k * (C / 4);
-  launch_k(shuffle_kernel<float, 4>, blocks_for(total, 256), 256, 0, s, in, out, n, h, w, k, C);
+  if (total * 4 < (1LL << 31)) launch_k(shuffle_kernel<float, 4, unsigned>, blocks_for(total, 256), 256, 0, s, in, out, n, h, w, k, C);
+  else launch_k(shuffle_kernel<float, 4>, blocks_for(total, 256), 256, 0, s, in, out, n, h, w, k, C);
   return cudaGetLastError();
 }
 
@@ -671,7 +734,9 @@ cudaError_t launch_im2col_s2(const __nv_bfloat16* in, __nv_bfloat16* out, int n,
                              cudaStream_t s) {
   if (C % 8) return cudaErrorInvalidValue;
   const long long total = (long long)n * oh * ow * 9 * (C / 8);
-  launch_k(im2col_s2_kernel, blocks_for(total, 256), 256, 0, s, in, out, n, h, w, C, oh, ow);
+  if (total * 8 < (1LL << 31) && (long long)n * h * w * C < (1LL << 31))
+    launch_k(im2col_s2_kernel<unsigned>, blocks_for(total, 256), 256, 0, s, in, out, n, h, w, C, oh, ow);
+  else launch_k(im2col_s2_kernel<long long>, blocks_for(total, 256), 256, 0, s, in, out, n, h, w, C, oh, ow);
   return cudaGetLastError();
 }
 
