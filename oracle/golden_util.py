@@ -57,6 +57,23 @@ def make_inputs(batch: int, H: int, W: int, seed: int = 1):
     return src, tgt
 
 
+# API-shell cases with foreign and DIFFERENT source / target sizes (base.py:253-334: AutomaticShapeSelection resize in,
+# un-map out).  The first four are the shapes of the reference's own example pairs (examples/image_pairs: bike 1080x1080 /
+# 607x1080, building 810x1080, cook 607x1080 / 1080x1080, fire_academy 580x1080) at one fifth of the size; the last one
+# mixes aspect ratios on both sides.  (h0, w0, h1, w1); model = tiny_base (168 x 224 trained resolution), head gain 8.
+SHAPE_CASES = [(216, 216, 121, 216), (162, 216, 162, 216), (121, 216, 216, 216), (116, 216, 116, 216), (162, 216, 100, 300)]
+SHAPE_GOLDEN = "tiny_shapes"
+
+
+def make_shape_inputs(i: int):
+    """Seeded uint8 BHWC pair (batch 1) of SHAPE_CASES[i]."""
+    h0, w0, h1, w1 = SHAPE_CASES[i]
+    g = torch.Generator(device="cpu").manual_seed(100 + i)
+    src = torch.randint(0, 256, (1, h0, w0, 3), dtype=torch.uint8, generator=g)
+    tgt = torch.randint(0, 256, (1, h1, w1, 3), dtype=torch.uint8, generator=g)
+    return src, tgt
+
+
 def subsample(t: torch.Tensor, max_elems: int = 40000) -> torch.Tensor:
     """Deterministic strided subsample of the two trailing spatial dims so a fixture stays small."""
     t = t.detach().float()

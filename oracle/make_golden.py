@@ -20,7 +20,8 @@ import torch
 
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 
-from oracle.golden_util import GOLDEN_CASES, case_config, make_inputs, pack_stages  # noqa: E402
+from oracle.golden_util import (GOLDEN_CASES, SHAPE_CASES, SHAPE_GOLDEN, case_config, make_inputs, make_shape_inputs,  # noqa: E402
+                                pack_stages)
 from oracle.ref_harness import build_reference  # noqa: E402
 from ufm_b200.weights import make_state_dict  # noqa: E402
 
@@ -104,10 +105,31 @@ def run_reference(name: str):
     return st, dt
 
 
+def run_reference_shapes():
+    """The reference's API shell on source / target images of foreign and different sizes (golden_util.SHAPE_CASES)."""
+    cfg = case_config("tiny_base")
+    sd = make_state_dict(cfg, seed=0, out_gain=8.0)
+    model = build_reference(cfg, sd)
+    st = {}
+    for i in range(len(SHAPE_CASES)):
+        src, tgt = make_shape_inputs(i)
+        with torch.no_grad():
+            out = model.predict_correspondences_batched(src, tgt)
+        st[f"flow{i}"] = out.flow.flow_output
+        st[f"covis{i}"] = out.covisibility.mask
+    return st
+
+
 def main(argv):
     os.makedirs(OUT, exist_ok=True)
-    names = argv or list(GOLDEN_CASES)
+    names = argv or (list(GOLDEN_CASES) + [SHAPE_GOLDEN])
     torch.set_num_threads(len(os.sched_getaffinity(0)))
+    if SHAPE_GOLDEN in names:
+        names = [n for n in names if n != SHAPE_GOLDEN]
+        path = os.path.join(OUT, SHAPE_GOLDEN + ".npz")
+        st = run_reference_shapes()
+        np.savez_compressed(path, **pack_stages(st))
+        print(f"{SHAPE_GOLDEN}: {len(st)} outputs, {os.path.getsize(path) / 1e6:.2f} MB")
     for name in names:
         st, dt = run_reference(name)
         packed = pack_stages(st)

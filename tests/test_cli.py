@@ -40,11 +40,14 @@ def test_cli_batch_matches_api(tmp_path):
     from ufm_b200 import UniFlowMatchConfidence, get_config
 
     rng = np.random.default_rng(0)
-    sizes = [(168, 224), (168, 224), (120, 200)]  # native twice, one foreign size (resize + un-map path)
+    # native twice, one foreign size (resize + un-map path), one pair whose target has another size than its source (as the
+    # reference's example pairs bike_0 / bike_1 do)
+    sizes = [(168, 224), (168, 224), (120, 200), (216, 216)]
+    tsizes = [(168, 224), (168, 224), (120, 200), (121, 216)]
     lines = []
     for i, (h, w) in enumerate(sizes):
-        for side in "st":
-            cv2.imwrite(str(tmp_path / f"{i}{side}.png"), rng.integers(0, 256, (h, w, 3), dtype=np.uint8))
+        for side, (hh, ww) in (("s", (h, w)), ("t", tsizes[i])):
+            cv2.imwrite(str(tmp_path / f"{i}{side}.png"), rng.integers(0, 256, (hh, ww, 3), dtype=np.uint8))
         lines.append(f"{i}s.png {i}t.png")
     (tmp_path / "pairs.txt").write_text("\n".join(lines) + "\n")
     out = tmp_path / "out"
@@ -59,6 +62,15 @@ def test_cli_batch_matches_api(tmp_path):
         assert np.allclose(flow, ref.flow.flow_output[0].cpu().numpy(), atol=1e-5)
         cov = cv2.imread(str(out / f"{i:06d}_covisibility.png"), cv2.IMREAD_GRAYSCALE)
         assert np.array_equal(cov, (ref.covisibility.mask[0].cpu().numpy() * 255).astype(np.uint8))
+        if i >= 2:
+            # ... and against the CPU oracle's restatement of the reference shell on the decoded images (foreign sizes)
+            from oracle import ufm_oracle as O
+            from oracle.golden_util import rel_l2
+
+            with torch.no_grad():
+                sd = {k: v.detach().cpu() for k, v in model.state_dict().items()}
+                orc = O.predict_correspondences_batched(s.unsqueeze(0), t.unsqueeze(0), sd, get_config("tiny_base"))
+            assert rel_l2(torch.from_numpy(flow)[None], orc["flow"]) < 1.6e-2
     assert cli.main(["infer", str(tmp_path / "0s.png"), str(tmp_path / "0t.png"), "-o", str(out / "one"), "--config", "tiny_base"]) == 0
     assert os.path.exists(out / "one" / "flow.npy") and os.path.exists(out / "one" / "covisibility_mask.png")
     assert os.path.exists(out / "one" / "flow_visualization.png")

@@ -24,7 +24,8 @@ import torch
 pytestmark = pytest.mark.gpu
 
 from oracle import ufm_oracle as O  # noqa: E402
-from oracle.golden_util import GOLDEN_CASES, case_config, make_inputs, max_abs, rel_l2, subsample  # noqa: E402
+from oracle.golden_util import (GOLDEN_CASES, SHAPE_CASES, SHAPE_GOLDEN, case_config, make_inputs, make_shape_inputs,  # noqa: E402
+                                max_abs, rel_l2, subsample)
 from ufm_b200 import UniFlowMatchClassificationRefinement, UniFlowMatchConfidence, _lib  # noqa: E402
 from ufm_b200.weights import make_state_dict  # noqa: E402
 
@@ -193,6 +194,28 @@ def test_api_vs_reference_golden(name):
     assert rlg <= LOGIT_TOL
     assert mc <= 0.25 * mlg + 1e-5
     assert out.covisibility.logits is None and flow.shape == (src.shape[0], 2, H, W)
+
+
+@pytest.mark.parametrize("host", [False, True])
+def test_api_foreign_and_different_sizes_vs_reference_golden(host):
+    """Source and target images of foreign and DIFFERENT sizes (the shapes of the reference's example pairs at 1/5 scale;
+    base.py:253-334): prep_resize_kernel in, unmap_kernel out, against outputs recorded from the unmodified reference
+    (tests/golden/tiny_shapes.npz).  The covisibility of a head with gain 8 is compared through the mean: single pixels near
+    a logit zero crossing flip by bf16 noise."""
+    model, cfg, sd = _model("tiny_base")
+    g = np.load(os.path.join(GOLDEN, SHAPE_GOLDEN + ".npz"))
+    for i, (h0, w0, h1, w1) in enumerate(SHAPE_CASES):
+        src, tgt = make_shape_inputs(i)
+        out = model.predict_correspondences_batched(src if host else src.cuda(), tgt if host else tgt.cuda())
+        flow, cov = out.flow.flow_output, out.covisibility.mask
+        assert flow.shape == (1, 2, h0, w0) and cov.shape == (1, h0, w0)
+        assert flow.device.type == ("cpu" if host else "cuda")
+        rf, rc = torch.from_numpy(g[f"sub:flow{i}"]), torch.from_numpy(g[f"sub:covis{i}"])
+        r = rel_l2(subsample(flow.cpu()), rf)
+        mc = (subsample(cov.cpu()) - rc).abs().mean().item()
+        print(f"\n[shapes {h0}x{w0} / {h1}x{w1}] flow rel-L2 {r:.3e} (ref max {rf.abs().max():.1f} px); covis mean-abs {mc:.3e}")
+        assert r <= FLOW_TOL
+        assert mc <= 1e-2
 
 
 def test_api_contract_shapes_layouts_errors():

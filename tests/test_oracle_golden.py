@@ -8,7 +8,8 @@ import pytest
 import torch
 
 from oracle import ufm_oracle as O
-from oracle.golden_util import GOLDEN_CASES, case_config, make_inputs, rel_l2, stats, subsample
+from oracle.golden_util import (GOLDEN_CASES, SHAPE_CASES, SHAPE_GOLDEN, case_config, make_inputs, make_shape_inputs, rel_l2,
+                                stats, subsample)
 from ufm_b200.weights import make_state_dict
 
 GOLDEN = os.path.join(os.path.dirname(__file__), "golden")
@@ -56,3 +57,20 @@ def test_oracle_matches_reference_golden(name):
         np.testing.assert_allclose(stats(mine), g["stat:" + stage], rtol=2e-4, atol=1e-6, err_msg=f"{name}:{stage}")
         checked += 1
     assert checked >= 10
+
+
+def test_oracle_api_shell_on_foreign_and_different_sizes():
+    """Source and target images of foreign and DIFFERENT sizes (the shapes of the reference's own example pairs, scaled
+    down): the oracle's API shell (resize in, un-map out) against the unmodified reference's outputs."""
+    torch.set_num_threads(len(os.sched_getaffinity(0)))
+    g = np.load(os.path.join(GOLDEN, SHAPE_GOLDEN + ".npz"))
+    cfg = case_config("tiny_base")
+    sd = make_state_dict(cfg, seed=0, out_gain=8.0)
+    for i, (h0, w0, h1, w1) in enumerate(SHAPE_CASES):
+        src, tgt = make_shape_inputs(i)
+        with torch.no_grad():
+            api = O.predict_correspondences_batched(src, tgt, sd, cfg)
+        assert api["flow"].shape == (1, 2, h0, w0) and api["covisibility"].shape == (1, h0, w0)
+        for key, mine in ((f"flow{i}", api["flow"]), (f"covis{i}", api["covisibility"])):
+            assert rel_l2(subsample(mine), torch.from_numpy(g["sub:" + key])) < 1e-5, key
+            np.testing.assert_allclose(stats(mine), g["stat:" + key], rtol=2e-4, atol=1e-6, err_msg=key)
