@@ -240,6 +240,8 @@ def test_api_contract_shapes_layouts_errors():
         model.predict_correspondences_batched(torch.zeros(1, 5, 8, 4).cuda(), torch.zeros(1, 5, 8, 4).cuda())
     with pytest.raises(ValueError):
         model.predict_correspondences_batched(src.cuda().half(), tgt.cuda().half())
+    with pytest.raises(RuntimeError):  # B = 0: the reference raises (reshape of 0 elements), so does the engine shell
+        model.predict_correspondences_batched(src[:0].cuda(), tgt[:0].cuda())
     # non-native input size: resized in, un-mapped out, compared with the oracle's shell
     g = torch.Generator().manual_seed(3)
     s2 = torch.randint(0, 256, (300, 400, 3), dtype=torch.uint8, generator=g)

@@ -335,6 +335,10 @@ class UniFlowMatchModelsBase(nn.Module):
                 f"data_norm_type must be one of {list(prepost.IMAGE_NORMALIZATION.keys())}"
         elif source_image.dtype != torch.uint8:
             raise ValueError("source_image and target_image must be of type torch.float32 or torch.uint8")
+        if source_image.shape[0] == 0 or target_image.shape[0] == 0:
+            # the reference fails on an empty batch too (a reshape of 0 elements with an inferred dimension inside the
+            # encoder wrapper); stated here instead of surfacing as an index error further down
+            raise RuntimeError("predict_correspondences_batched: empty batch (the reference raises on B = 0 as well)")
         in_device = source_image.device
         dev = self._device()
         if dev.type != "cuda":
