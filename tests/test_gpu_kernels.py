@@ -76,9 +76,10 @@ def test_gemm_gelu_scale_residual_inplace():
 # (M, K, N): the UFM-Base encoder shapes (74 x 512 rows + 544 -> 12 half tiles in quarter slices, 36 in half slices), an
 # exact multiple (37 x 512 rows x 2 column tiles: one wave, no half items), 77 rows behind a whole wave (2 half tiles in
 # 64-column quarter slices taken by one warp half), a case too small for any 512-row wave (falls back entirely), and a
-# long-K shape that the shape rule of mode bit 3 admits (the short-K ones then run on the 256-row kernel).
+# long-K shape that the shape rule of mode bit 3 admits (the short-K ones then run on the 256-row kernel), and 12 pairs' worth
+# of rows, where more than a wave of half items would remain behind the one whole wave (falls back entirely).
 @pytest.mark.parametrize("M,K,N", [(32 * 1201, 256, 1024), (32 * 1201, 128, 3072), (37 * 512, 192, 512), (37 * 512 + 77, 64, 512),
-                                   (3000, 128, 512), (74 * 512 + 300, 2048, 256), (32 * 1201, 128, 4096)])
+                                   (3000, 128, 512), (74 * 512 + 300, 2048, 256), (32 * 1201, 128, 4096), (24 * 1201, 128, 1024)])
 @pytest.mark.parametrize("mode,shift", [(3, 0), (1, 0), (3, 4), (7, 0), (11, 0)])
 def test_gemm_rows2_pair_tiles(M, K, N, mode, shift):
     """bf16 output with bias and the in-place fp32 residual (TMA reduce-add) through the 512-row tiles: against fp32 torch

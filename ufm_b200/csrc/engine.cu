@@ -291,7 +291,11 @@ long long rows2_rows(const AView& a, int n_out, int taps, const Epi& e, int num_
   int g = units, t = tiles_n;  // step = units / gcd(units, tiles_n)
   while (t) { const int r = g % t; g = t; t = r; }
   const long long step = units / g;
-  return items_m / step * step * 512;
+  const long long r2 = items_m / step * step * 512;
+  // the rows behind the whole waves run as half items without a second accumulator stage: worth it for one (sliced) wave of
+  // them, not when a large share of the matrix would take that path (e.g. 12 pairs: 34 % of the rows)
+  if (r2 > 0 && (a.X - r2 + 255) / 256 * tiles_n > units) return 0;
+  return r2;
 }
 
 bool build_attn(AttnParams* ap, const void* qkv, int n_seq, int seq_len, int heads, float scale, void* out, char* err,
